@@ -1,0 +1,170 @@
+/*
+ * b200ops -- C ABI of the B200-native (sm_100a) decode hot path.
+ *
+ * This is the drop-in boundary for the operator surface of yiliu30/vllm-fork that BASELINE.json's
+ * north_star names.  Every entry point replaces ONE reference operator (cited per function as
+ * file:line relative to the reference tree) and keeps that operator's conventions
+ * (SURVEY.md section 8b):
+ *   - outputs are preallocated by the caller; nothing is allocated, nothing synchronises;
+ *   - the launch is asynchronous on the `stream` handle given (a cudaStream_t); CUDA-graph capturable;
+ *   - argument validation happens before any launch; a failed check returns a negative code and
+ *     b200_last_error() describes it (the Python shim raises RuntimeError, like STD_TORCH_CHECK);
+ *   - tensors are raw device pointers + explicit ELEMENT strides (strides are part of the ABI:
+ *     K/V are views of the fused QKV output, the KV cache is a permuted view);
+ *   - scales stay on the device as `const float*` and are read in-kernel.
+ * No torch types appear here.  There is no CPU fallback: without a CUDA device every compute
+ * entry point fails with B200_ERR_CUDA.
+ */
+#ifndef B200OPS_H_
+#define B200OPS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_API __attribute__((visibility("default")))
+
+/* element types */
+enum {
+  B200_F32 = 0,
+  B200_F16 = 1,
+  B200_BF16 = 2,
+  B200_FP8_E4M3 = 3,
+  B200_U8 = 4,
+  B200_I32 = 5,
+  B200_I64 = 6
+};
+
+/* return codes */
+enum {
+  B200_OK = 0,
+  B200_ERR_INVALID = -1,     /* argument check failed (shape / stride / alignment / dtype) */
+  B200_ERR_UNSUPPORTED = -2, /* valid request this build does not cover */
+  B200_ERR_CUDA = -3,        /* CUDA runtime / driver error (message holds cudaGetErrorString) */
+  B200_ERR_WORKSPACE = -4    /* workspace too small */
+};
+
+typedef void* b200_stream_t; /* cudaStream_t */
+
+/* Message of the last failure on the calling thread ("" if none). */
+B200_API const char* b200_last_error(void);
+/* ABI version: major*1000 + minor. */
+B200_API int b200_version(void);
+/* Number of SMs of the current CUDA device (148 on B200), or a negative error code. */
+B200_API int b200_sm_count(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * KV-cache write.
+ * Replaces torch.ops._C_cache_ops.reshape_and_cache_flash
+ *   (csrc/libtorch_stable/cache_kernels.cu:314-400 kernel, :795-864 host; vllm/_custom_ops.py:2614-2633).
+ * key/value: [num_tokens, num_heads, head_size], last dim contiguous, token stride given.
+ * key_cache/value_cache: logical [num_blocks, block_size, num_heads, head_size] views with element
+ * strides (block_stride, page_stride, head_stride) -- NHD and HND are both just strides.
+ * slot_mapping: int64 [num_tokens]; slot < 0 => token skipped. num_tokens = slot_mapping.size(0).
+ * cache_dtype == in_dtype: plain copy ("auto"); cache_dtype == B200_FP8_E4M3:
+ *   byte = e4m3_satfinite_rne(float(x) / scale), scale = k_scale[head * kv_scale_stride].
+ * kv_scale_stride is 0 (per-tensor scale [1]) or 1 (per-head scale [num_heads]).
+ */
+B200_API int b200_reshape_and_cache_flash(const void* key, const void* value, void* key_cache,
+                                          void* value_cache, const int64_t* slot_mapping,
+                                          int64_t num_tokens, int num_heads, int head_size,
+                                          int block_size, int64_t key_stride, int64_t value_stride,
+                                          int64_t block_stride, int64_t page_stride,
+                                          int64_t head_stride, int in_dtype, int cache_dtype,
+                                          const float* k_scale, const float* v_scale,
+                                          int kv_scale_stride, b200_stream_t stream);
+
+/* Replaces torch.ops._C_cache_ops.reshape_and_cache (legacy x-packed layout used by
+ * paged_attention_v1/v2): csrc/libtorch_stable/cache_kernels.cu:254-312, :749-777.
+ * key_cache [num_blocks, num_heads, head_size/x, block_size, x], value_cache
+ * [num_blocks, num_heads, head_size, block_size], both contiguous; x = 16 / sizeof(cache elem). */
+B200_API int b200_reshape_and_cache(const void* key, const void* value, void* key_cache,
+                                    void* value_cache, const int64_t* slot_mapping,
+                                    int64_t num_tokens, int num_heads, int head_size, int block_size,
+                                    int x, int64_t key_stride, int64_t value_stride, int in_dtype,
+                                    int cache_dtype, const float* k_scale, const float* v_scale,
+                                    b200_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * FP8 activation quantisers.  Replace torch.ops._C.{static,dynamic,dynamic_per_token}_scaled_fp8_quant
+ *   (csrc/libtorch_stable/quantization/w8a8/fp8/common.cu:13-179 kernels, :183-422 hosts;
+ *    conversion csrc/quantization/w8a8/fp8/common.cuh:58-79; vllm/_custom_ops.py:1832-1898).
+ * input [num_tokens, hidden] with row stride in_row_stride (elements), out e4m3 with out_row_stride.
+ */
+/* out = e4m3(clamp(x * (1.0f / scale[gi*scale_stride_i + gj*scale_stride_j]), +-448)),
+ * gi = row / group_m, gj = col / group_n  (per-tensor: both strides 0). */
+B200_API int b200_fp8_quant_static(void* out, const void* input, const float* scale,
+                                   int64_t num_tokens, int hidden, int64_t in_row_stride,
+                                   int64_t out_row_stride, int group_m, int group_n,
+                                   int64_t scale_stride_i, int64_t scale_stride_j, int in_dtype,
+                                   b200_stream_t stream);
+/* scale[0] = max|x| / 448 over the whole tensor (written), out = e4m3(clamp(x * (1/scale))). */
+B200_API int b200_fp8_quant_dynamic_tensor(void* out, const void* input, float* scale,
+                                           int64_t num_tokens, int hidden, int64_t in_row_stride,
+                                           int64_t out_row_stride, int in_dtype,
+                                           b200_stream_t stream);
+/* scales[t] = max(min(max|x_t|, *scale_ub) / 448, 1/(448*512)); out = e4m3(clamp(x / scales[t])). */
+B200_API int b200_fp8_quant_dynamic_token(void* out, const void* input, float* scales,
+                                          const float* scale_ub /* nullable */, int64_t num_tokens,
+                                          int hidden, int64_t in_row_stride, int64_t out_row_stride,
+                                          int in_dtype, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Paged-attention decode (one query token per sequence).
+ * Replaces the decode branch of AttentionImpl.forward (vllm/v1/attention/backend.py:895-934) as
+ * implemented by TritonAttentionImpl.forward -> unified_attention
+ * (vllm/v1/attention/backends/triton_attn.py:580-730, ops/triton_unified_attention.py:179-772) and
+ * FlashAttentionImpl.forward (backends/flash_attn.py:874-1110); the legacy
+ * torch.ops._C.paged_attention_v1/v2 adapters below call the same kernel.
+ *
+ *   out[s,h,:] = softmax_t( softcap( scale*k_scale * q[s,h,:].K[s,t,h/g,:] ) + alibi[h]*(t-L_s+1) ) . V * v_scale
+ *   over t in [max(0, L_s - sliding_window), L_s),  g = num_heads / num_kv_heads.
+ *
+ * q/out: [num_seqs, num_heads, head_size] (element strides q_stride_s/q_stride_h, last dim
+ * contiguous), dtype q_dtype (BF16 or F16). lse (nullable): float [num_seqs, num_heads], natural log.
+ * k_cache/v_cache: paged cache views, element (t, h, d) of physical block b lives at
+ *   base + b*kv_block_stride + t*kv_token_stride + h*kv_head_stride + d   (elements of kv_dtype),
+ * kv_dtype = q_dtype ("auto") or B200_FP8_E4M3 (dequant = float(byte) * *k_scale / *v_scale).
+ * All byte strides and base pointers must be 16-byte aligned; head_size*sizeof(kv) >= 64.
+ * block_table int32 [num_seqs, bt_stride]; seq_lens int32 [num_seqs]; block_size % 16 == 0.
+ * workspace: b200_paged_attention_workspace_bytes(...) bytes of device memory owned by the caller
+ * (the AttentionMetadataBuilder keeps one persistent buffer, like triton_attn.py:154-175).
+ * Everything is read on the device: no host sync, CUDA-graph safe.
+ */
+typedef struct b200_paged_attn_args {
+  void* out;
+  float* lse; /* nullable */
+  const void* q;
+  const void* k_cache;
+  const void* v_cache;
+  const int32_t* block_table;
+  const int32_t* seq_lens;
+  const float* k_scale;      /* device scalar; nullable => 1.0 */
+  const float* v_scale;      /* device scalar; nullable => 1.0 */
+  const float* alibi_slopes; /* [num_heads] float, nullable */
+  void* workspace;
+  size_t workspace_bytes;
+  int64_t num_blocks; /* physical blocks in the cache (bounds the TMA descriptor) */
+  int64_t q_stride_s, q_stride_h;
+  int64_t out_stride_s, out_stride_h;
+  int64_t kv_block_stride, kv_token_stride, kv_head_stride;
+  int64_t bt_stride;
+  int32_t num_seqs, num_heads, num_kv_heads, head_size, block_size;
+  int32_t max_seq_len; /* upper bound, used only for validation / heuristics */
+  int32_t q_dtype, kv_dtype;
+  int32_t sliding_window; /* <= 0: none */
+  float scale;
+  float softcap; /* <= 0: none */
+} b200_paged_attn_args;
+
+B200_API size_t b200_paged_attention_workspace_bytes(int num_seqs, int num_heads, int num_kv_heads,
+                                                     int head_size);
+B200_API int b200_paged_attention_decode(const b200_paged_attn_args* args, b200_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200OPS_H_ */

@@ -1,0 +1,283 @@
+"""TEST INFRASTRUCTURE ONLY -- CPU restatement of the reference's algorithms for the decode hot path.
+
+Nothing under ``oracle/`` is imported by the product (``vllm-fork_b200/``); only ``tests/``,
+``__graft_entry__.smoke()`` and the ``cpu_baseline`` / ``--impl reference`` legs of ``bench.py`` use it,
+and only as the checker / the timed CPU baseline.
+
+Each function cites the reference file:line (relative to /root/reference) it restates.
+
+Parity pinning (SURVEY.md section 8c -- the reference holds NO golden-vector files for this path):
+  * paged attention / KV-cache write: pinned against outputs of the reference's OWN CPU kernels
+    (csrc/cpu/cpu_attn.cpp, compiled unmodified into oracle/_ref/refcpu.so by
+    oracle/build_ref_cpu_attn.sh) -> fixtures tests/golden/cpu_attn_*.npz made by
+    tests/golden/make_golden.py; checked in tests/test_oracle.py.
+  * e4m3 conversion: pinned bit-for-bit against torch's float8_e4m3fn cast for all finite inputs
+    in range (tests/test_oracle.py) and against the E4M3 code table.
+  * moe_align_block_size: pinned against the worked example in
+    vllm/model_executor/layers/fused_moe/moe_align_block_size.py:59-72.
+  * quantisers: restated from the CUDA sources; the reference's own oracle
+    (tests/kernels/quant_utils.py:22-88) is restated beside them and cross-checked.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+FP8_MAX = 448.0
+
+
+# --------------------------------------------------------------------------------------------
+# e4m3 (fn) conversion, RNE + saturate-to-finite.
+# Reference: __nv_cvt_float_to_fp8(x, __NV_SATFINITE, __NV_E4M3)
+#            csrc/quantization/w8a8/fp8/nvidia/quant_utils.cuh:492-503
+# --------------------------------------------------------------------------------------------
+def f32_to_e4m3_bits(x) -> np.ndarray:
+    x = np.asarray(x, dtype=np.float32)
+    sign = (np.signbit(x)).astype(np.uint8) << 7
+    a = np.abs(x).astype(np.float64)
+    nan = np.isnan(a)
+    a = np.where(nan, 0.0, a)
+    a = np.minimum(a, FP8_MAX)  # satfinite (also maps +-inf to +-448)
+    out = np.zeros(a.shape, dtype=np.int64)
+    sub = a < 2.0 ** -6
+    # subnormals: multiples of 2^-9; rint = round-half-even; q == 8 rolls into the first normal
+    out_sub = np.rint(a * 2.0 ** 9).astype(np.int64)
+    m, e = np.frexp(np.where(sub, 1.0, a))  # a = m * 2^e, m in [0.5, 1)
+    e = e - 1
+    frac = m * 2.0 - 1.0  # [0, 1)
+    q = np.rint(frac * 8.0).astype(np.int64)
+    carry = q == 8
+    e = np.where(carry, e + 1, e)
+    q = np.where(carry, 0, q)
+    out_norm = ((e + 7) << 3) | q
+    out_norm = np.minimum(out_norm, 0x7E)
+    out = np.where(sub, out_sub, out_norm)
+    out = np.where(nan, 0x7F, out)
+    return (out.astype(np.uint8) | sign).astype(np.uint8)
+
+
+def e4m3_bits_to_f32(b) -> np.ndarray:
+    b = np.asarray(b, dtype=np.uint8).astype(np.int64)
+    s = np.where(b & 0x80, -1.0, 1.0)
+    e = (b >> 3) & 0xF
+    m = b & 7
+    v = np.where(e == 0, m / 8.0 * 2.0 ** -6, (1.0 + m / 8.0) * np.exp2((e - 7).astype(np.float64)))
+    v = np.where((e == 15) & (m == 7), np.nan, v)
+    return (s * v).astype(np.float32)
+
+
+def _f32(t: torch.Tensor) -> np.ndarray:
+    return t.detach().to(torch.float32).cpu().numpy()
+
+
+def _fminf(a, b):
+    """CUDA fminf: returns the non-NaN operand."""
+    return np.where(np.isnan(a), b, np.where(np.isnan(b), a, np.minimum(a, b)))
+
+
+def _fmaxf(a, b):
+    return np.where(np.isnan(a), b, np.where(np.isnan(b), a, np.maximum(a, b)))
+
+
+def _scaled_fp8_conversion(val: np.ndarray, scale, inverted: bool) -> np.ndarray:
+    """csrc/quantization/w8a8/fp8/common.cuh:58-79 (fp32 arithmetic, IEEE division)."""
+    val = val.astype(np.float32)
+    scale = np.asarray(scale, dtype=np.float32)
+    with np.errstate(all="ignore"):
+        x = (val * scale).astype(np.float32) if inverted else (val / scale).astype(np.float32)
+    r = _fmaxf(np.float32(-FP8_MAX), _fminf(x, np.float32(FP8_MAX)))
+    return f32_to_e4m3_bits(r)
+
+
+# --------------------------------------------------------------------------------------------
+# KV-cache write.  csrc/libtorch_stable/cache_kernels.cu:314-400 (kernel), :795-864 (host)
+# --------------------------------------------------------------------------------------------
+def reshape_and_cache_flash(key, value, key_cache, value_cache, slot_mapping, kv_cache_dtype,
+                            k_scale, v_scale) -> None:
+    """In-place on CPU tensors. key/value [T,H,D]; caches [nb, bs, H, D] views; slot < 0 skipped;
+    num_tokens = slot_mapping.size(0). fp8: byte = e4m3(float(x) / scale) (true division)."""
+    T = slot_mapping.shape[0]
+    bs = key_cache.shape[1]
+    H = key.shape[1]
+    fp8 = kv_cache_dtype in ("fp8", "fp8_e4m3")
+    ks = _f32(k_scale).reshape(-1)
+    vs = _f32(v_scale).reshape(-1)
+    sm = slot_mapping.cpu().tolist()
+    for t in range(T):
+        slot = sm[t]
+        if slot < 0:
+            continue
+        blk, off = slot // bs, slot % bs
+        if not fp8:
+            key_cache[blk, off] = key[t]
+            value_cache[blk, off] = value[t]
+        else:
+            kf, vf = _f32(key[t]), _f32(value[t])
+            ksc = ks if ks.size == 1 else ks.reshape(H, 1)
+            vsc = vs if vs.size == 1 else vs.reshape(H, 1)
+            with np.errstate(all="ignore"):
+                kb = f32_to_e4m3_bits((kf / ksc).astype(np.float32))
+                vb = f32_to_e4m3_bits((vf / vsc).astype(np.float32))
+            key_cache[blk, off].view(torch.uint8).copy_(torch.from_numpy(kb))
+            value_cache[blk, off].view(torch.uint8).copy_(torch.from_numpy(vb))
+
+
+def reshape_and_cache(key, value, key_cache, value_cache, slot_mapping, kv_cache_dtype, k_scale,
+                      v_scale) -> None:
+    """Legacy layout. csrc/libtorch_stable/cache_kernels.cu:254-312.
+    key_cache [nb, H, D/x, bs, x]; value_cache [nb, H, D, bs]."""
+    T = slot_mapping.shape[0]
+    nb, H, Dx, bs, x = key_cache.shape
+    fp8 = kv_cache_dtype in ("fp8", "fp8_e4m3")
+    sm = slot_mapping.cpu().tolist()
+    ks = float(_f32(k_scale).reshape(-1)[0])
+    vs = float(_f32(v_scale).reshape(-1)[0])
+    for t in range(T):
+        slot = sm[t]
+        if slot < 0:
+            continue
+        blk, off = slot // bs, slot % bs
+        if not fp8:
+            key_cache[blk, :, :, off, :] = key[t].reshape(H, Dx, x)
+            value_cache[blk, :, :, off] = value[t]
+        else:
+            with np.errstate(all="ignore"):
+                kb = f32_to_e4m3_bits((_f32(key[t]) / np.float32(ks)).astype(np.float32))
+                vb = f32_to_e4m3_bits((_f32(value[t]) / np.float32(vs)).astype(np.float32))
+            key_cache.view(torch.uint8)[blk, :, :, off, :] = torch.from_numpy(kb).reshape(H, Dx, x)
+            value_cache.view(torch.uint8)[blk, :, :, off] = torch.from_numpy(vb)
+
+
+# --------------------------------------------------------------------------------------------
+# FP8 quantisers.  csrc/libtorch_stable/quantization/w8a8/fp8/common.cu:13-179
+# Return (uint8 bits [M, K], float32 scales).
+# --------------------------------------------------------------------------------------------
+def static_scaled_fp8_quant(x: torch.Tensor, scale: torch.Tensor, group_shape=None):
+    """common.cu:13-76 + host :183-335. out = e4m3(clamp(x * (1.0f / scale)))."""
+    xf = _f32(x).reshape(-1, x.shape[-1])
+    M, K = xf.shape
+    sc = _f32(scale)
+    if sc.size == 1:
+        full = np.full((M, K), sc.reshape(-1)[0], dtype=np.float32)
+    elif sc.ndim == 1:
+        assert group_shape is not None
+        gm = M if group_shape[0] == -1 else group_shape[0]
+        gn = K if group_shape[1] == -1 else group_shape[1]
+        grid = sc.reshape(M // gm, K // gn)
+        full = np.repeat(np.repeat(grid, gm, axis=0), gn, axis=1)
+    else:
+        gm, gn = M // sc.shape[0], K // sc.shape[1]
+        full = np.repeat(np.repeat(sc, gm, axis=0), gn, axis=1)
+    with np.errstate(all="ignore"):
+        inv = (np.float32(1.0) / full).astype(np.float32)
+    return _scaled_fp8_conversion(xf, inv, True).reshape(x.shape)
+
+
+def dynamic_scaled_fp8_quant(x: torch.Tensor):
+    """common.cu:78-135 + host :337-381. scale = max_rows(rowmax / 448); out via 1/scale multiply."""
+    xf = _f32(x).reshape(-1, x.shape[-1])
+    rowmax = np.max(np.abs(xf), axis=1) if xf.size else np.zeros(0, np.float32)
+    # fmaxf-based reduction starting from 0 drops NaNs
+    rowmax = np.where(np.isnan(rowmax), np.float32(0), rowmax).astype(np.float32)
+    scale = np.float32(0.0)
+    for rm in rowmax:
+        scale = max(scale, np.float32(rm / np.float32(FP8_MAX)))
+    scale = np.float32(scale)
+    with np.errstate(all="ignore"):
+        inv = np.float32(1.0) / scale
+    return _scaled_fp8_conversion(xf, inv, True).reshape(x.shape), np.array([scale], np.float32)
+
+
+def dynamic_per_token_scaled_fp8_quant(x: torch.Tensor, scale_ub: torch.Tensor | None = None):
+    """common.cu:137-179. scale_t = max(min(absmax_t, ub) / 448, 1/(448*512)); out = x / scale_t."""
+    xf = _f32(x).reshape(-1, x.shape[-1])
+    absmax = np.max(np.abs(xf), axis=1, keepdims=True).astype(np.float32)
+    if scale_ub is not None:
+        absmax = np.minimum(absmax, _f32(scale_ub).reshape(-1)[0]).astype(np.float32)
+    min_sf = np.float32(1.0) / (np.float32(FP8_MAX) * np.float32(512.0))
+    scales = np.maximum((absmax / np.float32(FP8_MAX)).astype(np.float32), min_sf).astype(np.float32)
+    return _scaled_fp8_conversion(xf, scales, False).reshape(x.shape), scales
+
+
+def ref_dynamic_per_token_quant(x: torch.Tensor, scale_ub: torch.Tensor | None = None):
+    """The reference's own python oracle, tests/kernels/quant_utils.py:22-60 (restated): returns
+    (torch fp8 tensor, scales) -- used to cross-check the restatement above."""
+    qmax = torch.finfo(torch.float8_e4m3fn).max
+    x32 = x.to(torch.float32)
+    x_token_max = x32.abs().max(dim=-1, keepdim=True)[0]
+    if scale_ub is not None:
+        x_token_max = x_token_max.clamp(max=scale_ub.to(torch.float32))
+    scales = (x_token_max / qmax).clamp(min=1.0 / (qmax * 512.0))
+    out = (x32 / scales).clamp(-qmax, qmax).to(torch.float8_e4m3fn)
+    return out, scales
+
+
+# --------------------------------------------------------------------------------------------
+# Slot mapping.  vllm/v1/worker/block_table.py:182-211, 379-441 (no DCP)
+# --------------------------------------------------------------------------------------------
+PAD_SLOT_ID = -1
+
+
+def compute_slot_mapping(block_table: np.ndarray, req_indices: np.ndarray, positions: np.ndarray,
+                         block_size: int) -> np.ndarray:
+    """slot = block_table[req, pos // bs] * bs + pos % bs  (int64)."""
+    blk = block_table[req_indices, positions // block_size].astype(np.int64)
+    return blk * block_size + positions % block_size
+
+
+# --------------------------------------------------------------------------------------------
+# Paged attention decode.
+# Semantics: ref_paged_attn, tests/kernels/attention/test_triton_unified_attention.py:33-88 with
+# query_len == 1 (flash layout [nb, bs, Hkv, D]); FP8 KV dequant = float(byte) * scale
+# (triton_unified_attention.py k_descale / v_descale); ALiBi bias as in
+# tests/kernels/attention/test_attention.py:96-103.
+# Everything in fp32 (probabilities are NOT rounded to the V dtype -> the GPU tolerance covers it).
+# --------------------------------------------------------------------------------------------
+def _cache_f32(cache: torch.Tensor) -> np.ndarray:
+    if cache.element_size() == 1:
+        return e4m3_bits_to_f32(cache.view(torch.uint8).cpu().numpy())
+    return _f32(cache)
+
+
+def paged_attention_decode(query, key_cache, value_cache, block_table, seq_lens, scale,
+                           k_scale=None, v_scale=None, alibi_slopes=None, sliding_window=None,
+                           softcap=None, return_lse=False):
+    """query [S,Hq,D]; caches [nb,bs,Hkv,D] (torch CPU, bf16/f16 or fp8/uint8 bytes).
+    Returns float32 [S,Hq,D] (and natural-log LSE [S,Hq])."""
+    q = _f32(query)
+    S, Hq, D = q.shape
+    kc, vc = _cache_f32(key_cache), _cache_f32(value_cache)
+    nb, bs, Hkv, _ = kc.shape
+    g = Hq // Hkv
+    ks = 1.0 if k_scale is None else float(_f32(k_scale).reshape(-1)[0])
+    vs = 1.0 if v_scale is None else float(_f32(v_scale).reshape(-1)[0])
+    bt = block_table.cpu().numpy()
+    sl = seq_lens.cpu().numpy()
+    out = np.zeros((S, Hq, D), dtype=np.float32)
+    lse = np.full((S, Hq), -np.inf, dtype=np.float32)
+    for s in range(S):
+        L = int(sl[s])
+        if L <= 0:
+            continue
+        nblk = (L + bs - 1) // bs
+        idx = bt[s, :nblk]
+        k = kc[idx].reshape(-1, Hkv, D)[:L].astype(np.float64) * ks  # [L,Hkv,D]
+        v = vc[idx].reshape(-1, Hkv, D)[:L].astype(np.float64) * vs
+        k = np.repeat(k, g, axis=1)
+        v = np.repeat(v, g, axis=1)
+        att = np.einsum("hd,khd->hk", q[s].astype(np.float64) * scale, k)
+        if softcap is not None and softcap > 0:
+            att = softcap * np.tanh(att / softcap)
+        if alibi_slopes is not None:
+            pos = np.arange(L) - L + 1
+            att = att + _f32(alibi_slopes).astype(np.float64)[:, None] * pos[None, :]
+        if sliding_window is not None and sliding_window > 0 and L > sliding_window:
+            att[:, : L - sliding_window] = -np.inf
+        m = att.max(axis=1, keepdims=True)
+        p = np.exp(att - m)
+        den = p.sum(axis=1, keepdims=True)
+        out[s] = np.einsum("hk,khd->hd", p / den, v).astype(np.float32)
+        lse[s] = (m[:, 0] + np.log(den[:, 0])).astype(np.float32)
+    if return_lse:
+        return out, lse
+    return out

@@ -1,0 +1,138 @@
+"""CPU tests: pin oracle/ref_ops.py against the reference (golden fixtures, torch's e4m3 cast,
+the reference's own python oracles)."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ref_ops
+from helpers import bits_to_bf16, make_kv_cache
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def test_e4m3_matches_torch_cast_all_codes():
+    # every e4m3 code decodes to the value torch gives, and re-encodes to itself
+    codes = np.arange(256, dtype=np.uint8)
+    ours = ref_ops.e4m3_bits_to_f32(codes)
+    theirs = torch.from_numpy(codes.copy()).view(torch.float8_e4m3fn).float().numpy()
+    finite = ~np.isnan(theirs)
+    assert np.array_equal(np.isnan(ours), np.isnan(theirs))
+    assert np.array_equal(ours[finite], theirs[finite])
+    re = ref_ops.f32_to_e4m3_bits(ours[finite])
+    # -0.0 / +0.0 keep their sign bit
+    assert np.array_equal(re, codes[finite])
+
+
+def test_e4m3_rne_matches_torch_cast_random():
+    g = np.random.default_rng(0)
+    x = np.concatenate([
+        g.uniform(-448, 448, 200000), g.normal(0, 1, 200000), g.normal(0, 1e-2, 100000),
+        g.uniform(-2 ** -6, 2 ** -6, 100000),
+    ]).astype(np.float32)
+    # exact ties between neighbouring codes
+    codes = np.arange(0, 0x7E, dtype=np.uint8)
+    v = ref_ops.e4m3_bits_to_f32(codes).astype(np.float64)
+    v2 = ref_ops.e4m3_bits_to_f32(codes + 1).astype(np.float64)
+    ties = ((v + v2) / 2).astype(np.float32)
+    x = np.concatenate([x, ties, -ties])
+    ours = ref_ops.f32_to_e4m3_bits(x)
+    theirs = torch.from_numpy(x).to(torch.float8_e4m3fn).view(torch.uint8).numpy()
+    assert np.array_equal(ours, theirs)
+
+
+def test_e4m3_saturates_to_finite():
+    x = np.array([449.0, 1e9, np.inf, -1e9, -np.inf, 464.0, 480.0], dtype=np.float32)
+    assert ref_ops.f32_to_e4m3_bits(x).tolist() == [0x7E, 0x7E, 0x7E, 0xFE, 0xFE, 0x7E, 0x7E]
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "cpu_attn_*.npz"))))
+def test_attention_oracle_matches_reference_cpu_kernel(path):
+    """oracle reshape_and_cache_flash + paged_attention_decode vs the outputs of the reference's own
+    CPU kernels (fixtures made by tests/golden/make_golden.py)."""
+    z = np.load(path)
+    Hq, Hkv, D, bs, nb, win, has_alibi = [int(v) for v in z["meta"]]
+    q = bits_to_bf16(z["query"])
+    key, value = bits_to_bf16(z["key"]), bits_to_bf16(z["value"])
+    _, kc, vc = make_kv_cache(nb, bs, Hkv, D, torch.bfloat16, "NHD")
+    one = torch.ones(1)
+    ref_ops.reshape_and_cache_flash(key, value, kc, vc, torch.from_numpy(z["slot_mapping"]), "auto",
+                                    one, one)
+    out = ref_ops.paged_attention_decode(
+        q, kc, vc, torch.from_numpy(z["block_table"]), torch.from_numpy(z["seq_lens"]),
+        float(z["scale"][0]), alibi_slopes=torch.from_numpy(z["alibi"]) if has_alibi else None,
+        sliding_window=win or None, softcap=float(z["softcap"][0]) or None)
+    golden = bits_to_bf16(z["out"]).float().numpy()
+    # reference CPU kernel: bf16 output, fp32 accumulate (3e-5 vs naive fp32 before
+    # the bf16 output rounding). bf16 rounding of |out| <= 1 => <= 2^-9 relative.
+    np.testing.assert_allclose(out, golden, atol=4e-3, rtol=8e-3)
+    assert np.abs(out - golden).mean() < 5e-4
+
+
+@pytest.mark.parametrize("hidden", [17, 1024, 1025, 5137])
+@pytest.mark.parametrize("tokens", [1, 7, 33])
+def test_per_token_quant_restatement_vs_reference_python_oracle(hidden, tokens):
+    torch.manual_seed(1)
+    x = (torch.rand(tokens, hidden) * 2 - 1).mul(8).to(torch.bfloat16)
+    ub = torch.tensor([5.0])
+    for scale_ub in (None, ub):
+        bits, scales = ref_ops.dynamic_per_token_scaled_fp8_quant(x, scale_ub)
+        ref_q, ref_s = ref_ops.ref_dynamic_per_token_quant(x, scale_ub)
+        np.testing.assert_array_equal(scales, ref_s.numpy())
+        np.testing.assert_array_equal(bits, ref_q.view(torch.uint8).numpy())
+
+
+def test_per_tensor_quant_restatement():
+    torch.manual_seed(2)
+    x = torch.randn(9, 130).to(torch.float16)
+    bits, scale = ref_ops.dynamic_scaled_fp8_quant(x)
+    assert scale[0] == np.float32(x.float().abs().max().item()) / np.float32(448.0)
+    # same thing through the static path
+    bits2 = ref_ops.static_scaled_fp8_quant(x, torch.from_numpy(scale))
+    np.testing.assert_array_equal(bits, bits2)
+    # dequantised error bounded by half an fp8 ulp (2^-4 relative) + subnormal step
+    deq = ref_ops.e4m3_bits_to_f32(bits) * scale[0]
+    err = np.abs(deq - x.float().numpy())
+    assert (err <= np.abs(x.float().numpy()) * 2 ** -4 + scale[0] * 2 ** -10 + 1e-7).all()
+
+
+def test_static_quant_group_shapes():
+    torch.manual_seed(3)
+    x = torch.randn(8, 256).to(torch.bfloat16)
+    s2d = torch.rand(8, 2) + 0.5
+    bits = ref_ops.static_scaled_fp8_quant(x, s2d)
+    for i in range(8):
+        for j in range(2):
+            blk = ref_ops.static_scaled_fp8_quant(x[i:i + 1, j * 128:(j + 1) * 128], s2d[i, j].reshape(1))
+            np.testing.assert_array_equal(bits[i:i + 1, j * 128:(j + 1) * 128], blk)
+    per_ch = ref_ops.static_scaled_fp8_quant(x, torch.rand(256) + 0.5, group_shape=(-1, 1))
+    assert per_ch.shape == (8, 256)
+
+
+def test_slot_mapping_restatement():
+    bt = np.arange(40, dtype=np.int32).reshape(4, 10)[:, ::-1].copy()
+    req = np.array([0, 0, 1, 3, 3, 3])
+    pos = np.array([0, 17, 159, 5, 16, 31])
+    sm = ref_ops.compute_slot_mapping(bt, req, pos, 16)
+    assert sm.dtype == np.int64
+    assert sm.tolist() == [9 * 16, 8 * 16 + 1, 10 * 16 + 15, 39 * 16 + 5, 38 * 16, 38 * 16 + 15]
+
+
+def test_reshape_and_cache_flash_oracle_fp8_and_skip():
+    torch.manual_seed(4)
+    T, H, D, bs, nb = 9, 3, 32, 16, 4
+    key = torch.randn(T, H, D).to(torch.bfloat16)
+    value = torch.randn(T, H, D).to(torch.bfloat16)
+    slots = torch.tensor([5, -1, 17, 0, 63, 33, -1, 16, 2])
+    for layout in ("NHD", "HND"):
+        raw, kc, vc = make_kv_cache(nb, bs, H, D, torch.uint8, layout)
+        ks, vs = torch.tensor([0.05, 0.1, 0.2]), torch.tensor([0.3, 0.02, 0.07])
+        ref_ops.reshape_and_cache_flash(key, value, kc, vc, slots, "fp8", ks, vs)
+        for t, s in enumerate(slots.tolist()):
+            if s < 0:
+                continue
+            exp = (key[t].float() / ks[:, None]).clamp(-448, 448).to(torch.float8_e4m3fn).view(torch.uint8)
+            assert torch.equal(kc[s // bs, s % bs], exp)
+        assert int((raw != 0).any(dim=-1).sum()) <= 7 * H  # only 7 valid tokens were written

@@ -1,0 +1,127 @@
+"""ctypes binding of libb200ops.so (the C ABI declared in include/b200ops.h).
+
+The library is built in-tree (``make -C vllm-fork_b200`` or ``__graft_entry__.build()``) and lives
+next to this file.  There is NO CPU fallback: if the library is missing, or a compute entry point is
+called without a CUDA device, a RuntimeError is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200ops.so")
+
+# element types (include/b200ops.h)
+F32, F16, BF16, FP8_E4M3, U8, I32, I64 = range(7)
+
+OK = 0
+ERR_INVALID, ERR_UNSUPPORTED, ERR_CUDA, ERR_WORKSPACE = -1, -2, -3, -4
+
+c_void_p, c_int, c_int64, c_float, c_size_t = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_size_t
+
+
+class PagedAttnArgs(C.Structure):
+    """struct b200_paged_attn_args (include/b200ops.h)."""
+
+    _fields_ = [
+        ("out", c_void_p),
+        ("lse", c_void_p),
+        ("q", c_void_p),
+        ("k_cache", c_void_p),
+        ("v_cache", c_void_p),
+        ("block_table", c_void_p),
+        ("seq_lens", c_void_p),
+        ("k_scale", c_void_p),
+        ("v_scale", c_void_p),
+        ("alibi_slopes", c_void_p),
+        ("workspace", c_void_p),
+        ("workspace_bytes", c_size_t),
+        ("num_blocks", c_int64),
+        ("q_stride_s", c_int64),
+        ("q_stride_h", c_int64),
+        ("out_stride_s", c_int64),
+        ("out_stride_h", c_int64),
+        ("kv_block_stride", c_int64),
+        ("kv_token_stride", c_int64),
+        ("kv_head_stride", c_int64),
+        ("bt_stride", c_int64),
+        ("num_seqs", C.c_int32),
+        ("num_heads", C.c_int32),
+        ("num_kv_heads", C.c_int32),
+        ("head_size", C.c_int32),
+        ("block_size", C.c_int32),
+        ("max_seq_len", C.c_int32),
+        ("q_dtype", C.c_int32),
+        ("kv_dtype", C.c_int32),
+        ("sliding_window", C.c_int32),
+        ("scale", c_float),
+        ("softcap", c_float),
+    ]
+
+
+# name -> (restype, argtypes); every symbol include/b200ops.h declares must be listed here
+# (tests/test_abi.py cross-checks this table against the header).
+SIGNATURES = {
+    "b200_last_error": (C.c_char_p, []),
+    "b200_version": (c_int, []),
+    "b200_sm_count": (c_int, []),
+    "b200_reshape_and_cache_flash": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int64,
+         c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p],
+    ),
+    "b200_reshape_and_cache": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int,
+         c_int64, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p],
+    ),
+    "b200_fp8_quant_static": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int64, c_int64, c_int, c_int, c_int64,
+         c_int64, c_int, c_void_p],
+    ),
+    "b200_fp8_quant_dynamic_tensor": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int64, c_int64, c_int, c_void_p]),
+    "b200_fp8_quant_dynamic_token": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int64, c_int64, c_int, c_void_p],
+    ),
+    "b200_paged_attention_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "b200_paged_attention_decode": (c_int, [C.POINTER(PagedAttnArgs), c_void_p]),
+}
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """Load libb200ops.so (once). Raises RuntimeError if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"b200ops: {LIB_PATH} not found - build it with `make -C vllm-fork_b200` "
+            "(or __graft_entry__.build()). There is no CPU / PyTorch fallback."
+        )
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError => ABI mismatch, fail loudly
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def last_error() -> str:
+    return load().b200_last_error().decode("utf-8", "replace")
+
+
+def check(rc: int, op: str) -> None:
+    """Turn a negative return code into the exception the reference op would raise."""
+    if rc == OK:
+        return
+    msg = last_error() or f"{op} failed with code {rc}"
+    if rc == ERR_UNSUPPORTED:
+        raise NotImplementedError(msg)
+    raise RuntimeError(msg)

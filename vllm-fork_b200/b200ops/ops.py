@@ -1,0 +1,350 @@
+"""Host-side mirror of the reference operator surface (vllm/_custom_ops.py) over libb200ops.so.
+
+Same function names, argument meaning and error behaviour as the reference's Python wrappers, so that
+parity tests read like the reference's own kernel tests and a maintainer can rebind
+``vllm._custom_ops.<name> = b200ops.ops.<name>``.  PyTorch is used only for
+device memory and the current CUDA stream.  There is no CPU fallback.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+from ._lib import BF16, F16, F32, FP8_E4M3
+
+FP8_DTYPE = torch.float8_e4m3fn
+_FP8_KV_NAMES = ("fp8", "fp8_e4m3")
+
+
+def _dt(t: torch.Tensor) -> int:
+    if t.dtype == torch.bfloat16:
+        return BF16
+    if t.dtype == torch.float16:
+        return F16
+    if t.dtype == torch.float32:
+        return F32
+    if t.dtype in (torch.float8_e4m3fn, torch.uint8):
+        return FP8_E4M3
+    raise RuntimeError(f"b200ops: unsupported dtype {t.dtype}")
+
+
+def _cuda(*ts: torch.Tensor | None) -> None:
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError(
+                "b200ops: tensors must live on a CUDA device (there is no CPU fallback)")
+
+
+def _p(t: torch.Tensor | None) -> int | None:
+    return None if t is None else t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+# ------------------------------------------------------------------------------------------------
+# KV-cache write                                      reference: vllm/_custom_ops.py:2614-2633
+# ------------------------------------------------------------------------------------------------
+def reshape_and_cache_flash(
+    key: torch.Tensor,
+    value: torch.Tensor,
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    slot_mapping: torch.Tensor,
+    kv_cache_dtype: str,
+    k_scale: torch.Tensor,
+    v_scale: torch.Tensor,
+) -> None:
+    """key/value [T, H, D]; key_cache/value_cache [num_blocks, block_size, H, D] views (NHD or HND
+    strides); slot_mapping int64 [T'] (T' <= T, -1 = skip); kv_cache_dtype "auto" | "fp8" | "fp8_e4m3";
+    k_scale/v_scale float32 [1] or [H]."""
+    _cuda(key, value, key_cache, value_cache, slot_mapping, k_scale, v_scale)
+    lib = _lib.load()
+    if key.dim() != 3 or value.dim() != 3 or key_cache.dim() != 4:
+        raise RuntimeError("reshape_and_cache_flash: key/value must be 3-D and the caches 4-D")
+    if key.stride(2) != 1 or value.stride(2) != 1 or key_cache.stride(3) != 1:
+        raise RuntimeError("reshape_and_cache_flash: last dimension must be contiguous")
+    if key_cache.stride(0) != value_cache.stride(0):
+        raise RuntimeError("reshape_and_cache_flash: key_cache/value_cache block strides differ")
+    if slot_mapping.dtype != torch.int64:
+        raise RuntimeError("reshape_and_cache_flash: slot_mapping must be int64")
+    if k_scale.shape != v_scale.shape:
+        raise RuntimeError("k_scale and v_scale must have the same shape")
+    num_heads, head_size = key.shape[1], key.shape[2]
+    if k_scale.numel() not in (1, num_heads):
+        raise RuntimeError("k_scale and v_scale must be of shape [1] or [num_heads]")
+    if kv_cache_dtype == "auto":
+        cache_dt = _dt(key)
+        if key_cache.dtype != key.dtype:
+            raise RuntimeError("reshape_and_cache_flash: kv_cache_dtype 'auto' needs cache dtype == key dtype")
+    elif kv_cache_dtype in _FP8_KV_NAMES:
+        cache_dt = FP8_E4M3
+        if key_cache.element_size() != 1:
+            raise RuntimeError("reshape_and_cache_flash: fp8 kv cache must have 1-byte elements")
+    else:
+        raise RuntimeError(f"Unsupported data type of kv cache: {kv_cache_dtype}")
+    rc = lib.b200_reshape_and_cache_flash(
+        _p(key), _p(value), _p(key_cache), _p(value_cache), _p(slot_mapping),
+        slot_mapping.shape[0], num_heads, head_size, key_cache.shape[1],
+        key.stride(0), value.stride(0), key_cache.stride(0), key_cache.stride(1),
+        key_cache.stride(2), _dt(key), cache_dt, _p(k_scale), _p(v_scale),
+        1 if k_scale.numel() > 1 else 0, _stream())
+    _lib.check(rc, "reshape_and_cache_flash")
+
+
+def reshape_and_cache(
+    key: torch.Tensor,
+    value: torch.Tensor,
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    slot_mapping: torch.Tensor,
+    kv_cache_dtype: str,
+    k_scale: torch.Tensor,
+    v_scale: torch.Tensor,
+) -> None:
+    """Legacy layout: key_cache [nb, H, D/x, bs, x], value_cache [nb, H, D, bs] (contiguous)."""
+    _cuda(key, value, key_cache, value_cache, slot_mapping, k_scale, v_scale)
+    lib = _lib.load()
+    if key_cache.dim() != 5 or value_cache.dim() != 4:
+        raise RuntimeError("reshape_and_cache: key_cache must be 5-D and value_cache 4-D")
+    if not (key_cache.is_contiguous() and value_cache.is_contiguous()):
+        raise RuntimeError("reshape_and_cache: caches must be contiguous")
+    if kv_cache_dtype == "auto":
+        cache_dt = _dt(key)
+    elif kv_cache_dtype in _FP8_KV_NAMES:
+        cache_dt = FP8_E4M3
+    else:
+        raise RuntimeError(f"Unsupported data type of kv cache: {kv_cache_dtype}")
+    rc = lib.b200_reshape_and_cache(
+        _p(key), _p(value), _p(key_cache), _p(value_cache), _p(slot_mapping),
+        slot_mapping.shape[0], key.shape[1], key.shape[2], key_cache.shape[3], key_cache.shape[4],
+        key.stride(0), value.stride(0), _dt(key), cache_dt, _p(k_scale), _p(v_scale), _stream())
+    _lib.check(rc, "reshape_and_cache")
+
+
+# ------------------------------------------------------------------------------------------------
+# FP8 activation quantisation                         reference: vllm/_custom_ops.py:1832-1898
+# ------------------------------------------------------------------------------------------------
+def static_scaled_fp8_quant(result: torch.Tensor, input: torch.Tensor, scale: torch.Tensor,
+                            group_shape: tuple[int, int] | None = None) -> None:
+    """torch.ops._C.static_scaled_fp8_quant (csrc/libtorch_stable/.../fp8/common.cu:183-335)."""
+    _cuda(result, input, scale)
+    lib = _lib.load()
+    if input.stride(-1) != 1:
+        raise RuntimeError("last dimension of input must be contiguous")
+    if result.stride(-1) != 1:
+        raise RuntimeError("last dimension of output must be contiguous")
+    hidden = input.shape[-1]
+    num_tokens = input.numel() // hidden if hidden else 0
+    if scale.dim() == 0 or scale.numel() == 1:
+        gm, gn, si, sj = max(num_tokens, 1), hidden, 0, 0
+    elif scale.dim() == 1:
+        if group_shape is None:
+            raise RuntimeError(
+                "1D scale requires explicit group_shape to disambiguate per-channel vs per-token "
+                "quantization. Use group_shape=(-1, 1) for per-channel or group_shape=(1, -1) for "
+                "per-token.")
+        if len(group_shape) != 2:
+            raise RuntimeError(f"group_shape must have exactly 2 elements, got {len(group_shape)}")
+        gm = num_tokens if group_shape[0] == -1 else int(group_shape[0])
+        gn = hidden if group_shape[1] == -1 else int(group_shape[1])
+        em, en = num_tokens // gm, hidden // gn
+        if scale.numel() != em * en:
+            raise RuntimeError(
+                f"1D scale length ({scale.numel()}) does not match expected size ({em * en}) for "
+                f"group_shape {tuple(group_shape)} with input shape ({num_tokens}, {hidden})")
+        if em == 1:
+            si, sj = 0, scale.stride(0)
+        elif en == 1:
+            si, sj = scale.stride(0), 0
+        else:
+            raise RuntimeError(
+                "1D scale can only be used when one of the scale dimensions is 1. For 2D group "
+                "scaling, use a 2D scale tensor.")
+    elif scale.dim() == 2:
+        s0, s1 = scale.shape
+        if num_tokens % s0 != 0:
+            raise RuntimeError(f"num_tokens ({num_tokens}) must be divisible by scale.size(0) ({s0})")
+        if hidden % s1 != 0:
+            raise RuntimeError(f"hidden_size ({hidden}) must be divisible by scale.size(1) ({s1})")
+        gm, gn = num_tokens // s0, hidden // s1
+        if group_shape is not None:
+            if len(group_shape) != 2:
+                raise RuntimeError(
+                    f"group_shape must have exactly 2 elements, got {len(group_shape)}")
+            egm = num_tokens if group_shape[0] == -1 else int(group_shape[0])
+            egn = hidden if group_shape[1] == -1 else int(group_shape[1])
+            if (egm, egn) != (gm, gn):
+                raise RuntimeError(
+                    f"Explicit group_shape {tuple(group_shape)} does not match inferred group shape "
+                    f"({gm}, {gn}) from 2D scale tensor shape ({s0}, {s1})")
+        si, sj = scale.stride(0), scale.stride(1)
+    else:
+        raise RuntimeError(f"scale must be 0D, 1D, or 2D tensor, but got {scale.dim()}D")
+    rc = lib.b200_fp8_quant_static(
+        _p(result), _p(input), _p(scale), num_tokens, hidden,
+        input.stride(-2) if input.dim() > 1 else hidden,
+        result.stride(-2) if result.dim() > 1 else hidden,
+        gm, gn, si, sj, _dt(input), _stream())
+    _lib.check(rc, "static_scaled_fp8_quant")
+
+
+def dynamic_scaled_fp8_quant(result: torch.Tensor, input: torch.Tensor, scale: torch.Tensor) -> None:
+    """torch.ops._C.dynamic_scaled_fp8_quant (common.cu:337-381): scale[0] is written."""
+    _cuda(result, input, scale)
+    lib = _lib.load()
+    if input.stride(-1) != 1:
+        raise RuntimeError("last dimension of input must be contiguous")
+    if result.stride(-1) != 1:
+        raise RuntimeError("last dimension of output must be contiguous")
+    hidden = input.shape[-1]
+    num_tokens = input.numel() // hidden if hidden else 0
+    rc = lib.b200_fp8_quant_dynamic_tensor(
+        _p(result), _p(input), _p(scale), num_tokens, hidden,
+        input.stride(-2) if input.dim() > 1 else hidden,
+        result.stride(-2) if result.dim() > 1 else hidden, _dt(input), _stream())
+    _lib.check(rc, "dynamic_scaled_fp8_quant")
+
+
+def dynamic_per_token_scaled_fp8_quant(result: torch.Tensor, input: torch.Tensor,
+                                       scale: torch.Tensor, scale_ub: torch.Tensor | None) -> None:
+    """torch.ops._C.dynamic_per_token_scaled_fp8_quant (common.cu:383-422): scale[t] is written."""
+    _cuda(result, input, scale, scale_ub)
+    lib = _lib.load()
+    if input.stride(-1) != 1:
+        raise RuntimeError("last dimension of input must be contiguous")
+    if result.stride(-1) != 1:
+        raise RuntimeError("last dimension of output must be contiguous")
+    hidden = input.shape[-1]
+    num_tokens = input.numel() // hidden if hidden else 0
+    rc = lib.b200_fp8_quant_dynamic_token(
+        _p(result), _p(input), _p(scale), _p(scale_ub), num_tokens, hidden,
+        input.stride(-2) if input.dim() > 1 else hidden,
+        result.stride(-2) if result.dim() > 1 else hidden, _dt(input), _stream())
+    _lib.check(rc, "dynamic_per_token_scaled_fp8_quant")
+
+
+def scaled_fp8_quant(
+    input: torch.Tensor,
+    scale: torch.Tensor | None = None,
+    num_token_padding: int | None = None,
+    scale_ub: torch.Tensor | None = None,
+    use_per_token_if_dynamic: bool = False,
+    output: torch.Tensor | None = None,
+    group_shape: tuple[int, int] | None = None,
+) -> tuple[torch.Tensor, torch.Tensor]:
+    """Same contract as vllm._custom_ops.scaled_fp8_quant (vllm/_custom_ops.py:1832-1898)."""
+    assert input.ndim == 2
+    shape = tuple(input.shape)
+    if num_token_padding:
+        shape = (max(num_token_padding, input.shape[0]), shape[1])
+    if output is None:
+        output = torch.empty(shape, device=input.device, dtype=FP8_DTYPE)
+    else:
+        assert num_token_padding is None, "padding not supported if output passed in"
+        assert output.dtype == FP8_DTYPE
+    if scale is None:
+        if use_per_token_if_dynamic:
+            scale = torch.empty((shape[0], 1), device=input.device, dtype=torch.float32)
+            dynamic_per_token_scaled_fp8_quant(output, input, scale, scale_ub)
+        else:
+            scale = torch.empty(1, device=input.device, dtype=torch.float32)
+            dynamic_scaled_fp8_quant(output, input, scale)
+    else:
+        static_scaled_fp8_quant(output, input, scale, group_shape)
+    return output, scale
+
+
+# ------------------------------------------------------------------------------------------------
+# Paged-attention decode
+# ------------------------------------------------------------------------------------------------
+_workspaces: dict[tuple, torch.Tensor] = {}
+
+
+def paged_attention_workspace(num_seqs: int, num_heads: int, num_kv_heads: int, head_size: int,
+                              device: torch.device) -> torch.Tensor:
+    """Persistent split-KV workspace (the metadata builder owns it in the backend; cached here for
+    direct op calls). Sized once for the largest batch seen, like triton_attn.py:154-175."""
+    lib = _lib.load()
+    n = lib.b200_paged_attention_workspace_bytes(num_seqs, num_heads, num_kv_heads, head_size)
+    key = (str(device), num_heads, head_size)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < n:
+        ws = torch.empty(n, dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+def paged_attention_decode(
+    out: torch.Tensor,
+    query: torch.Tensor,
+    key_cache: torch.Tensor,
+    value_cache: torch.Tensor,
+    block_table: torch.Tensor,
+    seq_lens: torch.Tensor,
+    scale: float,
+    *,
+    k_scale: torch.Tensor | None = None,
+    v_scale: torch.Tensor | None = None,
+    alibi_slopes: torch.Tensor | None = None,
+    sliding_window: int | None = None,
+    softcap: float | None = None,
+    lse: torch.Tensor | None = None,
+    max_seq_len: int = 0,
+    workspace: torch.Tensor | None = None,
+) -> torch.Tensor:
+    """Decode attention over a paged KV cache.
+
+    query/out [S, Hq, D]; key_cache/value_cache [num_blocks, block_size, Hkv, D] views (any of the
+    NHD / HND / split layouts - strides are forwarded); block_table int32 [S, max_blocks];
+    seq_lens int32 [S]. fp8 caches (float8_e4m3fn or uint8) need k_scale / v_scale device scalars.
+    Semantics: ref_paged_attn in tests/kernels/attention/test_triton_unified_attention.py:33-88
+    with query_len == 1.
+    """
+    _cuda(out, query, key_cache, value_cache, block_table, seq_lens, k_scale, v_scale,
+          alibi_slopes, lse, workspace)
+    lib = _lib.load()
+    if query.dim() != 3 or key_cache.dim() != 4 or value_cache.dim() != 4:
+        raise RuntimeError("paged_attention_decode: query must be 3-D and the caches 4-D")
+    if query.stride(2) != 1 or out.stride(2) != 1 or key_cache.stride(3) != 1:
+        raise RuntimeError("paged_attention_decode: last dimension must be contiguous")
+    if key_cache.stride() != value_cache.stride() or key_cache.shape != value_cache.shape:
+        raise RuntimeError("paged_attention_decode: key_cache and value_cache must share shape and strides")
+    if block_table.dtype != torch.int32 or seq_lens.dtype != torch.int32:
+        raise RuntimeError("paged_attention_decode: block_table and seq_lens must be int32")
+    if block_table.stride(1) != 1:
+        raise RuntimeError("paged_attention_decode: block_table rows must be contiguous")
+    S, Hq, D = query.shape
+    nb, bs, Hkv, Dk = key_cache.shape
+    if Dk != D:
+        raise RuntimeError("paged_attention_decode: head_size mismatch between query and cache")
+    kv_fp8 = key_cache.element_size() == 1
+    if kv_fp8 and (k_scale is None or v_scale is None):
+        raise RuntimeError("paged_attention_decode: fp8 kv cache needs k_scale and v_scale")
+    if workspace is None:
+        workspace = paged_attention_workspace(S, Hq, Hkv, D, query.device)
+    a = _lib.PagedAttnArgs()
+    a.out, a.lse, a.q = _p(out), _p(lse), _p(query)
+    a.k_cache, a.v_cache = _p(key_cache), _p(value_cache)
+    a.block_table, a.seq_lens = _p(block_table), _p(seq_lens)
+    a.k_scale, a.v_scale = _p(k_scale), _p(v_scale)
+    a.alibi_slopes = _p(alibi_slopes)
+    a.workspace, a.workspace_bytes = _p(workspace), workspace.numel() * workspace.element_size()
+    a.num_blocks = nb
+    a.q_stride_s, a.q_stride_h = query.stride(0), query.stride(1)
+    a.out_stride_s, a.out_stride_h = out.stride(0), out.stride(1)
+    a.kv_block_stride, a.kv_token_stride, a.kv_head_stride = (
+        key_cache.stride(0), key_cache.stride(1), key_cache.stride(2))
+    a.bt_stride = block_table.stride(0)
+    a.num_seqs, a.num_heads, a.num_kv_heads, a.head_size, a.block_size = S, Hq, Hkv, D, bs
+    a.max_seq_len = int(max_seq_len)
+    a.q_dtype = _dt(query)
+    a.kv_dtype = FP8_E4M3 if kv_fp8 else _dt(key_cache)
+    a.sliding_window = int(sliding_window) if sliding_window else 0
+    a.scale = float(scale)
+    a.softcap = float(softcap) if softcap else 0.0
+    import ctypes
+    rc = lib.b200_paged_attention_decode(ctypes.byref(a), _stream())
+    _lib.check(rc, "paged_attention_decode")
+    return out
