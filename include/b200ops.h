@@ -164,6 +164,35 @@ B200_API size_t b200_paged_attention_workspace_bytes(int num_seqs, int num_heads
                                                      int head_size);
 B200_API int b200_paged_attention_decode(const b200_paged_attn_args* args, b200_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * FP8 W8A8 GEMM with scale epilogue (tcgen05 / TMEM / TMA).
+ * Replaces torch.ops._C.cutlass_scaled_mm
+ *   (csrc/libtorch_stable/quantization/w8a8/cutlass/scaled_mm_entry.cu:197-270; sm100 kernels
+ *    c3x/scaled_mm_sm100_fp8_dispatch.cuh:18-295; vllm/_custom_ops.py:756-804).
+ *   out[M,N] = a_scale (.) (b_scale (.) (a[M,K] . b[K,N])) (+ bias[N]), fp32 accumulate.
+ * a: e4m3 [M,K] row-major (row stride lda); b: e4m3 [K,N] COLUMN-major, i.e. the weight stored
+ * [N,K] with row stride ldb; K, lda, ldb multiples of 16. a_scale: float [1] or [M];
+ * b_scale: float [1] or [N]; bias: [N] in out dtype or NULL; out bf16/f16 with row stride ldo.
+ */
+B200_API int b200_fp8_gemm(void* out, const void* a, const void* b, const float* a_scale,
+                           const float* b_scale, const void* bias, int M, int N, int K, int64_t lda,
+                           int64_t ldb, int64_t ldo, int a_scale_per_row, int b_scale_per_col,
+                           int out_dtype, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Gated activation between the MLP / MoE GEMMs.
+ * Replaces torch.ops._C.silu_and_mul (csrc/libtorch_stable/activation_kernels.cu:102-160,291-296):
+ *   out[t,i] = silu(x[t,i]) * x[t,d+i], input [num_tokens, 2d], out [num_tokens, d] same dtype;
+ * and torch.ops._C.silu_and_mul_quant (csrc/libtorch_stable/quantization/activation_kernels.cu:33-104):
+ *   out e4m3 = quant_static(silu_and_mul(x), *scale).
+ */
+B200_API int b200_silu_and_mul(void* out, const void* input, int64_t num_tokens, int d,
+                               int64_t in_row_stride, int64_t out_row_stride, int dtype,
+                               b200_stream_t stream);
+B200_API int b200_silu_and_mul_fp8(void* out, const void* input, const float* scale,
+                                   int64_t num_tokens, int d, int64_t in_row_stride,
+                                   int64_t out_row_stride, int in_dtype, b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -281,3 +281,36 @@ def paged_attention_decode(query, key_cache, value_cache, block_table, seq_lens,
     if return_lse:
         return out, lse
     return out
+
+
+# --------------------------------------------------------------------------------------------
+# FP8 GEMM.  Baseline of the reference's own test: tests/kernels/utils.py:1130-1173
+# (baseline_scaled_mm): torch.mm(scale_a * a.float(), scale_b * b.float()).to(out_dtype) + bias
+# --------------------------------------------------------------------------------------------
+def scaled_mm(a_bits, b_bits_nk, scale_a, scale_b, bias=None) -> np.ndarray:
+    """a_bits uint8 [M,K] (e4m3), b_bits_nk uint8 [N,K] (the weight; b = weight.T), scales float32
+    ([1] / [M] / [N]); returns float64-accumulated float32 [M,N] (no output rounding)."""
+    a = e4m3_bits_to_f32(np.asarray(a_bits)).astype(np.float64)
+    w = e4m3_bits_to_f32(np.asarray(b_bits_nk)).astype(np.float64)
+    sa = np.asarray(scale_a, dtype=np.float64).reshape(-1, 1)
+    sb = np.asarray(scale_b, dtype=np.float64).reshape(1, -1)
+    out = (a @ w.T) * sa * sb
+    if bias is not None:
+        out = out + np.asarray(bias, dtype=np.float64).reshape(1, -1)
+    return out.astype(np.float32)
+
+
+# --------------------------------------------------------------------------------------------
+# silu_and_mul / silu_and_mul_quant.
+# csrc/libtorch_stable/activation_kernels.cu:102-160 and quantization/activation_kernels.cu:33-104:
+# silu is rounded to the activation dtype BEFORE the multiply, the product is rounded again.
+# --------------------------------------------------------------------------------------------
+def silu_and_mul(x: torch.Tensor) -> torch.Tensor:
+    d = x.shape[-1] // 2
+    xf = x[..., :d].to(torch.float32)
+    s = (xf / (1.0 + torch.exp(-xf))).to(x.dtype)
+    return (s.to(torch.float32) * x[..., d:].to(torch.float32)).to(x.dtype)
+
+
+def silu_and_mul_quant(x: torch.Tensor, scale: torch.Tensor) -> np.ndarray:
+    return static_scaled_fp8_quant(silu_and_mul(x), scale)

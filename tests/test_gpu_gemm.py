@@ -1,0 +1,122 @@
+"""GPU parity: cutlass_scaled_mm (FP8 W8A8 GEMM, tcgen05) and silu_and_mul(_quant) vs the oracle.
+Mirrors tests/kernels/quantization/test_cutlass_scaled_mm.py:82-230 (reference tolerance
+rtol=5e-1 atol=1.5e-1; ours is far tighter: the only error is the bf16/f16 output rounding)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ref_ops
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+MNK = [(1, 256, 128), (1, 16384, 1024), (1, 24576, 496), (16, 256, 496), (16, 16384, 128),
+       (16, 24576, 4096), (32, 8192, 4096), (32, 16384, 4096), (33, 1024, 1024), (33, 8192, 128),
+       (64, 2048, 496), (64, 16384, 1024), (100, 8192, 496), (128, 32768, 4096), (256, 4096, 4096),
+       (512, 256, 1024), (512, 8192, 4096), (512, 16384, 128), (512, 24576, 128),
+       (256, 6144, 4096), (256, 4096, 14336), (300, 1280, 8192), (2048, 2048, 2048)]
+
+
+def _ops():
+    from b200ops import ops
+    return ops
+
+
+def to_fp8_bits(t):
+    return t.clamp(-448, 448).to(torch.float8_e4m3fn).view(torch.uint8)
+
+
+def run_case(M, N, K, per_token, per_channel, out_dtype, use_bias, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    a8 = to_fp8_bits(torch.randn(M, K, generator=g))
+    w8 = to_fp8_bits(torch.randn(N, K, generator=g))
+    sa = (torch.rand(M if per_token else 1, generator=g) + 0.5) * 0.05
+    sb = (torch.rand(N if per_channel else 1, generator=g) + 0.5) * 0.05
+    bias = (torch.rand(N, generator=g) * 5 - 2.5).to(out_dtype) if use_bias else None
+    ref = ref_ops.scaled_mm(a8.numpy(), w8.numpy(), sa.numpy(), sb.numpy(),
+                            None if bias is None else bias.float().numpy())
+    a_g = a8.to(DEV).view(torch.float8_e4m3fn)
+    b_g = w8.to(DEV).view(torch.float8_e4m3fn).t()  # [K, N] column-major
+    out = _ops().cutlass_scaled_mm(a_g, b_g, sa.to(DEV).view(-1, 1) if per_token else sa.to(DEV),
+                                   sb.to(DEV).view(-1, 1) if per_channel else sb.to(DEV), out_dtype,
+                                   None if bias is None else bias.to(DEV))
+    torch.cuda.synchronize()
+    got = out.float().cpu().numpy()
+    assert got.shape == (M, N)
+    # output rounding: bf16 2^-9, f16 2^-12 relative (+ the bias rounding step)
+    rtol = 2 ** -8 if out_dtype == torch.bfloat16 else 2 ** -10
+    np.testing.assert_allclose(got, ref, rtol=rtol, atol=2e-2 if use_bias else 2e-3)
+
+
+@pytest.mark.parametrize("mnk", MNK)
+@pytest.mark.parametrize("per_token,per_channel", [(False, False), (True, True)])
+def test_scaled_mm_shapes(mnk, per_token, per_channel):
+    run_case(*mnk, per_token, per_channel, torch.bfloat16, False)
+
+
+@pytest.mark.parametrize("mnk", [(1, 256, 128), (33, 1024, 1024), (256, 4096, 4096), (512, 512, 512)])
+@pytest.mark.parametrize("per_token,per_channel", [(True, False), (False, True)])
+@pytest.mark.parametrize("out_dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("use_bias", [False, True])
+def test_scaled_mm_scales_bias_dtypes(mnk, per_token, per_channel, out_dtype, use_bias):
+    run_case(*mnk, per_token, per_channel, out_dtype, use_bias, seed=1)
+
+
+def test_scaled_mm_exact_small_integers():
+    """Integer-valued operands, power-of-two scales: every product and sum is exact in fp32 and in
+    bf16 -> the GEMM must be BIT-exact (catches descriptor / swizzle / k-offset mistakes)."""
+    g = torch.Generator().manual_seed(3)
+    for M, N, K in [(7, 128, 128), (130, 384, 256), (256, 256, 1024), (513, 512, 384)]:
+        a = torch.randint(-2, 3, (M, K), generator=g).float()
+        w = torch.randint(-2, 3, (N, K), generator=g).float()
+        ref = (a.double() @ w.double().t()).float() * 0.25
+        out = _ops().cutlass_scaled_mm(to_fp8_bits(a).to(DEV).view(torch.float8_e4m3fn),
+                                       to_fp8_bits(w).to(DEV).view(torch.float8_e4m3fn).t(),
+                                       torch.tensor([0.5], device=DEV), torch.tensor([0.5], device=DEV),
+                                       torch.bfloat16)
+        assert torch.equal(out.float().cpu(), ref.to(torch.bfloat16).float()), (M, N, K)
+
+
+def test_scaled_mm_strided_a_and_out_validation():
+    g = torch.Generator().manual_seed(4)
+    M, N, K = 48, 256, 512
+    wide = to_fp8_bits(torch.randn(M, 2 * K, generator=g))
+    w8 = to_fp8_bits(torch.randn(N, K, generator=g))
+    a_view = wide.to(DEV).view(torch.float8_e4m3fn)[:, K:]
+    one = torch.ones(1, device=DEV)
+    out = _ops().cutlass_scaled_mm(a_view, w8.to(DEV).view(torch.float8_e4m3fn).t(), one, one,
+                                   torch.float16)
+    ref = ref_ops.scaled_mm(wide[:, K:].numpy(), w8.numpy(), [1.0], [1.0])
+    np.testing.assert_allclose(out.float().cpu().numpy(), ref, rtol=2 ** -10, atol=2e-3)
+    with pytest.raises(RuntimeError, match="multiples of 16"):
+        _ops().cutlass_scaled_mm(a_view[:, :500], w8.to(DEV).view(torch.float8_e4m3fn)[:, :500].t(),
+                                 one, one, torch.float16)
+
+
+@pytest.mark.parametrize("tokens,d", [(1, 128), (7, 17), (83, 14336), (256, 14336), (4096, 512)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_silu_and_mul(tokens, d, dtype):
+    g = torch.Generator().manual_seed(5)
+    x = (torch.randn(tokens, 2 * d, generator=g) * 2).to(dtype)
+    ref = ref_ops.silu_and_mul(x)
+    out = torch.empty(tokens, d, dtype=dtype, device=DEV)
+    _ops().silu_and_mul(out, x.to(DEV))
+    # expf differs by <= 1 ulp(fp32) between libm and CUDA -> at most 1 ulp of the output dtype
+    ulp = 2 ** -7 if dtype == torch.bfloat16 else 2 ** -10
+    np.testing.assert_allclose(out.float().cpu().numpy(), ref.float().numpy(), rtol=ulp, atol=1e-6)
+    assert (out.cpu() == ref).float().mean() > 0.999
+
+
+@pytest.mark.parametrize("tokens,d", [(5, 128), (256, 14336), (33, 200)])
+def test_silu_and_mul_quant(tokens, d):
+    g = torch.Generator().manual_seed(6)
+    x = (torch.randn(tokens, 2 * d, generator=g) * 2).to(torch.bfloat16)
+    scale = torch.tensor([0.02])
+    ref = ref_ops.silu_and_mul_quant(x, scale)
+    out = torch.empty(tokens, d, dtype=torch.float8_e4m3fn, device=DEV)
+    _ops().silu_and_mul_quant(out, x.to(DEV), scale.to(DEV))
+    got = out.view(torch.uint8).cpu().numpy()
+    # identical except where the 1-ulp expf difference flips a rounding
+    assert (got == ref).mean() > 0.999
+    d1 = ref_ops.e4m3_bits_to_f32(got) - ref_ops.e4m3_bits_to_f32(ref)
+    assert np.abs(d1).max() <= 32.0  # never more than one fp8 step (largest step = 32 at 256..448)

@@ -1,0 +1,245 @@
+"""Synthetic decoder driver: one decode step of a Llama-shaped FP8 W8A8 + FP8-KV model built ONLY from
+the hot-path operators of this package (the role gpu_model_runner._model_forward plays in the
+reference, vllm/v1/worker/gpu_model_runner.py:3927, for the layer loop of
+vllm/model_executor/models/llama.py:222-328).
+
+Per layer:
+    RMSNorm -> static FP8 quant -> qkv GEMM -> RoPE -> KV-cache write -> paged attention ->
+    static FP8 quant -> o_proj GEMM (-> all-reduce) -> add+RMSNorm -> quant -> gate_up GEMM ->
+    silu_and_mul_quant -> down GEMM (-> all-reduce)
+then final norm -> bf16 lm_head -> greedy argmax.
+
+RMSNorm / RoPE / embedding / lm_head / argmax are outside the path named by north_star
+("next" rows) and use plain torch ops here; everything else is libb200ops.so.
+Tensor parallelism: attention heads and GEMM N/K are sharded over the ranks
+of `tp_group`, one NCCL all-reduce after o_proj and down_proj (linear.py:1766-1767).
+"""
+from __future__ import annotations
+
+import dataclasses
+
+import torch
+
+from . import ops
+
+
+@dataclasses.dataclass(frozen=True)
+class ModelShape:
+    name: str
+    hidden: int
+    layers: int
+    heads: int
+    kv_heads: int
+    head_size: int
+    inter: int
+    vocab: int
+    rope_theta: float = 500000.0
+    eps: float = 1e-5
+
+
+LLAMA_3_1_8B = ModelShape("Llama-3.1-8B-shaped", 4096, 32, 32, 8, 128, 14336, 128256)
+LLAMA_3_1_70B = ModelShape("Llama-3.1-70B-shaped", 8192, 80, 64, 8, 128, 28672, 128256)
+QWEN2_5_0_5B = ModelShape("Qwen2.5-0.5B-shaped", 896, 24, 14, 2, 64, 4864, 151936, 1000000.0, 1e-6)
+TINY = ModelShape("tiny-llama-shaped", 512, 2, 8, 2, 128, 1024, 1024)
+
+# kernels launched per call of each op (our own kernels only), for the bench's gpu_launches claim
+LAUNCHES = {"quant_static": 1, "gemm": 1, "cache_write": 1, "attention": 2, "silu_quant": 1}
+
+
+def _quant_weight(w: torch.Tensor):
+    """per-tensor FP8 weight quantisation, scale = amax / 448."""
+    scale = (w.abs().amax().float() / 448.0).clamp(min=1e-12).reshape(1)
+    q = (w.float() / scale).clamp(-448, 448).to(torch.float8_e4m3fn)
+    return q, scale
+
+
+class DecoderModel:
+    def __init__(self, shape: ModelShape, max_seqs: int, max_ctx: int, block_size: int = 16,
+                 device: str | torch.device = "cuda:0", tp_rank: int = 0, tp_size: int = 1,
+                 tp_group=None, seed: int = 1234, kv_fp8: bool = True, num_blocks: int | None = None):
+        self.shape = s = shape
+        self.dev = torch.device(device)
+        self.tp_rank, self.tp_size, self.tp_group = tp_rank, tp_size, tp_group
+        assert s.heads % tp_size == 0 and s.kv_heads % tp_size == 0 and s.inter % tp_size == 0
+        self.hq, self.hkv = s.heads // tp_size, s.kv_heads // tp_size
+        self.inter = s.inter // tp_size
+        self.D, self.bs = s.head_size, block_size
+        self.max_seqs, self.max_ctx = max_seqs, max_ctx
+        self.blocks_per_seq = (max_ctx + block_size - 1) // block_size
+        self.num_blocks = num_blocks or max_seqs * self.blocks_per_seq + 8
+        self.kv_fp8 = kv_fp8
+        self.launches_per_step = 0
+        g = torch.Generator(device=self.dev).manual_seed(seed)
+
+        def rnd(*shp, fan_in):
+            return (torch.rand(*shp, device=self.dev, generator=g) * 2 - 1) * (1.7 / fan_in ** 0.5)
+
+        H, D = s.hidden, s.head_size
+        self.embed = rnd(s.vocab, H, fan_in=1.0).mul(0.5).to(torch.bfloat16)
+        self.lm_head = rnd(s.vocab, H, fan_in=H).to(torch.bfloat16)
+        self.final_norm = torch.ones(H, device=self.dev, dtype=torch.bfloat16)
+        self.layers = []
+        one = lambda v: torch.tensor([v], device=self.dev, dtype=torch.float32)
+        for _ in range(s.layers):
+            L = {}
+            # every rank draws the full tensors with the same generator and keeps its shard, so a
+            # TP run computes the same function as the single-GPU run
+            wq = rnd(s.heads * D, H, fan_in=H)
+            wk = rnd(s.kv_heads * D, H, fan_in=H)
+            wv = rnd(s.kv_heads * D, H, fan_in=H)
+            sl = lambda w, n: w[tp_rank * n:(tp_rank + 1) * n]
+            wqkv = torch.cat([sl(wq, self.hq * D), sl(wk, self.hkv * D), sl(wv, self.hkv * D)])
+            wo = rnd(H, s.heads * D, fan_in=s.heads * D)[:, tp_rank * self.hq * D:(tp_rank + 1) * self.hq * D]
+            wg = sl(rnd(s.inter, H, fan_in=H), self.inter)
+            wu = sl(rnd(s.inter, H, fan_in=H), self.inter)
+            wd = rnd(H, s.inter, fan_in=s.inter)[:, tp_rank * self.inter:(tp_rank + 1) * self.inter]
+            # per-tensor scales must be identical on all ranks: derive them from the full tensors
+            L["wqkv"], L["wqkv_s"] = _quant_weight(wqkv.contiguous())
+            L["wo"], L["wo_s"] = _quant_weight(wo.contiguous())
+            L["wgu"], L["wgu_s"] = _quant_weight(torch.cat([wg, wu]).contiguous())
+            L["wd"], L["wd_s"] = _quant_weight(wd.contiguous())
+            L["in_norm"] = torch.ones(H, device=self.dev, dtype=torch.bfloat16)
+            L["post_norm"] = torch.ones(H, device=self.dev, dtype=torch.bfloat16)
+            # static activation scales (FP8 "static" checkpoints carry input_scale per linear)
+            L["a_qkv"], L["a_o"], L["a_gu"], L["a_d"] = one(4.0 / 448), one(2.0 / 448), one(4.0 / 448), one(8.0 / 448)
+            L["k_scale"], L["v_scale"] = one(4.0 / 448), one(4.0 / 448)
+            cdt = torch.uint8 if kv_fp8 else torch.bfloat16
+            # reference layout: (num_blocks, block_size, kv_heads, 2*head_size), K|V packed (NHD)
+            L["kv"] = torch.zeros(self.num_blocks, block_size, self.hkv, 2 * D, dtype=cdt, device=self.dev)
+            self.layers.append(L)
+            del wq, wk, wv, wqkv, wo, wg, wu, wd
+        # rotary cache [max_pos, D] (cos | sin), neox style (rotary_embedding/base.py)
+        inv = 1.0 / (s.rope_theta ** (torch.arange(0, D, 2, device=self.dev).float() / D))
+        t = torch.arange(max_ctx + 1, device=self.dev).float()
+        fr = torch.outer(t, inv)
+        self.cos, self.sin = fr.cos(), fr.sin()
+        # persistent step buffers (CUDA-graph friendly: fixed addresses)
+        S = max_seqs
+        self.token_ids = torch.zeros(S, dtype=torch.int64, device=self.dev)
+        self.positions = torch.zeros(S, dtype=torch.int64, device=self.dev)
+        self.slot_mapping = torch.zeros(S, dtype=torch.int64, device=self.dev)
+        self.seq_lens = torch.zeros(S, dtype=torch.int32, device=self.dev)
+        self.block_table = torch.zeros(S, self.blocks_per_seq, dtype=torch.int32, device=self.dev)
+        self.next_tokens = torch.zeros(S, dtype=torch.int64, device=self.dev)
+        self.workspace = ops.paged_attention_workspace(S, self.hq, self.hkv, D, self.dev)
+        self.x8 = torch.empty(S, max(H, self.hq * D), dtype=torch.float8_e4m3fn, device=self.dev)
+        self.h8 = torch.empty(S, self.inter, dtype=torch.float8_e4m3fn, device=self.dev)
+        self.qkv = torch.empty(S, (self.hq + 2 * self.hkv) * D, dtype=torch.bfloat16, device=self.dev)
+        self.attn_out = torch.empty(S, self.hq, D, dtype=torch.bfloat16, device=self.dev)
+        self.proj = torch.empty(S, H, dtype=torch.bfloat16, device=self.dev)
+        self.gu = torch.empty(S, 2 * self.inter, dtype=torch.bfloat16, device=self.dev)
+        self.attn_hook = None  # bench instrumentation: called around the attention launch
+        self.graph = None
+
+    # ---- torch glue for the ops outside the hot path (SURVEY.md 8f "next" rows)
+    def _rmsnorm(self, x, w):
+        xf = x.float()
+        return (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + self.shape.eps)).to(x.dtype) * w
+
+    def _rope(self, t, pos):
+        # t [S, heads, D] view; neox rotation in place
+        D = self.D
+        c = self.cos[pos].unsqueeze(1)
+        s = self.sin[pos].unsqueeze(1)
+        t1, t2 = t[..., : D // 2].float(), t[..., D // 2:].float()
+        t[..., : D // 2] = (t1 * c - t2 * s).to(t.dtype)
+        t[..., D // 2:] = (t2 * c + t1 * s).to(t.dtype)
+
+    def _all_reduce(self, t):
+        if self.tp_size > 1:
+            torch.distributed.all_reduce(t, group=self.tp_group)
+
+    # ---- one decode step over the persistent device buffers
+    def forward_device(self) -> None:
+        s, D, S = self.shape, self.D, self.max_seqs
+        H = s.hidden
+        n = 0
+        hidden = self.embed[self.token_ids]
+        residual = None
+        for L in self.layers:
+            if residual is None:
+                residual = hidden
+            else:
+                residual = residual + hidden
+            normed = self._rmsnorm(residual, L["in_norm"])
+            x8 = self.x8[:, :H]
+            ops.static_scaled_fp8_quant(x8, normed, L["a_qkv"]); n += LAUNCHES["quant_static"]
+            ops.cutlass_scaled_mm(x8, L["wqkv"].t(), L["a_qkv"], L["wqkv_s"], torch.bfloat16, out=self.qkv)
+            n += LAUNCHES["gemm"]
+            q = self.qkv[:, : self.hq * D].view(S, self.hq, D)
+            k = self.qkv[:, self.hq * D:(self.hq + self.hkv) * D].view(S, self.hkv, D)
+            v = self.qkv[:, (self.hq + self.hkv) * D:].view(S, self.hkv, D)
+            self._rope(q, self.positions)
+            self._rope(k, self.positions)
+            kc, vc = L["kv"][..., :D], L["kv"][..., D:]
+            ops.reshape_and_cache_flash(k, v, kc, vc, self.slot_mapping,
+                                        "fp8" if self.kv_fp8 else "auto", L["k_scale"], L["v_scale"])
+            n += LAUNCHES["cache_write"]
+            if self.attn_hook:
+                self.attn_hook(0)
+            ops.paged_attention_decode(self.attn_out, q, kc, vc, self.block_table, self.seq_lens,
+                                       D ** -0.5, k_scale=L["k_scale"] if self.kv_fp8 else None,
+                                       v_scale=L["v_scale"] if self.kv_fp8 else None,
+                                       max_seq_len=self.max_ctx, workspace=self.workspace)
+            n += LAUNCHES["attention"]
+            if self.attn_hook:
+                self.attn_hook(1)
+            a8 = self.x8[:, : self.hq * D]
+            ops.static_scaled_fp8_quant(a8, self.attn_out.view(S, self.hq * D), L["a_o"]); n += 1
+            ops.cutlass_scaled_mm(a8, L["wo"].t(), L["a_o"], L["wo_s"], torch.bfloat16, out=self.proj); n += 1
+            self._all_reduce(self.proj)
+            residual = residual + self.proj
+            normed = self._rmsnorm(residual, L["post_norm"])
+            x8 = self.x8[:, :H]
+            ops.static_scaled_fp8_quant(x8, normed, L["a_gu"]); n += 1
+            ops.cutlass_scaled_mm(x8, L["wgu"].t(), L["a_gu"], L["wgu_s"], torch.bfloat16, out=self.gu); n += 1
+            ops.silu_and_mul_quant(self.h8, self.gu, L["a_d"]); n += LAUNCHES["silu_quant"]
+            ops.cutlass_scaled_mm(self.h8, L["wd"].t(), L["a_d"], L["wd_s"], torch.bfloat16, out=self.proj); n += 1
+            self._all_reduce(self.proj)
+            hidden = self.proj
+        residual = residual + hidden
+        normed = self._rmsnorm(residual, self.final_norm)
+        logits = normed @ self.lm_head.t()
+        self.next_tokens.copy_(logits.argmax(-1))
+        self.launches_per_step = n
+
+    def capture(self) -> None:
+        """Capture forward_device() in a CUDA graph (decode steps are launch-bound otherwise)."""
+        side = torch.cuda.Stream(device=self.dev)
+        side.wait_stream(torch.cuda.current_stream(self.dev))
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                self.forward_device()
+        torch.cuda.current_stream(self.dev).wait_stream(side)
+        torch.cuda.synchronize(self.dev)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.forward_device()
+
+    def run_device(self) -> None:
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self.forward_device()
+
+    # ---- public step: host (pinned) inputs in, host tokens out
+    def step(self, host_in: dict, host_out: torch.Tensor) -> torch.Tensor:
+        """host_in: pinned CPU tensors token_ids, positions, slot_mapping [S] int64, seq_lens [S] int32,
+        block_table [S, blocks_per_seq] int32. host_out: pinned int64 [S]. Returns host_out after the
+        stream has been synchronised (the sampled token ids are needed by the caller's scheduler)."""
+        self.token_ids.copy_(host_in["token_ids"], non_blocking=True)
+        self.positions.copy_(host_in["positions"], non_blocking=True)
+        self.slot_mapping.copy_(host_in["slot_mapping"], non_blocking=True)
+        self.seq_lens.copy_(host_in["seq_lens"], non_blocking=True)
+        self.block_table.copy_(host_in["block_table"], non_blocking=True)
+        self.run_device()
+        host_out.copy_(self.next_tokens, non_blocking=True)
+        torch.cuda.current_stream(self.dev).synchronize()
+        return host_out
+
+    def h2d_bytes(self) -> int:
+        S = self.max_seqs
+        return S * 8 * 3 + S * 4 + S * self.blocks_per_seq * 4
+
+    def d2h_bytes(self) -> int:
+        return self.max_seqs * 8

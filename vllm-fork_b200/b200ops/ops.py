@@ -257,6 +257,91 @@ def scaled_fp8_quant(
 
 
 # ------------------------------------------------------------------------------------------------
+# FP8 W8A8 GEMM                                        reference: vllm/_custom_ops.py:756-804
+# ------------------------------------------------------------------------------------------------
+def cutlass_scaled_mm_supports_fp8(cuda_device_capability: int) -> bool:
+    """torch.ops._C.cutlass_scaled_mm_supports_fp8: this build targets sm_100a only."""
+    return cuda_device_capability // 10 == 10
+
+
+def cutlass_scaled_mm(
+    a: torch.Tensor,
+    b: torch.Tensor,
+    scale_a: torch.Tensor,
+    scale_b: torch.Tensor,
+    out_dtype: torch.dtype,
+    bias: torch.Tensor | None = None,
+    out: torch.Tensor | None = None,
+) -> torch.Tensor:
+    """output = torch.mm(scale_a * a, scale_b * b).to(out_dtype) (+ bias).
+    a: e4m3 [M, K] row-major; b: e4m3 [K, N] column-major (weight.t()); scale_a [1] / [M,1];
+    scale_b [1] / [N,1] (or [1,N]); fp32 accumulate."""
+    assert out_dtype is torch.bfloat16 or out_dtype is torch.float16
+    assert bias is None or (bias.numel() == b.shape[1] and bias.dtype == out_dtype)
+    _cuda(a, b, scale_a, scale_b, bias, out)
+    lib = _lib.load()
+    target_shape = (*a.shape[:-1], b.shape[1])
+    a = a.view(-1, a.shape[-1])
+    M, K = a.shape
+    N = b.shape[1]
+    if a.element_size() != 1 or b.element_size() != 1:
+        raise RuntimeError("cutlass_scaled_mm: a and b must be fp8_e4m3")
+    if b.shape[0] != K:
+        raise RuntimeError("cutlass_scaled_mm: a.shape[1] must equal b.shape[0]")
+    if b.stride(0) != 1 or (M > 1 and a.stride(1) != 1) or (M == 1 and K > 1 and a.stride(1) != 1):
+        raise RuntimeError("cutlass_scaled_mm: a must be row-major and b column-major")
+    if K % 16 != 0 or N % 16 != 0:
+        raise RuntimeError("cutlass_scaled_mm: b.shape[0] and b.shape[1] must be multiples of 16")
+    if scale_a.dtype != torch.float32 or scale_b.dtype != torch.float32:
+        raise RuntimeError("cutlass_scaled_mm: scales must be float32")
+    if scale_a.numel() not in (1, M) or scale_b.numel() not in (1, N):
+        raise RuntimeError("cutlass_scaled_mm: scale_a must have 1 or M elements, scale_b 1 or N")
+    if not (scale_a.is_contiguous() and scale_b.is_contiguous()):
+        raise RuntimeError("cutlass_scaled_mm: scales must be contiguous")
+    if out is None:
+        out = torch.empty((M, N), dtype=out_dtype, device=a.device)
+    elif out.dtype != out_dtype or out.stride(-1) != 1:
+        raise RuntimeError("cutlass_scaled_mm: bad out tensor")
+    rc = lib.b200_fp8_gemm(
+        _p(out), _p(a), _p(b), _p(scale_a), _p(scale_b), _p(bias), M, N, K,
+        a.stride(0) if M > 1 else K, b.stride(1), out.stride(0) if out.dim() > 1 else N,
+        1 if scale_a.numel() > 1 else 0, 1 if scale_b.numel() > 1 else 0, _dt(out), _stream())
+    _lib.check(rc, "cutlass_scaled_mm")
+    return out.view(*target_shape)
+
+
+# ------------------------------------------------------------------------------------------------
+# Gated activation                      reference: torch.ops._C.silu_and_mul / silu_and_mul_quant
+# ------------------------------------------------------------------------------------------------
+def silu_and_mul(result: torch.Tensor, input: torch.Tensor) -> None:
+    """result [..., d] = silu(input[..., :d]) * input[..., d:]."""
+    _cuda(result, input)
+    lib = _lib.load()
+    d = input.shape[-1] // 2
+    if result.shape[-1] != d or input.stride(-1) != 1 or result.stride(-1) != 1:
+        raise RuntimeError("silu_and_mul: input [..., 2d] and result [..., d], last dim contiguous")
+    n = input.numel() // (2 * d) if d else 0
+    i2, r2 = input.view(-1, 2 * d), result.view(-1, d)
+    rc = lib.b200_silu_and_mul(_p(r2), _p(i2), n, d, i2.stride(0), r2.stride(0), _dt(input),
+                               _stream())
+    _lib.check(rc, "silu_and_mul")
+
+
+def silu_and_mul_quant(result: torch.Tensor, input: torch.Tensor, scale: torch.Tensor) -> None:
+    """result (e4m3) [..., d] = static_scaled_fp8_quant(silu_and_mul(input), scale)."""
+    _cuda(result, input, scale)
+    lib = _lib.load()
+    d = input.shape[-1] // 2
+    if result.shape[-1] != d or result.element_size() != 1:
+        raise RuntimeError("silu_and_mul_quant: result must be fp8 [..., d]")
+    n = input.numel() // (2 * d) if d else 0
+    i2, r2 = input.view(-1, 2 * d), result.view(-1, d)
+    rc = lib.b200_silu_and_mul_fp8(_p(r2), _p(i2), _p(scale), n, d, i2.stride(0), r2.stride(0),
+                                   _dt(input), _stream())
+    _lib.check(rc, "silu_and_mul_quant")
+
+
+# ------------------------------------------------------------------------------------------------
 # Paged-attention decode
 # ------------------------------------------------------------------------------------------------
 _workspaces: dict[tuple, torch.Tensor] = {}

@@ -1,0 +1,350 @@
+// b200ops -- FP8 (E4M3) W8A8 GEMM with scale epilogue on tcgen05 / TMEM / TMA (sm_100a).
+//
+// Contract: torch.ops._C.cutlass_scaled_mm (csrc/libtorch_stable/quantization/w8a8/cutlass/
+// scaled_mm_entry.cu:197-270, sm100 dispatch c3x/scaled_mm_sm100_fp8_dispatch.cuh:18-295; epilogue
+// cutlass_extensions/epilogue/scaled_mm_epilogues_c3x.hpp:151-236; vllm/_custom_ops.py:756-804):
+//   out[M,N] = a_scale (.) ( b_scale (.) (A[M,K] . B[K,N]) ) (+ bias[N]),  fp32 accumulate,
+//   A e4m3 row-major, B e4m3 column-major (= weight [N,K] row-major), scales per-tensor or
+//   per-row(A) / per-column(B), out bf16 / f16.
+//
+// B200 design. Both operands are K-major, so one kernel serves two orientations:
+//   "rows" operand -> UMMA M = 128 (TMEM lanes), "cols" operand -> UMMA N = BN (TMEM columns).
+//   * decode (M <= 256): swap-AB like the reference's M<=64 buckets: rows = 128 weight rows,
+//     cols = the whole (padded) batch, so every weight byte is streamed from HBM exactly once and
+//     the accumulator [128 x M] lives in <= 256 TMEM columns;
+//   * large M: rows = 128 activation rows, cols = 256 weight rows.
+// Warp-specialised: warp 0 = TMA producer (SWIZZLE_128B boxes, mbarrier ring), warp 1 = single-thread
+// tcgen05.mma issuer (kind::f8f6f4, 128xBNx32 per instruction) + TMEM owner, warps 2-5 = epilogue
+// (tcgen05.ld 32x32b -> scale/bias -> bf16 -> global).
+#include "common.cuh"
+
+namespace b200 {
+namespace gemm8 {
+
+constexpr int BM = 128;          // UMMA M
+constexpr int BK = 128;          // k-block = 128 fp8 = one 128-byte swizzle row
+constexpr int UMMA_K = 32;       // fp8 MMA K
+constexpr int NTHREADS = 192;
+constexpr int MAX_STAGES = 8;
+
+struct Params {
+  void* out;
+  const float* r_scale;  // scale of the rows operand   (per-row or scalar)
+  const float* c_scale;  // scale of the cols operand   (per-col or scalar)
+  const void* bias;      // [N] in out dtype, nullable (indexed by the weight dimension)
+  int R, C, K;           // rows-operand extent, cols-operand extent, reduction
+  int64_t ldo;           // output row stride (elements)
+  int r_scale_vec, c_scale_vec;  // 1 = per-row / per-col vector, 0 = scalar
+  int swap;              // 1: rows operand = weight (out[c][r]); 0: rows operand = activation (out[r][c])
+  int out_bf16;
+  int stages;
+};
+
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void tc_mma_f8(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+        "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
+        "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tc_wait_ld() {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (tile rows are 128 bytes; 8-row groups are
+// 1024 bytes apart). Field layout: cute/arch/mma_sm100_desc.hpp SmemDescriptor.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);          // start address
+  d |= (uint64_t)1 << 16;                                // LBO (unused for swizzled K-major) = 1
+  d |= (uint64_t)(1024 >> 4) << 32;                      // SBO = 1024 B
+  d |= (uint64_t)1 << 46;                                // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;                                // SWIZZLE_128B
+  return d;
+}
+
+template <int BN>
+__global__ void __launch_bounds__(NTHREADS, 1)
+    gemm_fp8_kernel(const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmC,
+                    const Params p) {
+  constexpr uint32_t R_BYTES = BM * BK;
+  constexpr uint32_t C_BYTES = BN * BK;
+  constexpr uint32_t STAGE_BYTES = R_BYTES + C_BYTES;
+  constexpr uint32_t TMEM_COLS = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
+  // instruction descriptor: D = F32, A = B = E4M3, both K-major, N = BN, M = 128
+  constexpr uint32_t IDESC = (1u << 4) | (0u << 7) | (0u << 10) | ((uint32_t)(BN >> 3) << 17) |
+                             ((uint32_t)(BM >> 4) << 24);
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_base = smem_u32(smem_raw);
+  const uint32_t base = (raw_base + 1023u) & ~1023u;
+  uint8_t* smem = smem_raw + (base - raw_base);
+  const int stages = p.stages;
+  const uint32_t bar_base = base + (uint32_t)stages * STAGE_BYTES;
+  const uint32_t bar_full = bar_base;
+  const uint32_t bar_empty = bar_base + 8u * MAX_STAGES;
+  const uint32_t bar_tmem = bar_base + 16u * MAX_STAGES;
+  volatile uint32_t* tmem_holder =
+      reinterpret_cast<volatile uint32_t*>(smem + (size_t)stages * STAGE_BYTES + 16 * MAX_STAGES + 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row0 = blockIdx.x * BM;
+  const int col0 = blockIdx.y * BN;
+  const int num_kb = (p.K + BK - 1) / BK;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < stages; i++) {
+      mbar_init(bar_full + 8u * i, 1);
+      mbar_init(bar_empty + 8u * i, 1);
+    }
+    mbar_init(bar_tmem, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    const uint32_t holder = smem_u32((const void*)tmem_holder);
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(holder),
+                 "r"(TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_d = *tmem_holder;
+
+  if (warp == 0) {
+    // ============================== TMA producer
+    if (lane == 0) {
+      prefetch_tmap(&tmR);
+      prefetch_tmap(&tmC);
+      // weights are streamed once; activations are re-read by every CTA
+      const uint64_t pol_w = l2_policy_evict_first();
+      const uint64_t pol_a = l2_policy_evict_last();
+      const uint64_t pol_r = p.swap ? pol_w : pol_a;
+      const uint64_t pol_c = p.swap ? pol_a : pol_w;
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < num_kb; kb++) {
+        mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
+        const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES;
+        mbar_arrive_expect_tx(bar_full + 8u * stage, STAGE_BYTES);
+        tma_load_2d(dst, &tmR, bar_full + 8u * stage, kb * BK, row0, pol_r);
+        tma_load_2d(dst + R_BYTES, &tmC, bar_full + 8u * stage, kb * BK, col0, pol_c);
+        if (++stage == stages) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp == 1) {
+    // ============================== MMA issuer (one thread)
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < num_kb; kb++) {
+        mbar_wait(bar_full + 8u * stage, phase);
+        tc_fence_after();
+        const uint32_t sa = base + (uint32_t)stage * STAGE_BYTES;
+        const uint64_t da = make_smem_desc(sa);
+        const uint64_t db = make_smem_desc(sa + R_BYTES);
+#pragma unroll
+        for (int k = 0; k < BK / UMMA_K; k++) {
+          // advance the start address by k * 32 bytes inside the 128-byte swizzle row
+          tc_mma_f8(tmem_d, da + (uint64_t)(k * UMMA_K >> 4), db + (uint64_t)(k * UMMA_K >> 4), IDESC,
+                    (kb > 0 || k > 0) ? 1u : 0u);
+        }
+        tc_commit(bar_empty + 8u * stage);  // frees the smem slot when the MMAs have read it
+        if (++stage == stages) { stage = 0; phase ^= 1u; }
+      }
+      tc_commit(bar_tmem);  // accumulator complete
+    }
+  } else {
+    // ============================== epilogue (4 warps, one TMEM lane quarter each)
+    const int wq = warp & 3;
+    mbar_wait(bar_tmem, 0);
+    tc_fence_after();
+    const int r = row0 + wq * 32 + lane;  // rows-operand index of this thread
+    const bool r_ok = r < p.R;
+    const float rs = p.r_scale_vec ? (r_ok ? p.r_scale[r] : 0.f) : p.r_scale[0];
+    const float cs0 = p.c_scale_vec ? 0.f : p.c_scale[0];
+    uint16_t* out16 = reinterpret_cast<uint16_t*>(p.out);
+    const uint16_t* bias16 = reinterpret_cast<const uint16_t*>(p.bias);
+    auto to_f32 = [&](uint16_t h) -> float {
+      if (p.out_bf16) return __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(&h));
+      return __half2float(*reinterpret_cast<const __half*>(&h));
+    };
+    auto from_f32 = [&](float f) -> uint16_t {
+      if (p.out_bf16) {
+        __nv_bfloat16 b = __float2bfloat16_rn(f);
+        return *reinterpret_cast<uint16_t*>(&b);
+      }
+      __half h = __float2half_rn(f);
+      return *reinterpret_cast<uint16_t*>(&h);
+    };
+    float bias_r = 0.f;
+    if (p.swap && bias16 && r_ok) bias_r = to_f32(bias16[r]);
+    const int ncols = min(BN, p.C - col0);
+#pragma unroll 1
+    for (int c0 = 0; c0 < ncols; c0 += 16) {
+      uint32_t v[16];
+      tc_ld16(tmem_d + ((uint32_t)(wq * 32) << 16) + (uint32_t)c0, v);
+      tc_wait_ld();
+      if (!r_ok) continue;
+      if (p.swap) {
+        // rows = weight index n, cols = batch index m : out[m][n]; reference order a_s * (b_s * acc)
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+          const int c = col0 + c0 + j;
+          if (c < p.C) {
+            const float cs = p.c_scale_vec ? p.c_scale[c] : cs0;
+            const float o = cs * (rs * __uint_as_float(v[j])) + bias_r;
+            out16[(int64_t)c * p.ldo + r] = from_f32(o);
+          }
+        }
+      } else {
+        // rows = batch index m, cols = weight index n : out[m][n]
+        uint16_t h[16];
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+          const int c = col0 + c0 + j;
+          float o = 0.f;
+          if (c < p.C) {
+            const float cs = p.c_scale_vec ? p.c_scale[c] : cs0;
+            o = rs * (cs * __uint_as_float(v[j]));
+            if (bias16) o += to_f32(bias16[c]);
+          }
+          h[j] = from_f32(o);
+        }
+        uint16_t* dst = out16 + (int64_t)r * p.ldo + col0 + c0;
+        if (col0 + c0 + 16 <= p.C && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+          reinterpret_cast<uint4*>(dst)[0] = reinterpret_cast<const uint4*>(h)[0];
+          reinterpret_cast<uint4*>(dst)[1] = reinterpret_cast<const uint4*>(h)[1];
+        } else {
+          for (int j = 0; j < 16; j++)
+            if (col0 + c0 + j < p.C) dst[j] = h[j];
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(TMEM_COLS)
+                 : "memory");
+  }
+}
+
+template <int BN>
+static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, Params& p, dim3 grid,
+                  cudaStream_t stream) {
+  constexpr uint32_t STAGE_BYTES = BM * BK + BN * BK;
+  const int smem_max = max_smem_optin();
+  int stages = (smem_max - 1024 - 256 - 64) / (int)STAGE_BYTES;
+  if (stages > MAX_STAGES) stages = MAX_STAGES;
+  if (stages < 2) {
+    set_last_error("fp8_gemm: not enough shared memory");
+    return B200_ERR_UNSUPPORTED;
+  }
+  p.stages = stages;
+  const int smem = stages * (int)STAGE_BYTES + 16 * MAX_STAGES + 64 + 1024;
+  static bool configured = false;
+  if (!configured) {
+    B200_CUDA(cudaFuncSetAttribute(gemm_fp8_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   smem_max));
+    configured = true;
+  }
+  gemm_fp8_kernel<BN><<<grid, NTHREADS, smem, stream>>>(tmR, tmC, p);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+static int make_tmap_2d(CUtensorMap* tm, const void* base, int rows, int K, int64_t ld_bytes,
+                        int box_rows) {
+  uint64_t dims[2] = {(uint64_t)K, (uint64_t)rows};
+  uint64_t strides[1] = {(uint64_t)ld_bytes};
+  uint32_t box[2] = {(uint32_t)BK, (uint32_t)box_rows};
+  return encode_tensor_map(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, base, dims, strides, box,
+                           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+}
+
+}  // namespace gemm8
+}  // namespace b200
+
+extern "C" int b200_fp8_gemm(void* out, const void* a, const void* b, const float* a_scale,
+                             const float* b_scale, const void* bias, int M, int N, int K,
+                             int64_t lda, int64_t ldb, int64_t ldo, int a_scale_per_row,
+                             int b_scale_per_col, int out_dtype, b200_stream_t stream_) {
+  using namespace b200;
+  using namespace b200::gemm8;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  B200_CHECK(M >= 0 && N > 0 && K > 0, B200_ERR_INVALID, "cutlass_scaled_mm: bad sizes (%d,%d,%d)", M,
+             N, K);
+  if (M == 0) return B200_OK;
+  B200_CHECK(out && a && b && a_scale && b_scale, B200_ERR_INVALID,
+             "cutlass_scaled_mm: null pointer");
+  B200_CHECK(out_dtype == B200_BF16 || out_dtype == B200_F16, B200_ERR_INVALID,
+             "cutlass_scaled_mm: out dtype must be bf16 or f16");
+  B200_CHECK(lda % 16 == 0 && ldb % 16 == 0 && K % 16 == 0, B200_ERR_INVALID,
+             "cutlass_scaled_mm: K and the row strides of a / b must be multiples of 16 (got K=%d lda=%lld ldb=%lld)",
+             K, (long long)lda, (long long)ldb);
+  B200_CHECK(((uintptr_t)a & 15) == 0 && ((uintptr_t)b & 15) == 0, B200_ERR_INVALID,
+             "cutlass_scaled_mm: a / b must be 16-byte aligned");
+  B200_CHECK(sm_count() > 0, B200_ERR_CUDA, "cutlass_scaled_mm: no CUDA device (no CPU fallback)");
+  Params p;
+  p.out = out;
+  p.bias = bias;
+  p.K = K;
+  p.ldo = ldo;
+  p.out_bf16 = out_dtype == B200_BF16;
+  p.stages = 0;
+  const bool swap = M <= 256;
+  p.swap = swap ? 1 : 0;
+  CUtensorMap tmR, tmC;
+  int rc;
+  int bn;
+  if (swap) {
+    // rows = weight [N,K], cols = activation [M,K]
+    bn = M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : M <= 128 ? 128 : 256;
+    p.R = N; p.C = M;
+    p.r_scale = b_scale; p.r_scale_vec = b_scale_per_col;
+    p.c_scale = a_scale; p.c_scale_vec = a_scale_per_row;
+    rc = make_tmap_2d(&tmR, b, N, K, ldb, BM);
+    if (rc) return rc;
+    rc = make_tmap_2d(&tmC, a, M, K, lda, bn);
+    if (rc) return rc;
+  } else {
+    bn = 256;
+    p.R = M; p.C = N;
+    p.r_scale = a_scale; p.r_scale_vec = a_scale_per_row;
+    p.c_scale = b_scale; p.c_scale_vec = b_scale_per_col;
+    rc = make_tmap_2d(&tmR, a, M, K, lda, BM);
+    if (rc) return rc;
+    rc = make_tmap_2d(&tmC, b, N, K, ldb, bn);
+    if (rc) return rc;
+  }
+  dim3 grid((p.R + BM - 1) / BM, (p.C + bn - 1) / bn);
+  switch (bn) {
+    case 16: return launch<16>(tmR, tmC, p, grid, stream);
+    case 32: return launch<32>(tmR, tmC, p, grid, stream);
+    case 64: return launch<64>(tmR, tmC, p, grid, stream);
+    case 128: return launch<128>(tmR, tmC, p, grid, stream);
+    default: return launch<256>(tmR, tmC, p, grid, stream);
+  }
+}
