@@ -193,6 +193,39 @@ B200_API int b200_silu_and_mul_fp8(void* out, const void* input, const float* sc
                                    int64_t num_tokens, int d, int64_t in_row_stride,
                                    int64_t out_row_stride, int in_dtype, b200_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Neighbours of the hot path: RMSNorm (+ residual add) fused with the
+ * static FP8 quantisation of the next GEMM input, and rotary embedding.
+ * Replace torch.ops._C.rms_norm / fused_add_rms_norm (csrc/libtorch_stable/layernorm_kernels.cu),
+ * rms_norm_static_fp8_quant / fused_add_rms_norm_static_fp8_quant
+ * (csrc/libtorch_stable/layernorm_quant_kernels.cu:21-156) and rotary_embedding
+ * (csrc/libtorch_stable/pos_encoding_kernels.cu:8-160). hidden % 8 == 0, half / bfloat16.
+ */
+B200_API int b200_rms_norm(void* out, const void* input, const void* weight, float eps,
+                           int64_t num_tokens, int hidden, int64_t in_row_stride, int dtype,
+                           b200_stream_t stream);
+/* residual += input (rounded to dtype); input = rms_norm(residual) * weight  (both in place) */
+B200_API int b200_fused_add_rms_norm(void* input, void* residual, const void* weight, float eps,
+                                     int64_t num_tokens, int hidden, int64_t in_row_stride, int dtype,
+                                     b200_stream_t stream);
+B200_API int b200_rms_norm_static_fp8_quant(void* out, const void* input, const void* weight,
+                                            const float* scale, float eps, int64_t num_tokens,
+                                            int hidden, int64_t in_row_stride, int dtype,
+                                            b200_stream_t stream);
+/* residual += input; out(e4m3) = quant_static(rms_norm(residual) * weight, *scale) */
+B200_API int b200_fused_add_rms_norm_static_fp8_quant(void* out, void* input, void* residual,
+                                                      const void* weight, const float* scale,
+                                                      float eps, int64_t num_tokens, int hidden,
+                                                      int64_t in_row_stride, int dtype,
+                                                      b200_stream_t stream);
+/* In-place RoPE on query [T, num_heads, head] and key [T, num_kv_heads, head] (key nullable);
+ * cos_sin_cache [max_pos, rot_dim] (cos | sin) in the same dtype; positions int64 [T]. */
+B200_API int b200_rotary_embedding(const int64_t* positions, void* query, void* key,
+                                   const void* cos_sin_cache, int64_t num_tokens, int rot_dim,
+                                   int64_t query_stride, int64_t key_stride, int64_t head_stride,
+                                   int num_heads, int num_kv_heads, int is_neox, int dtype,
+                                   b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -314,3 +314,52 @@ def silu_and_mul(x: torch.Tensor) -> torch.Tensor:
 
 def silu_and_mul_quant(x: torch.Tensor, scale: torch.Tensor) -> np.ndarray:
     return static_scaled_fp8_quant(silu_and_mul(x), scale)
+
+
+# --------------------------------------------------------------------------------------------
+# RMSNorm family.  csrc/libtorch_stable/layernorm_kernels.cu, layernorm_quant_kernels.cu:21-156
+# --------------------------------------------------------------------------------------------
+def rms_norm(x: torch.Tensor, weight: torch.Tensor, eps: float, residual: torch.Tensor | None = None):
+    """Returns (out, new_residual). z = T(x + r); out = T(T(z * rsqrt(mean(z^2)+eps)) * w)."""
+    if residual is not None:
+        x = (x.float() + residual.float()).to(x.dtype)
+    xf = x.float()
+    s = torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + eps)
+    out = ((xf * s).to(x.dtype).float() * weight.float()).to(x.dtype)
+    return out, x
+
+
+def rms_norm_static_fp8_quant(x, weight, scale, eps, residual=None):
+    """out8 = e4m3(clamp(float(T(z * s * w)) * (1/scale))) (layernorm_quant_kernels.cu:66-71)."""
+    if residual is not None:
+        x = (x.float() + residual.float()).to(x.dtype)
+    xf = x.float()
+    s = torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + eps)
+    normed = (xf * s * weight.float()).to(x.dtype)
+    return static_scaled_fp8_quant(normed, scale), x
+
+
+# --------------------------------------------------------------------------------------------
+# RoPE.  csrc/libtorch_stable/pos_encoding_kernels.cu:8-99
+# --------------------------------------------------------------------------------------------
+def rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox):
+    """Returns rotated (query, key) copies; query [T, H, D]."""
+    rot = cos_sin_cache.shape[1]
+    emb = rot // 2
+    cs = cos_sin_cache[positions].float()
+    cos, sin = cs[:, None, :emb], cs[:, None, emb:]
+
+    def rot_one(t):
+        t = t.clone()
+        tf = t.float()
+        if is_neox:
+            x, y = tf[..., :emb], tf[..., emb:rot]
+            t[..., :emb] = (x * cos - y * sin).to(t.dtype)
+            t[..., emb:rot] = (y * cos + x * sin).to(t.dtype)
+        else:
+            x, y = tf[..., 0:rot:2], tf[..., 1:rot:2]
+            t[..., 0:rot:2] = (x * cos - y * sin).to(t.dtype)
+            t[..., 1:rot:2] = (y * cos + x * sin).to(t.dtype)
+        return t
+
+    return rot_one(query), (None if key is None else rot_one(key))

@@ -96,6 +96,19 @@ SIGNATURES = {
         c_int, [c_void_p, c_void_p, c_int64, c_int, c_int64, c_int64, c_int, c_void_p]),
     "b200_silu_and_mul_fp8": (
         c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int64, c_int64, c_int, c_void_p]),
+    "b200_rms_norm": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_float, c_int64, c_int, c_int64, c_int, c_void_p]),
+    "b200_fused_add_rms_norm": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_float, c_int64, c_int, c_int64, c_int, c_void_p]),
+    "b200_rms_norm_static_fp8_quant": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_int64, c_int, c_int64, c_int,
+                c_void_p]),
+    "b200_fused_add_rms_norm_static_fp8_quant": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_int64, c_int, c_int64,
+                c_int, c_void_p]),
+    "b200_rotary_embedding": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int64, c_int64, c_int64,
+                c_int, c_int, c_int, c_int, c_void_p]),
     "b200_paged_attention_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200_paged_attention_decode": (c_int, [C.POINTER(PagedAttnArgs), c_void_p]),
 }

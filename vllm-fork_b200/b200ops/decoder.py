@@ -9,8 +9,9 @@ Per layer:
     silu_and_mul_quant -> down GEMM (-> all-reduce)
 then final norm -> bf16 lm_head -> greedy argmax.
 
-RMSNorm / RoPE / embedding / lm_head / argmax are outside the path named by north_star
-("next" rows) and use plain torch ops here; everything else is libb200ops.so.
+Embedding lookup / bf16 lm_head / argmax are outside the path named by north_star and use plain torch
+ops (a library GEMM for lm_head); everything else - including the SURVEY.md section 8f rank-1 rows
+RMSNorm(+residual)+FP8-quant and RoPE - is libb200ops.so.
 Tensor parallelism: attention heads and GEMM N/K are sharded over the ranks
 of `tp_group`, one NCCL all-reduce after o_proj and down_proj (linear.py:1766-1767).
 """
@@ -112,7 +113,8 @@ class DecoderModel:
         inv = 1.0 / (s.rope_theta ** (torch.arange(0, D, 2, device=self.dev).float() / D))
         t = torch.arange(max_ctx + 1, device=self.dev).float()
         fr = torch.outer(t, inv)
-        self.cos, self.sin = fr.cos(), fr.sin()
+        self.cos_sin = torch.cat([fr.cos(), fr.sin()], dim=-1).to(torch.bfloat16).contiguous()
+        self.residual = torch.empty(max_seqs, H, dtype=torch.bfloat16, device=self.dev)
         # persistent step buffers (CUDA-graph friendly: fixed addresses)
         S = max_seqs
         self.token_ids = torch.zeros(S, dtype=torch.int64, device=self.dev)
@@ -131,20 +133,6 @@ class DecoderModel:
         self.attn_hook = None  # bench instrumentation: called around the attention launch
         self.graph = None
 
-    # ---- torch glue for the ops outside the hot path (SURVEY.md 8f "next" rows)
-    def _rmsnorm(self, x, w):
-        xf = x.float()
-        return (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + self.shape.eps)).to(x.dtype) * w
-
-    def _rope(self, t, pos):
-        # t [S, heads, D] view; neox rotation in place
-        D = self.D
-        c = self.cos[pos].unsqueeze(1)
-        s = self.sin[pos].unsqueeze(1)
-        t1, t2 = t[..., : D // 2].float(), t[..., D // 2:].float()
-        t[..., : D // 2] = (t1 * c - t2 * s).to(t.dtype)
-        t[..., D // 2:] = (t2 * c + t1 * s).to(t.dtype)
-
     def _all_reduce(self, t):
         if self.tp_size > 1:
             torch.distributed.all_reduce(t, group=self.tp_group)
@@ -154,23 +142,22 @@ class DecoderModel:
         s, D, S = self.shape, self.D, self.max_seqs
         H = s.hidden
         n = 0
-        hidden = self.embed[self.token_ids]
-        residual = None
-        for L in self.layers:
-            if residual is None:
-                residual = hidden
+        x8 = self.x8[:, :H]
+        a8 = self.x8[:, : self.hq * D]
+        q = self.qkv[:, : self.hq * D].view(S, self.hq, D)
+        k = self.qkv[:, self.hq * D:(self.hq + self.hkv) * D].view(S, self.hkv, D)
+        v = self.qkv[:, (self.hq + self.hkv) * D:].view(S, self.hkv, D)
+        torch.index_select(self.embed, 0, self.token_ids, out=self.residual)
+        for li, L in enumerate(self.layers):
+            if li == 0:
+                ops.rms_norm_static_fp8_quant(x8, self.residual, L["in_norm"], L["a_qkv"], s.eps)
             else:
-                residual = residual + hidden
-            normed = self._rmsnorm(residual, L["in_norm"])
-            x8 = self.x8[:, :H]
-            ops.static_scaled_fp8_quant(x8, normed, L["a_qkv"]); n += LAUNCHES["quant_static"]
+                ops.fused_add_rms_norm_static_fp8_quant(x8, self.proj, self.residual, L["in_norm"],
+                                                        L["a_qkv"], s.eps)
+            n += 1
             ops.cutlass_scaled_mm(x8, L["wqkv"].t(), L["a_qkv"], L["wqkv_s"], torch.bfloat16, out=self.qkv)
             n += LAUNCHES["gemm"]
-            q = self.qkv[:, : self.hq * D].view(S, self.hq, D)
-            k = self.qkv[:, self.hq * D:(self.hq + self.hkv) * D].view(S, self.hkv, D)
-            v = self.qkv[:, (self.hq + self.hkv) * D:].view(S, self.hkv, D)
-            self._rope(q, self.positions)
-            self._rope(k, self.positions)
+            ops.rotary_embedding(self.positions, q, k, D, self.cos_sin, True); n += 1
             kc, vc = L["kv"][..., :D], L["kv"][..., D:]
             ops.reshape_and_cache_flash(k, v, kc, vc, self.slot_mapping,
                                         "fp8" if self.kv_fp8 else "auto", L["k_scale"], L["v_scale"])
@@ -184,22 +171,17 @@ class DecoderModel:
             n += LAUNCHES["attention"]
             if self.attn_hook:
                 self.attn_hook(1)
-            a8 = self.x8[:, : self.hq * D]
             ops.static_scaled_fp8_quant(a8, self.attn_out.view(S, self.hq * D), L["a_o"]); n += 1
             ops.cutlass_scaled_mm(a8, L["wo"].t(), L["a_o"], L["wo_s"], torch.bfloat16, out=self.proj); n += 1
             self._all_reduce(self.proj)
-            residual = residual + self.proj
-            normed = self._rmsnorm(residual, L["post_norm"])
-            x8 = self.x8[:, :H]
-            ops.static_scaled_fp8_quant(x8, normed, L["a_gu"]); n += 1
+            ops.fused_add_rms_norm_static_fp8_quant(x8, self.proj, self.residual, L["post_norm"],
+                                                    L["a_gu"], s.eps); n += 1
             ops.cutlass_scaled_mm(x8, L["wgu"].t(), L["a_gu"], L["wgu_s"], torch.bfloat16, out=self.gu); n += 1
             ops.silu_and_mul_quant(self.h8, self.gu, L["a_d"]); n += LAUNCHES["silu_quant"]
             ops.cutlass_scaled_mm(self.h8, L["wd"].t(), L["a_d"], L["wd_s"], torch.bfloat16, out=self.proj); n += 1
             self._all_reduce(self.proj)
-            hidden = self.proj
-        residual = residual + hidden
-        normed = self._rmsnorm(residual, self.final_norm)
-        logits = normed @ self.lm_head.t()
+        ops.fused_add_rms_norm(self.proj, self.residual, self.final_norm, s.eps); n += 1
+        logits = self.proj @ self.lm_head.t()
         self.next_tokens.copy_(logits.argmax(-1))
         self.launches_per_step = n
 

@@ -342,6 +342,80 @@ def silu_and_mul_quant(result: torch.Tensor, input: torch.Tensor, scale: torch.T
 
 
 # ------------------------------------------------------------------------------------------------
+# RMSNorm (+ residual, + static FP8 quant) and RoPE     reference: vllm/_custom_ops.py rms_norm,
+# fused_add_rms_norm, rms_norm_static_fp8_quant, fused_add_rms_norm_static_fp8_quant, rotary_embedding
+# ------------------------------------------------------------------------------------------------
+def _rows(t: torch.Tensor):
+    h = t.shape[-1]
+    t2 = t.view(-1, h)
+    return t2, t2.shape[0], h
+
+
+def rms_norm(out: torch.Tensor, input: torch.Tensor, weight: torch.Tensor, epsilon: float) -> None:
+    _cuda(out, input, weight)
+    i2, n, h = _rows(input)
+    if not out.is_contiguous():
+        raise RuntimeError("rms_norm: out must be contiguous")
+    rc = _lib.load().b200_rms_norm(_p(out), _p(i2), _p(weight), float(epsilon), n, h, i2.stride(0),
+                                   _dt(input), _stream())
+    _lib.check(rc, "rms_norm")
+
+
+def fused_add_rms_norm(input: torch.Tensor, residual: torch.Tensor, weight: torch.Tensor,
+                       epsilon: float) -> None:
+    _cuda(input, residual, weight)
+    i2, n, h = _rows(input)
+    if not residual.is_contiguous():
+        raise RuntimeError("fused_add_rms_norm: residual must be contiguous")
+    rc = _lib.load().b200_fused_add_rms_norm(_p(i2), _p(residual), _p(weight), float(epsilon), n, h,
+                                             i2.stride(0), _dt(input), _stream())
+    _lib.check(rc, "fused_add_rms_norm")
+
+
+def rms_norm_static_fp8_quant(out: torch.Tensor, input: torch.Tensor, weight: torch.Tensor,
+                              scale: torch.Tensor, epsilon: float) -> None:
+    _cuda(out, input, weight, scale)
+    i2, n, h = _rows(input)
+    if not out.is_contiguous():
+        raise RuntimeError("rms_norm_static_fp8_quant: out must be contiguous")
+    rc = _lib.load().b200_rms_norm_static_fp8_quant(_p(out), _p(i2), _p(weight), _p(scale),
+                                                    float(epsilon), n, h, i2.stride(0), _dt(input),
+                                                    _stream())
+    _lib.check(rc, "rms_norm_static_fp8_quant")
+
+
+def fused_add_rms_norm_static_fp8_quant(out: torch.Tensor, input: torch.Tensor,
+                                        residual: torch.Tensor, weight: torch.Tensor,
+                                        scale: torch.Tensor, epsilon: float) -> None:
+    _cuda(out, input, residual, weight, scale)
+    i2, n, h = _rows(input)
+    if not (out.is_contiguous() and residual.is_contiguous()):
+        raise RuntimeError("fused_add_rms_norm_static_fp8_quant: out / residual must be contiguous")
+    rc = _lib.load().b200_fused_add_rms_norm_static_fp8_quant(
+        _p(out), _p(i2), _p(residual), _p(weight), _p(scale), float(epsilon), n, h, i2.stride(0),
+        _dt(input), _stream())
+    _lib.check(rc, "fused_add_rms_norm_static_fp8_quant")
+
+
+def rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor | None,
+                     head_size: int, cos_sin_cache: torch.Tensor, is_neox: bool) -> None:
+    """In place. query [T, Hq*D] or [T, Hq, D]; key likewise or None; positions int64 [T]."""
+    _cuda(positions, query, key, cos_sin_cache)
+    T = positions.numel()
+    if positions.dtype != torch.int64:
+        raise RuntimeError("rotary_embedding: positions must be int64")
+    if cos_sin_cache.dtype != query.dtype:
+        raise RuntimeError("rotary_embedding: cos_sin_cache must have the query dtype")
+    q2 = query.view(T, -1, head_size) if query.dim() == 2 else query
+    k2 = None if key is None else (key.view(T, -1, head_size) if key.dim() == 2 else key)
+    rc = _lib.load().b200_rotary_embedding(
+        _p(positions), _p(q2), _p(k2), _p(cos_sin_cache), T, cos_sin_cache.shape[1], q2.stride(0),
+        0 if k2 is None else k2.stride(0), q2.stride(1), q2.shape[1],
+        0 if k2 is None else k2.shape[1], 1 if is_neox else 0, _dt(query), _stream())
+    _lib.check(rc, "rotary_embedding")
+
+
+# ------------------------------------------------------------------------------------------------
 # Paged-attention decode
 # ------------------------------------------------------------------------------------------------
 _workspaces: dict[tuple, torch.Tensor] = {}

@@ -115,7 +115,9 @@ static int launch(const CUtensorMap& tmK, const CUtensorMap& tmV, const Params& 
   B200_LAUNCH_CHECK();
   dim3 rgrid(p.S, pl.n_chunks);
   constexpr bool QBF16 = (MODE == BF16_BF16 || MODE == BF16_FP8);
-  paged_attn_reduce_kernel<QBF16><<<rgrid, 128, 0, stream>>>(p, D, pl.grid_x);
+  int rthreads = p.hc * p.g * (D / 4);
+  rthreads = rthreads > 1024 ? 1024 : ((rthreads + 31) / 32) * 32;
+  paged_attn_reduce_kernel<QBF16><<<rgrid, rthreads, 0, stream>>>(p, D, pl.grid_x);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

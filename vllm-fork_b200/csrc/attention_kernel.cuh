@@ -567,9 +567,9 @@ __global__ void __launch_bounds__(NTHREADS, 1)
 }
 
 // Merge the partials of sequences that were cut by CTA boundaries; zero-fill empty sequences.
-// grid (S, n_chunks), 128 threads.
+// grid (S, n_chunks); each thread owns 4 consecutive d of one q-head (float4 partial loads).
 template <bool QBF16>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(1024)
     paged_attn_reduce_kernel(const Params p, int D, int grid_x) {
   const int s = blockIdx.x;
   const int y = blockIdx.y;
@@ -579,11 +579,14 @@ __global__ void __launch_bounds__(128)
   const int tpc = p.cum[p.S + 1];
   const float v_scale = (p.v_scale) ? *p.v_scale : 1.f;
   uint16_t* obase = reinterpret_cast<uint16_t*>(p.out) + (int64_t)s * p.out_stride_s;
+  const int d4n = D >> 2;
+  const int items = hq_chunk * d4n;
   if (c1 == c0) {
     // empty sequence: defined output (zeros), lse = -inf
-    for (int i = threadIdx.x; i < hq_chunk * D; i += blockDim.x) {
-      const int h = i / D, d = i - h * D;
-      obase[(int64_t)(y * hq_chunk + h) * p.out_stride_h + d] = 0;
+    for (int i = threadIdx.x; i < items; i += blockDim.x) {
+      const int h = i / d4n, d = (i - h * d4n) << 2;
+      *reinterpret_cast<uint2*>(obase + (int64_t)(y * hq_chunk + h) * p.out_stride_h + d) =
+          make_uint2(0u, 0u);
     }
     if (p.lse)
       for (int h = threadIdx.x; h < hq_chunk; h += blockDim.x)
@@ -592,31 +595,30 @@ __global__ void __launch_bounds__(128)
   }
   const int cta0 = c0 / tpc, cta1 = (c1 - 1) / tpc;
   if (cta0 == cta1) return;  // written directly by the attention kernel
-  for (int i = threadIdx.x; i < hq_chunk * D; i += blockDim.x) {
-    const int h = i / D, d = i - h * D;
+  for (int i = threadIdx.x; i < items; i += blockDim.x) {
+    const int h = i / d4n, d = (i - h * d4n) << 2;
     float mstar = -INFINITY;
     for (int c = cta0; c <= cta1; c++) {
       const int slot = (c * tpc >= c0) ? 0 : 1;
       const int64_t ps = ((int64_t)(y * grid_x + c)) * 2 + slot;
-      mstar = fmaxf(mstar, p.part_ml[(ps * hq_chunk + h) * 2]);
+      mstar = fmaxf(mstar, __ldg(p.part_ml + (ps * hq_chunk + h) * 2));
     }
-    float num = 0.f, den = 0.f;
+    float4 num = make_float4(0.f, 0.f, 0.f, 0.f);
+    float den = 0.f;
     for (int c = cta0; c <= cta1; c++) {
       const int slot = (c * tpc >= c0) ? 0 : 1;
       const int64_t ps = ((int64_t)(y * grid_x + c)) * 2 + slot;
-      const float f = ex2(p.part_ml[(ps * hq_chunk + h) * 2] - mstar);
-      den += f * p.part_ml[(ps * hq_chunk + h) * 2 + 1];
-      num += f * p.part_acc[(ps * hq_chunk + h) * D + d];
+      const float2 ml = __ldg(reinterpret_cast<const float2*>(p.part_ml + (ps * hq_chunk + h) * 2));
+      const float f = ex2(ml.x - mstar);
+      const float4 a = __ldg(reinterpret_cast<const float4*>(p.part_acc + (ps * hq_chunk + h) * D + d));
+      den += f * ml.y;
+      num.x += f * a.x; num.y += f * a.y; num.z += f * a.z; num.w += f * a.w;
     }
-    const float o = num / den * v_scale;
-    const int64_t oi = (int64_t)(y * hq_chunk + h) * p.out_stride_h + d;
-    if (QBF16) {
-      __nv_bfloat16 v = __float2bfloat16_rn(o);
-      obase[oi] = *reinterpret_cast<uint16_t*>(&v);
-    } else {
-      __half v = __float2half_rn(o);
-      obase[oi] = *reinterpret_cast<uint16_t*>(&v);
-    }
+    const float inv = v_scale / den;
+    uint2 o;
+    o.x = pack2<QBF16>(num.x * inv, num.y * inv);
+    o.y = pack2<QBF16>(num.z * inv, num.w * inv);
+    *reinterpret_cast<uint2*>(obase + (int64_t)(y * hq_chunk + h) * p.out_stride_h + d) = o;
     if (p.lse && d == 0) p.lse[(int64_t)s * p.Hq + y * hq_chunk + h] = (mstar + lg2(den)) * LN2;
   }
 }
