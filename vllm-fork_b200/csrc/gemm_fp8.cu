@@ -18,6 +18,9 @@
 // (tcgen05.ld 32x32b -> scale/bias -> bf16 -> global).
 #include "common.cuh"
 
+#include <cmath>
+#include <cstring>
+
 namespace b200 {
 namespace gemm8 {
 
@@ -38,6 +41,7 @@ struct Params {
   int swap;              // 1: rows operand = weight (out[c][r]); 0: rows operand = activation (out[r][c])
   int out_bf16;
   int stages;
+  int tma_store;         // swap mode: stage the tile in smem and write it with one TMA store
 };
 
 __device__ __forceinline__ void tc_fence_before() {
@@ -85,7 +89,7 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
 template <int BN>
 __global__ void __launch_bounds__(NTHREADS, 1)
     gemm_fp8_kernel(const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmC,
-                    const Params p) {
+                    const __grid_constant__ CUtensorMap tmO, const Params p) {
   constexpr uint32_t R_BYTES = BM * BK;
   constexpr uint32_t C_BYTES = BN * BK;
   constexpr uint32_t STAGE_BYTES = R_BYTES + C_BYTES;
@@ -200,44 +204,107 @@ __global__ void __launch_bounds__(NTHREADS, 1)
     float bias_r = 0.f;
     if (p.swap && bias16 && r_ok) bias_r = to_f32(bias16[r]);
     const int ncols = min(BN, p.C - col0);
-#pragma unroll 1
-    for (int c0 = 0; c0 < ncols; c0 += 16) {
-      uint32_t v[16];
-      tc_ld16(tmem_d + ((uint32_t)(wq * 32) << 16) + (uint32_t)c0, v);
-      tc_wait_ld();
-      if (!r_ok) continue;
-      if (p.swap) {
-        // rows = weight index n, cols = batch index m : out[m][n]; reference order a_s * (b_s * acc)
+    const int nchunks = (ncols + 15) >> 4;
+    const uint32_t tbase = tmem_d + ((uint32_t)(wq * 32) << 16);
+    uint32_t v0[16], v1[16];
+    tc_ld16(tbase, v0);
+    if (p.swap && p.tma_store) {
+      // rows = weight index n (TMEM lane), cols = batch index m. Stage the [m][128 n] tile in the
+      // (now idle) pipeline smem and let one TMA store write it: rows of 256 contiguous bytes.
+      const uint32_t stile = base;  // 1024-aligned, >= BN * 256 bytes
+      auto stage_chunk = [&](const uint32_t (&vv)[16], int ch) {
 #pragma unroll
-        for (int j = 0; j < 16; j++) {
-          const int c = col0 + c0 + j;
-          if (c < p.C) {
-            const float cs = p.c_scale_vec ? p.c_scale[c] : cs0;
-            const float o = cs * (rs * __uint_as_float(v[j])) + bias_r;
-            out16[(int64_t)c * p.ldo + r] = from_f32(o);
+        for (int j = 0; j < 16; j += 2) {
+          const int c = col0 + (ch << 4) + j;
+          const float cs_a = p.c_scale_vec ? (c < p.C ? p.c_scale[c] : 0.f) : cs0;
+          const float cs_b = p.c_scale_vec ? (c + 1 < p.C ? p.c_scale[c + 1] : 0.f) : cs0;
+          const float oa = cs_a * (rs * __uint_as_float(vv[j])) + bias_r;
+          const float ob = cs_b * (rs * __uint_as_float(vv[j + 1])) + bias_r;
+          // 2x2 transpose between lane pairs: even lane ends with column j of rows (n, n+1),
+          // odd lane with column j+1 of rows (n-1, n)
+          const float send = (lane & 1) ? oa : ob;
+          const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
+          const float lo = (lane & 1) ? recv : oa;
+          const float hi = (lane & 1) ? ob : recv;
+          uint32_t packed;
+          if (p.out_bf16) {
+            __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
+            packed = *reinterpret_cast<uint32_t*>(&t);
+          } else {
+            __half2 t = __floats2half2_rn(lo, hi);
+            packed = *reinterpret_cast<uint32_t*>(&t);
           }
+          const int m_local = (ch << 4) + j + (lane & 1);
+          const uint32_t addr = stile + (uint32_t)m_local * (BM * 2) + (uint32_t)(wq * 32 + (lane & ~1)) * 2u;
+          asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(packed) : "memory");
         }
-      } else {
-        // rows = batch index m, cols = weight index n : out[m][n]
-        uint16_t h[16];
+      };
+      for (int ch = 0; ch < nchunks; ch += 2) {
+        tc_wait_ld();
+        if (ch + 1 < nchunks) tc_ld16(tbase + (uint32_t)((ch + 1) << 4), v1);
+        stage_chunk(v0, ch);
+        if (ch + 1 < nchunks) {
+          tc_wait_ld();
+          if (ch + 2 < nchunks) tc_ld16(tbase + (uint32_t)((ch + 2) << 4), v0);
+          stage_chunk(v1, ch + 1);
+        }
+      }
+      fence_proxy_async();  // generic-proxy smem writes -> visible to the TMA (async proxy)
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (warp == 2 && lane == 0) {
+        asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];" ::"l"(&tmO),
+                     "r"(row0), "r"(col0), "r"(stile)
+                     : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+      }
+    } else {
+      auto store_chunk = [&](const uint32_t (&vv)[16], int ch) {
+        const int c0 = ch << 4;
+        if (!r_ok) return;
+        if (p.swap) {
+          // rows = weight index n, cols = batch index m : out[m][n]; reference order a_s * (b_s * acc)
 #pragma unroll
-        for (int j = 0; j < 16; j++) {
-          const int c = col0 + c0 + j;
-          float o = 0.f;
-          if (c < p.C) {
-            const float cs = p.c_scale_vec ? p.c_scale[c] : cs0;
-            o = rs * (cs * __uint_as_float(v[j]));
-            if (bias16) o += to_f32(bias16[c]);
+          for (int j = 0; j < 16; j++) {
+            const int c = col0 + c0 + j;
+            if (c < p.C) {
+              const float cs = p.c_scale_vec ? p.c_scale[c] : cs0;
+              const float o = cs * (rs * __uint_as_float(vv[j])) + bias_r;
+              out16[(int64_t)c * p.ldo + r] = from_f32(o);
+            }
           }
-          h[j] = from_f32(o);
-        }
-        uint16_t* dst = out16 + (int64_t)r * p.ldo + col0 + c0;
-        if (col0 + c0 + 16 <= p.C && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
-          reinterpret_cast<uint4*>(dst)[0] = reinterpret_cast<const uint4*>(h)[0];
-          reinterpret_cast<uint4*>(dst)[1] = reinterpret_cast<const uint4*>(h)[1];
         } else {
-          for (int j = 0; j < 16; j++)
-            if (col0 + c0 + j < p.C) dst[j] = h[j];
+          // rows = batch index m, cols = weight index n : out[m][n]
+          uint16_t h[16];
+#pragma unroll
+          for (int j = 0; j < 16; j++) {
+            const int c = col0 + c0 + j;
+            float o = 0.f;
+            if (c < p.C) {
+              const float cs = p.c_scale_vec ? p.c_scale[c] : cs0;
+              o = rs * (cs * __uint_as_float(vv[j]));
+              if (bias16) o += to_f32(bias16[c]);
+            }
+            h[j] = from_f32(o);
+          }
+          uint16_t* dst = out16 + (int64_t)r * p.ldo + col0 + c0;
+          if (col0 + c0 + 16 <= p.C && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+            reinterpret_cast<uint4*>(dst)[0] = reinterpret_cast<const uint4*>(h)[0];
+            reinterpret_cast<uint4*>(dst)[1] = reinterpret_cast<const uint4*>(h)[1];
+          } else {
+            for (int j = 0; j < 16; j++)
+              if (col0 + c0 + j < p.C) dst[j] = h[j];
+          }
+        }
+      };
+      for (int ch = 0; ch < nchunks; ch += 2) {
+        tc_wait_ld();
+        if (ch + 1 < nchunks) tc_ld16(tbase + (uint32_t)((ch + 1) << 4), v1);
+        store_chunk(v0, ch);
+        if (ch + 1 < nchunks) {
+          tc_wait_ld();
+          if (ch + 2 < nchunks) tc_ld16(tbase + (uint32_t)((ch + 2) << 4), v0);
+          store_chunk(v1, ch + 1);
         }
       }
     }
@@ -252,7 +319,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
 }
 
 template <int BN>
-static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, Params& p, dim3 grid,
+static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, const CUtensorMap& tmO, Params& p, dim3 grid,
                   cudaStream_t stream) {
   constexpr uint32_t STAGE_BYTES = BM * BK + BN * BK;
   const int smem_max = max_smem_optin();
@@ -270,7 +337,7 @@ static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, Params& p, dim
                                    smem_max));
     configured = true;
   }
-  gemm_fp8_kernel<BN><<<grid, NTHREADS, smem, stream>>>(tmR, tmC, p);
+  gemm_fp8_kernel<BN><<<grid, NTHREADS, smem, stream>>>(tmR, tmC, tmO, p);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -316,12 +383,32 @@ extern "C" int b200_fp8_gemm(void* out, const void* a, const void* b, const floa
   p.stages = 0;
   const bool swap = M <= 256;
   p.swap = swap ? 1 : 0;
-  CUtensorMap tmR, tmC;
+  p.tma_store = 0;
+  CUtensorMap tmR, tmC, tmO;
+  memset(&tmO, 0, sizeof(tmO));
   int rc;
   int bn;
+  const int sms = sm_count();
   if (swap) {
-    // rows = weight [N,K], cols = activation [M,K]
-    bn = M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : M <= 128 ? 128 : 256;
+    // rows = weight [N,K], cols = activation [M,K]. Pick the batch tile BN (and with it the number
+    // of CTAs per weight slab) with a small cost model: per k-block a CTA needs max(MMA cycles,
+    // bytes / per-SM ingest rate); waves over the SMs; fixed prologue + epilogue.
+    const int slabs = (N + BM - 1) / BM;
+    const int num_kb = (K + BK - 1) / BK;
+    const int cands[5] = {256, 128, 64, 32, 16};
+    double best = 1e30;
+    bn = 16;
+    for (int ci = 0; ci < 5; ci++) {
+      const int c = cands[ci];
+      if (c >= 2 * M && c > 16) continue;  // never pad the batch by more than 2x
+      const int gy = (M + c - 1) / c;
+      const double ctas = (double)slabs * gy;
+      const double waves = ceil(ctas / sms);
+      const double mma = 4.0 * (128.0 * c / 256.0);
+      const double ingest = (BM * BK + c * BK) / 70.0;
+      const double t = waves * (num_kb * (mma > ingest ? mma : ingest) + 5000.0 + 12.0 * c);
+      if (t < best) { best = t; bn = c; }
+    }
     p.R = N; p.C = M;
     p.r_scale = b_scale; p.r_scale_vec = b_scale_per_col;
     p.c_scale = a_scale; p.c_scale_vec = a_scale_per_row;
@@ -329,6 +416,15 @@ extern "C" int b200_fp8_gemm(void* out, const void* a, const void* b, const floa
     if (rc) return rc;
     rc = make_tmap_2d(&tmC, a, M, K, lda, bn);
     if (rc) return rc;
+    if (((uintptr_t)out & 15) == 0 && (ldo * 2) % 16 == 0) {
+      uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
+      uint64_t strides[1] = {(uint64_t)ldo * 2};
+      uint32_t box[2] = {(uint32_t)BM, (uint32_t)bn};
+      rc = encode_tensor_map(&tmO, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, out, dims, strides, box,
+                             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE);
+      if (rc) return rc;
+      p.tma_store = 1;
+    }
   } else {
     bn = 256;
     p.R = M; p.C = N;
@@ -341,10 +437,10 @@ extern "C" int b200_fp8_gemm(void* out, const void* a, const void* b, const floa
   }
   dim3 grid((p.R + BM - 1) / BM, (p.C + bn - 1) / bn);
   switch (bn) {
-    case 16: return launch<16>(tmR, tmC, p, grid, stream);
-    case 32: return launch<32>(tmR, tmC, p, grid, stream);
-    case 64: return launch<64>(tmR, tmC, p, grid, stream);
-    case 128: return launch<128>(tmR, tmC, p, grid, stream);
-    default: return launch<256>(tmR, tmC, p, grid, stream);
+    case 16: return launch<16>(tmR, tmC, tmO, p, grid, stream);
+    case 32: return launch<32>(tmR, tmC, tmO, p, grid, stream);
+    case 64: return launch<64>(tmR, tmC, tmO, p, grid, stream);
+    case 128: return launch<128>(tmR, tmC, tmO, p, grid, stream);
+    default: return launch<256>(tmR, tmC, tmO, p, grid, stream);
   }
 }
