@@ -226,6 +226,53 @@ B200_API int b200_rotary_embedding(const int64_t* positions, void* query, void* 
                                    int num_heads, int num_kv_heads, int is_neox, int dtype,
                                    b200_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Fused MoE.
+ * b200_moe_align_block_size replaces torch.ops._moe_C.moe_align_block_size
+ *   (csrc/libtorch_stable/moe/moe_align_sum_kernels.cu:100-350,625-723): histogram of topk_ids per
+ *   (mapped) expert, counts padded to block_size, exclusive scan; sorted_token_ids (pad = numel),
+ *   expert_ids per block (-1 tail), num_tokens_post_pad. ids < 0, >= num_experts or mapped to -1
+ *   by expert_map (int32 [num_experts], nullable) are dropped. Tokens of one expert keep ascending
+ *   flat-index order (deterministic). inv_perm (nullable, int32 [numel]): sorted position of each
+ *   flat (token, k) index, -1 if dropped -- consumed by b200_moe_unpermute_reduce.
+ * b200_moe_topk_softmax replaces torch.ops._moe_C.topk_softmax (topk_softmax_kernels.cu:76-262).
+ * b200_moe_sum replaces torch.ops._moe_C.moe_sum (moe_align_sum_kernels.cu:352-500, 757-930).
+ * b200_moe_permute_fp8 / b200_moe_unpermute_reduce: moe_permute / moe_unpermute
+ *   (csrc/libtorch_stable/moe/moe_permute_unpermute_op.cu) fused with the static FP8 quantisation
+ *   of the GEMM input and with the topk-weighted sum respectively.
+ * b200_moe_grouped_gemm_fp8: the grouped GEMM of fused_experts
+ *   (vllm/model_executor/layers/fused_moe/fused_moe.py:299-612; cutlass_moe_mm,
+ *   csrc/libtorch_stable/quantization/w8a8/cutlass/moe/grouped_mm_c3x_sm100.cu:16-115):
+ *   out[i,:] = a_scale * w_scale[e] * (a_sorted[i,:] . w[e]^T) (* row_weight[i]) for every block of
+ *   block_size sorted rows with expert e = expert_ids[block] >= 0. w: e4m3 [E, N, K] contiguous.
+ */
+B200_API int b200_moe_align_block_size(const void* topk_ids, int topk_ids_dtype, int64_t numel,
+                                       int num_experts, int block_size, int32_t* sorted_token_ids,
+                                       int64_t sorted_len, int32_t* expert_ids, int64_t expert_ids_len,
+                                       int32_t* num_tokens_post_pad, const int32_t* expert_map,
+                                       int32_t* inv_perm, b200_stream_t stream);
+B200_API int b200_moe_topk_softmax(float* topk_weights, int32_t* topk_ids,
+                                   int32_t* token_expert_indices, const void* gating_output,
+                                   const float* bias, int64_t num_tokens, int num_experts, int topk,
+                                   int renormalize, int gating_dtype, b200_stream_t stream);
+B200_API int b200_moe_sum(void* out, const void* input, int64_t num_tokens, int topk, int d,
+                          int64_t stride_token, int64_t stride_topk, const void* topk_ids,
+                          int topk_ids_dtype, const int32_t* expert_map, int dtype,
+                          b200_stream_t stream);
+B200_API int b200_moe_permute_fp8(void* dst, const void* src, const int32_t* sorted_token_ids,
+                                  const int32_t* num_tokens_post_pad, const float* scale,
+                                  int64_t max_rows, int topk, int64_t numel, int hidden,
+                                  int64_t src_stride, int src_dtype, b200_stream_t stream);
+B200_API int b200_moe_unpermute_reduce(void* out, const void* src, const int32_t* inv_perm,
+                                       const float* topk_weights, int64_t num_tokens, int topk,
+                                       int hidden, int64_t out_stride, int dtype, b200_stream_t stream);
+B200_API int b200_moe_grouped_gemm_fp8(void* out, const void* a_sorted, const void* w,
+                                       const int32_t* expert_ids, const int32_t* num_tokens_post_pad,
+                                       const float* a_scale, const float* w_scale,
+                                       const float* row_weight, int64_t max_rows, int num_experts,
+                                       int N, int K, int block_size, int w_scale_per_channel,
+                                       int out_dtype, b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -363,3 +363,107 @@ def rotary_embedding(positions, query, key, head_size, cos_sin_cache, is_neox):
         return t
 
     return rot_one(query), (None if key is None else rot_one(key))
+
+
+# --------------------------------------------------------------------------------------------
+# MoE routing.
+# moe_align_block_size: csrc/libtorch_stable/moe/moe_align_sum_kernels.cu:85-350 and the golden
+# torch_moe_align_block_size of tests/kernels/moe/test_moe_align_block_size.py:92-181 (stable sort).
+# --------------------------------------------------------------------------------------------
+def moe_align_block_size(topk_ids: np.ndarray, block_size: int, num_experts: int,
+                         expert_map: np.ndarray | None = None, pad_sorted_ids: bool = False,
+                         ignore_invalid_experts: bool = False):
+    """Returns (sorted_token_ids int32 [max_padded], expert_ids int32 [max_blocks],
+    num_tokens_post_pad int). Pad value = numel, expert_ids tail = -1, stable order."""
+    flat = np.asarray(topk_ids).reshape(-1).astype(np.int64)
+    numel = flat.size
+    max_padded = numel + num_experts * (block_size - 1)
+    if pad_sorted_ids:
+        max_padded = (max_padded + block_size - 1) // block_size * block_size
+    if numel < num_experts:
+        max_padded = min(numel * block_size, max_padded)
+    max_blocks = (max_padded + block_size - 1) // block_size
+    local = flat.copy()
+    bad = (local < 0) | (local >= num_experts)
+    if ignore_invalid_experts and expert_map is not None:
+        m = np.asarray(expert_map).astype(np.int64)
+        local = np.where(bad, -1, m[np.clip(local, 0, num_experts - 1)])
+    else:
+        local = np.where(bad, -1, local)
+    sorted_ids = np.full(max_padded, numel, dtype=np.int32)
+    expert_ids = np.full(max_blocks, -1, dtype=np.int32)
+    pos = 0
+    for e in range(num_experts):
+        idx = np.nonzero(local == e)[0]  # ascending = stable
+        n = idx.size
+        padded = (n + block_size - 1) // block_size * block_size
+        sorted_ids[pos:pos + n] = idx
+        expert_ids[pos // block_size:(pos + padded) // block_size] = e
+        pos += padded
+    if expert_map is not None and not ignore_invalid_experts:
+        m = np.asarray(expert_map).astype(np.int64)
+        expert_ids = np.where(expert_ids >= 0, m[np.clip(expert_ids, 0, num_experts - 1)], -1).astype(np.int32)
+    return sorted_ids, expert_ids, pos
+
+
+def topk_softmax(gating: torch.Tensor, topk: int, renormalize: bool, bias: torch.Tensor | None = None):
+    """csrc/libtorch_stable/moe/topk_softmax_kernels.cu:76-262 (softmax fp32, iterative arg-max with
+    ties to the lower index, weights = softmax value, optional renormalise);
+    token_expert_indices[m, k] = k * M + m."""
+    g = gating.to(torch.float32)
+    M, E = g.shape
+    p = torch.softmax(g, dim=-1)
+    sel = p + bias.float() if bias is not None else p.clone()
+    ids = torch.empty(M, topk, dtype=torch.int32)
+    w = torch.empty(M, topk, dtype=torch.float32)
+    for k in range(topk):
+        mx = sel.max(dim=-1, keepdim=True).values
+        first = (sel == mx).float().argmax(dim=-1)  # lowest index among ties
+        ids[:, k] = first.to(torch.int32)
+        w[:, k] = p[torch.arange(M), first]
+        sel[torch.arange(M), first] = -float("inf")
+    if renormalize:
+        den = w.sum(-1, keepdim=True)
+        w = w * (1.0 / torch.where(den > 0, den, torch.ones_like(den)))
+    tei = (torch.arange(topk, dtype=torch.int32)[None, :] * M + torch.arange(M, dtype=torch.int32)[:, None])
+    return w, ids, tei
+
+
+def moe_sum(x: torch.Tensor) -> torch.Tensor:
+    """moe_align_sum_kernels.cu:352-420: fp32 sum over topk, rounded once."""
+    return x.float().sum(dim=1).to(x.dtype)
+
+
+# --------------------------------------------------------------------------------------------
+# fused_experts (FP8 W8A8, per-tensor activation scales).
+# Where quantisation happens: fused_moe.py:1764-1851; per-expert dense loop as torch_experts,
+# tests/kernels/utils.py:912-1078.
+# --------------------------------------------------------------------------------------------
+def fused_experts_fp8(x: torch.Tensor, w1_bits: torch.Tensor, w2_bits: torch.Tensor,
+                      topk_weights: torch.Tensor, topk_ids: torch.Tensor, w1_scale, w2_scale, a1_scale,
+                      a2_scale, expert_map: torch.Tensor | None = None) -> torch.Tensor:
+    """x [M,H] bf16; w1_bits uint8 [E,2I,H]; w2_bits uint8 [E,H,I]; scales float tensors
+    ([E] weights, [1] activations). Returns float32 [M,H] (fp32 accumulate, bf16 intermediates)."""
+    M, H = x.shape
+    E = w1_bits.shape[0]
+    x8 = torch.from_numpy(e4m3_bits_to_f32(static_scaled_fp8_quant(x, a1_scale)))
+    a1 = float(a1_scale.reshape(-1)[0]); a2 = float(a2_scale.reshape(-1)[0])
+    out = torch.zeros(M, H, dtype=torch.float32)
+    for t in range(M):
+        for k in range(topk_ids.shape[1]):
+            e = int(topk_ids[t, k])
+            if e < 0:
+                continue
+            if expert_map is not None:
+                e = int(expert_map[e])
+                if e < 0:
+                    continue
+            w1 = torch.from_numpy(e4m3_bits_to_f32(w1_bits[e].numpy()))
+            w2 = torch.from_numpy(e4m3_bits_to_f32(w2_bits[e].numpy()))
+            h = (x8[t] @ w1.t()) * (a1 * float(w1_scale[e]))
+            h = h.to(x.dtype)
+            act = silu_and_mul(h[None, :])
+            act8 = torch.from_numpy(e4m3_bits_to_f32(static_scaled_fp8_quant(act, a2_scale)))[0]
+            o = (act8 @ w2.t()) * (a2 * float(w2_scale[e]))
+            out[t] += float(topk_weights[t, k]) * o.to(x.dtype).float()
+    return out

@@ -3,6 +3,6 @@
 Python here is host glue only (device memory, streams): every op is hand-written CUDA in
 libb200ops.so, reached through the C ABI of include/b200ops.h. No CPU fallback exists.
 """
-from . import _lib, ops  # noqa: F401
+from . import _lib, ops, fused_moe  # noqa: F401
 
-__all__ = ["_lib", "ops"]
+__all__ = ["_lib", "ops", "fused_moe"]

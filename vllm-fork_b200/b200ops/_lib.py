@@ -109,6 +109,24 @@ SIGNATURES = {
     "b200_rotary_embedding": (
         c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int64, c_int64, c_int64,
                 c_int, c_int, c_int, c_int, c_void_p]),
+    "b200_moe_align_block_size": (
+        c_int, [c_void_p, c_int, c_int64, c_int, c_int, c_void_p, c_int64, c_void_p, c_int64, c_void_p,
+                c_void_p, c_void_p, c_void_p]),
+    "b200_moe_topk_softmax": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int,
+                c_void_p]),
+    "b200_moe_sum": (
+        c_int, [c_void_p, c_void_p, c_int64, c_int, c_int, c_int64, c_int64, c_void_p, c_int, c_void_p,
+                c_int, c_void_p]),
+    "b200_moe_permute_fp8": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int64, c_int,
+                c_int64, c_int, c_void_p]),
+    "b200_moe_unpermute_reduce": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int64, c_int,
+                c_void_p]),
+    "b200_moe_grouped_gemm_fp8": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                c_int64, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "b200_paged_attention_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200_paged_attention_decode": (c_int, [C.POINTER(PagedAttnArgs), c_void_p]),
 }

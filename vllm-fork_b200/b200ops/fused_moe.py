@@ -1,0 +1,179 @@
+"""Fused MoE on libb200ops.so: routing ops with the reference's names and `fused_experts`.
+
+Reference surface: vllm/_custom_ops.py (moe_align_block_size :2237-2254, moe_sum :2228-2234,
+topk_softmax :2385-2402), vllm/model_executor/layers/fused_moe/moe_align_block_size.py:11-103 and
+fused_moe.py:1448-1535, 1587-1853 (fused_experts / fused_experts_impl).
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib, ops
+from ._lib import I32, I64
+from .ops import _cuda, _dt, _p, _stream
+
+
+def _idt(t: torch.Tensor) -> int:
+    if t.dtype == torch.int32:
+        return I32
+    if t.dtype == torch.int64:
+        return I64
+    raise RuntimeError(f"b200ops: index tensor must be int32 or int64, got {t.dtype}")
+
+
+def moe_align_block_size_op(topk_ids: torch.Tensor, num_experts: int, block_size: int,
+                            sorted_token_ids: torch.Tensor, experts_ids: torch.Tensor,
+                            num_tokens_post_pad: torch.Tensor,
+                            maybe_expert_map: torch.Tensor | None = None,
+                            inv_perm: torch.Tensor | None = None) -> None:
+    """torch.ops._moe_C.moe_align_block_size (csrc/libtorch_stable/moe/torch_bindings.cpp:27-32)."""
+    _cuda(topk_ids, sorted_token_ids, experts_ids, num_tokens_post_pad, maybe_expert_map, inv_perm)
+    if not topk_ids.is_contiguous():
+        raise RuntimeError("moe_align_block_size: topk_ids must be contiguous")
+    if maybe_expert_map is not None and maybe_expert_map.dtype != torch.int32:
+        raise RuntimeError("moe_align_block_size: expert_map must be int32")
+    rc = _lib.load().b200_moe_align_block_size(
+        _p(topk_ids), _idt(topk_ids), topk_ids.numel(), num_experts, block_size, _p(sorted_token_ids),
+        sorted_token_ids.numel(), _p(experts_ids), experts_ids.numel(), _p(num_tokens_post_pad),
+        _p(maybe_expert_map), _p(inv_perm), _stream())
+    _lib.check(rc, "moe_align_block_size")
+
+
+def moe_align_block_size(topk_ids: torch.Tensor, block_size: int, num_experts: int,
+                         expert_map: torch.Tensor | None = None, pad_sorted_ids: bool = False,
+                         ignore_invalid_experts: bool = False, return_inv_perm: bool = False):
+    """Same contract as fused_moe/moe_align_block_size.py:11-103."""
+    numel = topk_ids.numel()
+    max_num_tokens_padded = numel + num_experts * (block_size - 1)
+    if pad_sorted_ids:
+        max_num_tokens_padded = (max_num_tokens_padded + block_size - 1) // block_size * block_size
+    if numel < num_experts:
+        max_num_tokens_padded = min(numel * block_size, max_num_tokens_padded)
+    dev = topk_ids.device
+    sorted_ids = torch.empty((max_num_tokens_padded,), dtype=torch.int32, device=dev)
+    max_num_m_blocks = (max_num_tokens_padded + block_size - 1) // block_size
+    expert_ids = torch.empty((max_num_m_blocks,), dtype=torch.int32, device=dev)
+    num_tokens_post_pad = torch.empty((1,), dtype=torch.int32, device=dev)
+    inv = torch.empty((numel,), dtype=torch.int32, device=dev) if return_inv_perm else None
+    moe_align_block_size_op(topk_ids, num_experts, block_size, sorted_ids, expert_ids,
+                            num_tokens_post_pad, expert_map if ignore_invalid_experts else None, inv)
+    if expert_map is not None and not ignore_invalid_experts:
+        expert_ids = expert_map[expert_ids]
+    if return_inv_perm:
+        return sorted_ids, expert_ids, num_tokens_post_pad, inv
+    return sorted_ids, expert_ids, num_tokens_post_pad
+
+
+def topk_softmax(topk_weights: torch.Tensor, topk_ids: torch.Tensor,
+                 token_expert_indices: torch.Tensor, gating_output: torch.Tensor,
+                 renormalize: bool = False, bias: torch.Tensor | None = None) -> None:
+    """torch.ops._moe_C.topk_softmax: weights f32 [M,k], ids i32 [M,k], token_expert_indices i32 [M,k]."""
+    _cuda(topk_weights, topk_ids, token_expert_indices, gating_output, bias)
+    if topk_weights.dtype != torch.float32 or topk_ids.dtype != torch.int32 or \
+            token_expert_indices.dtype != torch.int32:
+        raise RuntimeError("topk_softmax: weights must be float32 and indices int32")
+    if not gating_output.is_contiguous():
+        raise RuntimeError("topk_softmax: gating_output must be contiguous")
+    M, E = gating_output.shape
+    rc = _lib.load().b200_moe_topk_softmax(
+        _p(topk_weights), _p(topk_ids), _p(token_expert_indices), _p(gating_output), _p(bias), M, E,
+        topk_weights.shape[-1], 1 if renormalize else 0, _dt(gating_output), _stream())
+    _lib.check(rc, "topk_softmax")
+
+
+def moe_sum(input: torch.Tensor, output: torch.Tensor, topk_ids: torch.Tensor | None = None,
+            expert_map: torch.Tensor | None = None) -> None:
+    """torch.ops._moe_C.moe_sum: output[t,:] = sum_k input[t,k,:] (fp32 accumulate)."""
+    _cuda(input, output, topk_ids, expert_map)
+    if input.dim() != 3 or input.stride(2) != 1 or not output.is_contiguous():
+        raise RuntimeError("moe_sum: input [tokens, topk, d] (d contiguous), output contiguous")
+    T, K, d = input.shape
+    rc = _lib.load().b200_moe_sum(
+        _p(output), _p(input), T, K, d, input.stride(0), input.stride(1), _p(topk_ids),
+        0 if topk_ids is None else _idt(topk_ids), _p(expert_map), _dt(input), _stream())
+    _lib.check(rc, "moe_sum")
+
+
+def _block_size_for(tokens_per_expert: float) -> int:
+    for b in (16, 32, 64):
+        if tokens_per_expert <= b:
+            return b
+    return 128
+
+
+def fused_experts(
+    hidden_states: torch.Tensor,
+    w1: torch.Tensor,
+    w2: torch.Tensor,
+    topk_weights: torch.Tensor,
+    topk_ids: torch.Tensor,
+    activation: str = "silu",
+    apply_router_weight_on_input: bool = False,
+    use_fp8_w8a8: bool = False,
+    per_channel_quant: bool = False,
+    global_num_experts: int = -1,
+    expert_map: torch.Tensor | None = None,
+    w1_scale: torch.Tensor | None = None,
+    w2_scale: torch.Tensor | None = None,
+    a1_scale: torch.Tensor | None = None,
+    a2_scale: torch.Tensor | None = None,
+    block_shape=None,
+    **unsupported,
+) -> torch.Tensor:
+    """out[t] = sum_k w[t,k] * W2[e] . silu_and_mul(W1[e] . x_t), FP8 W8A8 with per-tensor activation
+    scales (static if given, dynamic per-tensor otherwise) and per-expert (or per-channel) weight
+    scales. hidden_states [M,H] bf16/f16; w1 [E, 2I, H], w2 [E, H, I] e4m3; topk_weights f32 [M,k];
+    topk_ids int [M,k]; expert_map int32 [E_global] -> local id or -1 (expert parallel)."""
+    if not use_fp8_w8a8:
+        raise NotImplementedError("b200ops.fused_experts: only use_fp8_w8a8=True is built")
+    if activation != "silu" or apply_router_weight_on_input or block_shape is not None or \
+            any(v not in (None, False) for v in unsupported.values()):
+        raise NotImplementedError("b200ops.fused_experts: unsupported option")
+    _cuda(hidden_states, w1, w2, topk_weights, topk_ids, expert_map, w1_scale, w2_scale, a1_scale, a2_scale)
+    lib = _lib.load()
+    M, H = hidden_states.shape
+    E, N1, K1 = w1.shape
+    I = N1 // 2
+    if K1 != H or tuple(w2.shape) != (E, H, I):
+        raise RuntimeError("fused_experts: weight shapes do not match hidden_states")
+    if not (w1.is_contiguous() and w2.is_contiguous() and hidden_states.stride(1) == 1):
+        raise RuntimeError("fused_experts: weights must be contiguous")
+    topk = topk_ids.shape[1]
+    numel = M * topk
+    Eg = global_num_experts if global_num_experts > 0 else E
+    dev, dt = hidden_states.device, hidden_states.dtype
+    bs = _block_size_for(numel / max(E, 1))
+    sorted_ids, expert_ids, npp, inv = moe_align_block_size(
+        topk_ids, bs, Eg, expert_map, pad_sorted_ids=True, ignore_invalid_experts=True,
+        return_inv_perm=True)
+    P = sorted_ids.numel()
+    if a1_scale is None:  # dynamic per-tensor: scale = max|x| / 448 (same kernel as scaled_fp8_quant)
+        _, a1_scale = ops.scaled_fp8_quant(hidden_states)
+    a8 = torch.zeros(P, H, dtype=torch.uint8, device=dev)
+    rc = lib.b200_moe_permute_fp8(_p(a8), _p(hidden_states), _p(sorted_ids), _p(npp), _p(a1_scale), P,
+                                  topk, numel, H, hidden_states.stride(0), _dt(hidden_states), _stream())
+    _lib.check(rc, "moe_permute")
+    inter = torch.zeros(P, N1, dtype=dt, device=dev)
+    rc = lib.b200_moe_grouped_gemm_fp8(_p(inter), _p(a8), _p(w1), _p(expert_ids), _p(npp),
+                                       _p(a1_scale), _p(w1_scale), None, P, E, N1, H, bs,
+                                       1 if per_channel_quant else 0, _dt(inter), _stream())
+    _lib.check(rc, "moe_grouped_gemm_fp8")
+    h8 = torch.empty(P, I, dtype=torch.float8_e4m3fn, device=dev)
+    if a2_scale is None:
+        act = torch.empty(P, I, dtype=dt, device=dev)
+        ops.silu_and_mul(act, inter)
+        _, a2_scale = ops.scaled_fp8_quant(act, output=h8)
+    else:
+        ops.silu_and_mul_quant(h8, inter, a2_scale)
+    # row weights in sorted order: w_sorted[inv[t*k + j]] = topk_weights[t, j]
+    out2 = torch.zeros(P, H, dtype=dt, device=dev)
+    rc = lib.b200_moe_grouped_gemm_fp8(_p(out2), _p(h8), _p(w2), _p(expert_ids), _p(npp),
+                                       _p(a2_scale), _p(w2_scale), None, P, E, H, I, bs,
+                                       1 if per_channel_quant else 0, _dt(out2), _stream())
+    _lib.check(rc, "moe_grouped_gemm_fp8")
+    out = torch.empty(M, H, dtype=dt, device=dev)
+    tw = topk_weights.to(torch.float32).contiguous()
+    rc = lib.b200_moe_unpermute_reduce(_p(out), _p(out2), _p(inv), _p(tw), M, topk, H, out.stride(0),
+                                       _dt(out), _stream())
+    _lib.check(rc, "moe_unpermute")
+    return out

@@ -16,7 +16,7 @@
 // Warp-specialised: warp 0 = TMA producer (SWIZZLE_128B boxes, mbarrier ring), warp 1 = single-thread
 // tcgen05.mma issuer (kind::f8f6f4, 128xBNx32 per instruction) + TMEM owner, warps 2-5 = epilogue
 // (tcgen05.ld 32x32b -> scale/bias -> bf16 -> global).
-#include "common.cuh"
+#include "tcgen05.cuh"
 
 #include <cmath>
 #include <cstring>
@@ -44,47 +44,7 @@ struct Params {
   int tma_store;         // swap mode: stage the tile in smem and write it with one TMA store
 };
 
-__device__ __forceinline__ void tc_fence_before() {
-  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-}
-__device__ __forceinline__ void tc_fence_after() {
-  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-}
-__device__ __forceinline__ void tc_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
-               : "memory");
-}
-__device__ __forceinline__ void tc_mma_f8(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc,
-                                          uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-__device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&v)[16]) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
-        "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
-        "=r"(v[14]), "=r"(v[15])
-      : "r"(taddr));
-}
-__device__ __forceinline__ void tc_wait_ld() {
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-
-// K-major, SWIZZLE_128B shared-memory matrix descriptor (tile rows are 128 bytes; 8-row groups are
-// 1024 bytes apart). Field layout: cute/arch/mma_sm100_desc.hpp SmemDescriptor.
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
-  uint64_t d = 0;
-  d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);          // start address
-  d |= (uint64_t)1 << 16;                                // LBO (unused for swizzled K-major) = 1
-  d |= (uint64_t)(1024 >> 4) << 32;                      // SBO = 1024 B
-  d |= (uint64_t)1 << 46;                                // descriptor version (Blackwell)
-  d |= (uint64_t)2 << 61;                                // SWIZZLE_128B
-  return d;
-}
+using namespace b200::tc;
 
 template <int BN>
 __global__ void __launch_bounds__(NTHREADS, 1)
