@@ -273,6 +273,19 @@ B200_API int b200_moe_grouped_gemm_fp8(void* out, const void* a_sorted, const vo
                                        int N, int K, int block_size, int w_scale_per_channel,
                                        int out_dtype, b200_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * NVFP4 activation quantiser.
+ * Replaces torch.ops._C.scaled_fp4_quant.out (csrc/libtorch_stable/quantization/fp4/
+ * nvfp4_quant_kernels.cu:39-281, nvfp4_utils.cuh:158-302; vllm/_custom_ops.py:1523-1598).
+ * input [M, K] f16/bf16 (K % 16 == 0); out uint8 [M, K/2] (low nibble = even element);
+ * out_scale e4m3 bytes: swizzled 128x4 layout [round_up(M,128), round_up(K/16,4)] (pads zeroed) or
+ * row-major [M, K/16]; global_scale: device float[1].
+ */
+B200_API int b200_nvfp4_quant(void* out, void* out_scale, const void* input,
+                              const float* global_scale, int64_t num_tokens, int hidden,
+                              int64_t in_row_stride, int is_sf_swizzled_layout, int in_dtype,
+                              b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -467,3 +467,79 @@ def fused_experts_fp8(x: torch.Tensor, w1_bits: torch.Tensor, w2_bits: torch.Ten
             o = (act8 @ w2.t()) * (a2 * float(w2_scale[e]))
             out[t] += float(topk_weights[t, k]) * o.to(x.dtype).float()
     return out
+
+
+# --------------------------------------------------------------------------------------------
+# NVFP4 quantisation.  csrc/libtorch_stable/quantization/fp4/nvfp4_utils.cuh:158-302 and the
+# reference's own test oracle tests/kernels/quantization/test_nvfp4_quant.py:53-131
+# (ref_nvfp4_quant, cast_to_fp4, recover_swizzled_scales), restated.
+# The CUDA kernel uses rcp.approx.ftz (<= 1 ulp); this restatement uses exact reciprocals, so a
+# 1-code difference is possible exactly at rounding boundaries.
+# --------------------------------------------------------------------------------------------
+E2M1_VALUES = np.array([0.0, 0.5, 1.0, 1.5, 2.0, 3.0, 4.0, 6.0], dtype=np.float32)
+
+
+def f32_to_e2m1_code(x: np.ndarray) -> np.ndarray:
+    """RNE to {0,.5,1,1.5,2,3,4,6} with saturation (cvt.rn.satfinite.e2m1x2.f32); ties to even
+    mantissa: 0.25->0, 0.75->1, 1.25->1, 1.75->2, 2.5->2, 3.5->4, 5->4 (test_nvfp4_quant.py:84-95)."""
+    a = np.abs(x).astype(np.float32)
+    code = np.zeros(a.shape, dtype=np.uint8)
+    code[(a > 0.25) & (a < 0.75)] = 1
+    code[(a >= 0.75) & (a <= 1.25)] = 2
+    code[(a > 1.25) & (a < 1.75)] = 3
+    code[(a >= 1.75) & (a <= 2.5)] = 4
+    code[(a > 2.5) & (a < 3.5)] = 5
+    code[(a >= 3.5) & (a <= 5.0)] = 6
+    code[a > 5.0] = 7
+    return code | (np.signbit(x).astype(np.uint8) << 3)
+
+
+def e2m1_code_to_f32(code: np.ndarray) -> np.ndarray:
+    v = E2M1_VALUES[code & 7]
+    return np.where(code & 8, -v, v).astype(np.float32)
+
+
+def nvfp4_quant(x: torch.Tensor, global_scale: float):
+    """Returns (codes uint8 [M,K] one per element, scale bytes uint8 [M,K/16] row-major)."""
+    xf = _f32(x)
+    M, K = xf.shape
+    blk = xf.reshape(M, K // 16, 16)
+    amax = np.abs(blk).max(axis=-1).astype(np.float32)
+    gs = np.float32(global_scale)
+    sf = (gs * (amax * (np.float32(1.0) / np.float32(6.0))).astype(np.float32)).astype(np.float32)
+    sf_bits = f32_to_e4m3_bits(sf)
+    sfv = e4m3_bits_to_f32(sf_bits)
+    with np.errstate(all="ignore"):
+        os = np.where(sfv != 0, np.float32(1.0) / (sfv * (np.float32(1.0) / gs)).astype(np.float32), 0).astype(np.float32)
+    y = (blk * os[..., None]).astype(np.float32)
+    return f32_to_e2m1_code(y).reshape(M, K), sf_bits
+
+
+def nvfp4_pack(codes: np.ndarray) -> np.ndarray:
+    return (codes[:, 0::2] | (codes[:, 1::2] << 4)).astype(np.uint8)
+
+
+def nvfp4_unpack(packed: np.ndarray) -> np.ndarray:
+    M, K2 = packed.shape
+    out = np.empty((M, K2 * 2), dtype=np.uint8)
+    out[:, 0::2] = packed & 0xF
+    out[:, 1::2] = packed >> 4
+    return out
+
+
+def swizzle_sf(sf: np.ndarray) -> np.ndarray:
+    """row-major [M, K/16] -> tcgen05 128x4 layout, flat [round_up(M,128) * round_up(K/16,4)], pads 0
+    (offset formula nvfp4_utils.cuh:186-197; inverse of recover_swizzled_scales)."""
+    M, C = sf.shape
+    rm, rc = (M + 127) // 128 * 128, (C + 3) // 4 * 4
+    pad = np.zeros((rm, rc), dtype=sf.dtype)
+    pad[:M, :C] = sf
+    t = pad.reshape(rm // 128, 4, 32, rc // 4, 4)      # [mTile, innerM, outerM, kTile, innerK]
+    t = t.transpose(0, 3, 2, 1, 4)                      # [mTile, kTile, outerM, innerM, innerK]
+    return np.ascontiguousarray(t).reshape(-1)
+
+
+def unswizzle_sf(flat: np.ndarray, M: int, C: int) -> np.ndarray:
+    rm, rc = (M + 127) // 128 * 128, (C + 3) // 4 * 4
+    t = np.asarray(flat).reshape(rm // 128, rc // 4, 32, 4, 4).transpose(0, 3, 2, 1, 4)
+    return np.ascontiguousarray(t).reshape(rm, rc)[:M, :C]

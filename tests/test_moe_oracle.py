@@ -47,3 +47,25 @@ def test_topk_softmax_oracle():
     assert torch.equal(ids.long(), ref_i)
     torch.testing.assert_close(w, ref_w / ref_w.sum(-1, keepdim=True))
     assert tei[3, 1] == 1 * 17 + 3
+
+
+def test_nvfp4_oracle_matches_reference_test_helpers():
+    """restated ref_nvfp4_quant / recover_swizzled_scales (test_nvfp4_quant.py:98-131)."""
+    torch.manual_seed(42)
+    x = torch.randn(150, 160).to(torch.bfloat16)
+    gs = 448.0 * 6.0 / x.float().abs().max().item()
+    codes, sf = ref_ops.nvfp4_quant(x, gs)
+    # reference formulation, in torch
+    xb = x.float().reshape(150, 10, 16)
+    vec_max = xb.abs().max(-1, keepdim=True)[0]
+    scale = (torch.tensor(gs, dtype=torch.float32) * (vec_max * (1.0 / 6.0))).to(torch.float8_e4m3fn).float()
+    inv = torch.where(scale == 0, torch.zeros_like(scale), 1.0 / (scale * (1.0 / torch.tensor(gs, dtype=torch.float32))))
+    ref_vals = (xb * inv).clamp(-6, 6)
+    got_vals = torch.from_numpy(ref_ops.e2m1_code_to_f32(codes)).reshape(150, 10, 16)
+    assert (got_vals - ref_vals).abs().max() <= 1.0  # nearest representable
+    np.testing.assert_array_equal(ref_ops.e4m3_bits_to_f32(sf), scale.squeeze(-1).numpy())
+    # swizzle round trip + reference recover_swizzled_scales
+    flat = ref_ops.swizzle_sf(sf)
+    np.testing.assert_array_equal(ref_ops.unswizzle_sf(flat, 150, 10), sf)
+    t = torch.from_numpy(flat.copy()).reshape(1, 2, 3, 32, 4, 4).permute(0, 1, 4, 3, 2, 5).reshape(256, 12)
+    np.testing.assert_array_equal(t[:150, :10].numpy(), sf)

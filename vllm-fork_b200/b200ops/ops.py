@@ -342,6 +342,40 @@ def silu_and_mul_quant(result: torch.Tensor, input: torch.Tensor, scale: torch.T
 
 
 # ------------------------------------------------------------------------------------------------
+# NVFP4 activation quantisation                         reference: vllm/_custom_ops.py:1523-1598
+# ------------------------------------------------------------------------------------------------
+def create_fp4_scale_tensor(m: int, n: int, device, is_sf_swizzled_layout: bool) -> torch.Tensor:
+    """int32-packed e4m3 scales: [round_up(m,128), round_up(n/16,4)/4] swizzled, else uint8 [m, n/16]."""
+    if is_sf_swizzled_layout:
+        rm = (m + 127) // 128 * 128
+        rn = (n // 16 + 3) // 4 * 4
+        return torch.empty((rm, rn // 4), device=device, dtype=torch.int32)
+    return torch.empty((m, n // 16), device=device, dtype=torch.uint8)
+
+
+def scaled_fp4_quant(input: torch.Tensor, input_global_scale: torch.Tensor,
+                     is_sf_swizzled_layout: bool = True) -> tuple[torch.Tensor, torch.Tensor]:
+    """Returns (uint8 [m, n/2] packed e2m1, float8_e4m3fn scales in the swizzled / row-major layout)."""
+    _cuda(input, input_global_scale)
+    assert input.ndim >= 1, f"input.ndim needs to be >= 1, but got {input.ndim}."
+    other_dims = 1 if input.ndim == 1 else -1
+    input = input.reshape(other_dims, input.shape[-1])
+    m, n = input.shape
+    assert n % 16 == 0, f"last dim has to be multiple of 16, but got {n}."
+    assert input.dtype in (torch.float16, torch.bfloat16), (
+        f"input.dtype needs to be fp16 or bf16 but got {input.dtype}.")
+    if input.stride(1) != 1:
+        input = input.contiguous()
+    output = torch.empty((m, n // 2), device=input.device, dtype=torch.uint8)
+    output_scale = create_fp4_scale_tensor(m, n, input.device, is_sf_swizzled_layout)
+    rc = _lib.load().b200_nvfp4_quant(_p(output), _p(output_scale), _p(input), _p(input_global_scale),
+                                      m, n, input.stride(0), 1 if is_sf_swizzled_layout else 0,
+                                      _dt(input), _stream())
+    _lib.check(rc, "scaled_fp4_quant")
+    return output, output_scale.view(torch.float8_e4m3fn)
+
+
+# ------------------------------------------------------------------------------------------------
 # RMSNorm (+ residual, + static FP8 quant) and RoPE     reference: vllm/_custom_ops.py rms_norm,
 # fused_add_rms_norm, rms_norm_static_fp8_quant, fused_add_rms_norm_static_fp8_quant, rotary_embedding
 # ------------------------------------------------------------------------------------------------
