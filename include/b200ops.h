@@ -286,6 +286,21 @@ B200_API int b200_nvfp4_quant(void* out, void* out_scale, const void* input,
                               int64_t in_row_stride, int is_sf_swizzled_layout, int in_dtype,
                               b200_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * NVFP4 W4A4 GEMM (block-scaled tcgen05 MMA).
+ * Replaces torch.ops._C.cutlass_scaled_fp4_mm (csrc/libtorch_stable/quantization/fp4/
+ * nvfp4_scaled_mm_kernels.cu:76-140,279-348; vllm/_custom_ops.py:733-745).
+ * out[M,N] = alpha * (a (.) block_scale_a)(b (.) block_scale_b)^T, fp32 accumulate.
+ * a uint8 [M, K/2], b uint8 [N, K/2] (two e2m1 per byte, low nibble = even k; row strides in BYTES);
+ * block_scale_a / block_scale_b: e4m3 bytes in the swizzled 128x4 layout of b200_nvfp4_quant,
+ * [round_up(rows,128), round_up(K/16,4)]; alpha: device float[1]; out bf16/f16 [M, N], row stride ldo.
+ * K is the number of e2m1 ELEMENTS (K % 32 == 0).
+ */
+B200_API int b200_nvfp4_gemm(void* out, const void* a, const void* b, const void* block_scale_a,
+                             const void* block_scale_b, const float* alpha, int M, int N, int K,
+                             int64_t lda_bytes, int64_t ldb_bytes, int64_t ldo, int out_dtype,
+                             b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -499,7 +499,7 @@ def e2m1_code_to_f32(code: np.ndarray) -> np.ndarray:
     return np.where(code & 8, -v, v).astype(np.float32)
 
 
-def nvfp4_quant(x: torch.Tensor, global_scale: float):
+def nvfp4_quant(x: torch.Tensor, global_scale: float, return_scaled: bool = False):
     """Returns (codes uint8 [M,K] one per element, scale bytes uint8 [M,K/16] row-major)."""
     xf = _f32(x)
     M, K = xf.shape
@@ -512,7 +512,20 @@ def nvfp4_quant(x: torch.Tensor, global_scale: float):
     with np.errstate(all="ignore"):
         os = np.where(sfv != 0, np.float32(1.0) / (sfv * (np.float32(1.0) / gs)).astype(np.float32), 0).astype(np.float32)
     y = (blk * os[..., None]).astype(np.float32)
+    if return_scaled:
+        return f32_to_e2m1_code(y).reshape(M, K), sf_bits, y.reshape(M, K)
     return f32_to_e2m1_code(y).reshape(M, K), sf_bits
+
+
+E2M1_BOUNDARIES = np.array([0.25, 0.75, 1.25, 1.75, 2.5, 3.5, 5.0], dtype=np.float32)
+
+
+def nvfp4_near_tie(y: np.ndarray, rel: float = 6e-7) -> np.ndarray:
+    """True where |y| sits within `rel` (a few fp32 ulp = the error of the kernel's two rcp.approx.ftz
+    against this restatement's exact reciprocals) of an e2m1 rounding boundary. Only there may the
+    CUDA kernel's code legitimately differ from the restatement (by one e2m1 step)."""
+    a = np.abs(y).astype(np.float32)[..., None]
+    return (np.abs(a - E2M1_BOUNDARIES) <= rel * E2M1_BOUNDARIES).any(-1)
 
 
 def nvfp4_pack(codes: np.ndarray) -> np.ndarray:
@@ -543,3 +556,25 @@ def unswizzle_sf(flat: np.ndarray, M: int, C: int) -> np.ndarray:
     rm, rc = (M + 127) // 128 * 128, (C + 3) // 4 * 4
     t = np.asarray(flat).reshape(rm // 128, rc // 4, 32, 4, 4).transpose(0, 3, 2, 1, 4)
     return np.ascontiguousarray(t).reshape(rm, rc)[:M, :C]
+
+
+def nvfp4_dequant(codes: np.ndarray, sf_bits: np.ndarray, global_scale: float) -> np.ndarray:
+    """codes uint8 [M,K] (one per element), sf_bits uint8 [M,K/16] row-major -> fp32 [M,K]:
+    value = e2m1(code) * (e4m3(sf) / global_scale)   (tests/kernels/quantization/nvfp4_utils.py
+    dequantize_nvfp4_to_dtype / test_nvfp4_scaled_mm.py:27-49)."""
+    M, K = codes.shape
+    v = e2m1_code_to_f32(codes).reshape(M, K // 16, 16)
+    sf = (e4m3_bits_to_f32(sf_bits) / np.float32(global_scale)).astype(np.float32)
+    return (v * sf[..., None]).astype(np.float32).reshape(M, K)
+
+
+def nvfp4_scaled_mm(a_codes, a_sf_bits, b_codes, b_sf_bits, alpha: float) -> np.ndarray:
+    """out = alpha * (a (.) sfa)(b (.) sfb)^T in float64-accumulated fp32: the exact value the block-scaled
+    MMA approximates (products of e2m1 x e2m1 x e4m3 x e4m3 are exact in fp32; only the accumulation
+    order differs). Equals get_ref_results (test_nvfp4_scaled_mm.py:27-49) with alpha = 1/(gs_a*gs_b)
+    up to that function's rounding of the dequantised operands to bf16/f16."""
+    M, K = a_codes.shape
+    av = e2m1_code_to_f32(a_codes).reshape(M, K // 16, 16).astype(np.float64) * e4m3_bits_to_f32(a_sf_bits).astype(np.float64)[..., None]
+    N = b_codes.shape[0]
+    bv = e2m1_code_to_f32(b_codes).reshape(N, K // 16, 16).astype(np.float64) * e4m3_bits_to_f32(b_sf_bits).astype(np.float64)[..., None]
+    return (np.float64(alpha) * (av.reshape(M, K) @ bv.reshape(N, K).T)).astype(np.float32)

@@ -375,6 +375,48 @@ def scaled_fp4_quant(input: torch.Tensor, input_global_scale: torch.Tensor,
     return output, output_scale.view(torch.float8_e4m3fn)
 
 
+def cutlass_scaled_fp4_mm(a: torch.Tensor, b: torch.Tensor, block_scale_a: torch.Tensor,
+                          block_scale_b: torch.Tensor, alpha: torch.Tensor, out_dtype: torch.dtype,
+                          out: torch.Tensor | None = None) -> torch.Tensor:
+    """out = alpha * (a (.) block_scale_a) @ (b (.) block_scale_b).T  (vllm/_custom_ops.py:733-745; checks of
+    nvfp4_scaled_mm_kernels.cu:279-348). a uint8 [m, k/2], b uint8 [n, k/2] packed e2m1; block scales
+    float8_e4m3fn in the swizzled layout scaled_fp4_quant returns; alpha f32 [1]."""
+    _cuda(a, b, block_scale_a, block_scale_b, alpha, out)
+    assert a.ndim == 2 and b.ndim == 2
+    if a.dtype != torch.uint8 or b.dtype != torch.uint8:
+        raise RuntimeError("cutlass_scaled_fp4_mm: a and b must be uint8 (packed fp4)")
+    if block_scale_a.element_size() not in (1, 4) or block_scale_b.element_size() not in (1, 4):
+        raise RuntimeError("cutlass_scaled_fp4_mm: scale_a / scale_b must be float8_e4m3fn")
+    if alpha.dtype != torch.float32:
+        raise RuntimeError("cutlass_scaled_fp4_mm: alpha must be float32")
+    m, n = a.shape[0], b.shape[0]
+    if a.shape[1] != b.shape[1]:
+        raise RuntimeError(f"cutlass_scaled_fp4_mm: a and b shapes cannot be multiplied ({tuple(a.shape)} and {tuple(b.shape)})")
+    k = a.shape[1] * 2
+    if k % 32 != 0:
+        raise RuntimeError(f"cutlass_scaled_fp4_mm: Expected k to be divisible by 32, but got a shape {tuple(a.shape)}")
+    if n % 32 != 0:
+        raise RuntimeError(f"cutlass_scaled_fp4_mm: Expected n to be divisible by 32, but got b shape {tuple(b.shape)}")
+    if a.stride(1) != 1 or b.stride(1) != 1:
+        raise RuntimeError("cutlass_scaled_fp4_mm: a and b must be row-major")
+    ru = lambda x, y: (x + y - 1) // y * y
+    sf_k = ru(k // 16, 4)
+    for name, sf, rows in (("scale_a", block_scale_a, m), ("scale_b", block_scale_b, n)):
+        if not sf.is_contiguous() or sf.numel() * sf.element_size() != ru(rows, 128) * sf_k:
+            raise RuntimeError(
+                f"cutlass_scaled_fp4_mm: {name} must be padded and swizzled to a shape ({ru(rows, 128)}x{sf_k}), "
+                f"but got a shape {tuple(sf.shape)}")
+    assert out_dtype is torch.bfloat16 or out_dtype is torch.float16
+    if out is None:
+        out = torch.empty((m, n), dtype=out_dtype, device=a.device)
+    elif out.dtype != out_dtype or out.stride(-1) != 1 or tuple(out.shape) != (m, n):
+        raise RuntimeError("cutlass_scaled_fp4_mm: bad out tensor")
+    rc = _lib.load().b200_nvfp4_gemm(_p(out), _p(a), _p(b), _p(block_scale_a), _p(block_scale_b), _p(alpha),
+                                     m, n, k, a.stride(0), b.stride(0), out.stride(0), _dt(out), _stream())
+    _lib.check(rc, "cutlass_scaled_fp4_mm")
+    return out
+
+
 # ------------------------------------------------------------------------------------------------
 # RMSNorm (+ residual, + static FP8 quant) and RoPE     reference: vllm/_custom_ops.py rms_norm,
 # fused_add_rms_norm, rms_norm_static_fp8_quant, fused_add_rms_norm_static_fp8_quant, rotary_embedding
