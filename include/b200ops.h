@@ -274,6 +274,42 @@ B200_API int b200_moe_grouped_gemm_fp8(void* out, const void* a_sorted, const vo
                                        int out_dtype, b200_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Legacy-layout paged attention. Replaces torch.ops._C.paged_attention_v1 / paged_attention_v2
+ * (op absent from the reference tree, present in the wheel; semantics
+ * tests/kernels/attention/test_attention.py:57-109, docs/design/paged_attention.md:45-139,
+ * vllm/v1/attention/ops/paged_attn.py:15-51; schema SURVEY.md section 8b).
+ * query/out [num_seqs, num_heads, head_size] (q_stride = query.stride(0), heads contiguous; out
+ * contiguous); key_cache [num_blocks, num_kv_heads, head_size/x, block_size, x], value_cache
+ * [num_blocks, num_kv_heads, head_size, block_size] with kv_block_stride = key_cache.stride(0),
+ * kv_head_stride = key_cache.stride(1) (elements), x = 16 / sizeof(cache element);
+ * block_tables int32 [num_seqs, bt_stride]; seq_lens int32; alibi_slopes float[num_heads] or NULL;
+ * kv_dtype = q_dtype ("auto") or B200_FP8_E4M3 with device scalars k_scale / v_scale.
+ * v2: exp_sums, max_logits float [num_seqs, num_heads, max_num_partitions] and tmp_out (q dtype)
+ * [num_seqs, num_heads, max_num_partitions, head_size] are written (512-token partitions, natural-log
+ * max logits, partition outputs normalised by exp_sum + 1e-6) and then reduced into out.
+ * blocksparse_vert_stride > 1 (block-sparse attention) is B200_ERR_UNSUPPORTED.
+ */
+B200_API int b200_paged_attention_v1(void* out, const void* query, const void* key_cache,
+                                     const void* value_cache, int num_seqs, int num_heads,
+                                     int num_kv_heads, int head_size, float scale,
+                                     const int32_t* block_tables, const int32_t* seq_lens,
+                                     int block_size, int max_seq_len, const float* alibi_slopes,
+                                     int q_dtype, int kv_dtype, const float* k_scale,
+                                     const float* v_scale, int64_t q_stride, int64_t kv_block_stride,
+                                     int64_t kv_head_stride, int64_t bt_stride,
+                                     int blocksparse_vert_stride, b200_stream_t stream);
+B200_API int b200_paged_attention_v2(void* out, float* exp_sums, float* max_logits, void* tmp_out,
+                                     const void* query, const void* key_cache,
+                                     const void* value_cache, int num_seqs, int num_heads,
+                                     int num_kv_heads, int head_size, float scale,
+                                     const int32_t* block_tables, const int32_t* seq_lens,
+                                     int block_size, int max_seq_len, const float* alibi_slopes,
+                                     int q_dtype, int kv_dtype, const float* k_scale,
+                                     const float* v_scale, int64_t q_stride, int64_t kv_block_stride,
+                                     int64_t kv_head_stride, int64_t bt_stride, int max_num_partitions,
+                                     int blocksparse_vert_stride, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
  * NVFP4 activation quantiser.
  * Replaces torch.ops._C.scaled_fp4_quant.out (csrc/libtorch_stable/quantization/fp4/
  * nvfp4_quant_kernels.cu:39-281, nvfp4_utils.cuh:158-302; vllm/_custom_ops.py:1523-1598).

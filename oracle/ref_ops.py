@@ -578,3 +578,33 @@ def nvfp4_scaled_mm(a_codes, a_sf_bits, b_codes, b_sf_bits, alpha: float) -> np.
     N = b_codes.shape[0]
     bv = e2m1_code_to_f32(b_codes).reshape(N, K // 16, 16).astype(np.float64) * e4m3_bits_to_f32(b_sf_bits).astype(np.float64)[..., None]
     return (np.float64(alpha) * (av.reshape(M, K) @ bv.reshape(N, K).T)).astype(np.float32)
+
+
+# --------------------------------------------------------------------------------------------
+# Legacy x-packed cache layout (paged_attention_v1/v2): ref_single_query_cached_kv_attention,
+# tests/kernels/attention/test_attention.py:57-109 gathers k = key_cache[block, :, :, offset, :]
+# .reshape(Hkv, D) and v = value_cache[block, :, :, offset]. Same gather, done once for the whole
+# cache: the result is the flash layout paged_attention_decode() consumes.
+# --------------------------------------------------------------------------------------------
+def legacy_cache_to_flash(key_cache: torch.Tensor, value_cache: torch.Tensor):
+    """key_cache [nb,Hkv,D/x,bs,x], value_cache [nb,Hkv,D,bs] -> ([nb,bs,Hkv,D], [nb,bs,Hkv,D])."""
+    nb, Hkv, Dx, bs, x = key_cache.shape
+    k = key_cache.permute(0, 3, 1, 2, 4).reshape(nb, bs, Hkv, Dx * x)
+    v = value_cache.permute(0, 3, 1, 2)
+    return k.contiguous(), v.contiguous()
+
+
+def flash_cache_to_legacy(k: torch.Tensor, v: torch.Tensor):
+    """inverse of legacy_cache_to_flash (test-input construction)."""
+    nb, bs, Hkv, D = k.shape
+    x = 16 // k.element_size()
+    kc = k.reshape(nb, bs, Hkv, D // x, x).permute(0, 2, 3, 1, 4).contiguous()
+    vc = v.permute(0, 2, 3, 1).contiguous()
+    return kc, vc
+
+
+def paged_attention_legacy(query, key_cache, value_cache, block_tables, seq_lens, scale,
+                           k_scale=None, v_scale=None, alibi_slopes=None):
+    k, v = legacy_cache_to_flash(key_cache, value_cache)
+    return paged_attention_decode(query, k, v, block_tables, seq_lens, scale, k_scale=k_scale,
+                                  v_scale=v_scale, alibi_slopes=alibi_slopes)

@@ -132,6 +132,14 @@ SIGNATURES = {
     "b200_nvfp4_gemm": (
         c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64,
                 c_int64, c_int64, c_int, c_void_p]),
+    "b200_paged_attention_v1": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_void_p,
+                c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p, c_int64, c_int64,
+                c_int64, c_int64, c_int, c_void_p]),
+    "b200_paged_attention_v2": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                c_int, c_float, c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_void_p,
+                c_void_p, c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_void_p]),
     "b200_paged_attention_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200_paged_attention_decode": (c_int, [C.POINTER(PagedAttnArgs), c_void_p]),
 }

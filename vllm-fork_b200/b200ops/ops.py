@@ -583,3 +583,76 @@ def paged_attention_decode(
     rc = lib.b200_paged_attention_decode(ctypes.byref(a), _stream())
     _lib.check(rc, "paged_attention_decode")
     return out
+
+
+# ------------------------------------------------------------------------------------------------
+# Legacy paged attention     reference: torch.ops._C.paged_attention_v1 / v2 (wheel-only)
+# ------------------------------------------------------------------------------------------------
+def _legacy_common(op, out, query, key_cache, value_cache, num_kv_heads, block_tables, seq_lens,
+                   block_size, kv_cache_dtype, k_scale, v_scale, alibi_slopes):
+    _cuda(out, query, key_cache, value_cache, block_tables, seq_lens, k_scale, v_scale, alibi_slopes)
+    if query.dim() != 3 or key_cache.dim() != 5 or value_cache.dim() != 4:
+        raise RuntimeError(f"{op}: query [S,H,D], key_cache [nb,Hkv,D/x,bs,x], value_cache [nb,Hkv,D,bs]")
+    if query.stride(2) != 1 or query.stride(1) != query.shape[2] or not out.is_contiguous():
+        raise RuntimeError(f"{op}: query heads and out must be contiguous")
+    if not (key_cache[0].is_contiguous() and value_cache[0].is_contiguous()):
+        raise RuntimeError(f"{op}: each cache block must be contiguous")
+    if block_tables.dtype != torch.int32 or seq_lens.dtype != torch.int32:
+        raise RuntimeError(f"{op}: block_tables and seq_lens must be int32")
+    if kv_cache_dtype not in ("auto", "fp8", "fp8_e4m3"):
+        raise RuntimeError(f"{op}: Unsupported data type of kv cache: {kv_cache_dtype}")
+    fp8 = kv_cache_dtype != "auto"
+    if fp8 and key_cache.element_size() != 1:
+        raise RuntimeError(f"{op}: fp8 kv_cache_dtype needs a 1-byte cache tensor")
+    if value_cache.shape[3] != block_size or value_cache.shape[1] != num_kv_heads:
+        raise RuntimeError(f"{op}: value_cache shape does not match num_kv_heads / block_size")
+    if key_cache.stride(0) != value_cache.stride(0) or key_cache.stride(1) != value_cache.stride(1):
+        raise RuntimeError(f"{op}: key_cache and value_cache must share block / head strides")
+    return _lib.FP8_E4M3 if fp8 else _dt(query)
+
+
+def paged_attention_v1(out: torch.Tensor, query: torch.Tensor, key_cache: torch.Tensor,
+                       value_cache: torch.Tensor, num_kv_heads: int, scale: float,
+                       block_tables: torch.Tensor, seq_lens: torch.Tensor, block_size: int,
+                       max_seq_len: int, alibi_slopes: torch.Tensor | None, kv_cache_dtype: str,
+                       k_scale: torch.Tensor, v_scale: torch.Tensor, tp_rank: int = 0,
+                       blocksparse_local_blocks: int = 0, blocksparse_vert_stride: int = 0,
+                       blocksparse_block_size: int = 64, blocksparse_head_sliding_step: int = 0) -> None:
+    """torch.ops._C.paged_attention_v1: single-pass decode attention over the x-packed cache layout."""
+    kvdt = _legacy_common("paged_attention_v1", out, query, key_cache, value_cache, num_kv_heads,
+                          block_tables, seq_lens, block_size, kv_cache_dtype, k_scale, v_scale, alibi_slopes)
+    S, H, D = query.shape
+    rc = _lib.load().b200_paged_attention_v1(
+        _p(out), _p(query), _p(key_cache), _p(value_cache), S, H, num_kv_heads, D, float(scale),
+        _p(block_tables), _p(seq_lens), block_size, int(max_seq_len), _p(alibi_slopes), _dt(query), kvdt,
+        _p(k_scale), _p(v_scale), query.stride(0), key_cache.stride(0), key_cache.stride(1),
+        block_tables.stride(0), int(blocksparse_vert_stride), _stream())
+    _lib.check(rc, "paged_attention_v1")
+
+
+def paged_attention_v2(out: torch.Tensor, exp_sums: torch.Tensor, max_logits: torch.Tensor,
+                       tmp_out: torch.Tensor, query: torch.Tensor, key_cache: torch.Tensor,
+                       value_cache: torch.Tensor, num_kv_heads: int, scale: float,
+                       block_tables: torch.Tensor, seq_lens: torch.Tensor, block_size: int,
+                       max_seq_len: int, alibi_slopes: torch.Tensor | None, kv_cache_dtype: str,
+                       k_scale: torch.Tensor, v_scale: torch.Tensor, tp_rank: int = 0,
+                       blocksparse_local_blocks: int = 0, blocksparse_vert_stride: int = 0,
+                       blocksparse_block_size: int = 64, blocksparse_head_sliding_step: int = 0) -> None:
+    """torch.ops._C.paged_attention_v2: 512-token partitions (exp_sums / max_logits / tmp_out) + reduce."""
+    kvdt = _legacy_common("paged_attention_v2", out, query, key_cache, value_cache, num_kv_heads,
+                          block_tables, seq_lens, block_size, kv_cache_dtype, k_scale, v_scale, alibi_slopes)
+    _cuda(exp_sums, max_logits, tmp_out)
+    S, H, D = query.shape
+    P = exp_sums.shape[2]
+    if (exp_sums.dtype != torch.float32 or max_logits.dtype != torch.float32 or tmp_out.dtype != query.dtype
+            or tuple(exp_sums.shape) != (S, H, P) or tuple(max_logits.shape) != (S, H, P)
+            or tuple(tmp_out.shape) != (S, H, P, D)
+            or not (exp_sums.is_contiguous() and max_logits.is_contiguous() and tmp_out.is_contiguous())):
+        raise RuntimeError("paged_attention_v2: exp_sums / max_logits [S,H,P] f32 and tmp_out [S,H,P,D] contiguous")
+    rc = _lib.load().b200_paged_attention_v2(
+        _p(out), _p(exp_sums), _p(max_logits), _p(tmp_out), _p(query), _p(key_cache), _p(value_cache),
+        S, H, num_kv_heads, D, float(scale), _p(block_tables), _p(seq_lens), block_size, int(max_seq_len),
+        _p(alibi_slopes), _dt(query), kvdt, _p(k_scale), _p(v_scale), query.stride(0),
+        key_cache.stride(0), key_cache.stride(1), block_tables.stride(0), P,
+        int(blocksparse_vert_stride), _stream())
+    _lib.check(rc, "paged_attention_v2")
