@@ -193,6 +193,36 @@ B200_API int b200_silu_and_mul_fp8(void* out, const void* input, const float* sc
                                    int64_t num_tokens, int d, int64_t in_row_stride,
                                    int64_t out_row_stride, int in_dtype, b200_stream_t stream);
 
+/* Replaces torch.ops._C.silu_and_mul_nvfp4_quant (csrc/libtorch_stable/quantization/fp4/
+ * activation_nvfp4_quant_fusion_kernels.cu:37-175): input [num_tokens, 2d] f16/bf16,
+ * out uint8 [num_tokens, d/2] = nvfp4(T(silu(gate) * up)), out_scale in the swizzled 128x4 layout
+ * (see b200_nvfp4_quant), global_scale device float[1]; d % 16 == 0. */
+B200_API int b200_silu_and_mul_nvfp4(void* out, void* out_scale, const void* input,
+                                     const float* global_scale, int64_t num_tokens, int d,
+                                     int64_t in_row_stride, int in_dtype, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Merge of two partial attention results by log-sum-exp.
+ * Replaces torch.ops._C.merge_attn_states (csrc/libtorch_stable/attention/merge_attn_states.cu:13-330;
+ * vllm/v1/attention/ops/merge_attn_states.py:9-60).
+ * prefix_output / suffix_output [T, H, D] f32/f16/bf16 (token strides given, one shared head stride,
+ * last dim contiguous, D % (16/sizeof) == 0); prefix_lse / suffix_lse float [H, T] (strides given);
+ * output [T, H, D] same dtype, or e4m3 when output_scale != NULL (static quantisation by 1/scale);
+ * output_lse nullable. Tokens >= prefill_tokens_with_context copy the suffix.
+ * prefill_tokens_with_context < 0 means "all tokens have context".
+ */
+B200_API int b200_merge_attn_states(void* output, float* output_lse, const void* prefix_output,
+                                    const float* prefix_lse, const void* suffix_output,
+                                    const float* suffix_lse, const float* output_scale,
+                                    int64_t num_tokens, int num_heads, int head_size,
+                                    int64_t prefix_tok_stride, int64_t suffix_tok_stride,
+                                    int64_t in_head_stride, int64_t out_tok_stride,
+                                    int64_t out_head_stride, int64_t prefix_lse_head_stride,
+                                    int64_t prefix_lse_tok_stride, int64_t suffix_lse_head_stride,
+                                    int64_t suffix_lse_tok_stride, int64_t out_lse_head_stride,
+                                    int64_t out_lse_tok_stride, int64_t prefill_tokens_with_context,
+                                    int in_dtype, int out_dtype, b200_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Neighbours of the hot path: RMSNorm (+ residual add) fused with the
  * static FP8 quantisation of the next GEMM input, and rotary embedding.

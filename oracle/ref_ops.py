@@ -608,3 +608,47 @@ def paged_attention_legacy(query, key_cache, value_cache, block_tables, seq_lens
     k, v = legacy_cache_to_flash(key_cache, value_cache)
     return paged_attention_decode(query, k, v, block_tables, seq_lens, scale, k_scale=k_scale,
                                   v_scale=v_scale, alibi_slopes=alibi_slopes)
+
+
+# --------------------------------------------------------------------------------------------
+# merge_attn_states: csrc/libtorch_stable/attention/merge_attn_states.cu:13-200 (same case split,
+# same operation order), vllm/v1/attention/ops/merge_attn_states.py:9-60.
+# --------------------------------------------------------------------------------------------
+def merge_attn_states(prefix_out, prefix_lse, suffix_out, suffix_lse, prefill_tokens_with_context=None,
+                      output_scale=None):
+    """prefix_out / suffix_out torch [T,H,D]; LSEs torch f32 [H,T]. Returns (out f32 [T,H,D] - or e4m3
+    bits uint8 when output_scale is given -, out_lse f32 [H,T])."""
+    po, so = _f32(prefix_out), _f32(suffix_out)
+    T, H, D = po.shape
+    pl = _f32(prefix_lse).T.copy()   # [T,H]
+    sl = _f32(suffix_lse).T.copy()
+    npre = T if prefill_tokens_with_context is None else int(prefill_tokens_with_context)
+    pl = np.where(np.isinf(pl), -np.inf, pl).astype(np.float32)
+    sl = np.where(np.isinf(sl), -np.inf, sl).astype(np.float32)
+    mx = np.maximum(pl, sl)
+    with np.errstate(all="ignore"):
+        pe = np.exp((pl - mx).astype(np.float32)).astype(np.float32)
+        se = np.exp((sl - mx).astype(np.float32)).astype(np.float32)
+        tot = (pe + se).astype(np.float32)
+        wp, ws = (pe / tot).astype(np.float32), (se / tot).astype(np.float32)
+        merged = (po * wp[..., None]).astype(np.float32) + (so * ws[..., None]).astype(np.float32)
+        lse = (np.log(tot) + mx).astype(np.float32)
+    inf_case = np.isinf(mx)
+    out = np.where(inf_case[..., None], po, merged).astype(np.float32)
+    lse = np.where(inf_case, mx, lse).astype(np.float32)
+    copy_case = np.arange(T)[:, None] >= npre
+    out = np.where(copy_case[..., None], so, out).astype(np.float32)
+    lse = np.where(copy_case, _f32(suffix_lse).T, lse).astype(np.float32)
+    if output_scale is not None:
+        inv = np.float32(1.0) / np.float32(_f32(output_scale).reshape(-1)[0])
+        out = f32_to_e4m3_bits(np.clip((out * inv).astype(np.float32), -448.0, 448.0))
+    return out, lse.T.copy()
+
+
+def silu_and_mul_nvfp4_quant(x: torch.Tensor, global_scale: float, return_scaled: bool = False):
+    """nvfp4_quant( T( silu_f32(gate) * up ) ): compute_silu_mul, nvfp4_utils.cuh:304-329 (one rounding
+    to the activation dtype, unlike silu_and_mul), then cvt_warp_fp16_to_fp4."""
+    d = x.shape[-1] // 2
+    g, u = x[..., :d].float(), x[..., d:].float()
+    act = ((g / (1.0 + torch.exp(-g))) * u).to(x.dtype)
+    return nvfp4_quant(act, global_scale, return_scaled=return_scaled)

@@ -140,6 +140,11 @@ SIGNATURES = {
         c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                 c_int, c_float, c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_void_p,
                 c_void_p, c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_void_p]),
+    "b200_silu_and_mul_nvfp4": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int64, c_int, c_void_p]),
+    "b200_merge_attn_states": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int]
+        + [c_int64] * 12 + [c_int, c_int, c_void_p]),
     "b200_paged_attention_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200_paged_attention_decode": (c_int, [C.POINTER(PagedAttnArgs), c_void_p]),
 }

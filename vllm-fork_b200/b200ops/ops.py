@@ -375,6 +375,29 @@ def scaled_fp4_quant(input: torch.Tensor, input_global_scale: torch.Tensor,
     return output, output_scale.view(torch.float8_e4m3fn)
 
 
+def silu_and_mul_nvfp4_quant(result: torch.Tensor, result_block_scale: torch.Tensor, input: torch.Tensor,
+                             input_global_scale: torch.Tensor) -> None:
+    """torch.ops._C.silu_and_mul_nvfp4_quant(result, result_block_scale, input, input_global_scale):
+    result uint8 [m, d/2], result_block_scale swizzled e4m3 (as scaled_fp4_quant), input [m, 2d]."""
+    _cuda(result, result_block_scale, input, input_global_scale)
+    if input.dim() != 2 or input.stride(1) != 1:
+        raise RuntimeError("silu_and_mul_nvfp4_quant: input must be 2-D with a contiguous last dim")
+    m, d = input.shape[0], input.shape[1] // 2
+    if d % 16 != 0:
+        raise RuntimeError("silu_and_mul_nvfp4_quant: The N dimension must be multiple of 16.")
+    if input.dtype not in (torch.float16, torch.bfloat16):
+        raise RuntimeError("silu_and_mul_nvfp4_quant: Unsupported input data type for quantize_to_fp4.")
+    rm, rn = (m + 127) // 128 * 128, (d // 16 + 3) // 4 * 4
+    if (tuple(result.shape) != (m, d // 2) or result.dtype != torch.uint8 or not result.is_contiguous()
+            or result_block_scale.numel() * result_block_scale.element_size() != rm * rn
+            or not result_block_scale.is_contiguous()):
+        raise RuntimeError("silu_and_mul_nvfp4_quant: result [m, d/2] uint8 and a swizzled block-scale buffer")
+    rc = _lib.load().b200_silu_and_mul_nvfp4(_p(result), _p(result_block_scale), _p(input),
+                                             _p(input_global_scale), m, d, input.stride(0), _dt(input),
+                                             _stream())
+    _lib.check(rc, "silu_and_mul_nvfp4_quant")
+
+
 def cutlass_scaled_fp4_mm(a: torch.Tensor, b: torch.Tensor, block_scale_a: torch.Tensor,
                           block_scale_b: torch.Tensor, alpha: torch.Tensor, out_dtype: torch.dtype,
                           out: torch.Tensor | None = None) -> torch.Tensor:
@@ -656,3 +679,46 @@ def paged_attention_v2(out: torch.Tensor, exp_sums: torch.Tensor, max_logits: to
         key_cache.stride(0), key_cache.stride(1), block_tables.stride(0), P,
         int(blocksparse_vert_stride), _stream())
     _lib.check(rc, "paged_attention_v2")
+
+
+# ------------------------------------------------------------------------------------------------
+# merge_attn_states                     reference: vllm/_custom_ops.py:178-197, ops/merge_attn_states.py
+# ------------------------------------------------------------------------------------------------
+def merge_attn_states(output: torch.Tensor, prefix_output: torch.Tensor, prefix_lse: torch.Tensor,
+                      suffix_output: torch.Tensor, suffix_lse: torch.Tensor,
+                      output_lse: torch.Tensor | None = None,
+                      prefill_tokens_with_context: int | None = None,
+                      output_scale: torch.Tensor | None = None) -> None:
+    """Merge prefix (KV-cache context) and suffix (new tokens) partial attention by their LSEs.
+    outputs [T, H, D]; LSEs float32 [H, T]."""
+    _cuda(output, prefix_output, prefix_lse, suffix_output, suffix_lse, output_lse, output_scale)
+    assert prefix_output.stride(1) == suffix_output.stride(1), (
+        "merge_attn_states requires prefix_output and suffix_output to have matching head strides, got "
+        f"{prefix_output.stride(1)} and {suffix_output.stride(1)}")
+    if prefix_output.dim() != 3 or prefix_output.shape != suffix_output.shape or output.shape != prefix_output.shape:
+        raise RuntimeError("merge_attn_states: outputs must be [T, H, D] of one shape")
+    if prefix_output.dtype != suffix_output.dtype or prefix_output.dtype not in (
+            torch.float32, torch.float16, torch.bfloat16):
+        raise RuntimeError("merge_attn_states: inputs must be float32 / float16 / bfloat16")
+    if prefix_lse.dtype != torch.float32 or suffix_lse.dtype != torch.float32:
+        raise RuntimeError("merge_attn_states: LSEs must be float32")
+    if prefix_output.stride(2) != 1 or suffix_output.stride(2) != 1 or output.stride(2) != 1:
+        raise RuntimeError("merge_attn_states: last dim must be contiguous")
+    T, H, D = prefix_output.shape
+    if tuple(prefix_lse.shape) != (H, T) or tuple(suffix_lse.shape) != (H, T):
+        raise RuntimeError("merge_attn_states: LSEs must be [num_heads, num_tokens]")
+    fp8_out = output.dtype not in (torch.float32, torch.float16, torch.bfloat16)
+    if fp8_out:
+        assert output_scale is not None, f"output_scale is required when output is {output.dtype}"
+    elif output.dtype != prefix_output.dtype:
+        raise RuntimeError("merge_attn_states: output dtype must match the inputs or be FP8")
+    ol = output_lse
+    rc = _lib.load().b200_merge_attn_states(
+        _p(output), _p(ol), _p(prefix_output), _p(prefix_lse), _p(suffix_output), _p(suffix_lse),
+        _p(output_scale), T, H, D, prefix_output.stride(0), suffix_output.stride(0), prefix_output.stride(1),
+        output.stride(0), output.stride(1), prefix_lse.stride(0), prefix_lse.stride(1),
+        suffix_lse.stride(0), suffix_lse.stride(1), 0 if ol is None else ol.stride(0),
+        0 if ol is None else ol.stride(1),
+        -1 if prefill_tokens_with_context is None else int(prefill_tokens_with_context),
+        _dt(prefix_output), _lib.FP8_E4M3 if fp8_out else _dt(output), _stream())
+    _lib.check(rc, "merge_attn_states")

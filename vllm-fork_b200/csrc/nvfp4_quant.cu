@@ -39,7 +39,18 @@ __device__ __forceinline__ uint32_t f32x8_to_e2m1(const float (&a)[8]) {
   return val;
 }
 
+// silu(x) * y in fp32, rounded ONCE to the activation dtype: compute_silu_mul, nvfp4_utils.cuh:304-329
+// (this differs from the stand-alone silu_and_mul op, which also rounds silu(x) first)
 template <typename T>
+__device__ __forceinline__ float silu_mul_f32_rounded(T x, T y) {
+  const float xf = Cvt<T>::to_f32(x);
+  const float s = __fdividef(xf, 1.f + __expf(-xf));
+  return Cvt<T>::to_f32(Cvt<T>::from_f32(s * Cvt<T>::to_f32(y)));
+}
+
+// GATED: the input row is [gate(K) | up(K)] and the quantised tensor is silu(gate) * up
+// (torch.ops._C.silu_and_mul_nvfp4_quant, activation_nvfp4_quant_fusion_kernels.cu:37-118).
+template <typename T, bool GATED>
 __global__ void __launch_bounds__(256)
     nvfp4_quant_kernel(uint8_t* __restrict__ out, uint8_t* __restrict__ sf_out,
                        const T* __restrict__ in, const float* __restrict__ global_scale, int M, int K,
@@ -63,6 +74,17 @@ __global__ void __launch_bounds__(256)
       for (int i = 0; i < 8; i++) {
         x[i] = Cvt<T>::to_f32(e0[i]);
         x[8 + i] = Cvt<T>::to_f32(e1[i]);
+      }
+      if constexpr (GATED) {
+        const uint4 u0 = *reinterpret_cast<const uint4*>(in + (int64_t)row * in_stride + K + kb * 16);
+        const uint4 u1 = *reinterpret_cast<const uint4*>(in + (int64_t)row * in_stride + K + kb * 16 + 8);
+        const T* f0 = reinterpret_cast<const T*>(&u0);
+        const T* f1 = reinterpret_cast<const T*>(&u1);
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+          x[i] = silu_mul_f32_rounded(e0[i], f0[i]);
+          x[8 + i] = silu_mul_f32_rounded(e1[i], f1[i]);
+        }
       }
     } else {
 #pragma unroll
@@ -101,22 +123,20 @@ __global__ void __launch_bounds__(256)
 
 using namespace b200;
 
-extern "C" int b200_nvfp4_quant(void* out, void* out_scale, const void* input,
-                                const float* global_scale, int64_t num_tokens, int hidden,
-                                int64_t in_row_stride, int is_sf_swizzled_layout, int in_dtype,
-                                b200_stream_t stream_) {
-  cudaStream_t stream = (cudaStream_t)stream_;
-  B200_CHECK(num_tokens >= 0 && hidden > 0, B200_ERR_INVALID, "scaled_fp4_quant: bad sizes");
-  B200_CHECK(hidden % 16 == 0, B200_ERR_INVALID,
-             "scaled_fp4_quant: last dim has to be multiple of 16, but got %d", hidden);
+static int nvfp4_quant_launch(void* out, void* out_scale, const void* input, const float* global_scale,
+                              int64_t num_tokens, int hidden, int64_t in_row_stride,
+                              int is_sf_swizzled_layout, int in_dtype, bool gated, cudaStream_t stream,
+                              const char* op) {
+  B200_CHECK(num_tokens >= 0 && hidden > 0, B200_ERR_INVALID, "%s: bad sizes", op);
+  B200_CHECK(hidden % 16 == 0, B200_ERR_INVALID, "%s: last dim has to be multiple of 16, but got %d", op,
+             hidden);
   B200_CHECK(in_dtype == B200_BF16 || in_dtype == B200_F16, B200_ERR_INVALID,
-             "scaled_fp4_quant: input.dtype needs to be fp16 or bf16");
+             "%s: input.dtype needs to be fp16 or bf16", op);
   if (num_tokens == 0) return B200_OK;
-  B200_CHECK(out && out_scale && input && global_scale, B200_ERR_INVALID,
-             "scaled_fp4_quant: null pointer");
+  B200_CHECK(out && out_scale && input && global_scale, B200_ERR_INVALID, "%s: null pointer", op);
   B200_CHECK(((uintptr_t)input & 15) == 0 && (in_row_stride * 2) % 16 == 0 && ((uintptr_t)out & 7) == 0,
-             B200_ERR_INVALID, "scaled_fp4_quant: input rows must be 16-byte aligned");
-  B200_CHECK(num_tokens < (1LL << 31), B200_ERR_UNSUPPORTED, "scaled_fp4_quant: too many rows");
+             B200_ERR_INVALID, "%s: input rows must be 16-byte aligned", op);
+  B200_CHECK(num_tokens < (1LL << 31), B200_ERR_UNSUPPORTED, "%s: too many rows", op);
   const int M = (int)num_tokens;
   const int sf_cols_pad = is_sf_swizzled_layout ? (hidden / 16 + 3) / 4 * 4 : hidden / 16;
   const int rows_pad = is_sf_swizzled_layout ? (M + 127) / 128 * 128 : M;
@@ -126,14 +146,34 @@ extern "C" int b200_nvfp4_quant(void* out, void* out_scale, const void* input,
   const int cap = (148 * 8 + gy - 1) / gy;
   if (gx > cap) gx = cap;
   dim3 grid(gx, gy);
-  if (in_dtype == B200_BF16)
-    nvfp4_quant_kernel<__nv_bfloat16><<<grid, threads, 0, stream>>>(
-        (uint8_t*)out, (uint8_t*)out_scale, (const __nv_bfloat16*)input, global_scale, M, hidden,
-        in_row_stride, is_sf_swizzled_layout);
-  else
-    nvfp4_quant_kernel<__half><<<grid, threads, 0, stream>>>(
-        (uint8_t*)out, (uint8_t*)out_scale, (const __half*)input, global_scale, M, hidden,
-        in_row_stride, is_sf_swizzled_layout);
+#define B200_NVFP4_LAUNCH(T, G)                                                                       \
+  nvfp4_quant_kernel<T, G><<<grid, threads, 0, stream>>>((uint8_t*)out, (uint8_t*)out_scale,          \
+                                                         (const T*)input, global_scale, M, hidden,    \
+                                                         in_row_stride, is_sf_swizzled_layout)
+  if (in_dtype == B200_BF16) {
+    if (gated) B200_NVFP4_LAUNCH(__nv_bfloat16, true);
+    else B200_NVFP4_LAUNCH(__nv_bfloat16, false);
+  } else {
+    if (gated) B200_NVFP4_LAUNCH(__half, true);
+    else B200_NVFP4_LAUNCH(__half, false);
+  }
+#undef B200_NVFP4_LAUNCH
   B200_LAUNCH_CHECK();
   return B200_OK;
+}
+
+extern "C" int b200_nvfp4_quant(void* out, void* out_scale, const void* input,
+                                const float* global_scale, int64_t num_tokens, int hidden,
+                                int64_t in_row_stride, int is_sf_swizzled_layout, int in_dtype,
+                                b200_stream_t stream_) {
+  return nvfp4_quant_launch(out, out_scale, input, global_scale, num_tokens, hidden, in_row_stride,
+                            is_sf_swizzled_layout, in_dtype, false, (cudaStream_t)stream_,
+                            "scaled_fp4_quant");
+}
+
+extern "C" int b200_silu_and_mul_nvfp4(void* out, void* out_scale, const void* input,
+                                       const float* global_scale, int64_t num_tokens, int d,
+                                       int64_t in_row_stride, int in_dtype, b200_stream_t stream_) {
+  return nvfp4_quant_launch(out, out_scale, input, global_scale, num_tokens, d, in_row_stride, 1, in_dtype,
+                            true, (cudaStream_t)stream_, "silu_and_mul_nvfp4_quant");
 }
