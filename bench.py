@@ -40,6 +40,9 @@ def parse():
     ap.add_argument("--ctx", type=int, default=CTX)
     ap.add_argument("--model", default="llama-3.1-8b")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--comm", default="nvlink", choices=["nccl", "nvlink", "fused"],
+                    help="TP collective (N>1): NCCL all-reduce, own NVLink all-reduce, or the fused "
+                         "reduce-scatter+add+RMSNorm+FP8-quant+all-gather kernel")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
@@ -224,7 +227,8 @@ def main():
         group = dist.group.WORLD
     shape = model_shape(a.model)
     S, ctx = a.batch, a.ctx
-    model = decoder.DecoderModel(shape, S, ctx, BLOCK, dev, tp_rank=rank, tp_size=world, tp_group=group)
+    model = decoder.DecoderModel(shape, S, ctx, BLOCK, dev, tp_rank=rank, tp_size=world, tp_group=group,
+                                 comm=a.comm)
     D = shape.head_size
     # ---- synthetic state: KV caches full of random (non-NaN) fp8 codes; block table = random
     # permutation without repetition
@@ -316,7 +320,7 @@ def main():
         "data": "synthetic",
         "config": {"workload": f"{shape.name} decode step, FP8 W8A8 + FP8 KV cache, batch {S}, "
                                f"context {ctx}, block_size {BLOCK} (BASELINE.json configs[1])",
-                   "parallelism": f"tp{world}", "weights": "random init (dummy), per-tensor FP8 scales",
+                   "parallelism": f"tp{world}", "tp_collective": (a.comm if world > 1 else None), "weights": "random init (dummy), per-tensor FP8 scales",
                    "cuda_graph": not a.no_graph,
                    "l2": "inputs larger than L2 (KV cache %.1f GB + weights per GPU)" %
                          (sum(L["kv"].numel() for L in model.layers) / 1e9),
@@ -347,8 +351,17 @@ def main():
                                     "sample": f"failed: {e}"}
     if rank == 0:
         print(json.dumps(line))
+    sys.stdout.flush()
     if world > 1:
-        torch.distributed.destroy_process_group()
+        # tear down in a fixed order and leave without running NCCL's destructors: destroying a process
+        # group whose collectives were captured in a live CUDA graph can hang at interpreter exit
+        model.graph = None
+        torch.cuda.synchronize(dev)
+        torch.distributed.barrier()
+        if model.ar is not None:
+            model.ar.close()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":

@@ -367,6 +367,44 @@ B200_API int b200_nvfp4_gemm(void* out, const void* a, const void* b, const void
                              int64_t lda_bytes, int64_t ldb_bytes, int64_t ldo, int out_dtype,
                              b200_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Tensor-parallel all-reduce over NVLink peer memory (one process per GPU).
+ * Replaces torch.ops._C_custom_ar.{init_custom_ar, register_buffer, all_reduce, dispose, meta_size}
+ * (csrc/custom_all_reduce.cuh:7-120, csrc/custom_all_reduce.cu; python life cycle
+ * vllm/distributed/device_communicators/custom_all_reduce.py:56-560) and, fused, the pair
+ * all_reduce -> fused_add_rms_norm_static_fp8_quant (docs/design/fusions.md:23 fuse_allreduce_rms).
+ *
+ * Life cycle: every rank b200_ipc_alloc()s one symmetric buffer, the 64-byte handles are exchanged by
+ * the host (torch.distributed all_gather), peers b200_ipc_open() them, and b200_allreduce_init() gets
+ * the per-rank pointers (own buffer at index `rank`). Buffer layout: [signals (b200_allreduce_meta_bytes)
+ * | staging (max_message_bytes) | scratch (max_message_bytes) | user heap]. Tensors placed in the user
+ * heap at the same offset on every rank are reduced in place by the peers (zero copy); any other input
+ * is staged by the kernel. These calls DO allocate / synchronise (init-time only); run/fused do not.
+ */
+B200_API int b200_ipc_alloc(size_t bytes, void** ptr, void* handle64);   /* cudaMalloc + zero + IPC handle */
+B200_API int b200_ipc_open(const void* handle64, void** ptr);
+B200_API int b200_ipc_close(void* ptr);
+B200_API int b200_ipc_free(void* ptr);
+B200_API size_t b200_allreduce_meta_bytes(void);
+B200_API int b200_allreduce_init(void** ctx_out, int rank, int world, void* const* buffer_ptrs,
+                                 size_t buffer_bytes, size_t max_message_bytes);
+B200_API int b200_allreduce_heap(void* ctx, size_t* offset, size_t* bytes);
+B200_API int b200_allreduce_register(void* ctx, void* const* buffer_ptrs, size_t bytes);
+B200_API int b200_allreduce_destroy(void* ctx);
+/* out = sum over ranks of in (fp32 accumulate in rank order: bit-identical on all ranks), out-of-place
+ * (in == out allowed only for staged inputs). numel * sizeof(dtype) % 16 == 0.
+ * algo: 0 auto (reference thresholds), 1 one-shot, 2 two-shot. */
+B200_API int b200_allreduce_run(void* ctx, const void* in, void* out, int64_t numel, int dtype, int algo,
+                                b200_stream_t stream);
+/* One kernel: z = T(T(sum_r in_r) + residual); residual = z; y = rmsnorm(z) * weight;
+ * out = scale ? e4m3(clamp(T(y) / *scale)) : T(y), for all num_tokens rows on every rank.
+ * Rank r computes rows [r*Mp, (r+1)*Mp), Mp = ceil(num_tokens / world), and `residual` holds ONLY those
+ * rows ([Mp, hidden], NULL = no residual add). `out` must live in the symmetric heap. */
+B200_API int b200_allreduce_fused_add_rms_norm(void* ctx, void* out, const void* in, void* residual,
+                                               const void* weight, const float* scale, float eps,
+                                               int64_t num_tokens, int hidden, int dtype,
+                                               b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

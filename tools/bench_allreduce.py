@@ -1,0 +1,63 @@
+"""Latency table of the NVLink all-reduce vs NCCL (CUDA-graph timed, device time).
+torchrun --nproc-per-node N --master-addr 127.0.0.1 tools/bench_allreduce.py"""
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "vllm-fork_b200")):
+    sys.path.insert(0, p)
+from b200ops.all_reduce import B200AllReduce  # noqa: E402
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(rank)
+    dev = torch.device(f"cuda:{rank}")
+    dist.init_process_group("nccl", device_id=dev)
+    ar = B200AllReduce(None, dev, max_size=16 << 20, heap_size=64 << 20)
+
+    def timeit(fn, iters=20, reps=5):
+        s2 = torch.cuda.Stream()
+        s2.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s2):
+            for _ in range(3):
+                fn()
+        torch.cuda.current_stream().wait_stream(s2)
+        torch.cuda.synchronize(); dist.barrier()
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            for _ in range(iters):
+                fn()
+        gr.replay(); torch.cuda.synchronize(); dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            gr.replay()
+        e1.record(); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / (iters * reps) * 1e3
+
+    for nbytes in (16, 4096, 65536, 262144, 1 << 20, 2 << 20, 8 << 20):
+        n = nbytes // 2
+        start = ar._heap_used
+        x = ar.alloc(n, torch.bfloat16); x.fill_(1.0)
+        o = torch.empty(n, dtype=torch.bfloat16, device=dev)
+        xn = torch.ones(n, dtype=torch.bfloat16, device=dev)
+        t1 = timeit(lambda: ar.all_reduce(x, out=o, algo=1))
+        t2 = timeit(lambda: ar.all_reduce(x, out=o, algo=2))
+        ts = timeit(lambda: ar.all_reduce(xn, out=o, algo=1))
+        tn = timeit(lambda: dist.all_reduce(xn))
+        if rank == 0:
+            print(json.dumps({"bytes": nbytes, "world": world, "one_shot_us": round(t1, 2), "two_shot_us": round(t2, 2),
+                              "one_shot_staged_us": round(ts, 2), "nccl_us": round(tn, 2)}), flush=True)
+        torch.cuda.synchronize(); dist.barrier()
+        ar._heap_used = start
+    ar.close()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

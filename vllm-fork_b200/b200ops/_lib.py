@@ -145,6 +145,19 @@ SIGNATURES = {
     "b200_merge_attn_states": (
         c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int]
         + [c_int64] * 12 + [c_int, c_int, c_void_p]),
+    "b200_ipc_alloc": (c_int, [c_size_t, C.POINTER(c_void_p), c_void_p]),
+    "b200_ipc_open": (c_int, [c_void_p, C.POINTER(c_void_p)]),
+    "b200_ipc_close": (c_int, [c_void_p]),
+    "b200_ipc_free": (c_int, [c_void_p]),
+    "b200_allreduce_meta_bytes": (c_size_t, []),
+    "b200_allreduce_init": (c_int, [C.POINTER(c_void_p), c_int, c_int, C.POINTER(c_void_p), c_size_t, c_size_t]),
+    "b200_allreduce_heap": (c_int, [c_void_p, C.POINTER(c_size_t), C.POINTER(c_size_t)]),
+    "b200_allreduce_register": (c_int, [c_void_p, C.POINTER(c_void_p), c_size_t]),
+    "b200_allreduce_destroy": (c_int, [c_void_p]),
+    "b200_allreduce_run": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
+    "b200_allreduce_fused_add_rms_norm": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_int64, c_int, c_int,
+                c_void_p]),
     "b200_paged_attention_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200_paged_attention_decode": (c_int, [C.POINTER(PagedAttnArgs), c_void_p]),
 }

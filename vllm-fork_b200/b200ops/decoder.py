@@ -13,7 +13,11 @@ Embedding lookup / bf16 lm_head / argmax are outside the path named by north_sta
 ops (a library GEMM for lm_head); everything else - including the SURVEY.md section 8f rank-1 rows
 RMSNorm(+residual)+FP8-quant and RoPE - is libb200ops.so.
 Tensor parallelism: attention heads and GEMM N/K are sharded over the ranks
-of `tp_group`, one NCCL all-reduce after o_proj and down_proj (linear.py:1766-1767).
+of `tp_group`, one all-reduce after o_proj and down_proj (linear.py:1766-1767). `comm` picks the rung
+of the SURVEY 8e ladder: "nccl" (torch.distributed, NVLS), "nvlink" (own one-shot all-reduce over peer
+memory, b200ops/all_reduce.py, GEMM outputs in the symmetric heap = zero copy), "fused" (one kernel:
+reduce-scatter + residual add + RMSNorm + FP8 quant + all-gather; the residual stream is then kept
+row-sharded across the ranks).
 """
 from __future__ import annotations
 
@@ -57,7 +61,8 @@ def _quant_weight(w: torch.Tensor):
 class DecoderModel:
     def __init__(self, shape: ModelShape, max_seqs: int, max_ctx: int, block_size: int = 16,
                  device: str | torch.device = "cuda:0", tp_rank: int = 0, tp_size: int = 1,
-                 tp_group=None, seed: int = 1234, kv_fp8: bool = True, num_blocks: int | None = None):
+                 tp_group=None, seed: int = 1234, kv_fp8: bool = True, num_blocks: int | None = None,
+                 comm: str = "nccl"):
         self.shape = s = shape
         self.dev = torch.device(device)
         self.tp_rank, self.tp_size, self.tp_group = tp_rank, tp_size, tp_group
@@ -70,6 +75,9 @@ class DecoderModel:
         self.num_blocks = num_blocks or max_seqs * self.blocks_per_seq + 8
         self.kv_fp8 = kv_fp8
         self.launches_per_step = 0
+        assert comm in ("nccl", "nvlink", "fused")
+        self.comm = comm if tp_size > 1 else "nccl"
+        self.ar = None
         g = torch.Generator(device=self.dev).manual_seed(seed)
 
         def rnd(*shp, fan_in):
@@ -129,13 +137,32 @@ class DecoderModel:
         self.qkv = torch.empty(S, (self.hq + 2 * self.hkv) * D, dtype=torch.bfloat16, device=self.dev)
         self.attn_out = torch.empty(S, self.hq, D, dtype=torch.bfloat16, device=self.dev)
         self.proj = torch.empty(S, H, dtype=torch.bfloat16, device=self.dev)
+        self.proj_in = [self.proj, self.proj]   # GEMM outputs feeding the collective (o_proj, down_proj)
+        if self.comm != "nccl":
+            from .all_reduce import B200AllReduce
+            self.ar = B200AllReduce(tp_group, self.dev, max_size=max(8 << 20, S * H * 2),
+                                    heap_size=4 * S * H * 2 + (1 << 20))
+            # alternating GEMM-output buffers in the symmetric heap: peers read them in place, and the
+            # start barrier of the next collective doubles as the end barrier of this one
+            self.proj_in = [self.ar.alloc((S, H), torch.bfloat16), self.ar.alloc((S, H), torch.bfloat16)]
+            if self.comm == "fused":
+                self.x8_sym = self.ar.alloc((S, H), torch.float8_e4m3fn)
+                self.final_sym = self.ar.alloc((S, H), torch.bfloat16)
+                lo, hi = self.ar.rows_of_rank(S)
+                self.row_lo, self.row_hi = lo, hi
+                self.res_shard = torch.zeros((S + tp_size - 1) // tp_size, H, dtype=torch.bfloat16, device=self.dev)
         self.gu = torch.empty(S, 2 * self.inter, dtype=torch.bfloat16, device=self.dev)
         self.attn_hook = None  # bench instrumentation: called around the attention launch
         self.graph = None
 
     def _all_reduce(self, t):
-        if self.tp_size > 1:
+        """sum over the TP group; returns the tensor holding the result."""
+        if self.tp_size == 1:
+            return t
+        if self.comm == "nccl":
             torch.distributed.all_reduce(t, group=self.tp_group)
+            return t
+        return self.ar.all_reduce(t, out=self.proj, algo=1, skip_end_barrier=True)
 
     # ---- one decode step over the persistent device buffers
     def forward_device(self) -> None:
@@ -147,14 +174,25 @@ class DecoderModel:
         q = self.qkv[:, : self.hq * D].view(S, self.hq, D)
         k = self.qkv[:, self.hq * D:(self.hq + self.hkv) * D].view(S, self.hkv, D)
         v = self.qkv[:, (self.hq + self.hkv) * D:].view(S, self.hkv, D)
+        fused = self.comm == "fused"
+        if fused:
+            x8 = self.x8_sym
+        pa, pb = self.proj_in
+        red = self.proj
         torch.index_select(self.embed, 0, self.token_ids, out=self.residual)
+        if fused:  # the residual stream lives row-sharded across the ranks from here on
+            self.res_shard[: self.row_hi - self.row_lo].copy_(self.residual[self.row_lo:self.row_hi])
         for li, L in enumerate(self.layers):
             if li == 0:
                 ops.rms_norm_static_fp8_quant(x8, self.residual, L["in_norm"], L["a_qkv"], s.eps)
+                n += 1
+            elif fused:
+                self.ar.fused_add_rms_norm(x8, pb, self.res_shard, L["in_norm"], s.eps, L["a_qkv"])
+                n += 1
             else:
-                ops.fused_add_rms_norm_static_fp8_quant(x8, self.proj, self.residual, L["in_norm"],
+                ops.fused_add_rms_norm_static_fp8_quant(x8, red, self.residual, L["in_norm"],
                                                         L["a_qkv"], s.eps)
-            n += 1
+                n += 1
             ops.cutlass_scaled_mm(x8, L["wqkv"].t(), L["a_qkv"], L["wqkv_s"], torch.bfloat16, out=self.qkv)
             n += LAUNCHES["gemm"]
             ops.rotary_embedding(self.positions, q, k, D, self.cos_sin, True); n += 1
@@ -172,16 +210,26 @@ class DecoderModel:
             if self.attn_hook:
                 self.attn_hook(1)
             ops.static_scaled_fp8_quant(a8, self.attn_out.view(S, self.hq * D), L["a_o"]); n += 1
-            ops.cutlass_scaled_mm(a8, L["wo"].t(), L["a_o"], L["wo_s"], torch.bfloat16, out=self.proj); n += 1
-            self._all_reduce(self.proj)
-            ops.fused_add_rms_norm_static_fp8_quant(x8, self.proj, self.residual, L["post_norm"],
-                                                    L["a_gu"], s.eps); n += 1
+            ops.cutlass_scaled_mm(a8, L["wo"].t(), L["a_o"], L["wo_s"], torch.bfloat16, out=pa); n += 1
+            if fused:
+                self.ar.fused_add_rms_norm(x8, pa, self.res_shard, L["post_norm"], s.eps, L["a_gu"]); n += 1
+            else:
+                red = self._all_reduce(pa)
+                n += 1 if self.ar is not None else 0
+                ops.fused_add_rms_norm_static_fp8_quant(x8, red, self.residual, L["post_norm"],
+                                                        L["a_gu"], s.eps); n += 1
             ops.cutlass_scaled_mm(x8, L["wgu"].t(), L["a_gu"], L["wgu_s"], torch.bfloat16, out=self.gu); n += 1
             ops.silu_and_mul_quant(self.h8, self.gu, L["a_d"]); n += LAUNCHES["silu_quant"]
-            ops.cutlass_scaled_mm(self.h8, L["wd"].t(), L["a_d"], L["wd_s"], torch.bfloat16, out=self.proj); n += 1
-            self._all_reduce(self.proj)
-        ops.fused_add_rms_norm(self.proj, self.residual, self.final_norm, s.eps); n += 1
-        logits = self.proj @ self.lm_head.t()
+            ops.cutlass_scaled_mm(self.h8, L["wd"].t(), L["a_d"], L["wd_s"], torch.bfloat16, out=pb); n += 1
+            if not fused:
+                red = self._all_reduce(pb)
+                n += 1 if self.ar is not None else 0
+        if fused:
+            self.ar.fused_add_rms_norm(self.final_sym, pb, self.res_shard, self.final_norm, s.eps, None); n += 1
+            red = self.final_sym
+        else:
+            ops.fused_add_rms_norm(red, self.residual, self.final_norm, s.eps); n += 1
+        logits = red @ self.lm_head.t()
         self.next_tokens.copy_(logits.argmax(-1))
         self.launches_per_step = n
 

@@ -1,0 +1,266 @@
+// b200ops -- tensor-parallel all-reduce over NVLink peer memory (one process per GPU, CUDA IPC).
+//
+// Contract: torch.ops._C_custom_ar.all_reduce and its helpers (csrc/custom_all_reduce.cuh:7-120
+// cross_device_reduce_1stage / 2stage, csrc/custom_collective_common.cuh barriers,
+// vllm/distributed/device_communicators/custom_all_reduce.py:56-560): out = sum over ranks of inp,
+// fp32 accumulation in rank order 0..N-1 on every rank (bit-identical results on all ranks),
+// out-of-place, CUDA-graph capturable, no host synchronisation.
+//
+// B200 design. Every rank owns one cudaMalloc'ed SYMMETRIC buffer [signals | data heap], opened on all
+// peers through CUDA IPC; NVSwitch gives each GPU full bandwidth to every peer, so the kernels simply
+// issue 16-byte peer loads.
+//   * inputs that live inside the symmetric heap (the decoder allocates its GEMM outputs there) are
+//     read in place by the peers: zero copies; other inputs are first staged into the heap by the
+//     same kernel;
+//   * one-shot (small messages): barrier, every rank reads all N copies and reduces, barrier;
+//   * two-shot (large): reduce-scatter of a 1/N slice into the heap, barrier (release/acquire),
+//     all-gather of the reduced slices;
+//   * fused TP epilogue (csrc/allreduce_fused.cuh): reduce-scatter + residual add + RMSNorm +
+//     static FP8 quant + all-gather of the FP8 rows in ONE kernel - the reference's
+//     fuse_allreduce_rms target (docs/design/fusions.md:23) done sequence-parallel style, moving
+//     (N-1)/N * (2 + 1) bytes per element instead of (N-1)/N * (2 + 2).
+// Barriers are flag arrays in peer memory with a per-CTA epoch kept on the device, so a captured
+// graph replays without any host-side state.
+#include "common.cuh"
+
+#include <cstring>
+
+namespace b200 {
+namespace ar {
+
+constexpr int MAX_RANKS = 8;
+constexpr int MAX_BLOCKS = 160;
+constexpr int MAX_REGIONS = 16;
+constexpr int NTHREADS = 512;
+
+// lives at the start of every rank's symmetric buffer
+struct Signal {
+  uint32_t arrive[2][MAX_BLOCKS][MAX_RANKS];  // [epoch parity][cta][source rank]
+  uint32_t epoch[MAX_BLOCKS];                 // this rank's per-CTA barrier count
+};
+constexpr size_t SIGNAL_BYTES = (sizeof(Signal) + 1023) / 1024 * 1024;
+
+struct Region {
+  uint8_t* base[MAX_RANKS];  // the same buffer as seen from this process, per rank
+  size_t bytes;
+};
+
+struct Context {
+  int rank, world;
+  int device;
+  Region regions[MAX_REGIONS];
+  int num_regions;
+  size_t heap_bytes;      // data part of region 0 (after the signals)
+  size_t staging_off;     // byte offset (from region 0 base) of the staging area = SIGNAL_BYTES
+  size_t staging_bytes;   // the staging area covers the first half of the heap by convention
+};
+
+struct Peers {
+  Signal* sig[MAX_RANKS];
+  const uint8_t* in[MAX_RANKS];   // input of every rank (already offset)
+  uint8_t* tmp[MAX_RANKS];        // scratch of every rank (two-shot result slices)
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 ld_peer_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
+
+// All CTAs with the same blockIdx.x on all ranks meet. `epoch` is the CTA's running barrier count
+// (register copy of Signal::epoch[cta]); consecutive barriers alternate between two flag arrays, and
+// a rank can be at most one barrier ahead of a peer, so a flag is never overwritten before it is read.
+// ORDER = true : release/acquire at system scope - data written by this kernel before the barrier is
+//                visible to the peers after it (staged inputs, two-shot slices, pushed rows).
+// ORDER = false: pure rendezvous (volatile flag traffic, no fence) - enough when the data was written by
+//                an EARLIER kernel (complete at the kernel boundary) or when the barrier only protects
+//                reads (end of the all-reduce). Same split as barrier_at_start / barrier_at_end of the
+//                reference (custom_collective_common.cuh). A fence costs ~1 us per barrier here.
+template <int N, bool ORDER>
+__device__ __forceinline__ void barrier(const Peers& pe, int rank, uint32_t& epoch) {
+  __syncthreads();  // all of this CTA's prior global accesses are issued (loads have returned)
+  epoch++;
+  if (threadIdx.x < N) {
+    uint32_t* theirs = &pe.sig[threadIdx.x]->arrive[epoch & 1][blockIdx.x][rank];
+    const uint32_t* mine = &pe.sig[rank]->arrive[epoch & 1][blockIdx.x][threadIdx.x];
+    if constexpr (ORDER) {
+      __threadfence_system();
+      st_release_sys(theirs, epoch);
+      while (ld_acquire_sys(mine) != epoch) {
+      }
+    } else {
+      asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(theirs), "r"(epoch) : "memory");
+      uint32_t v;
+      do {
+        asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+      } while (v != epoch);
+    }
+  }
+  __syncthreads();
+}
+
+template <typename T> struct Pack;  // 16 bytes of T <-> fp32
+template <> struct Pack<float> {
+  static constexpr int N = 4;
+  static __device__ __forceinline__ void add(float (&a)[8], const uint4& v) {
+    const float* f = reinterpret_cast<const float*>(&v);
+#pragma unroll
+    for (int i = 0; i < 4; i++) a[i] += f[i];
+  }
+  static __device__ __forceinline__ uint4 pack(const float (&a)[8]) {
+    return make_uint4(__float_as_uint(a[0]), __float_as_uint(a[1]), __float_as_uint(a[2]), __float_as_uint(a[3]));
+  }
+};
+template <> struct Pack<__half> {
+  static constexpr int N = 8;
+  static __device__ __forceinline__ void add(float (&a)[8], const uint4& v) {
+    const __half2* h = reinterpret_cast<const __half2*>(&v);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const float2 t = __half22float2(h[i]);
+      a[2 * i] += t.x; a[2 * i + 1] += t.y;
+    }
+  }
+  static __device__ __forceinline__ uint4 pack(const float (&a)[8]) {
+    uint4 r;
+    __half2* h = reinterpret_cast<__half2*>(&r);
+#pragma unroll
+    for (int i = 0; i < 4; i++) h[i] = __floats2half2_rn(a[2 * i], a[2 * i + 1]);
+    return r;
+  }
+};
+template <> struct Pack<__nv_bfloat16> {
+  static constexpr int N = 8;
+  static __device__ __forceinline__ void add(float (&a)[8], const uint4& v) {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const float2 t = __bfloat1622float2(h[i]);
+      a[2 * i] += t.x; a[2 * i + 1] += t.y;
+    }
+  }
+  static __device__ __forceinline__ uint4 pack(const float (&a)[8]) {
+    uint4 r;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&r);
+#pragma unroll
+    for (int i = 0; i < 4; i++) h[i] = __floats2bfloat162_rn(a[2 * i], a[2 * i + 1]);
+    return r;
+  }
+};
+
+// sum of pack `idx` over all ranks, in rank order 0..N-1 (same order on every rank)
+template <typename T, int N>
+__device__ __forceinline__ uint4 reduce_pack(const Peers& pe, int64_t idx) {
+  uint4 v[N];
+#pragma unroll
+  for (int r = 0; r < N; r++) v[r] = ld_peer_v4(pe.in[r] + idx * 16);
+  float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int r = 0; r < N; r++) Pack<T>::add(a, v[r]);
+  return Pack<T>::pack(a);
+}
+
+// If `stage_src` is set the input is outside the symmetric heap: copy it into this rank's staging
+// area (pe.in[rank]) first; the start barrier then publishes it.
+template <int N>
+__device__ __forceinline__ void stage_input(const Peers& pe, int rank, const uint8_t* stage_src, int64_t packs) {
+  if (stage_src) {
+    uint4* dst = reinterpret_cast<uint4*>(const_cast<uint8_t*>(pe.in[rank]));
+    const uint4* src = reinterpret_cast<const uint4*>(stage_src);
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < packs; i += (int64_t)gridDim.x * blockDim.x)
+      dst[i] = src[i];
+  }
+}
+
+// `U` packs per thread per trip: all U*N peer loads are issued before the first add, so a trip costs one
+// NVLink round trip instead of U (the kernels are latency-bound: 2 MiB is 2.3 us of NVLink bandwidth).
+template <typename T, int N, int U, typename F>
+__device__ __forceinline__ void reduce_range(const Peers& pe, int64_t lo, int64_t hi, F&& store) {
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i0 = lo + tid; i0 < hi; i0 += stride * U) {
+    uint4 v[U][N];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int64_t i = i0 + u * stride;
+      if (i < hi) {
+#pragma unroll
+        for (int r = 0; r < N; r++) v[u][r] = ld_peer_v4(pe.in[r] + i * 16);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int64_t i = i0 + u * stride;
+      if (i < hi) {
+        float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int r = 0; r < N; r++) Pack<T>::add(a, v[u][r]);
+        store(i, Pack<T>::pack(a));
+      }
+    }
+  }
+}
+
+template <typename T, int N>
+__global__ void __launch_bounds__(NTHREADS, 1)
+    allreduce_one_shot_kernel(Peers pe, uint8_t* __restrict__ out, const uint8_t* stage_src, int rank,
+                              int64_t packs, int skip_end) {
+  uint32_t epoch = pe.sig[rank]->epoch[blockIdx.x];
+  stage_input<N>(pe, rank, stage_src, packs);
+  if (stage_src) barrier<N, true>(pe, rank, epoch);
+  else barrier<N, false>(pe, rank, epoch);
+  reduce_range<T, N, (N <= 4 ? 4 : 2)>(pe, 0, packs, [&](int64_t i, uint4 v) { reinterpret_cast<uint4*>(out)[i] = v; });
+  // peers may overwrite their inputs only after everyone has read them. skip_end: the caller promises
+  // not to touch the input before the NEXT collective of this context (e.g. alternating buffers), whose
+  // start barrier then plays this role.
+  if (!skip_end) barrier<N, false>(pe, rank, epoch);
+  if (threadIdx.x == 0) pe.sig[rank]->epoch[blockIdx.x] = epoch;
+}
+
+template <typename T, int N>
+__global__ void __launch_bounds__(NTHREADS, 1)
+    allreduce_two_shot_kernel(Peers pe, uint8_t* __restrict__ out, const uint8_t* stage_src, int rank,
+                              int64_t packs, int skip_end) {
+  uint32_t epoch = pe.sig[rank]->epoch[blockIdx.x];
+  const int64_t part = (packs + N - 1) / N;          // packs per rank slice
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  stage_input<N>(pe, rank, stage_src, packs);
+  if (stage_src) barrier<N, true>(pe, rank, epoch);
+  else barrier<N, false>(pe, rank, epoch);
+  {  // stage 1: reduce my slice into my scratch
+    const int64_t lo = rank * part, hi = min(packs, lo + part);
+    uint4* mine = reinterpret_cast<uint4*>(pe.tmp[rank]);
+    reduce_range<T, N, 2>(pe, lo, hi, [&](int64_t i, uint4 v) { mine[i - lo] = v; });
+  }
+  barrier<N, true>(pe, rank, epoch);
+  // stage 2: gather every rank's reduced slice (the barrier above is release/acquire at system scope)
+#pragma unroll
+  for (int r = 0; r < N; r++) {
+    const int src = (rank + r) % N;  // start with the local slice, spread the peers
+    const int64_t lo = src * part, hi = min(packs, lo + part);
+    const uint4* theirs = reinterpret_cast<const uint4*>(pe.tmp[src]);
+    for (int64_t i = lo + tid; i < hi; i += stride) reinterpret_cast<uint4*>(out)[i] = ld_peer_v4(theirs + (i - lo));
+  }
+  // the scratch slices are re-written by the next two-shot call: always rendezvous here
+  (void)skip_end;
+  barrier<N, false>(pe, rank, epoch);
+  if (threadIdx.x == 0) pe.sig[rank]->epoch[blockIdx.x] = epoch;
+}
+
+}  // namespace ar
+}  // namespace b200
+
+#include "allreduce_fused.cuh"
+#include "allreduce_host.cuh"

@@ -102,6 +102,18 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
+// sum over the CTA (<= 1024 threads); `red` = 32 floats of shared memory. The reduction tree depends
+// only on blockDim.x, so two kernels with the same block size produce the same bits.
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  v = warp_sum(v);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = (blockDim.x + 31) >> 5;
+  __syncthreads();
+  if (l == 0) red[w] = v;
+  __syncthreads();
+  float r = l < nw ? red[l] : 0.f;
+  return warp_sum(r);
+}
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);
 }

@@ -15,16 +15,6 @@
 
 namespace b200 {
 
-__device__ __forceinline__ float block_sum(float v, float* red) {
-  v = warp_sum(v);
-  const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = (blockDim.x + 31) >> 5;
-  __syncthreads();
-  if (l == 0) red[w] = v;
-  __syncthreads();
-  float r = l < nw ? red[l] : 0.f;
-  return warp_sum(r);
-}
-
 // MODE: 0 = norm -> T out, 1 = norm -> fp8 out
 template <typename T, bool ADD, bool QUANT, int R>
 __global__ void __launch_bounds__(256)
