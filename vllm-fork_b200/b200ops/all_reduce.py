@@ -21,7 +21,7 @@ import ctypes as C
 import torch
 import torch.distributed as dist
 
-from . import _lib
+from . import _lib, tp
 from .ops import _dt, _p, _stream
 
 _SUPPORTED_WORLD_SIZES = [2, 4, 6, 8]
@@ -51,6 +51,8 @@ class B200AllReduce:
         if isinstance(device, int):
             device = torch.device(f"cuda:{device}")
         self.device = torch.device(device)
+        if not torch.cuda.is_available():
+            raise RuntimeError("B200AllReduce needs CUDA devices with peer access (no CPU fallback)")
         if self.world_size == 1:
             return  # like the reference: nothing to do for a single rank
         if self.world_size not in _SUPPORTED_WORLD_SIZES:
@@ -157,8 +159,7 @@ class B200AllReduce:
         _lib.check(rc, "allreduce_fused_add_rms_norm")
 
     def rows_of_rank(self, M: int) -> tuple[int, int]:
-        mp = (M + self.world_size - 1) // self.world_size
-        return self.rank * mp, min(M, (self.rank + 1) * mp)
+        return tp.rows_of_rank(M, self.rank, self.world_size)
 
     def close(self) -> None:
         if self._ctx is None:

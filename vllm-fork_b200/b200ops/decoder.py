@@ -25,7 +25,7 @@ import dataclasses
 
 import torch
 
-from . import ops
+from . import ops, tp
 
 
 @dataclasses.dataclass(frozen=True)
@@ -96,12 +96,13 @@ class DecoderModel:
             wq = rnd(s.heads * D, H, fan_in=H)
             wk = rnd(s.kv_heads * D, H, fan_in=H)
             wv = rnd(s.kv_heads * D, H, fan_in=H)
-            sl = lambda w, n: w[tp_rank * n:(tp_rank + 1) * n]
-            wqkv = torch.cat([sl(wq, self.hq * D), sl(wk, self.hkv * D), sl(wv, self.hkv * D)])
-            wo = rnd(H, s.heads * D, fan_in=s.heads * D)[:, tp_rank * self.hq * D:(tp_rank + 1) * self.hq * D]
-            wg = sl(rnd(s.inter, H, fan_in=H), self.inter)
-            wu = sl(rnd(s.inter, H, fan_in=H), self.inter)
-            wd = rnd(H, s.inter, fan_in=s.inter)[:, tp_rank * self.inter:(tp_rank + 1) * self.inter]
+            sq, sk, sv = tp.qkv_shard(s.heads, s.kv_heads, D, tp_rank, tp_size)
+            wqkv = torch.cat([wq[sq], wk[sk], wv[sv]])
+            wo = rnd(H, s.heads * D, fan_in=s.heads * D)[:, tp.row_shard(s.heads * D, tp_rank, tp_size)]
+            cs = tp.column_shard(s.inter, tp_rank, tp_size)
+            wg = rnd(s.inter, H, fan_in=H)[cs]
+            wu = rnd(s.inter, H, fan_in=H)[cs]
+            wd = rnd(H, s.inter, fan_in=s.inter)[:, tp.row_shard(s.inter, tp_rank, tp_size)]
             # per-tensor scales must be identical on all ranks: derive them from the full tensors
             L["wqkv"], L["wqkv_s"] = _quant_weight(wqkv.contiguous())
             L["wo"], L["wo_s"] = _quant_weight(wo.contiguous())
