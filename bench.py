@@ -40,6 +40,9 @@ def parse():
     ap.add_argument("--ctx", type=int, default=CTX)
     ap.add_argument("--model", default="llama-3.1-8b")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--profile-step", action="store_true",
+                    help="bracket ONE eager decode step with cudaProfilerStart/Stop and exit "
+                         "(for `ncu --profile-from-start off`; prints no bench line)")
     ap.add_argument("--comm", default="nvlink", choices=["nccl", "nvlink", "fused"],
                     help="TP collective (N>1): NCCL all-reduce, own NVLink all-reduce, or the fused "
                          "reduce-scatter+add+RMSNorm+FP8-quant+all-gather kernel")
@@ -253,6 +256,14 @@ def main():
     host_out = pin(torch.zeros(S, dtype=torch.int64))
     model.step(host[0], host_out)  # eager once (sets launches_per_step, loads the inputs)
     launches = model.launches_per_step
+    if a.profile_step:
+        model.step(host[1], host_out)
+        torch.cuda.synchronize(dev)
+        torch.cuda.profiler.start()
+        model.step(host[2], host_out)
+        torch.cuda.synchronize(dev)
+        torch.cuda.profiler.stop()
+        return
     if not a.no_graph:
         model.capture()
 

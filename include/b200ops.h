@@ -179,6 +179,18 @@ B200_API int b200_fp8_gemm(void* out, const void* a, const void* b, const float*
                            int64_t ldb, int64_t ldo, int a_scale_per_row, int b_scale_per_col,
                            int out_dtype, b200_stream_t stream);
 
+/* Same contract as b200_fp8_gemm, third-generation kernel (persistent CTA pairs with
+ * tcgen05.mma.cta_group::2, stream-K split of the (tile, k-block) space, double-buffered TMEM).
+ * Needs a caller-owned, 256-byte aligned workspace of b200_fp8_gemm_v3_workspace_bytes() bytes that was
+ * ZEROED once (it carries the stream-K partial tiles and their flags; the kernel restores the flags
+ * to zero before it ends, so the same workspace serves every call on one stream). */
+B200_API size_t b200_fp8_gemm_v3_workspace_bytes(void);
+B200_API int b200_fp8_gemm_v3(void* out, const void* a, const void* b, const float* a_scale,
+                              const float* b_scale, const void* bias, int M, int N, int K, int64_t lda,
+                              int64_t ldb, int64_t ldo, int a_scale_per_row, int b_scale_per_col,
+                              int out_dtype, void* workspace, size_t workspace_bytes,
+                              b200_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Gated activation between the MLP / MoE GEMMs.
  * Replaces torch.ops._C.silu_and_mul (csrc/libtorch_stable/activation_kernels.cu:102-160,291-296):

@@ -26,7 +26,12 @@ def to_fp8_bits(t):
     return t.clamp(-448, 448).to(torch.float8_e4m3fn).view(torch.uint8)
 
 
-def run_case(M, N, K, per_token, per_channel, out_dtype, use_bias, seed=0):
+IMPLS = ["v2", "v3"]
+V3_MNK = [(1, 16384, 1024), (33, 1024, 1024), (128, 32768, 4096), (256, 4096, 4096), (256, 4096, 14336),
+          (300, 1280, 8192), (2048, 2048, 2048), (512, 24576, 128)]
+
+
+def run_case(M, N, K, per_token, per_channel, out_dtype, use_bias, seed=0, impl=None):
     g = torch.Generator().manual_seed(seed)
     a8 = to_fp8_bits(torch.randn(M, K, generator=g))
     w8 = to_fp8_bits(torch.randn(N, K, generator=g))
@@ -39,7 +44,7 @@ def run_case(M, N, K, per_token, per_channel, out_dtype, use_bias, seed=0):
     b_g = w8.to(DEV).view(torch.float8_e4m3fn).t()  # [K, N] column-major
     out = _ops().cutlass_scaled_mm(a_g, b_g, sa.to(DEV).view(-1, 1) if per_token else sa.to(DEV),
                                    sb.to(DEV).view(-1, 1) if per_channel else sb.to(DEV), out_dtype,
-                                   None if bias is None else bias.to(DEV))
+                                   None if bias is None else bias.to(DEV), impl=impl)
     torch.cuda.synchronize()
     got = out.float().cpu().numpy()
     assert got.shape == (M, N)
@@ -48,36 +53,44 @@ def run_case(M, N, K, per_token, per_channel, out_dtype, use_bias, seed=0):
     np.testing.assert_allclose(got, ref, rtol=rtol, atol=2e-2 if use_bias else 2e-3)
 
 
+@pytest.mark.parametrize("impl", IMPLS)
 @pytest.mark.parametrize("mnk", MNK)
 @pytest.mark.parametrize("per_token,per_channel", [(False, False), (True, True)])
-def test_scaled_mm_shapes(mnk, per_token, per_channel):
-    run_case(*mnk, per_token, per_channel, torch.bfloat16, False)
+def test_scaled_mm_shapes(mnk, per_token, per_channel, impl):
+    if impl == "v3" and (per_token or mnk not in V3_MNK):
+        pytest.skip("v3 (non-default kernel) runs a thinned grid")
+    run_case(*mnk, per_token, per_channel, torch.bfloat16, False, impl=impl)
 
 
 @pytest.mark.parametrize("mnk", [(1, 256, 128), (33, 1024, 1024), (256, 4096, 4096), (512, 512, 512)])
 @pytest.mark.parametrize("per_token,per_channel", [(True, False), (False, True)])
 @pytest.mark.parametrize("out_dtype", [torch.bfloat16, torch.float16])
 @pytest.mark.parametrize("use_bias", [False, True])
-def test_scaled_mm_scales_bias_dtypes(mnk, per_token, per_channel, out_dtype, use_bias):
-    run_case(*mnk, per_token, per_channel, out_dtype, use_bias, seed=1)
+@pytest.mark.parametrize("impl", IMPLS)
+def test_scaled_mm_scales_bias_dtypes(mnk, per_token, per_channel, out_dtype, use_bias, impl):
+    run_case(*mnk, per_token, per_channel, out_dtype, use_bias, seed=1, impl=impl)
 
 
-def test_scaled_mm_exact_small_integers():
+@pytest.mark.parametrize("impl", IMPLS)
+def test_scaled_mm_exact_small_integers(impl):
     """Integer-valued operands, power-of-two scales: every product and sum is exact in fp32 and in
     bf16 -> the GEMM must be BIT-exact (catches descriptor / swizzle / k-offset mistakes)."""
     g = torch.Generator().manual_seed(3)
-    for M, N, K in [(7, 128, 128), (130, 384, 256), (256, 256, 1024), (513, 512, 384)]:
+    # the last shapes cut tiles across CTA pairs (stream-K partials) in the v3 kernel
+    for M, N, K in [(7, 128, 128), (130, 384, 256), (256, 256, 1024), (513, 512, 384), (256, 4096, 4096),
+                    (64, 1024, 14336), (1024, 1280, 2048)]:
         a = torch.randint(-2, 3, (M, K), generator=g).float()
         w = torch.randint(-2, 3, (N, K), generator=g).float()
         ref = (a.double() @ w.double().t()).float() * 0.25
         out = _ops().cutlass_scaled_mm(to_fp8_bits(a).to(DEV).view(torch.float8_e4m3fn),
                                        to_fp8_bits(w).to(DEV).view(torch.float8_e4m3fn).t(),
                                        torch.tensor([0.5], device=DEV), torch.tensor([0.5], device=DEV),
-                                       torch.bfloat16)
+                                       torch.bfloat16, impl=impl)
         assert torch.equal(out.float().cpu(), ref.to(torch.bfloat16).float()), (M, N, K)
 
 
-def test_scaled_mm_strided_a_and_out_validation():
+@pytest.mark.parametrize("impl", IMPLS)
+def test_scaled_mm_strided_a_and_out_validation(impl):
     g = torch.Generator().manual_seed(4)
     M, N, K = 48, 256, 512
     wide = to_fp8_bits(torch.randn(M, 2 * K, generator=g))
@@ -85,12 +98,12 @@ def test_scaled_mm_strided_a_and_out_validation():
     a_view = wide.to(DEV).view(torch.float8_e4m3fn)[:, K:]
     one = torch.ones(1, device=DEV)
     out = _ops().cutlass_scaled_mm(a_view, w8.to(DEV).view(torch.float8_e4m3fn).t(), one, one,
-                                   torch.float16)
+                                   torch.float16, impl=impl)
     ref = ref_ops.scaled_mm(wide[:, K:].numpy(), w8.numpy(), [1.0], [1.0])
     np.testing.assert_allclose(out.float().cpu().numpy(), ref, rtol=2 ** -10, atol=2e-3)
     with pytest.raises(RuntimeError, match="multiples of 16"):
         _ops().cutlass_scaled_mm(a_view[:, :500], w8.to(DEV).view(torch.float8_e4m3fn)[:, :500].t(),
-                                 one, one, torch.float16)
+                                 one, one, torch.float16, impl=impl)
 
 
 @pytest.mark.parametrize("tokens,d", [(1, 128), (7, 17), (83, 14336), (256, 14336), (4096, 512)])

@@ -18,6 +18,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--shapes", default=DEFAULT)
     ap.add_argument("--iters", type=int, default=30)
+    ap.add_argument("--impl", default=None, help="v2 | v3 (default: ops.GEMM_IMPL)")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     for shp in a.shapes.split(";"):
@@ -30,14 +31,14 @@ def main():
         sb = torch.ones(1, device=dev)
         out = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
         for i in range(3):
-            ops.cutlass_scaled_mm(x, ws[i % ncopy].t(), sa, sb, torch.bfloat16, out=out)
+            ops.cutlass_scaled_mm(x, ws[i % ncopy].t(), sa, sb, torch.bfloat16, out=out, impl=a.impl)
         torch.cuda.synchronize()
         # capture one pass over all weight copies in a CUDA graph: python launch cost (~20 us per
         # call: ctypes + 3 tensor-map encodes) must not be part of a kernel number
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
             for i in range(ncopy):
-                ops.cutlass_scaled_mm(x, ws[i].t(), sa, sb, torch.bfloat16, out=out)
+                ops.cutlass_scaled_mm(x, ws[i].t(), sa, sb, torch.bfloat16, out=out, impl=a.impl)
         g.replay()
         torch.cuda.synchronize()
         reps = max(1, a.iters // ncopy)
@@ -51,7 +52,7 @@ def main():
         us = e0.elapsed_time(e1) / a_iters * 1e3
         flops = 2.0 * M * N * K
         byts = M * K + N * K + 2 * M * N
-        print(json.dumps({"M": M, "N": N, "K": K, "us": round(us, 2), "TFLOPs": round(flops / us / 1e6, 1),
+        print(json.dumps({"impl": a.impl or ops.GEMM_IMPL, "M": M, "N": N, "K": K, "us": round(us, 2), "TFLOPs": round(flops / us / 1e6, 1),
                           "GBps": round(byts / us / 1e3, 1)}))
 
 

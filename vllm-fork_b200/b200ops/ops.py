@@ -7,6 +7,8 @@ device memory and the current CUDA stream.  There is no CPU fallback.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from . import _lib
@@ -264,6 +266,27 @@ def cutlass_scaled_mm_supports_fp8(cuda_device_capability: int) -> bool:
     return cuda_device_capability // 10 == 10
 
 
+# which FP8 GEMM kernel cutlass_scaled_mm launches: "v2" = one CTA per tile (csrc/gemm_fp8.cu),
+# "v3" = persistent CTA pairs (cta_group::2) + stream-K (csrc/gemm_fp8_v3.cu). Both are tcgen05 kernels
+# with the same arithmetic and both are parity-green; this is a tuning switch (env B200_GEMM_IMPL), not a
+# fallback. Measured on B200 (gpurun_out/bench_gemm_v3.log): v3 ties v2 at large M (2.11 vs 2.22 PFLOP/s)
+# and loses at decode M (its stream-K fix-up reads fp32 partials from L2 latency-bound), so v2 is the
+# default until the fix-up is moved onto bulk copies.
+GEMM_IMPL = os.environ.get("B200_GEMM_IMPL", "v2")
+_gemm_ws: dict[str, torch.Tensor] = {}
+
+
+def _gemm_workspace(device: torch.device) -> torch.Tensor:
+    """zero-initialised stream-K workspace of the v3 kernel, one per device (the kernel leaves its
+    flags at zero, so it is shared by all calls that run on one stream at a time)."""
+    key = str(device)
+    ws = _gemm_ws.get(key)
+    if ws is None:
+        ws = torch.zeros(_lib.load().b200_fp8_gemm_v3_workspace_bytes(), dtype=torch.uint8, device=device)
+        _gemm_ws[key] = ws
+    return ws
+
+
 def cutlass_scaled_mm(
     a: torch.Tensor,
     b: torch.Tensor,
@@ -272,6 +295,7 @@ def cutlass_scaled_mm(
     out_dtype: torch.dtype,
     bias: torch.Tensor | None = None,
     out: torch.Tensor | None = None,
+    impl: str | None = None,
 ) -> torch.Tensor:
     """output = torch.mm(scale_a * a, scale_b * b).to(out_dtype) (+ bias).
     a: e4m3 [M, K] row-major; b: e4m3 [K, N] column-major (weight.t()); scale_a [1] / [M,1];
@@ -302,10 +326,14 @@ def cutlass_scaled_mm(
         out = torch.empty((M, N), dtype=out_dtype, device=a.device)
     elif out.dtype != out_dtype or out.stride(-1) != 1:
         raise RuntimeError("cutlass_scaled_mm: bad out tensor")
-    rc = lib.b200_fp8_gemm(
-        _p(out), _p(a), _p(b), _p(scale_a), _p(scale_b), _p(bias), M, N, K,
-        a.stride(0) if M > 1 else K, b.stride(1), out.stride(0) if out.dim() > 1 else N,
-        1 if scale_a.numel() > 1 else 0, 1 if scale_b.numel() > 1 else 0, _dt(out), _stream())
+    common = (_p(out), _p(a), _p(b), _p(scale_a), _p(scale_b), _p(bias), M, N, K,
+              a.stride(0) if M > 1 else K, b.stride(1), out.stride(0) if out.dim() > 1 else N,
+              1 if scale_a.numel() > 1 else 0, 1 if scale_b.numel() > 1 else 0, _dt(out))
+    if (impl or GEMM_IMPL) == "v3":
+        ws = _gemm_workspace(a.device)
+        rc = lib.b200_fp8_gemm_v3(*common, _p(ws), ws.numel(), _stream())
+    else:
+        rc = lib.b200_fp8_gemm(*common, _stream())
     _lib.check(rc, "cutlass_scaled_mm")
     return out.view(*target_shape)
 

@@ -1,0 +1,571 @@
+// b200ops -- FP8 (E4M3) W8A8 GEMM, third generation: persistent CTA PAIRS (cta_group::2), stream-K
+// work split, double-buffered TMEM accumulators (sm_100a).
+//
+// Contract: identical to gemm_fp8.cu (torch.ops._C.cutlass_scaled_mm,
+// csrc/libtorch_stable/quantization/w8a8/cutlass/scaled_mm_entry.cu:197-270):
+//   out[M,N] = a_scale (.) ( b_scale (.) (A[M,K] . B[K,N]) ) (+ bias[N]),  fp32 accumulate.
+//
+// Why a third kernel (measured on B200, profiles/r1b): at decode M = 256 the one-CTA kernel is bound
+// by what one SM can pull in per k-block (16 KB of weights + 32 KB of activations at ~100 GB/s per SM),
+// loses ~25 % to wave quantisation (224 weight slabs on 148 SMs) and pays prologue + epilogue once per
+// tile. Here:
+//   * a CTA pair issues ONE tcgen05.mma.cta_group::2 of 256 x BN x 32: each CTA stages its own 128
+//     "rows" and only HALF of the "cols" operand, so per-SM ingest per k-block drops from 48 to 32 KB;
+//   * the grid is persistent (one pair per 2 SMs) and the flattened (tile, k-block) space is cut into
+//     equal contiguous ranges (stream-K): every pair gets the same number of k-blocks whatever N is;
+//     a tile cut by a range boundary is finished by the pair that holds its FIRST k-blocks (it gets
+//     there last), the other pairs publish fp32 partials (L2-resident workspace + flag) first thing;
+//   * two TMEM accumulator buffers (2 x BN columns) let the epilogue of piece i overlap the MMAs of
+//     piece i+1.
+// Roles per CTA: warp 0 = TMA producer, warp 1 = MMA issuer (leader CTA only) + TMEM owner,
+// warps 2-5 = epilogue.
+#include "tcgen05.cuh"
+
+#include <cmath>
+#include <cstring>
+
+namespace b200 {
+namespace gemm8v3 {
+
+constexpr int BM = 128;          // rows per CTA (UMMA M = 256 per pair)
+constexpr int BK = 128;          // k-block bytes
+constexpr int UMMA_K = 32;
+constexpr int NTHREADS = 192;
+constexpr int MAX_STAGES = 8;
+constexpr uint32_t PEER_MASK = 0xFEFFFFFFu;  // clears the CTA-rank bit of a shared::cluster address
+
+struct Params {
+  void* out;
+  const float* r_scale;
+  const float* c_scale;
+  const void* bias;
+  float* ws_partials;     // [pairs][2 CTAs][BN/16][128][16] fp32
+  uint32_t* ws_flags;     // [pairs][2]: arrive count, consumer-done count
+  int R, C, K;
+  int64_t ldo;
+  int r_scale_vec, c_scale_vec;
+  int swap, out_bf16, stages, tma_store;
+  int row_tiles, col_tiles, num_kb;   // tiles of 256 rows x BN cols, k-blocks per tile
+  int pairs;
+};
+
+using namespace b200::tc;
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d_2sm(uint32_t dst, const void* tmap, uint32_t bar, int c0, int c1,
+                                                uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(dst),
+      "l"(tmap), "r"(bar & PEER_MASK), "r"(c0), "r"(c1), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ void tc_mma_f8_2sm(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc,
+                                              uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// arrive on the barrier at this smem offset in BOTH CTAs of the pair when the prior MMAs complete
+__device__ __forceinline__ void tc_commit_2sm(uint32_t bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+      "h"((uint16_t)3)
+      : "memory");
+}
+// arrive on the LEADER CTA's copy of a barrier
+__device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, 0;\n\t"
+      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}" ::"r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// One contiguous piece of one tile handled by this pair.
+struct Piece {
+  int tile, kb0, kb1;   // k-blocks [kb0, kb1) of `tile`
+};
+// The unit range of pair p in the flattened (tile, k-block) space.
+__device__ __forceinline__ void pair_range(const Params& p, int pair, int64_t* lo, int64_t* hi) {
+  const int64_t units = (int64_t)p.row_tiles * p.col_tiles * p.num_kb;
+  *lo = units * pair / p.pairs;
+  *hi = units * (pair + 1) / p.pairs;
+}
+// i-th piece of the range [lo, hi) in processing order (ascending units); returns false past the end
+__device__ __forceinline__ bool next_piece(const Params& p, int64_t& cur, int64_t hi, Piece* pc) {
+  if (cur >= hi) return false;
+  const int tile = (int)(cur / p.num_kb);
+  const int kb0 = (int)(cur - (int64_t)tile * p.num_kb);
+  const int64_t tile_end = (int64_t)(tile + 1) * p.num_kb;
+  const int64_t end = tile_end < hi ? tile_end : hi;
+  pc->tile = tile;
+  pc->kb0 = kb0;
+  pc->kb1 = kb0 + (int)(end - cur);
+  cur = end;
+  return true;
+}
+
+template <int BN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
+    gemm_fp8_v3_kernel(const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmC,
+                       const __grid_constant__ CUtensorMap tmO, const Params p) {
+  constexpr uint32_t R_BYTES = BM * BK;             // this CTA's 128 rows
+  constexpr uint32_t C_BYTES = (BN / 2) * BK;       // this CTA's half of the cols operand
+  constexpr uint32_t STAGE_BYTES = R_BYTES + C_BYTES;
+  constexpr uint32_t STAGING_BYTES = BN * BM * 2;   // transposed output tile [BN m][128 r] 16-bit
+  constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;   // two accumulator buffers
+  // instruction descriptor: D = F32, A = B = E4M3, K-major, N = BN, M = 256 (pair)
+  constexpr uint32_t IDESC = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_base = smem_u32(smem_raw);
+  const uint32_t base = (raw_base + 1023u) & ~1023u;
+  uint8_t* smem = smem_raw + (base - raw_base);
+  const int stages = p.stages;
+  const uint32_t staging = base + (uint32_t)stages * STAGE_BYTES;
+  const uint32_t bar_base = staging + STAGING_BYTES;
+  const uint32_t bar_full = bar_base;                          // [stages]   (leader's copy is used)
+  const uint32_t bar_empty = bar_base + 8u * MAX_STAGES;       // [stages]   per CTA
+  const uint32_t bar_tfull = bar_base + 16u * MAX_STAGES;      // [2]        per CTA
+  const uint32_t bar_tempty = bar_tfull + 16u;                 // [2]        (leader's copy is used)
+  volatile uint32_t* tmem_holder = reinterpret_cast<volatile uint32_t*>(
+      smem + (size_t)stages * STAGE_BYTES + STAGING_BYTES + 16 * MAX_STAGES + 32 + 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cta = cluster_ctarank();
+  const int pair = blockIdx.x >> 1;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < stages; i++) {
+      mbar_init(bar_full + 8u * i, 1);
+      mbar_init(bar_empty + 8u * i, 1);
+    }
+    for (int b = 0; b < 2; b++) {
+      mbar_init(bar_tfull + 8u * b, 1);
+      mbar_init(bar_tempty + 8u * b, 8);   // 4 epilogue warps x 2 CTAs
+    }
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    const uint32_t holder = smem_u32((const void*)tmem_holder);
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(holder), "r"(TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync();   // both CTAs' barriers are initialised before any remote arrive / multicast commit
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_holder;
+
+  int64_t lo, hi;
+  pair_range(p, pair, &lo, &hi);
+
+  if (warp == 0) {
+    // ============================== TMA producer (one thread per CTA)
+    if (lane == 0) {
+      prefetch_tmap(&tmR);
+      prefetch_tmap(&tmC);
+      const uint64_t pol_w = l2_policy_evict_first();
+      const uint64_t pol_a = l2_policy_evict_last();
+      const uint64_t pol_r = p.swap ? pol_w : pol_a;
+      const uint64_t pol_c = p.swap ? pol_a : pol_w;
+      int stage = 0;
+      uint32_t phase = 0;
+      int64_t cur = lo;
+      Piece pc;
+      while (next_piece(p, cur, hi, &pc)) {
+        const int rt = pc.tile % p.row_tiles, ct = pc.tile / p.row_tiles;
+        const int row0 = rt * 2 * BM + (int)cta * BM;
+        const int col0 = ct * BN + (int)cta * (BN / 2);
+        for (int kb = pc.kb0; kb < pc.kb1; kb++) {
+          mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
+          const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES;
+          // the leader's barrier counts the bytes of BOTH CTAs (the peer's complete_tx may land first:
+          // the tx-count simply goes negative until the leader's expect_tx)
+          if (cta == 0) mbar_arrive_expect_tx(bar_full + 8u * stage, 2 * STAGE_BYTES);
+          tma_load_2d_2sm(dst, &tmR, bar_full + 8u * stage, kb * BK, row0, pol_r);
+          tma_load_2d_2sm(dst + R_BYTES, &tmC, bar_full + 8u * stage, kb * BK, col0, pol_c);
+          if (++stage == stages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ============================== MMA issuer: one thread of the LEADER CTA drives both tensor cores
+    if (cta == 0 && lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t tphase[2] = {0, 0};
+      int64_t cur = lo;
+      Piece pc;
+      int n = 0;
+      while (next_piece(p, cur, hi, &pc)) {
+        const int buf = n & 1;
+        mbar_wait(bar_tempty + 8u * buf, tphase[buf] ^ 1u);   // epilogues of both CTAs drained this buffer
+        tphase[buf] ^= 1u;
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + (uint32_t)(buf * BN);
+        for (int kb = pc.kb0; kb < pc.kb1; kb++) {
+          mbar_wait(bar_full + 8u * stage, phase);
+          tc_fence_after();
+          const uint32_t sa = base + (uint32_t)stage * STAGE_BYTES;
+          const uint64_t da = make_smem_desc(sa);
+          const uint64_t db = make_smem_desc(sa + R_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; k++)
+            tc_mma_f8_2sm(tmem_d, da + (uint64_t)(k * UMMA_K >> 4), db + (uint64_t)(k * UMMA_K >> 4), IDESC,
+                          (kb > pc.kb0 || k > 0) ? 1u : 0u);
+          tc_commit_2sm(bar_empty + 8u * stage);
+          if (++stage == stages) { stage = 0; phase ^= 1u; }
+        }
+        tc_commit_2sm(bar_tfull + 8u * buf);
+        n++;
+      }
+    }
+  } else {
+    // ============================== epilogue warps (4 per CTA, one TMEM lane quarter each)
+    const int wq = warp & 3;
+    const int et = (warp - 2) * 32 + lane;   // 0..127 among the epilogue threads
+    uint32_t tphase[2] = {0, 0};
+    int64_t cur = lo;
+    Piece pc;
+    int n = 0;
+    uint16_t* out16 = reinterpret_cast<uint16_t*>(p.out);
+    const uint16_t* bias16 = reinterpret_cast<const uint16_t*>(p.bias);
+    auto to_f32 = [&](uint16_t h) -> float {
+      if (p.out_bf16) return __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(&h));
+      return __half2float(*reinterpret_cast<const __half*>(&h));
+    };
+    auto from_f32 = [&](float f) -> uint16_t {
+      if (p.out_bf16) {
+        __nv_bfloat16 b = __float2bfloat16_rn(f);
+        return *reinterpret_cast<uint16_t*>(&b);
+      }
+      __half h = __float2half_rn(f);
+      return *reinterpret_cast<uint16_t*>(&h);
+    };
+    const float cs0 = p.c_scale_vec ? 0.f : p.c_scale[0];
+    bool store_pending = false;
+    while (next_piece(p, cur, hi, &pc)) {
+      const int buf = n & 1;
+      const int rt = pc.tile % p.row_tiles, ct = pc.tile / p.row_tiles;
+      const int row0 = rt * 2 * BM + (int)cta * BM;   // this CTA's first row
+      const int col0 = ct * BN;
+      mbar_wait(bar_tfull + 8u * buf, tphase[buf]);
+      tphase[buf] ^= 1u;
+      tc_fence_after();
+      const uint32_t tbase = tmem_base + (uint32_t)(buf * BN) + ((uint32_t)(wq * 32) << 16);
+      const int ncols = min(BN, p.C - col0);
+      const int nchunks = (ncols + 15) >> 4;
+      const int trow = wq * 32 + lane;        // row of this thread inside the CTA's 128
+      if (pc.kb0 > 0) {
+        // ---------- not the owner of this tile: publish the fp32 partial, then raise the flag
+        float* slot = p.ws_partials + ((size_t)(pair * 2 + cta) * (BN / 16) * BM) * 16;
+        for (int ch = 0; ch < nchunks; ch++) {
+          uint32_t v[16];
+          tc_ld16(tbase + (uint32_t)(ch << 4), v);
+          tc_wait_ld();
+          uint4* dst = reinterpret_cast<uint4*>(slot + ((size_t)ch * BM + trow) * 16);
+#pragma unroll
+          for (int j = 0; j < 4; j++) dst[j] = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_leader(bar_tempty + 8u * buf);   // TMEM buffer free for the next piece
+        __threadfence();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (et == 0) atomicAdd(p.ws_flags + 2 * pair, 1u);
+      } else {
+        // ---------- owner: accumulator (+ partials of the pairs that hold the rest of this tile)
+        const int r = row0 + trow;
+        const bool r_ok = r < p.R;
+        const float rs = p.r_scale_vec ? (r_ok ? p.r_scale[r] : 0.f) : p.r_scale[0];
+        float bias_r = 0.f;
+        if (p.swap && bias16 && r_ok) bias_r = to_f32(bias16[r]);
+        // pairs q > pair whose range starts inside this tile hold its remaining k-blocks
+        int q_end = pair + 1;
+        if (pc.kb1 < p.num_kb) {
+          const int64_t tile_end = (int64_t)(pc.tile + 1) * p.num_kb;
+          while (q_end < p.pairs) {
+            int64_t qlo, qhi;
+            pair_range(p, q_end, &qlo, &qhi);
+            if (qlo >= tile_end) break;
+            q_end++;
+          }
+          for (int q = pair + 1; q < q_end; q++) {
+            const uint32_t* f = p.ws_flags + 2 * q;
+            while (ld_acquire_gpu(f) < 2u) {
+            }
+          }
+        }
+        if (p.swap && p.tma_store) {
+          if (store_pending) {   // the previous tile's TMA store must have read the staging tile
+            if (et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+          }
+        }
+        for (int ch = 0; ch < nchunks; ch++) {
+          uint32_t v[16];
+          tc_ld16(tbase + (uint32_t)(ch << 4), v);
+          tc_wait_ld();
+          float acc[16];
+#pragma unroll
+          for (int j = 0; j < 16; j++) acc[j] = __uint_as_float(v[j]);
+          for (int q = pair + 1; q < q_end; q++) {
+            const float* slot = p.ws_partials + ((size_t)(q * 2 + cta) * (BN / 16) * BM) * 16;
+            const float4* src = reinterpret_cast<const float4*>(slot + ((size_t)ch * BM + trow) * 16);
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+              const float4 t = __ldcg(src + j);
+              acc[4 * j] += t.x; acc[4 * j + 1] += t.y; acc[4 * j + 2] += t.z; acc[4 * j + 3] += t.w;
+            }
+          }
+          if (ch == nchunks - 1) {   // all TMEM reads of this buffer are done
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_leader(bar_tempty + 8u * buf);
+          }
+          const int c0 = ch << 4;
+          if (p.swap) {
+            if (p.tma_store) {
+#pragma unroll
+              for (int j = 0; j < 16; j += 2) {
+                const int c = col0 + c0 + j;
+                const float cs_a = p.c_scale_vec ? (c < p.C ? p.c_scale[c] : 0.f) : cs0;
+                const float cs_b = p.c_scale_vec ? (c + 1 < p.C ? p.c_scale[c + 1] : 0.f) : cs0;
+                const float oa = cs_a * (rs * acc[j]) + bias_r;
+                const float ob = cs_b * (rs * acc[j + 1]) + bias_r;
+                const float send = (lane & 1) ? oa : ob;
+                const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
+                const float lo_ = (lane & 1) ? recv : oa;
+                const float hi_ = (lane & 1) ? ob : recv;
+                uint32_t packed;
+                if (p.out_bf16) {
+                  __nv_bfloat162 t = __floats2bfloat162_rn(lo_, hi_);
+                  packed = *reinterpret_cast<uint32_t*>(&t);
+                } else {
+                  __half2 t = __floats2half2_rn(lo_, hi_);
+                  packed = *reinterpret_cast<uint32_t*>(&t);
+                }
+                const int m_local = c0 + j + (lane & 1);
+                const uint32_t addr = staging + (uint32_t)m_local * (BM * 2) + (uint32_t)(wq * 32 + (lane & ~1)) * 2u;
+                asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(packed) : "memory");
+              }
+            } else if (r_ok) {
+#pragma unroll
+              for (int j = 0; j < 16; j++) {
+                const int c = col0 + c0 + j;
+                if (c < p.C) {
+                  const float cs = p.c_scale_vec ? p.c_scale[c] : cs0;
+                  out16[(int64_t)c * p.ldo + r] = from_f32(cs * (rs * acc[j]) + bias_r);
+                }
+              }
+            }
+          } else if (r_ok) {
+            uint16_t h[16];
+#pragma unroll
+            for (int j = 0; j < 16; j++) {
+              const int c = col0 + c0 + j;
+              float o = 0.f;
+              if (c < p.C) {
+                const float cs = p.c_scale_vec ? p.c_scale[c] : cs0;
+                o = rs * (cs * acc[j]);
+                if (bias16) o += to_f32(bias16[c]);
+              }
+              h[j] = from_f32(o);
+            }
+            uint16_t* dst = out16 + (int64_t)r * p.ldo + col0 + c0;
+            if (col0 + c0 + 16 <= p.C && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+              reinterpret_cast<uint4*>(dst)[0] = reinterpret_cast<const uint4*>(h)[0];
+              reinterpret_cast<uint4*>(dst)[1] = reinterpret_cast<const uint4*>(h)[1];
+            } else {
+              for (int j = 0; j < 16; j++)
+                if (col0 + c0 + j < p.C) dst[j] = h[j];
+            }
+          }
+        }
+        if (p.swap && p.tma_store) {
+          fence_proxy_async();
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (et == 0) {
+            asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];" ::"l"(&tmO),
+                         "r"(row0), "r"(col0), "r"(staging)
+                         : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+          store_pending = true;
+        }
+        // release the partial slots: the second of the pair's two CTAs to finish resets the flags
+        if (q_end > pair + 1) {
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          if (et == 0) {
+            for (int q = pair + 1; q < q_end; q++) {
+              if (atomicAdd(p.ws_flags + 2 * q + 1, 1u) == 1u) {
+                p.ws_flags[2 * q + 1] = 0u;
+                __threadfence();
+                p.ws_flags[2 * q] = 0u;
+              }
+            }
+          }
+        }
+      }
+      n++;
+    }
+    if (store_pending && et == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync();   // the peer may still multicast-commit into / arrive on this CTA's barriers
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+  }
+}
+
+constexpr size_t WS_FLAG_BYTES = 4096;
+
+template <int BN>
+static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, const CUtensorMap& tmO, Params& p,
+                  cudaStream_t stream) {
+  constexpr uint32_t STAGE_BYTES = BM * BK + (BN / 2) * BK;
+  constexpr uint32_t STAGING_BYTES = BN * BM * 2;
+  const int smem_max = max_smem_optin();
+  int stages = (smem_max - 1024 - 256 - 64 - (int)STAGING_BYTES) / (int)STAGE_BYTES;
+  if (stages > MAX_STAGES) stages = MAX_STAGES;
+  if (stages < 2) {
+    set_last_error("fp8_gemm_v3: not enough shared memory");
+    return B200_ERR_UNSUPPORTED;
+  }
+  p.stages = stages;
+  const int smem = stages * (int)STAGE_BYTES + (int)STAGING_BYTES + 16 * MAX_STAGES + 32 + 64 + 1024;
+  static int max_pairs = 0;
+  if (max_pairs == 0) {
+    B200_CUDA(cudaFuncSetAttribute(gemm_fp8_v3_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+    // every pair must be co-resident (the tile owner spins on the other pairs' partials)
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(sm_count() / 2 * 2);
+    cfg.blockDim = dim3(NTHREADS);
+    cfg.dynamicSmemBytes = smem;
+    int clusters = 0;
+    cudaError_t e = cudaOccupancyMaxActiveClusters(&clusters, gemm_fp8_v3_kernel<BN>, &cfg);
+    if (e != cudaSuccess || clusters <= 0) {
+      cudaGetLastError();
+      clusters = sm_count() / 2;
+    }
+    max_pairs = clusters < sm_count() / 2 ? clusters : sm_count() / 2;
+  }
+  p.pairs = max_pairs;
+  const int64_t units = (int64_t)p.row_tiles * p.col_tiles * p.num_kb;
+  if (units < p.pairs) p.pairs = (int)units;
+  gemm_fp8_v3_kernel<BN><<<p.pairs * 2, NTHREADS, smem, stream>>>(tmR, tmC, tmO, p);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+static int make_tmap_2d(CUtensorMap* tm, const void* base, int rows, int K, int64_t ld_bytes, int box_rows) {
+  uint64_t dims[2] = {(uint64_t)K, (uint64_t)rows};
+  uint64_t strides[1] = {(uint64_t)ld_bytes};
+  uint32_t box[2] = {(uint32_t)BK, (uint32_t)box_rows};
+  return encode_tensor_map(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, base, dims, strides, box,
+                           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+}
+
+}  // namespace gemm8v3
+}  // namespace b200
+
+extern "C" size_t b200_fp8_gemm_v3_workspace_bytes(void) {
+  // flags + one fp32 partial tile (2 CTAs x 128 rows x 256 cols) per CTA pair
+  const int pairs = b200::sm_count() > 0 ? b200::sm_count() / 2 : 74;
+  return b200::gemm8v3::WS_FLAG_BYTES + (size_t)pairs * 2 * 128 * 256 * sizeof(float);
+}
+
+extern "C" int b200_fp8_gemm_v3(void* out, const void* a, const void* b, const float* a_scale,
+                                const float* b_scale, const void* bias, int M, int N, int K, int64_t lda,
+                                int64_t ldb, int64_t ldo, int a_scale_per_row, int b_scale_per_col,
+                                int out_dtype, void* workspace, size_t workspace_bytes,
+                                b200_stream_t stream_) {
+  using namespace b200;
+  using namespace b200::gemm8v3;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  B200_CHECK(M >= 0 && N > 0 && K > 0, B200_ERR_INVALID, "cutlass_scaled_mm: bad sizes (%d,%d,%d)", M, N, K);
+  if (M == 0) return B200_OK;
+  B200_CHECK(out && a && b && a_scale && b_scale, B200_ERR_INVALID, "cutlass_scaled_mm: null pointer");
+  B200_CHECK(out_dtype == B200_BF16 || out_dtype == B200_F16, B200_ERR_INVALID,
+             "cutlass_scaled_mm: out dtype must be bf16 or f16");
+  B200_CHECK(lda % 16 == 0 && ldb % 16 == 0 && K % 16 == 0, B200_ERR_INVALID,
+             "cutlass_scaled_mm: K and the row strides of a / b must be multiples of 16 (got K=%d lda=%lld ldb=%lld)",
+             K, (long long)lda, (long long)ldb);
+  B200_CHECK(((uintptr_t)a & 15) == 0 && ((uintptr_t)b & 15) == 0, B200_ERR_INVALID,
+             "cutlass_scaled_mm: a / b must be 16-byte aligned");
+  B200_CHECK(sm_count() > 0, B200_ERR_CUDA, "cutlass_scaled_mm: no CUDA device (no CPU fallback)");
+  B200_CHECK(workspace && ((uintptr_t)workspace & 255) == 0 && workspace_bytes >= b200_fp8_gemm_v3_workspace_bytes(),
+             B200_ERR_WORKSPACE, "cutlass_scaled_mm: workspace of %zu bytes (256-byte aligned, zero-initialised) required",
+             b200_fp8_gemm_v3_workspace_bytes());
+  Params p;
+  memset(&p, 0, sizeof(p));
+  p.out = out;
+  p.bias = bias;
+  p.K = K;
+  p.ldo = ldo;
+  p.out_bf16 = out_dtype == B200_BF16;
+  p.ws_flags = reinterpret_cast<uint32_t*>(workspace);
+  p.ws_partials = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + WS_FLAG_BYTES);
+  p.num_kb = (K + BK - 1) / BK;
+  const bool swap = M <= 256;
+  p.swap = swap ? 1 : 0;
+  CUtensorMap tmR, tmC, tmO;
+  memset(&tmO, 0, sizeof(tmO));
+  int rc, bn;
+  if (swap) {
+    bn = M <= 64 ? 64 : M <= 128 ? 128 : 256;
+    p.R = N; p.C = M;
+    p.r_scale = b_scale; p.r_scale_vec = b_scale_per_col;
+    p.c_scale = a_scale; p.c_scale_vec = a_scale_per_row;
+    rc = make_tmap_2d(&tmR, b, N, K, ldb, BM);
+    if (rc) return rc;
+    rc = make_tmap_2d(&tmC, a, M, K, lda, bn / 2);
+    if (rc) return rc;
+    if (((uintptr_t)out & 15) == 0 && (ldo * 2) % 16 == 0) {
+      uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
+      uint64_t strides[1] = {(uint64_t)ldo * 2};
+      uint32_t box[2] = {(uint32_t)BM, (uint32_t)bn};
+      rc = encode_tensor_map(&tmO, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, out, dims, strides, box,
+                             CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE);
+      if (rc) return rc;
+      p.tma_store = 1;
+    }
+  } else {
+    bn = 256;
+    p.R = M; p.C = N;
+    p.r_scale = a_scale; p.r_scale_vec = a_scale_per_row;
+    p.c_scale = b_scale; p.c_scale_vec = b_scale_per_col;
+    rc = make_tmap_2d(&tmR, a, M, K, lda, BM);
+    if (rc) return rc;
+    rc = make_tmap_2d(&tmC, b, N, K, ldb, bn / 2);
+    if (rc) return rc;
+  }
+  p.row_tiles = (p.R + 2 * BM - 1) / (2 * BM);
+  p.col_tiles = (p.C + bn - 1) / bn;
+  switch (bn) {
+    case 64: return launch<64>(tmR, tmC, tmO, p, stream);
+    case 128: return launch<128>(tmR, tmC, tmO, p, stream);
+    default: return launch<256>(tmR, tmC, tmO, p, stream);
+  }
+}
