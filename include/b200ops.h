@@ -179,6 +179,20 @@ B200_API int b200_fp8_gemm(void* out, const void* a, const void* b, const float*
                            int64_t ldb, int64_t ldo, int a_scale_per_row, int b_scale_per_col,
                            int out_dtype, b200_stream_t stream);
 
+/* gate_up GEMM + silu_and_mul + static FP8 quant in ONE kernel, decode batches (M <= 256).
+ * Replaces the sequence cutlass_scaled_mm (gate_up_proj) -> torch.ops._C.silu_and_mul_quant
+ * (csrc/libtorch_stable/quantization/activation_kernels.cu:33-104; the reference fuses the activation
+ * and the quantisation, this also folds them into the GEMM epilogue) and is bit-identical to that pair.
+ * w_gate_up: e4m3 [2*inter, K] row-major (gate rows then up rows, MergedColumnParallelLinear order),
+ * a: e4m3 [M, K]; scales as b200_fp8_gemm (w_scale per-tensor or per-row [2*inter]); bias [2*inter] in
+ * act_dtype or NULL; quant_scale: device float[1] of the next GEMM's static input scale;
+ * out8: e4m3 [M, inter], row stride ldo bytes. inter % 128 == 0. */
+B200_API int b200_fp8_gemm_silu_mul_fp8(void* out8, const void* a, const void* w_gate_up, const float* a_scale,
+                                        const float* w_scale, const void* bias, const float* quant_scale,
+                                        int M, int inter, int K, int64_t lda, int64_t ldw, int64_t ldo,
+                                        int a_scale_per_row, int w_scale_per_row, int act_dtype,
+                                        b200_stream_t stream);
+
 /* Same contract as b200_fp8_gemm, third-generation kernel (persistent CTA pairs with
  * tcgen05.mma.cta_group::2, stream-K split of the (tile, k-block) space, double-buffered TMEM).
  * Needs a caller-owned, 256-byte aligned workspace of b200_fp8_gemm_v3_workspace_bytes() bytes that was

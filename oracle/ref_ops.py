@@ -320,12 +320,13 @@ def silu_and_mul_quant(x: torch.Tensor, scale: torch.Tensor) -> np.ndarray:
 # RMSNorm family.  csrc/libtorch_stable/layernorm_kernels.cu, layernorm_quant_kernels.cu:21-156
 # --------------------------------------------------------------------------------------------
 def rms_norm(x: torch.Tensor, weight: torch.Tensor, eps: float, residual: torch.Tensor | None = None):
-    """Returns (out, new_residual). z = T(x + r); out = T(T(z * rsqrt(mean(z^2)+eps)) * w)."""
+    """Returns (out, new_residual). z = T(x + r); out = T(z * rsqrt(mean(z^2)+eps) * w): fp32 product,
+    ONE rounding (layernorm_kernels.cu:93 / :163 `static_cast<scalar_t>(x * s_variance * w)`)."""
     if residual is not None:
         x = (x.float() + residual.float()).to(x.dtype)
     xf = x.float()
     s = torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + eps)
-    out = ((xf * s).to(x.dtype).float() * weight.float()).to(x.dtype)
+    out = (xf * s * weight.float()).to(x.dtype)
     return out, x
 
 

@@ -133,3 +133,40 @@ def test_silu_and_mul_quant(tokens, d):
     assert (got == ref).mean() > 0.999
     d1 = ref_ops.e4m3_bits_to_f32(got) - ref_ops.e4m3_bits_to_f32(ref)
     assert np.abs(d1).max() <= 32.0  # never more than one fp8 step (largest step = 32 at 256..448)
+
+
+@pytest.mark.parametrize("M,I,K", [(256, 14336, 4096), (1, 256, 128), (33, 1792, 512), (128, 3584, 8192),
+                                   (200, 128, 496), (64, 4864 // 128 * 128, 896)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("per_token,per_channel,use_bias", [(False, False, False), (True, True, True)])
+def test_scaled_mm_silu_and_mul_quant_equals_unfused(M, I, K, dtype, per_token, per_channel, use_bias):
+    """gate_up GEMM + silu_and_mul + FP8 quant in one kernel == cutlass_scaled_mm -> silu_and_mul_quant,
+    BIT for bit (both halves of the pair are oracle-checked above)."""
+    g = torch.Generator().manual_seed(M + I)
+    a8 = to_fp8_bits(torch.randn(M, K, generator=g)).to(DEV).view(torch.float8_e4m3fn)
+    w8 = to_fp8_bits(torch.randn(2 * I, K, generator=g)).to(DEV).view(torch.float8_e4m3fn)
+    sa = ((torch.rand(M if per_token else 1, generator=g) + 0.5) * 0.03).to(DEV)
+    sb = ((torch.rand(2 * I if per_channel else 1, generator=g) + 0.5) * 0.03).to(DEV)
+    bias = (torch.rand(2 * I, generator=g) - 0.5).to(dtype).to(DEV) if use_bias else None
+    qs = torch.tensor([0.05], device=DEV)
+    ops = _ops()
+    gu = ops.cutlass_scaled_mm(a8, w8.t(), sa.view(-1, 1) if per_token else sa, sb.view(-1, 1) if per_channel else sb,
+                               dtype, bias, impl="v2")
+    ref = torch.empty(M, I, dtype=torch.float8_e4m3fn, device=DEV)
+    ops.silu_and_mul_quant(ref, gu, qs)
+    out = torch.full((M, I), 0x7F, dtype=torch.uint8, device=DEV).view(torch.float8_e4m3fn)
+    ops.scaled_mm_silu_and_mul_quant(out, a8, w8, sa, sb, qs, dtype, bias)
+    torch.cuda.synchronize()
+    assert torch.equal(out.view(torch.uint8).cpu(), ref.view(torch.uint8).cpu())
+
+
+def test_scaled_mm_silu_and_mul_quant_validation():
+    ops = _ops()
+    one = torch.ones(1, device=DEV)
+    a = torch.zeros(300, 128, dtype=torch.uint8, device=DEV).view(torch.float8_e4m3fn)
+    w = torch.zeros(256, 128, dtype=torch.uint8, device=DEV).view(torch.float8_e4m3fn)
+    with pytest.raises(NotImplementedError, match="M <= 256"):
+        ops.scaled_mm_silu_and_mul_quant(torch.empty(300, 128, dtype=torch.float8_e4m3fn, device=DEV), a, w, one, one, one)
+    w2 = torch.zeros(192, 128, dtype=torch.uint8, device=DEV).view(torch.float8_e4m3fn)
+    with pytest.raises(NotImplementedError, match="multiple of 128"):
+        ops.scaled_mm_silu_and_mul_quant(torch.empty(8, 96, dtype=torch.float8_e4m3fn, device=DEV), a[:8], w2, one, one, one)

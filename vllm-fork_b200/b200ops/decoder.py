@@ -153,6 +153,11 @@ class DecoderModel:
                 self.row_lo, self.row_hi = lo, hi
                 self.res_shard = torch.zeros((S + tp_size - 1) // tp_size, H, dtype=torch.bfloat16, device=self.dev)
         self.gu = torch.empty(S, 2 * self.inter, dtype=torch.bfloat16, device=self.dev)
+        # gate_up GEMM + silu_and_mul + FP8 quant in one kernel. Measured (gpurun_out/bench4.json): at
+        # batch 256 the GEMM is tensor-bound and the fused epilogue (silu on 4 warps of 112 CTAs, not
+        # overlapped) costs more than the separate full-GPU activation kernel: 16.55 vs 15.95 ms/step.
+        # It pays only while the GEMM is a weight stream (small batches).
+        self.fuse_gate_up = max_seqs <= 64 and self.inter % 128 == 0
         self.attn_hook = None  # bench instrumentation: called around the attention launch
         self.graph = None
 
@@ -219,8 +224,12 @@ class DecoderModel:
                 n += 1 if self.ar is not None else 0
                 ops.fused_add_rms_norm_static_fp8_quant(x8, red, self.residual, L["post_norm"],
                                                         L["a_gu"], s.eps); n += 1
-            ops.cutlass_scaled_mm(x8, L["wgu"].t(), L["a_gu"], L["wgu_s"], torch.bfloat16, out=self.gu); n += 1
-            ops.silu_and_mul_quant(self.h8, self.gu, L["a_d"]); n += LAUNCHES["silu_quant"]
+            if self.fuse_gate_up:
+                ops.scaled_mm_silu_and_mul_quant(self.h8, x8, L["wgu"], L["a_gu"], L["wgu_s"], L["a_d"],
+                                                 torch.bfloat16); n += 1
+            else:
+                ops.cutlass_scaled_mm(x8, L["wgu"].t(), L["a_gu"], L["wgu_s"], torch.bfloat16, out=self.gu); n += 1
+                ops.silu_and_mul_quant(self.h8, self.gu, L["a_d"]); n += LAUNCHES["silu_quant"]
             ops.cutlass_scaled_mm(self.h8, L["wd"].t(), L["a_d"], L["wd_s"], torch.bfloat16, out=pb); n += 1
             if not fused:
                 red = self._all_reduce(pb)

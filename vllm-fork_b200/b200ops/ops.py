@@ -338,6 +338,31 @@ def cutlass_scaled_mm(
     return out.view(*target_shape)
 
 
+def scaled_mm_silu_and_mul_quant(result: torch.Tensor, a: torch.Tensor, w_gate_up: torch.Tensor,
+                                 scale_a: torch.Tensor, scale_w: torch.Tensor, quant_scale: torch.Tensor,
+                                 act_dtype: torch.dtype = torch.bfloat16, bias: torch.Tensor | None = None) -> None:
+    """result (e4m3 [M, I]) = silu_and_mul_quant(cutlass_scaled_mm(a, w_gate_up.t(), ...).to(act_dtype), quant_scale)
+    in one kernel (decode batches, M <= 256; bit-identical to the unfused pair).
+    a e4m3 [M, K]; w_gate_up e4m3 [2I, K] row-major (gate rows, then up rows)."""
+    _cuda(result, a, w_gate_up, scale_a, scale_w, quant_scale, bias)
+    M, K = a.shape
+    I2, Kw = w_gate_up.shape
+    if Kw != K or I2 % 2 or a.element_size() != 1 or w_gate_up.element_size() != 1:
+        raise RuntimeError("scaled_mm_silu_and_mul_quant: a [M,K] and w_gate_up [2I,K] must be fp8 with equal K")
+    I = I2 // 2
+    if tuple(result.shape) != (M, I) or result.element_size() != 1 or result.stride(1) != 1:
+        raise RuntimeError("scaled_mm_silu_and_mul_quant: result must be fp8 [M, I]")
+    if a.stride(1) != 1 or w_gate_up.stride(1) != 1:
+        raise RuntimeError("scaled_mm_silu_and_mul_quant: a and w_gate_up must be row-major")
+    if scale_a.numel() not in (1, M) or scale_w.numel() not in (1, I2):
+        raise RuntimeError("scaled_mm_silu_and_mul_quant: scale_a must have 1 or M elements, scale_w 1 or 2I")
+    rc = _lib.load().b200_fp8_gemm_silu_mul_fp8(
+        _p(result), _p(a), _p(w_gate_up), _p(scale_a), _p(scale_w), _p(bias), _p(quant_scale), M, I, K,
+        a.stride(0), w_gate_up.stride(0), result.stride(0), 1 if scale_a.numel() > 1 else 0,
+        1 if scale_w.numel() > 1 else 0, BF16 if act_dtype is torch.bfloat16 else F16, _stream())
+    _lib.check(rc, "scaled_mm_silu_and_mul_quant")
+
+
 # ------------------------------------------------------------------------------------------------
 # Gated activation                      reference: torch.ops._C.silu_and_mul / silu_and_mul_quant
 # ------------------------------------------------------------------------------------------------

@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(256, 1)
           T* re = reinterpret_cast<T*>(&rr);
 #pragma unroll
           for (int j = 0; j < NP; j++)
-            re[j] = Cvt<T>::from_f32(Cvt<T>::to_f32(Cvt<T>::from_f32(Cvt<T>::to_f32(xe[j]) * s)) * Cvt<T>::to_f32(we[j]));
+            re[j] = Cvt<T>::from_f32(Cvt<T>::to_f32(xe[j]) * s * Cvt<T>::to_f32(we[j]));
           const int64_t off = ((int64_t)row * fp.hidden + (int64_t)v * NP) * sizeof(T);
 #pragma unroll
           for (int r = 0; r < N; r++) *reinterpret_cast<uint4*>(fp.out[(rank + r) % N] + off) = rr;

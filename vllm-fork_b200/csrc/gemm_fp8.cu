@@ -42,18 +42,37 @@ struct Params {
   int out_bf16;
   int stages;
   int tma_store;         // swap mode: stage the tile in smem and write it with one TMA store
+  // GATED kernel only (gate_up GEMM + silu_and_mul + static FP8 quant): rows r and gate_rows + r of
+  // the weight are the gate / up rows of output column r
+  int gate_rows;
+  const float* quant_scale;
 };
 
 using namespace b200::tc;
 
-template <int BN>
+// silu(x) * y with the roundings of the unfused pair (activation.cu silu_mul_rounded)
+template <bool BF16>
+__device__ __forceinline__ float gated_act(float g, float u) {
+  if constexpr (BF16) {
+    const float gf = __bfloat162float(__float2bfloat16_rn(g)), uf = __bfloat162float(__float2bfloat16_rn(u));
+    const float s = __bfloat162float(__float2bfloat16_rn(__fdiv_rn(gf, 1.0f + expf(-gf))));
+    return __bfloat162float(__float2bfloat16_rn(s * uf));
+  } else {
+    const float gf = __half2float(__float2half_rn(g)), uf = __half2float(__float2half_rn(u));
+    const float s = __half2float(__float2half_rn(__fdiv_rn(gf, 1.0f + expf(-gf))));
+    return __half2float(__float2half_rn(s * uf));
+  }
+}
+
+template <int BN, bool GATED = false>
 __global__ void __launch_bounds__(NTHREADS, 1)
     gemm_fp8_kernel(const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmC,
                     const __grid_constant__ CUtensorMap tmO, const Params p) {
-  constexpr uint32_t R_BYTES = BM * BK;
+  constexpr uint32_t R_BYTES = (GATED ? 2 : 1) * BM * BK;   // GATED: gate slab then up slab
   constexpr uint32_t C_BYTES = BN * BK;
   constexpr uint32_t STAGE_BYTES = R_BYTES + C_BYTES;
-  constexpr uint32_t TMEM_COLS = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
+  constexpr uint32_t ACC_COLS = (GATED ? 2 : 1) * BN;
+  constexpr uint32_t TMEM_COLS = ACC_COLS <= 32 ? 32 : ACC_COLS <= 64 ? 64 : ACC_COLS <= 128 ? 128 : ACC_COLS <= 256 ? 256 : 512;
   // instruction descriptor: D = F32, A = B = E4M3, both K-major, N = BN, M = 128
   constexpr uint32_t IDESC = (1u << 4) | (0u << 7) | (0u << 10) | ((uint32_t)(BN >> 3) << 17) |
                              ((uint32_t)(BM >> 4) << 24);
@@ -112,6 +131,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
         const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES;
         mbar_arrive_expect_tx(bar_full + 8u * stage, STAGE_BYTES);
         tma_load_2d(dst, &tmR, bar_full + 8u * stage, kb * BK, row0, pol_r);
+        if constexpr (GATED) tma_load_2d(dst + BM * BK, &tmR, bar_full + 8u * stage, kb * BK, p.gate_rows + row0, pol_r);
         tma_load_2d(dst + R_BYTES, &tmC, bar_full + 8u * stage, kb * BK, col0, pol_c);
         if (++stage == stages) { stage = 0; phase ^= 1u; }
       }
@@ -132,6 +152,13 @@ __global__ void __launch_bounds__(NTHREADS, 1)
           // advance the start address by k * 32 bytes inside the 128-byte swizzle row
           tc_mma_f8(tmem_d, da + (uint64_t)(k * UMMA_K >> 4), db + (uint64_t)(k * UMMA_K >> 4), IDESC,
                     (kb > 0 || k > 0) ? 1u : 0u);
+        }
+        if constexpr (GATED) {   // the up slab against the same activation tile, second accumulator
+          const uint64_t du = make_smem_desc(sa + BM * BK);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; k++)
+            tc_mma_f8(tmem_d + BN, du + (uint64_t)(k * UMMA_K >> 4), db + (uint64_t)(k * UMMA_K >> 4), IDESC,
+                      (kb > 0 || k > 0) ? 1u : 0u);
         }
         tc_commit(bar_empty + 8u * stage);  // frees the smem slot when the MMAs have read it
         if (++stage == stages) { stage = 0; phase ^= 1u; }
@@ -166,6 +193,43 @@ __global__ void __launch_bounds__(NTHREADS, 1)
     const int ncols = min(BN, p.C - col0);
     const int nchunks = (ncols + 15) >> 4;
     const uint32_t tbase = tmem_d + ((uint32_t)(wq * 32) << 16);
+    if constexpr (GATED) {
+      // out8[m][r] = e4m3(clamp(act(gate, up) * (1 / quant_scale))) where gate / up are the GEMM outputs
+      // rounded to the 16-bit activation dtype exactly like the unfused cutlass_scaled_mm ->
+      // silu_and_mul_quant pair. rows = intermediate index r (TMEM lane), cols = batch index m.
+      const float rs_u = p.r_scale_vec ? (r_ok ? p.r_scale[p.gate_rows + r] : 0.f) : rs;
+      float bias_u = 0.f;
+      if (bias16 && r_ok) bias_u = to_f32(bias16[p.gate_rows + r]);
+      const float inv = __fdiv_rn(1.0f, *p.quant_scale);
+      const uint32_t stile = base;   // [BN m][128 r] bytes, written by one TMA store
+      uint8_t* out8 = reinterpret_cast<uint8_t*>(p.out);
+      for (int ch = 0; ch < nchunks; ch++) {
+        uint32_t g[16], u[16];
+        tc_ld16(tbase + (uint32_t)(ch << 4), g);
+        tc_ld16(tbase + (uint32_t)(BN + (ch << 4)), u);
+        tc_wait_ld();
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+          const int c = col0 + (ch << 4) + j;
+          const float cs = p.c_scale_vec ? (c < p.C ? p.c_scale[c] : 0.f) : cs0;
+          const float gv = cs * (rs * __uint_as_float(g[j])) + bias_r;
+          const float uv = cs * (rs_u * __uint_as_float(u[j])) + bias_u;
+          const float a = p.out_bf16 ? gated_act<true>(gv, uv) : gated_act<false>(gv, uv);
+          const uint8_t q = f32_to_e4m3(fmaxf(-448.f, fminf(__fmul_rn(a, inv), 448.f)));
+          if (p.tma_store) {
+            const uint32_t addr = stile + (uint32_t)((ch << 4) + j) * BM + (uint32_t)(wq * 32 + lane);
+            asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"((uint32_t)q) : "memory");
+          } else if (r_ok && c < p.C) {
+            out8[(int64_t)c * p.ldo + r] = q;
+          }
+        }
+      }
+      if (p.tma_store) {
+        fence_proxy_async();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (warp == 2 && lane == 0) tma_store_2d(&tmO, stile, row0, col0);
+      }
+    } else {
     uint32_t v0[16], v1[16];
     tc_ld16(tbase, v0);
     if (p.swap && p.tma_store) {
@@ -268,6 +332,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
         }
       }
     }
+    }  // !GATED
   }
   tc_fence_before();
   __syncthreads();
@@ -278,10 +343,10 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   }
 }
 
-template <int BN>
+template <int BN, bool GATED = false>
 static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, const CUtensorMap& tmO, Params& p, dim3 grid,
                   cudaStream_t stream) {
-  constexpr uint32_t STAGE_BYTES = BM * BK + BN * BK;
+  constexpr uint32_t STAGE_BYTES = (GATED ? 2 : 1) * BM * BK + BN * BK;
   const int smem_max = max_smem_optin();
   int stages = (smem_max - 1024 - 256 - 64) / (int)STAGE_BYTES;
   if (stages > MAX_STAGES) stages = MAX_STAGES;
@@ -293,11 +358,11 @@ static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, const CUtensor
   const int smem = stages * (int)STAGE_BYTES + 16 * MAX_STAGES + 64 + 1024;
   static bool configured = false;
   if (!configured) {
-    B200_CUDA(cudaFuncSetAttribute(gemm_fp8_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    B200_CUDA(cudaFuncSetAttribute(gemm_fp8_kernel<BN, GATED>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    smem_max));
     configured = true;
   }
-  gemm_fp8_kernel<BN><<<grid, NTHREADS, smem, stream>>>(tmR, tmC, tmO, p);
+  gemm_fp8_kernel<BN, GATED><<<grid, NTHREADS, smem, stream>>>(tmR, tmC, tmO, p);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
@@ -335,6 +400,7 @@ extern "C" int b200_fp8_gemm(void* out, const void* a, const void* b, const floa
              "cutlass_scaled_mm: a / b must be 16-byte aligned");
   B200_CHECK(sm_count() > 0, B200_ERR_CUDA, "cutlass_scaled_mm: no CUDA device (no CPU fallback)");
   Params p;
+  memset(&p, 0, sizeof(p));
   p.out = out;
   p.bias = bias;
   p.K = K;
@@ -402,5 +468,72 @@ extern "C" int b200_fp8_gemm(void* out, const void* a, const void* b, const floa
     case 64: return launch<64>(tmR, tmC, tmO, p, grid, stream);
     case 128: return launch<128>(tmR, tmC, tmO, p, grid, stream);
     default: return launch<256>(tmR, tmC, tmO, p, grid, stream);
+  }
+}
+
+
+// gate_up GEMM + silu_and_mul + static FP8 quant in one kernel (decode batches, M <= 256):
+//   h8[m, i] = e4m3(clamp(T(T(silu(g)) * u) * (1 / *quant_scale))),  g = T(a_s * (b_s * A.Wg^T) + bias_g),
+//   u likewise with the up rows; T = act_dtype (bf16 / f16). Bit-identical to cutlass_scaled_mm followed by
+//   silu_and_mul_quant (csrc/libtorch_stable/quantization/activation_kernels.cu:33-104), without the
+//   [M, 2I] 16-bit round trip through HBM.
+extern "C" int b200_fp8_gemm_silu_mul_fp8(void* out8, const void* a, const void* w_gate_up, const float* a_scale,
+                                          const float* w_scale, const void* bias, const float* quant_scale,
+                                          int M, int inter, int K, int64_t lda, int64_t ldw, int64_t ldo,
+                                          int a_scale_per_row, int w_scale_per_row, int act_dtype,
+                                          b200_stream_t stream_) {
+  using namespace b200;
+  using namespace b200::gemm8;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  B200_CHECK(M >= 0 && inter > 0 && K > 0, B200_ERR_INVALID, "fp8_gemm_silu_mul_fp8: bad sizes (%d,%d,%d)", M, inter, K);
+  if (M == 0) return B200_OK;
+  B200_CHECK(M <= 256, B200_ERR_UNSUPPORTED,
+             "fp8_gemm_silu_mul_fp8: fused kernel covers decode batches (M <= 256); use the unfused pair above");
+  B200_CHECK(inter % BM == 0, B200_ERR_UNSUPPORTED,
+             "fp8_gemm_silu_mul_fp8: intermediate size %d must be a multiple of 128", inter);
+  B200_CHECK(out8 && a && w_gate_up && a_scale && w_scale && quant_scale, B200_ERR_INVALID,
+             "fp8_gemm_silu_mul_fp8: null pointer");
+  B200_CHECK(act_dtype == B200_BF16 || act_dtype == B200_F16, B200_ERR_INVALID,
+             "fp8_gemm_silu_mul_fp8: activation dtype must be bf16 or f16");
+  B200_CHECK(lda % 16 == 0 && ldw % 16 == 0 && K % 16 == 0, B200_ERR_INVALID,
+             "fp8_gemm_silu_mul_fp8: K and the row strides of a / w must be multiples of 16");
+  B200_CHECK(((uintptr_t)a & 15) == 0 && ((uintptr_t)w_gate_up & 15) == 0, B200_ERR_INVALID,
+             "fp8_gemm_silu_mul_fp8: a / w must be 16-byte aligned");
+  B200_CHECK(sm_count() > 0, B200_ERR_CUDA, "fp8_gemm_silu_mul_fp8: no CUDA device (no CPU fallback)");
+  Params p;
+  memset(&p, 0, sizeof(p));
+  p.out = out8;
+  p.bias = bias;
+  p.K = K;
+  p.ldo = ldo;
+  p.out_bf16 = act_dtype == B200_BF16;
+  p.swap = 1;
+  p.gate_rows = inter;
+  p.quant_scale = quant_scale;
+  p.R = inter; p.C = M;
+  p.r_scale = w_scale; p.r_scale_vec = w_scale_per_row;
+  p.c_scale = a_scale; p.c_scale_vec = a_scale_per_row;
+  const int bn = M <= 32 ? 32 : M <= 64 ? 64 : M <= 128 ? 128 : 256;
+  CUtensorMap tmR, tmC, tmO;
+  memset(&tmO, 0, sizeof(tmO));
+  int rc = make_tmap_2d(&tmR, w_gate_up, 2 * inter, K, ldw, BM);
+  if (rc) return rc;
+  rc = make_tmap_2d(&tmC, a, M, K, lda, bn);
+  if (rc) return rc;
+  if (((uintptr_t)out8 & 15) == 0 && ldo % 16 == 0) {
+    uint64_t dims[2] = {(uint64_t)inter, (uint64_t)M};
+    uint64_t strides[1] = {(uint64_t)ldo};
+    uint32_t box[2] = {(uint32_t)BM, (uint32_t)bn};
+    rc = encode_tensor_map(&tmO, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, out8, dims, strides, box,
+                           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE);
+    if (rc) return rc;
+    p.tma_store = 1;
+  }
+  dim3 grid(inter / BM, 1);
+  switch (bn) {
+    case 32: return launch<32, true>(tmR, tmC, tmO, p, grid, stream);
+    case 64: return launch<64, true>(tmR, tmC, tmO, p, grid, stream);
+    case 128: return launch<128, true>(tmR, tmC, tmO, p, grid, stream);
+    default: return launch<256, true>(tmR, tmC, tmO, p, grid, stream);
   }
 }

@@ -2,7 +2,7 @@
 // RMSNorm (+ residual add) fused with the static FP8 quantisation of the next GEMM input, and RoPE.
 //
 // Contracts (reference, csrc/libtorch_stable):
-//   rms_norm                              layernorm_kernels.cu         out = T(x * rsqrt(mean(x^2)+eps)) * w
+//   rms_norm                              layernorm_kernels.cu:93      out = T(x * rsqrt(mean(x^2)+eps) * w)  (fp32, one rounding)
 //   fused_add_rms_norm                    layernorm_kernels.cu         z = T(x + r); r = z; x = norm(z)
 //   rms_norm_static_fp8_quant             layernorm_quant_kernels.cu:21-75
 //        out8 = e4m3(clamp(float(T(x * s * w)) * (1/scale)))          (rounded through T first)
@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(256)
         T* re = reinterpret_cast<T*>(&r);
 #pragma unroll
         for (int j = 0; j < N; j++)
-          re[j] = Cvt<T>::from_f32(Cvt<T>::to_f32(Cvt<T>::from_f32(Cvt<T>::to_f32(xe[j]) * s)) * Cvt<T>::to_f32(we[j]));
+          re[j] = Cvt<T>::from_f32(Cvt<T>::to_f32(xe[j]) * s * Cvt<T>::to_f32(we[j]));  // one rounding (layernorm_kernels.cu:93,163)
         *reinterpret_cast<uint4*>(reinterpret_cast<T*>(out) + row * out_stride + v * N) = r;
       }
     }
