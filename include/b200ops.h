@@ -158,6 +158,10 @@ typedef struct b200_paged_attn_args {
   int32_t sliding_window; /* <= 0: none */
   float scale;
   float softcap; /* <= 0: none */
+  /* nullable. When set, `out` is e4m3 (1 byte / element, strides in elements) and holds
+   * e4m3(clamp(attention * (1 / *output_scale))): the fused static FP8 output the reference kernels
+   * offer through `output_scale` (backend.py:895-934, triton_unified_attention.py out_scale_inv). */
+  const float* output_scale;
 } b200_paged_attn_args;
 
 B200_API size_t b200_paged_attention_workspace_bytes(int num_seqs, int num_heads, int num_kv_heads,

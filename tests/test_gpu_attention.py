@@ -245,3 +245,37 @@ def test_decode_full_size_properties():
                                              torch.tensor([L], dtype=torch.int32), D ** -0.5,
                                              k_scale=ks.cpu(), v_scale=vs.cpu())
         np.testing.assert_allclose(out[s:s + 1].float().cpu().numpy(), ref, atol=ATOL, rtol=RTOL)
+
+
+@pytest.mark.parametrize("heads,D", [((32, 8), 128), ((14, 2), 64), ((16, 1), 128), ((8, 8), 256)])
+@pytest.mark.parametrize("kv_fp8", [False, True])
+def test_fused_fp8_output(heads, D, kv_fp8):
+    """output_scale: the kernel writes e4m3(attention / scale) itself (AttentionImpl.forward's fused FP8
+    output, backend.py:895-934; triton_unified_attention.py multiplies the fp32 accumulator by 1/scale
+    and clamps). Both write paths are exercised: sequences owned by one CTA and split sequences (reduce
+    kernel), plus an empty sequence. Bound: the decoded value is within the attention tolerance plus
+    one e4m3 rounding step of the oracle."""
+    Hq, Hkv = heads
+    lens = [4096, 1, 700, 0, 33, 2049, 512, 17]
+    c = build_case(lens, Hq, Hkv, D, 16, torch.bfloat16, kv_fp8, seed=11)
+    scale = D ** -0.5
+    ref = ref_ops.paged_attention_decode(c["q"], c["kc"], c["vc"], c["bt"], c["lens"], scale,
+                                         k_scale=c["ks"], v_scale=c["vs"])
+    oscale = torch.tensor([float(np.abs(ref).max()) / 200.0])
+    raw, kc, vc = to_dev_views(c)
+    out = torch.full((len(lens), Hq, D), 0x7F, dtype=torch.uint8, device=DEV).view(torch.float8_e4m3fn)
+    dev = lambda t: None if t is None else t.to(DEV)
+    _ops().paged_attention_decode(out, c["q"].to(DEV), kc, vc, c["bt"].to(DEV), c["lens"].to(DEV), scale,
+                                  k_scale=dev(c["ks"]), v_scale=dev(c["vs"]), output_scale=oscale.to(DEV))
+    torch.cuda.synchronize()
+    got_bits = out.view(torch.uint8).cpu().numpy()
+    assert not (got_bits == 0x7F).any() and not (got_bits == 0xFF).any()      # every byte written, no NaN
+    got = ref_ops.e4m3_bits_to_f32(got_bits) * oscale.item()
+    # e4m3 has 3 mantissa bits: half a step = 2^-4 relative; plus the attention tolerance
+    tol = ATOL + RTOL * np.abs(ref) + 2.0 ** -4 * np.abs(ref) + oscale.item() * 2.0 ** -10
+    assert (np.abs(got - ref) <= tol).all(), np.abs(got - ref).max()
+    assert (got_bits[3] == 0).all()                                           # empty sequence -> zeros
+    with pytest.raises(RuntimeError, match="fp8 exactly when output_scale"):
+        _ops().paged_attention_decode(torch.empty(len(lens), Hq, D, dtype=torch.bfloat16, device=DEV),
+                                      c["q"].to(DEV), kc, vc, c["bt"].to(DEV), c["lens"].to(DEV), scale,
+                                      k_scale=dev(c["ks"]), v_scale=dev(c["vs"]), output_scale=oscale.to(DEV))

@@ -57,6 +57,7 @@ class PagedAttnArgs(C.Structure):
         ("sliding_window", C.c_int32),
         ("scale", c_float),
         ("softcap", c_float),
+        ("output_scale", c_void_p),
     ]
 
 

@@ -144,8 +144,8 @@ class B200AttentionImpl(_ImplBase):
                 output: torch.Tensor | None = None, output_scale=None, output_block_scale=None,
                 lse: torch.Tensor | None = None) -> torch.Tensor:
         assert output is not None, "Output tensor must be provided."
-        if output_scale is not None or output_block_scale is not None:
-            raise NotImplementedError("fused output quantization is not supported by B200AttentionImpl")
+        if output_block_scale is not None:
+            raise NotImplementedError("fused block-scaled (NVFP4) output quantization is not supported by B200AttentionImpl")
         if attn_metadata is None:  # profiling run (triton_attn.py:610-612)
             return output.fill_(0)
         n = attn_metadata.num_actual_tokens
@@ -162,7 +162,7 @@ class B200AttentionImpl(_ImplBase):
             self.scale, k_scale=layer._k_scale if fp8 else None, v_scale=layer._v_scale if fp8 else None,
             alibi_slopes=self.alibi_slopes, sliding_window=self.sliding_window,
             softcap=self.logits_soft_cap, lse=lse, max_seq_len=attn_metadata.max_seq_len,
-            workspace=attn_metadata.workspace)
+            workspace=attn_metadata.workspace, output_scale=output_scale)
         return output
 
 

@@ -208,14 +208,15 @@ class DecoderModel:
             n += LAUNCHES["cache_write"]
             if self.attn_hook:
                 self.attn_hook(0)
-            ops.paged_attention_decode(self.attn_out, q, kc, vc, self.block_table, self.seq_lens,
+            # the attention kernel writes the statically quantised o_proj input itself (fused FP8 output)
+            ops.paged_attention_decode(a8.view(S, self.hq, D), q, kc, vc, self.block_table, self.seq_lens,
                                        D ** -0.5, k_scale=L["k_scale"] if self.kv_fp8 else None,
                                        v_scale=L["v_scale"] if self.kv_fp8 else None,
-                                       max_seq_len=self.max_ctx, workspace=self.workspace)
+                                       max_seq_len=self.max_ctx, workspace=self.workspace,
+                                       output_scale=L["a_o"])
             n += LAUNCHES["attention"]
             if self.attn_hook:
                 self.attn_hook(1)
-            ops.static_scaled_fp8_quant(a8, self.attn_out.view(S, self.hq * D), L["a_o"]); n += 1
             ops.cutlass_scaled_mm(a8, L["wo"].t(), L["a_o"], L["wo_s"], torch.bfloat16, out=pa); n += 1
             if fused:
                 self.ar.fused_add_rms_norm(x8, pa, self.res_shard, L["post_norm"], s.eps, L["a_gu"]); n += 1

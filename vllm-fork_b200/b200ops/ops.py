@@ -604,8 +604,11 @@ def paged_attention_decode(
     lse: torch.Tensor | None = None,
     max_seq_len: int = 0,
     workspace: torch.Tensor | None = None,
+    output_scale: torch.Tensor | None = None,
 ) -> torch.Tensor:
     """Decode attention over a paged KV cache.
+    output_scale (device f32 scalar): `out` is float8_e4m3fn and receives the statically quantised result
+    e4m3(attention / output_scale) - the fused FP8 output of AttentionImpl.forward (backend.py:895-934).
 
     query/out [S, Hq, D]; key_cache/value_cache [num_blocks, block_size, Hkv, D] views (any of the
     NHD / HND / split layouts - strides are forwarded); block_table int32 [S, max_blocks];
@@ -614,8 +617,10 @@ def paged_attention_decode(
     with query_len == 1.
     """
     _cuda(out, query, key_cache, value_cache, block_table, seq_lens, k_scale, v_scale,
-          alibi_slopes, lse, workspace)
+          alibi_slopes, lse, workspace, output_scale)
     lib = _lib.load()
+    if (output_scale is not None) != (out.element_size() == 1):
+        raise RuntimeError("paged_attention_decode: out must be fp8 exactly when output_scale is given")
     if query.dim() != 3 or key_cache.dim() != 4 or value_cache.dim() != 4:
         raise RuntimeError("paged_attention_decode: query must be 3-D and the caches 4-D")
     if query.stride(2) != 1 or out.stride(2) != 1 or key_cache.stride(3) != 1:
@@ -655,6 +660,7 @@ def paged_attention_decode(
     a.sliding_window = int(sliding_window) if sliding_window else 0
     a.scale = float(scale)
     a.softcap = float(softcap) if softcap else 0.0
+    a.output_scale = _p(output_scale)
     import ctypes
     rc = lib.b200_paged_attention_decode(ctypes.byref(a), _stream())
     _lib.check(rc, "paged_attention_decode")

@@ -48,6 +48,7 @@ struct Params {
   const int32_t* seq_lens;
   const float* k_scale;
   const float* v_scale;
+  const float* out_scale;   // nullable: fused static FP8 output
   const float* alibi;
   int32_t* cum;      // workspace: [S + 2] tile prefix sums (+ tiles-per-CTA at [S+1])
   float* part_acc;   // workspace: [n_cta * 2][hq_chunk][D]

@@ -203,6 +203,7 @@ extern "C" int b200_paged_attention_decode(const b200_paged_attn_args* a, b200_s
   p.k_scale = fp8 ? a->k_scale : nullptr;
   p.v_scale = fp8 ? a->v_scale : nullptr;
   p.alibi = a->alibi_slopes;
+  p.out_scale = a->output_scale;
   uint8_t* ws = reinterpret_cast<uint8_t*>(a->workspace);
   p.cum = reinterpret_cast<int32_t*>(ws);
   const int n_cta = pl.grid_x * pl.n_chunks;

@@ -495,7 +495,41 @@ __global__ void __launch_bounds__(NTHREADS, 1)
           if (gq >= g) continue;
           const int head = (h0 + hl) * g + gq;
           const float lsum = st.l[nt][a2];
-          if (whole) {
+          if (whole && p.out_scale) {
+            // fused static FP8 output: e4m3(clamp((acc / l * v_scale) * (1 / out_scale)))
+            const float inv = v_scale / lsum;
+            const float qinv = __fdiv_rn(1.0f, *p.out_scale);
+            uint8_t* op8 = reinterpret_cast<uint8_t*>(p.out) + (int64_t)s * p.out_stride_s +
+                           (int64_t)head * p.out_stride_h;
+            auto q2 = [&](float a, float b) -> uint16_t {
+              return f32x2_to_e4m3x2(fmaxf(-448.f, fminf(a * inv * qinv, 448.f)),
+                                     fmaxf(-448.f, fminf(b * inv * qinv, 448.f)));
+            };
+            if constexpr (G::VB >= 16) {
+#pragma unroll
+              for (int j = 0; j < G::NCV; j++) {
+                uint16_t w8[EPC / 2];
+#pragma unroll
+                for (int e = 0; e < EPC; e += 2) {
+                  const int i0 = j * EPC + e, i1 = i0 + 1;
+                  w8[e / 2] = q2(st.acc[nt][i0 >> 1][(i0 & 1) * 2 + a2], st.acc[nt][i1 >> 1][(i1 & 1) * 2 + a2]);
+                }
+                uint8_t* dst = op8 + (r + 8 * j) * EPC;
+#pragma unroll
+                for (int c = 0; c < EPC / 4; c++)
+                  *reinterpret_cast<uint32_t*>(dst + 4 * c) = (uint32_t)w8[2 * c] | ((uint32_t)w8[2 * c + 1] << 16);
+              }
+            } else {
+              constexpr int NE = 8 / ES;
+              uint8_t* dst = op8 + r * NE;
+#pragma unroll
+              for (int e = 0; e < NE; e += 2)
+                *reinterpret_cast<uint16_t*>(dst + e) =
+                    q2(st.acc[nt][e >> 1][(e & 1) * 2 + a2], st.acc[nt][(e + 1) >> 1][((e + 1) & 1) * 2 + a2]);
+            }
+            if (p.lse && r == 0)
+              p.lse[(int64_t)s * p.Hq + head] = (st.m[nt][a2] + lg2(lsum)) * LN2;
+          } else if (whole) {
             const float inv = v_scale / lsum;
             uint16_t* op = reinterpret_cast<uint16_t*>(p.out) + (int64_t)s * p.out_stride_s +
                            (int64_t)head * p.out_stride_h;
@@ -579,14 +613,20 @@ __global__ void __launch_bounds__(1024)
   const int tpc = p.cum[p.S + 1];
   const float v_scale = (p.v_scale) ? *p.v_scale : 1.f;
   uint16_t* obase = reinterpret_cast<uint16_t*>(p.out) + (int64_t)s * p.out_stride_s;
+  uint8_t* obase8 = reinterpret_cast<uint8_t*>(p.out) + (int64_t)s * p.out_stride_s;
+  const bool fp8_out = p.out_scale != nullptr;
+  const float qinv = fp8_out ? __fdiv_rn(1.0f, *p.out_scale) : 1.f;
   const int d4n = D >> 2;
   const int items = hq_chunk * d4n;
   if (c1 == c0) {
     // empty sequence: defined output (zeros), lse = -inf
     for (int i = threadIdx.x; i < items; i += blockDim.x) {
       const int h = i / d4n, d = (i - h * d4n) << 2;
-      *reinterpret_cast<uint2*>(obase + (int64_t)(y * hq_chunk + h) * p.out_stride_h + d) =
-          make_uint2(0u, 0u);
+      if (fp8_out)
+        *reinterpret_cast<uint32_t*>(obase8 + (int64_t)(y * hq_chunk + h) * p.out_stride_h + d) = 0u;
+      else
+        *reinterpret_cast<uint2*>(obase + (int64_t)(y * hq_chunk + h) * p.out_stride_h + d) =
+            make_uint2(0u, 0u);
     }
     if (p.lse)
       for (int h = threadIdx.x; h < hq_chunk; h += blockDim.x)
@@ -615,10 +655,17 @@ __global__ void __launch_bounds__(1024)
       num.x += f * a.x; num.y += f * a.y; num.z += f * a.z; num.w += f * a.w;
     }
     const float inv = v_scale / den;
-    uint2 o;
-    o.x = pack2<QBF16>(num.x * inv, num.y * inv);
-    o.y = pack2<QBF16>(num.z * inv, num.w * inv);
-    *reinterpret_cast<uint2*>(obase + (int64_t)(y * hq_chunk + h) * p.out_stride_h + d) = o;
+    if (fp8_out) {
+      const float a0 = fmaxf(-448.f, fminf(num.x * inv * qinv, 448.f)), a1 = fmaxf(-448.f, fminf(num.y * inv * qinv, 448.f));
+      const float a2 = fmaxf(-448.f, fminf(num.z * inv * qinv, 448.f)), a3 = fmaxf(-448.f, fminf(num.w * inv * qinv, 448.f));
+      *reinterpret_cast<uint32_t*>(obase8 + (int64_t)(y * hq_chunk + h) * p.out_stride_h + d) =
+          (uint32_t)f32x2_to_e4m3x2(a0, a1) | ((uint32_t)f32x2_to_e4m3x2(a2, a3) << 16);
+    } else {
+      uint2 o;
+      o.x = pack2<QBF16>(num.x * inv, num.y * inv);
+      o.y = pack2<QBF16>(num.z * inv, num.w * inv);
+      *reinterpret_cast<uint2*>(obase + (int64_t)(y * hq_chunk + h) * p.out_stride_h + d) = o;
+    }
     if (p.lse && d == 0) p.lse[(int64_t)s * p.Hq + y * hq_chunk + h] = (mstar + lg2(den)) * LN2;
   }
 }
