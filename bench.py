@@ -43,7 +43,7 @@ def parse():
     ap.add_argument("--profile-step", action="store_true",
                     help="bracket ONE eager decode step with cudaProfilerStart/Stop and exit "
                          "(for `ncu --profile-from-start off`; prints no bench line)")
-    ap.add_argument("--comm", default="nvlink", choices=["nccl", "nvlink", "fused"],
+    ap.add_argument("--comm", default="auto", choices=["auto", "nccl", "nvlink", "fused"],
                     help="TP collective (N>1): NCCL all-reduce, own NVLink all-reduce, or the fused "
                          "reduce-scatter+add+RMSNorm+FP8-quant+all-gather kernel")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -228,6 +228,11 @@ def main():
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
         group = dist.group.WORLD
+    if a.comm == "auto":
+        # measured (gpurun_out/bench_tp{2,4,8}_*.json): the one-shot all-reduce wins at 2 ranks (8.8 us per
+        # 2 MiB), the fused reduce-scatter + norm + quant + all-gather kernel from 4 ranks up (19 us at 8
+        # ranks where a one-shot pulls 14 MiB per rank and takes 32 us)
+        a.comm = "nvlink" if world <= 2 else "fused"
     shape = model_shape(a.model)
     S, ctx = a.batch, a.ctx
     model = decoder.DecoderModel(shape, S, ctx, BLOCK, dev, tp_rank=rank, tp_size=world, tp_group=group,
@@ -321,6 +326,12 @@ def main():
     alg_bytes = (S * 2 * ctx * model.hkv * D * es + S * model.hq * D * (2 + 2) + S * nblk * 4 + 4 * S)
     peak, peak_src = peaks()
     achieved = alg_bytes / (attn_ms * 1e-3) / 1e9
+    # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this kernel on this exact workload, from
+    # the ncu --set full capture summarised in profiles/r1b_ncu_full.md (a number taken under the profiler is
+    # only used for the byte count, never for time)
+    traffic, traffic_src = None, None
+    if world == 1 and S == 256 and ctx == 4096 and shape.name.startswith("Llama-3.1-8B"):
+        traffic, traffic_src = 2149912000 + 5132544, "profiles/r1b_ncu_full.md (ncu, per launch)"
     step_ms = ms_dev / a.steps
     value = S / (step_ms * 1e-3)
     e2e_value = S / (ms_e2e / a.steps * 1e-3)
@@ -343,7 +354,7 @@ def main():
         "clocks": clocks,
         "roofline": {"kernel": "paged_attn_decode_kernel<128,1,BF16_FP8>", "bound": "hbm",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "peak_source": peak_src, "traffic": None,
+                     "peak_source": peak_src, "traffic": traffic, "traffic_source": traffic_src,
                      "algorithmic_bytes_per_launch": alg_bytes, "ms_per_launch": attn_ms,
                      "launches_per_step": shape.layers,
                      "share_of_step": attn_ms * shape.layers / step_ms},

@@ -19,6 +19,7 @@ def main():
     ap.add_argument("--shapes", default=DEFAULT)
     ap.add_argument("--iters", type=int, default=30)
     ap.add_argument("--impl", default=None, help="v2 | v3 (default: ops.GEMM_IMPL)")
+    ap.add_argument("--eager", action="store_true", help="no CUDA graph, 3 launches per shape (for ncu)")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     for shp in a.shapes.split(";"):
@@ -33,6 +34,8 @@ def main():
         for i in range(3):
             ops.cutlass_scaled_mm(x, ws[i % ncopy].t(), sa, sb, torch.bfloat16, out=out, impl=a.impl)
         torch.cuda.synchronize()
+        if a.eager:
+            continue
         # capture one pass over all weight copies in a CUDA graph: python launch cost (~20 us per
         # call: ctypes + 3 tensor-map encodes) must not be part of a kernel number
         g = torch.cuda.CUDAGraph()
