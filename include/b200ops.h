@@ -231,6 +231,22 @@ B200_API int b200_silu_and_mul_nvfp4(void* out, void* out_scale, const void* inp
                                      const float* global_scale, int64_t num_tokens, int d,
                                      int64_t in_row_stride, int in_dtype, b200_stream_t stream);
 
+/* rotary_embedding + reshape_and_cache_flash in ONE launch: the backend hook
+ * AttentionImpl.do_rope_and_kv_cache_update (vllm/v1/attention/backend.py:950-1006) = the pair
+ * torch.ops._C.rotary_embedding (pos_encoding_kernels.cu:8-99) -> _C_cache_ops::reshape_and_cache_flash
+ * (cache_kernels.cu:314-400); bit-identical to running the two. query [T, num_heads, head_size] and key
+ * [T, num_kv_heads, head_size] are rotated in place (token strides given, heads contiguous); value
+ * [T, num_kv_heads, head_size]; cache arguments as b200_reshape_and_cache_flash; cos_sin_cache
+ * [max_pos, rot_dim] in the q dtype; positions, slot_mapping int64 [T] (slot < 0: rotated, not cached). */
+B200_API int b200_rope_and_cache_flash(const int64_t* positions, void* query, void* key, const void* value,
+                                       const void* cos_sin_cache, void* key_cache, void* value_cache,
+                                       const int64_t* slot_mapping, int64_t num_tokens, int rot_dim,
+                                       int head_size, int num_heads, int num_kv_heads, int block_size,
+                                       int64_t query_stride, int64_t key_stride, int64_t value_stride,
+                                       int64_t block_stride, int64_t page_stride, int64_t head_stride,
+                                       int is_neox, int dtype, int cache_dtype, const float* k_scale,
+                                       const float* v_scale, int kv_scale_stride, b200_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Merge of two partial attention results by log-sum-exp.
  * Replaces torch.ops._C.merge_attn_states (csrc/libtorch_stable/attention/merge_attn_states.cu:13-330;

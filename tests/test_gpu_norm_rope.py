@@ -90,3 +90,42 @@ def test_rotary_embedding(is_neox, dtype, heads, kv_heads, D, rot):
     close_in_ulps(kg, rk, dtype, frac=0.99)
     # v part of the fused tensor untouched
     assert torch.equal(qkv_g[:, (heads + kv_heads) * D:].cpu(), qkv[:, (heads + kv_heads) * D:])
+
+
+@pytest.mark.parametrize("kv", ["auto", "fp8"])
+@pytest.mark.parametrize("neox", [True, False])
+@pytest.mark.parametrize("heads,D,rot", [((32, 8), 128, 128), ((14, 2), 64, 64), ((8, 1), 128, 64), ((4, 4), 80, 40)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_rope_and_cache_flash_equals_unfused_pair(kv, neox, heads, D, rot, dtype):
+    """fused rotary_embedding + reshape_and_cache_flash (backend hook do_rope_and_kv_cache_update) must be
+    bit-identical to the two oracle-checked launches: rotated q / k and every cache byte."""
+    Hq, Hkv = heads
+    T, bs, nb = 57, 16, 9
+    g = torch.Generator().manual_seed(21)
+    qkv = torch.randn(T, (Hq + 2 * Hkv) * D, generator=g).to(dtype).to(DEV)
+    pos = torch.randint(0, 500, (T,), generator=g).to(DEV)
+    cache = torch.randn(500, rot, generator=g).to(dtype).to(DEV)
+    slots = torch.randperm(nb * bs, generator=g)[:T].long()
+    slots[3] = -1
+    slots = slots.to(DEV)
+    per_head = Hkv > 1
+    ks = (torch.rand(Hkv if per_head else 1, generator=g) * 0.05 + 0.01).to(DEV)
+    vs = (torch.rand(Hkv if per_head else 1, generator=g) * 0.05 + 0.01).to(DEV)
+    cdt = torch.uint8 if kv == "fp8" else dtype
+    ops = _ops()
+
+    def views(t):
+        return (t[:, :Hq * D].view(T, Hq, D), t[:, Hq * D:(Hq + Hkv) * D].view(T, Hkv, D),
+                t[:, (Hq + Hkv) * D:].view(T, Hkv, D))
+
+    a, b = qkv.clone(), qkv.clone()
+    c1 = torch.zeros(nb, bs, Hkv, 2 * D, dtype=cdt, device=DEV)
+    c2 = torch.zeros_like(c1)
+    q1, k1, v1 = views(a)
+    ops.rotary_embedding(pos, q1, k1, D, cache, neox)
+    ops.reshape_and_cache_flash(k1, v1, c1[..., :D], c1[..., D:], slots, kv, ks, vs)
+    q2, k2, v2 = views(b)
+    ops.rope_and_reshape_and_cache_flash(pos, q2, k2, v2, D, cache, neox, c2[..., :D], c2[..., D:], slots, kv, ks, vs)
+    torch.cuda.synchronize()
+    assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+    assert torch.equal(c1.view(torch.uint8), c2.view(torch.uint8))

@@ -121,6 +121,9 @@ SIGNATURES = {
     "b200_rotary_embedding": (
         c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int64, c_int64, c_int64,
                 c_int, c_int, c_int, c_int, c_void_p]),
+    "b200_rope_and_cache_flash": (
+        c_int, [c_void_p] * 8 + [c_int64, c_int, c_int, c_int, c_int, c_int] + [c_int64] * 6
+        + [c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p]),
     "b200_moe_align_block_size": (
         c_int, [c_void_p, c_int, c_int64, c_int, c_int, c_void_p, c_int64, c_void_p, c_int64, c_void_p,
                 c_void_p, c_void_p, c_void_p]),

@@ -140,6 +140,21 @@ class B200AttentionImpl(_ImplBase):
         ops.reshape_and_cache_flash(key, value, key_cache, value_cache, slot_mapping,
                                     self.kv_cache_dtype, layer._k_scale, layer._v_scale)
 
+    # ---- RoPE + KV-cache fusion hooks (AttentionImpl, vllm/v1/attention/backend.py:958-1006)
+    def fused_rope_kvcache_supported(self) -> bool:
+        return True
+
+    def do_rope_and_kv_cache_update(self, layer, query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
+                                    positions: torch.Tensor, cos_sin_cache: torch.Tensor, is_neox: bool,
+                                    kv_cache: torch.Tensor, layer_slot_mapping: torch.Tensor) -> None:
+        """in-place RoPE of query / key and the KV-cache write, one launch."""
+        key_cache, value_cache = self._views(kv_cache)
+        if self.kv_cache_dtype.startswith("fp8"):
+            key_cache, value_cache = key_cache.view(torch.uint8), value_cache.view(torch.uint8)
+        ops.rope_and_reshape_and_cache_flash(positions, query, key, value, self.head_size, cos_sin_cache, is_neox,
+                                             key_cache, value_cache, layer_slot_mapping, self.kv_cache_dtype,
+                                             layer._k_scale, layer._v_scale)
+
     def forward(self, layer, query: torch.Tensor, key, value, kv_cache: torch.Tensor, attn_metadata,
                 output: torch.Tensor | None = None, output_scale=None, output_block_scale=None,
                 lse: torch.Tensor | None = None) -> torch.Tensor:

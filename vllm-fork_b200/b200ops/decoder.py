@@ -22,6 +22,7 @@ row-sharded across the ranks).
 from __future__ import annotations
 
 import dataclasses
+import os
 
 import torch
 
@@ -158,6 +159,7 @@ class DecoderModel:
         # overlapped) costs more than the separate full-GPU activation kernel: 16.55 vs 15.95 ms/step.
         # It pays only while the GEMM is a weight stream (small batches).
         self.fuse_gate_up = max_seqs <= 64 and self.inter % 128 == 0
+        self.fuse_attn_quant = os.environ.get("B200_FUSE_ATTN_QUANT", "1") == "1"
         self.attn_hook = None  # bench instrumentation: called around the attention launch
         self.graph = None
 
@@ -201,22 +203,32 @@ class DecoderModel:
                 n += 1
             ops.cutlass_scaled_mm(x8, L["wqkv"].t(), L["a_qkv"], L["wqkv_s"], torch.bfloat16, out=self.qkv)
             n += LAUNCHES["gemm"]
-            ops.rotary_embedding(self.positions, q, k, D, self.cos_sin, True); n += 1
             kc, vc = L["kv"][..., :D], L["kv"][..., D:]
-            ops.reshape_and_cache_flash(k, v, kc, vc, self.slot_mapping,
-                                        "fp8" if self.kv_fp8 else "auto", L["k_scale"], L["v_scale"])
-            n += LAUNCHES["cache_write"]
+            # RoPE + KV-cache write in one launch (do_rope_and_kv_cache_update, backend.py:950-1006)
+            ops.rope_and_reshape_and_cache_flash(self.positions, q, k, v, D, self.cos_sin, True, kc, vc,
+                                                 self.slot_mapping, "fp8" if self.kv_fp8 else "auto",
+                                                 L["k_scale"], L["v_scale"])
+            n += 1
             if self.attn_hook:
                 self.attn_hook(0)
-            # the attention kernel writes the statically quantised o_proj input itself (fused FP8 output)
-            ops.paged_attention_decode(a8.view(S, self.hq, D), q, kc, vc, self.block_table, self.seq_lens,
-                                       D ** -0.5, k_scale=L["k_scale"] if self.kv_fp8 else None,
-                                       v_scale=L["v_scale"] if self.kv_fp8 else None,
-                                       max_seq_len=self.max_ctx, workspace=self.workspace,
-                                       output_scale=L["a_o"])
-            n += LAUNCHES["attention"]
+            if self.fuse_attn_quant:
+                # the attention kernel writes the statically quantised o_proj input itself (fused FP8 output)
+                ops.paged_attention_decode(a8.view(S, self.hq, D), q, kc, vc, self.block_table, self.seq_lens,
+                                           D ** -0.5, k_scale=L["k_scale"] if self.kv_fp8 else None,
+                                           v_scale=L["v_scale"] if self.kv_fp8 else None,
+                                           max_seq_len=self.max_ctx, workspace=self.workspace,
+                                           output_scale=L["a_o"])
+                n += LAUNCHES["attention"]
+            else:
+                ops.paged_attention_decode(self.attn_out, q, kc, vc, self.block_table, self.seq_lens,
+                                           D ** -0.5, k_scale=L["k_scale"] if self.kv_fp8 else None,
+                                           v_scale=L["v_scale"] if self.kv_fp8 else None,
+                                           max_seq_len=self.max_ctx, workspace=self.workspace)
+                n += LAUNCHES["attention"]
             if self.attn_hook:
                 self.attn_hook(1)
+            if not self.fuse_attn_quant:
+                ops.static_scaled_fp8_quant(a8, self.attn_out.view(S, self.hq * D), L["a_o"]); n += 1
             ops.cutlass_scaled_mm(a8, L["wo"].t(), L["a_o"], L["wo_s"], torch.bfloat16, out=pa); n += 1
             if fused:
                 self.ar.fused_add_rms_norm(x8, pa, self.res_shard, L["post_norm"], s.eps, L["a_gu"]); n += 1

@@ -567,6 +567,52 @@ def rotary_embedding(positions: torch.Tensor, query: torch.Tensor, key: torch.Te
     _lib.check(rc, "rotary_embedding")
 
 
+def rope_and_reshape_and_cache_flash(positions: torch.Tensor, query: torch.Tensor, key: torch.Tensor,
+                                     value: torch.Tensor, head_size: int, cos_sin_cache: torch.Tensor,
+                                     is_neox: bool, key_cache: torch.Tensor, value_cache: torch.Tensor,
+                                     slot_mapping: torch.Tensor, kv_cache_dtype: str, k_scale: torch.Tensor,
+                                     v_scale: torch.Tensor) -> None:
+    """rotary_embedding(positions, query, key, ...) followed by reshape_and_cache_flash(key, value, ...) in one
+    launch (AttentionImpl.do_rope_and_kv_cache_update, backend.py:950-1006); bit-identical to the pair.
+    query [T, Hq, D] / key, value [T, Hkv, D] (views of the fused QKV output are fine), rotated in place."""
+    _cuda(positions, query, key, value, cos_sin_cache, key_cache, value_cache, slot_mapping, k_scale, v_scale)
+    T = positions.numel()
+    if positions.dtype != torch.int64 or slot_mapping.dtype != torch.int64:
+        raise RuntimeError("rope_and_reshape_and_cache_flash: positions and slot_mapping must be int64")
+    if slot_mapping.shape[0] != T:
+        raise RuntimeError("rope_and_reshape_and_cache_flash: one slot per token is required")
+    if cos_sin_cache.dtype != query.dtype or key.dtype != query.dtype or value.dtype != query.dtype:
+        raise RuntimeError("rope_and_reshape_and_cache_flash: query / key / value / cos_sin_cache dtypes differ")
+    q3 = query.view(T, -1, head_size) if query.dim() == 2 else query
+    k3 = key.view(T, -1, head_size) if key.dim() == 2 else key
+    v3 = value.view(T, -1, head_size) if value.dim() == 2 else value
+    for t in (q3, k3, v3):
+        if t.stride(2) != 1 or t.stride(1) != head_size:
+            raise RuntimeError("rope_and_reshape_and_cache_flash: heads must be contiguous")
+    if key_cache.dim() != 4 or key_cache.stride(3) != 1 or key_cache.stride() != value_cache.stride():
+        raise RuntimeError("rope_and_reshape_and_cache_flash: caches must be 4-D views with equal strides")
+    hkv = k3.shape[1]
+    if k_scale.numel() not in (1, hkv) or k_scale.shape != v_scale.shape:
+        raise RuntimeError("k_scale and v_scale must be of shape [1] or [num_heads]")
+    if kv_cache_dtype == "auto":
+        cache_dt = _dt(query)
+        if key_cache.dtype != query.dtype:
+            raise RuntimeError("rope_and_reshape_and_cache_flash: kv_cache_dtype 'auto' needs cache dtype == key dtype")
+    elif kv_cache_dtype in _FP8_KV_NAMES:
+        cache_dt = FP8_E4M3
+        if key_cache.element_size() != 1:
+            raise RuntimeError("rope_and_reshape_and_cache_flash: fp8 kv cache must have 1-byte elements")
+    else:
+        raise RuntimeError(f"Unsupported data type of kv cache: {kv_cache_dtype}")
+    rc = _lib.load().b200_rope_and_cache_flash(
+        _p(positions), _p(q3), _p(k3), _p(v3), _p(cos_sin_cache), _p(key_cache), _p(value_cache),
+        _p(slot_mapping), T, cos_sin_cache.shape[1], head_size, q3.shape[1], hkv, key_cache.shape[1],
+        q3.stride(0), k3.stride(0), v3.stride(0), key_cache.stride(0), key_cache.stride(1), key_cache.stride(2),
+        1 if is_neox else 0, _dt(query), cache_dt, _p(k_scale), _p(v_scale), 1 if k_scale.numel() > 1 else 0,
+        _stream())
+    _lib.check(rc, "rope_and_reshape_and_cache_flash")
+
+
 # ------------------------------------------------------------------------------------------------
 # Paged-attention decode
 # ------------------------------------------------------------------------------------------------

@@ -114,6 +114,16 @@ __device__ __forceinline__ float block_sum(float v, float* red) {
   return warp_sum(r);
 }
 
+// one rotary pair: (x, y) <- (x*c - y*s, y*c + x*s), fp32, each result rounded once
+// (pos_encoding_kernels.cu:8-40 apply_token_rotary_embedding). Shared by rotary_kernel and the fused
+// rope + KV-write kernel so both produce the same bits.
+template <typename T>
+__device__ __forceinline__ void rope_rotate(T& xr, T& yr, float c, float sn) {
+  const float x = Cvt<T>::to_f32(xr), y = Cvt<T>::to_f32(yr);
+  xr = Cvt<T>::from_f32(x * c - y * sn);
+  yr = Cvt<T>::from_f32(y * c + x * sn);
+}
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return (uint32_t)__cvta_generic_to_shared(p);
 }

@@ -106,10 +106,10 @@ __global__ void __launch_bounds__(256)
     T* arr = (is_k ? key + tok * k_stride : query + tok * q_stride) + h * head_stride;
     const int xi = NEOX ? ro : 2 * ro;
     const int yi = NEOX ? embed + ro : 2 * ro + 1;
-    const float c = Cvt<T>::to_f32(cosp[ro]), sn = Cvt<T>::to_f32(sinp[ro]);
-    const float x = Cvt<T>::to_f32(arr[xi]), y = Cvt<T>::to_f32(arr[yi]);
-    arr[xi] = Cvt<T>::from_f32(x * c - y * sn);
-    arr[yi] = Cvt<T>::from_f32(y * c + x * sn);
+    T x = arr[xi], y = arr[yi];
+    rope_rotate<T>(x, y, Cvt<T>::to_f32(cosp[ro]), Cvt<T>::to_f32(sinp[ro]));
+    arr[xi] = x;
+    arr[yi] = y;
   }
 }
 
