@@ -134,7 +134,9 @@ class DecoderModel:
         self.block_table = torch.zeros(S, self.blocks_per_seq, dtype=torch.int32, device=self.dev)
         self.next_tokens = torch.zeros(S, dtype=torch.int64, device=self.dev)
         self.workspace = ops.paged_attention_workspace(S, self.hq, self.hkv, D, self.dev)
-        self.x8 = torch.empty(S, max(H, self.hq * D), dtype=torch.float8_e4m3fn, device=self.dev)
+        # FP8 GEMM inputs: normalised hidden states [S, H] and attention output [S, hq*D] (both contiguous)
+        self.x8 = torch.empty(S, H, dtype=torch.float8_e4m3fn, device=self.dev)
+        self.a8 = torch.empty(S, self.hq * D, dtype=torch.float8_e4m3fn, device=self.dev)
         self.h8 = torch.empty(S, self.inter, dtype=torch.float8_e4m3fn, device=self.dev)
         self.qkv = torch.empty(S, (self.hq + 2 * self.hkv) * D, dtype=torch.bfloat16, device=self.dev)
         self.attn_out = torch.empty(S, self.hq, D, dtype=torch.bfloat16, device=self.dev)
@@ -177,8 +179,8 @@ class DecoderModel:
         s, D, S = self.shape, self.D, self.max_seqs
         H = s.hidden
         n = 0
-        x8 = self.x8[:, :H]
-        a8 = self.x8[:, : self.hq * D]
+        x8 = self.x8
+        a8 = self.a8
         q = self.qkv[:, : self.hq * D].view(S, self.hq, D)
         k = self.qkv[:, self.hq * D:(self.hq + self.hkv) * D].view(S, self.hkv, D)
         v = self.qkv[:, (self.hq + self.hkv) * D:].view(S, self.hkv, D)
