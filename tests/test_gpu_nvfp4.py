@@ -119,7 +119,12 @@ def test_cutlass_scaled_fp4_mm(shape, dtype):
 def test_cutlass_scaled_fp4_mm_exact_small_integers():
     """all block scales = 1 (e4m3 0x38), codes in {0, +-1, +-2}: every product and partial sum is a
     small integer, so the result must be BIT-exact whatever the accumulation order."""
-    m, n, k = 48, 256, 512
+    _exact_case(48, 256, 512)
+    _exact_case(256, 512, 1024)    # several narrow batch tiles per weight slab (scale-column offset path)
+    _exact_case(200, 384, 256)
+
+
+def _exact_case(m, n, k):
     rng = np.random.default_rng(0)
     vals = np.array([0, 2, 4, 10, 12], dtype=np.uint8)  # e2m1 codes of 0, 1, 2, -1, -2
     ac = vals[rng.integers(0, 5, (m, k))]

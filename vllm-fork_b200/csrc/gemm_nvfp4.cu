@@ -167,6 +167,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
+      const uint32_t sfb_col_off = BN < 128 ? (uint32_t)((col0 & 127) >> 5) : 0u;
       for (int kb = 0; kb < num_kb; kb++) {
         mbar_wait(bar_full + 8u * stage, phase);
         tc_fence_after();
@@ -184,8 +185,9 @@ __global__ void __launch_bounds__(NTHREADS, 1)
         }
         for (int k = 0; k < kt; k++) {
           // 64 e2m1 = 32 bytes further inside the 128-byte swizzle row
+          // a batch tile narrower than 128 starts (col0 % 128) / 32 columns into its 128-row scale tile
           tc_mma_nvf4(tmem_d, da + (uint64_t)(k * 32 >> 4), db + (uint64_t)(k * 32 >> 4), IDESC,
-                      tmem_d + SFA_COL + 4u * k, tmem_d + SFB_COL + 4u * C_TILES * k,
+                      tmem_d + SFA_COL + 4u * k, tmem_d + SFB_COL + 4u * C_TILES * k + sfb_col_off,
                       (kb > 0 || k > 0) ? 1u : 0u);
         }
         tc_commit(bar_empty + 8u * stage);
@@ -364,8 +366,30 @@ extern "C" int b200_nvfp4_gemm(void* out, const void* a, const void* b, const vo
   memset(&tmO, 0, sizeof(tmO));
   int rc, bn;
   if (swap) {
-    // rows = weight [N,K], cols = activation [M,K]: batch tile = the smallest of {32,64,128,256} >= M
-    bn = M <= 32 ? 32 : M <= 64 ? 64 : M <= 128 ? 128 : 256;
+    // rows = weight [N,K], cols = activation [M,K]. Batch tile by the same small cost model as the FP8
+    // kernel: per k-block a CTA needs max(MMA cycles, bytes / per-SM ingest); waves over the SMs; fixed
+    // prologue + epilogue. Narrow tiles put more CTAs on a weight slab when N is small.
+    {
+      const int slabs = (N + BM - 1) / BM;
+      const int num_kb = (K + BK - 1) / BK;
+      const int sms = sm_count();
+      const int cands[4] = {256, 128, 64, 32};
+      double best = 1e30;
+      bn = 32;
+      for (int ci = 0; ci < 4; ci++) {
+        const int c = cands[ci];
+        if (c >= 2 * M && c > 32) continue;   // never pad the batch by more than 2x
+        // a 32-wide tile at a non-zero offset would need its scale columns at an odd TMEM column, which
+        // the block-scaled MMA rejects (misaligned address); 64-wide tiles use column offsets 0 / 2
+        if (c == 32 && M > 32) continue;
+        const int gy = (M + c - 1) / c;
+        const double waves = ceil((double)slabs * gy / sms);
+        const double mma = 4.0 * (128.0 * c / 256.0) / 2.0;           // fp4 MMAs run at twice the fp8 rate
+        const double ingest = (BM * BKB + c * BKB + 2048.0 + (c > 128 ? 4096.0 : 2048.0)) / 70.0;
+        const double t = waves * (num_kb * (mma > ingest ? mma : ingest) + 5000.0 + 12.0 * c);
+        if (t < best) { best = t; bn = c; }
+      }
+    }
     p.R = N; p.C = M;
     p.r_sf = (const uint8_t*)block_scale_b;
     p.c_sf = (const uint8_t*)block_scale_a;
