@@ -23,9 +23,19 @@
 
 #include <cmath>
 #include <cstring>
+#include <type_traits>
 
 namespace b200 {
 namespace gemm8v3 {
+
+#ifdef B200_V3_TRACE
+// development-only timeline: [pair][role 0 = MMA thread, 1 = epilogue thread 0 of the leader CTA][piece < 8][4]
+static unsigned long long* g_trace = nullptr;
+#define V3_TRACE(role, piece, slot)                                                            \
+  if (p.trace && (piece) < 8) p.trace[(((size_t)pair * 2 + (role)) * 8 + (piece)) * 4 + (slot)] = clock64()
+#else
+#define V3_TRACE(role, piece, slot)
+#endif
 
 constexpr int BM = 128;          // rows per CTA (UMMA M = 256 per pair)
 constexpr int BK = 128;          // k-block bytes
@@ -47,6 +57,14 @@ struct Params {
   int swap, out_bf16, stages, tma_store;
   int row_tiles, col_tiles, num_kb;   // tiles of 256 rows x BN cols, k-blocks per tile
   int pairs;
+  // Work split. interleave = 0: stream-K, pair i takes the i-th equal contiguous range of the flattened
+  // (tile, k-block) space (decode: fewer tiles than pairs). interleave = 1: whole tiles, pair i takes tiles
+  // i, i + pairs, ... of a grouped raster (large M): the `pairs` tiles in flight at any moment form a compact
+  // raster_group x (pairs / raster_group) block, so their operands stay L2-resident (contiguous ranges put
+  // concurrent pairs ~14 tiles apart = every column tile of B live at once).
+  int interleave, raster_group;
+  int staging_bytes;      // transposed-output staging tile (swap + TMA store only)
+  unsigned long long* trace;   // B200_V3_TRACE builds only
 };
 
 using namespace b200::tc;
@@ -107,18 +125,54 @@ __device__ __forceinline__ void pair_range(const Params& p, int pair, int64_t* l
   *lo = units * pair / p.pairs;
   *hi = units * (pair + 1) / p.pairs;
 }
-// i-th piece of the range [lo, hi) in processing order (ascending units); returns false past the end
-__device__ __forceinline__ bool next_piece(const Params& p, int64_t& cur, int64_t hi, Piece* pc) {
-  if (cur >= hi) return false;
-  const int tile = (int)(cur / p.num_kb);
-  const int kb0 = (int)(cur - (int64_t)tile * p.num_kb);
+struct Sched {
+  int64_t cur, hi;
+};
+__device__ __forceinline__ void sched_init(const Params& p, int pair, Sched* s) {
+  if (p.interleave) {
+    s->cur = pair;
+    s->hi = (int64_t)p.row_tiles * p.col_tiles;
+  } else {
+    pair_range(p, pair, &s->cur, &s->hi);
+  }
+}
+// next piece in processing order; returns false past the end
+__device__ __forceinline__ bool next_piece(const Params& p, Sched& s, Piece* pc) {
+  if (s.cur >= s.hi) return false;
+  if (p.interleave) {
+    pc->tile = (int)s.cur;
+    pc->kb0 = 0;
+    pc->kb1 = p.num_kb;
+    s.cur += p.pairs;
+    return true;
+  }
+  const int tile = (int)(s.cur / p.num_kb);
+  const int kb0 = (int)(s.cur - (int64_t)tile * p.num_kb);
   const int64_t tile_end = (int64_t)(tile + 1) * p.num_kb;
-  const int64_t end = tile_end < hi ? tile_end : hi;
+  const int64_t end = tile_end < s.hi ? tile_end : s.hi;
   pc->tile = tile;
   pc->kb0 = kb0;
-  pc->kb1 = kb0 + (int)(end - cur);
-  cur = end;
+  pc->kb1 = kb0 + (int)(end - s.cur);
+  s.cur = end;
   return true;
+}
+__device__ __forceinline__ void tile_coords(const Params& p, int tile, int* rt, int* ct) {
+  if (p.raster_group > 0) {
+    const int per_group = p.raster_group * p.col_tiles;
+    const int grp = tile / per_group, within = tile - grp * per_group;
+    const int rows_here = min(p.raster_group, p.row_tiles - grp * p.raster_group);
+    *rt = grp * p.raster_group + within % rows_here;
+    *ct = within / rows_here;
+  } else {
+    *rt = tile % p.row_tiles;
+    *ct = tile / p.row_tiles;
+  }
+}
+// 1-D bulk copy global -> this CTA's shared memory, completion on an mbarrier
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
 }
 
 template <int BN>
@@ -128,7 +182,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
   constexpr uint32_t R_BYTES = BM * BK;             // this CTA's 128 rows
   constexpr uint32_t C_BYTES = (BN / 2) * BK;       // this CTA's half of the cols operand
   constexpr uint32_t STAGE_BYTES = R_BYTES + C_BYTES;
-  constexpr uint32_t STAGING_BYTES = BN * BM * 2;   // transposed output tile [BN m][128 r] 16-bit
+  constexpr uint32_t CHUNK_BYTES = BM * 16 * 4;      // one 16-column fp32 chunk of this CTA's 128 rows
+  constexpr uint32_t FIX_BYTES = 2 * CHUNK_BYTES;    // fix-up buffer: 2 chunks (one drain iteration) of one contributor
   constexpr uint32_t TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;   // two accumulator buffers
   // instruction descriptor: D = F32, A = B = E4M3, K-major, N = BN, M = 256 (pair)
   constexpr uint32_t IDESC = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
@@ -138,14 +193,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
   const uint32_t base = (raw_base + 1023u) & ~1023u;
   uint8_t* smem = smem_raw + (base - raw_base);
   const int stages = p.stages;
-  const uint32_t staging = base + (uint32_t)stages * STAGE_BYTES;
-  const uint32_t bar_base = staging + STAGING_BYTES;
+  const uint32_t staging = base + (uint32_t)stages * STAGE_BYTES;   // [BN m][128 r] 16-bit (swap + TMA store)
+  const uint32_t bar_base = staging + (uint32_t)p.staging_bytes;
   const uint32_t bar_full = bar_base;                          // [stages]   (leader's copy is used)
   const uint32_t bar_empty = bar_base + 8u * MAX_STAGES;       // [stages]   per CTA
   const uint32_t bar_tfull = bar_base + 16u * MAX_STAGES;      // [2]        per CTA
   const uint32_t bar_tempty = bar_tfull + 16u;                 // [2]        (leader's copy is used)
+  const uint32_t bar_fix = bar_tempty + 16u;                   // [MAX_STAGES] fix-up bulk copies, per CTA
   volatile uint32_t* tmem_holder = reinterpret_cast<volatile uint32_t*>(
-      smem + (size_t)stages * STAGE_BYTES + STAGING_BYTES + 16 * MAX_STAGES + 32 + 8);
+      smem + (size_t)stages * STAGE_BYTES + p.staging_bytes + 24 * MAX_STAGES + 32 + 8);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t cta = cluster_ctarank();
@@ -160,6 +216,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
       mbar_init(bar_tfull + 8u * b, 1);
       mbar_init(bar_tempty + 8u * b, 8);   // 4 epilogue warps x 2 CTAs
     }
+    for (int i = 0; i < MAX_STAGES; i++) mbar_init(bar_fix + 8u * i, 1);
     mbar_fence_init();
   }
   if (warp == 1) {
@@ -174,8 +231,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
   tc_fence_after();
   const uint32_t tmem_base = *tmem_holder;
 
-  int64_t lo, hi;
-  pair_range(p, pair, &lo, &hi);
+  Sched sched;
+  sched_init(p, pair, &sched);
 
   if (warp == 0) {
     // ============================== TMA producer (one thread per CTA)
@@ -184,14 +241,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
       prefetch_tmap(&tmC);
       const uint64_t pol_w = l2_policy_evict_first();
       const uint64_t pol_a = l2_policy_evict_last();
+      // decode: weights stream once (evict first), the batch is re-read by every pair (evict last);
+      // large M: both operands are re-read by other tiles of the raster block
       const uint64_t pol_r = p.swap ? pol_w : pol_a;
-      const uint64_t pol_c = p.swap ? pol_a : pol_w;
+      const uint64_t pol_c = pol_a;
       int stage = 0;
       uint32_t phase = 0;
-      int64_t cur = lo;
       Piece pc;
-      while (next_piece(p, cur, hi, &pc)) {
-        const int rt = pc.tile % p.row_tiles, ct = pc.tile / p.row_tiles;
+      while (next_piece(p, sched, &pc)) {
+        int rt, ct;
+        tile_coords(p, pc.tile, &rt, &ct);
         const int row0 = rt * 2 * BM + (int)cta * BM;
         const int col0 = ct * BN + (int)cta * (BN / 2);
         for (int kb = pc.kb0; kb < pc.kb1; kb++) {
@@ -212,12 +271,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
       int stage = 0;
       uint32_t phase = 0;
       uint32_t tphase[2] = {0, 0};
-      int64_t cur = lo;
       Piece pc;
       int n = 0;
-      while (next_piece(p, cur, hi, &pc)) {
+      while (next_piece(p, sched, &pc)) {
         const int buf = n & 1;
+        V3_TRACE(0, n, 0);
         mbar_wait(bar_tempty + 8u * buf, tphase[buf] ^ 1u);   // epilogues of both CTAs drained this buffer
+        V3_TRACE(0, n, 1);
         tphase[buf] ^= 1u;
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + (uint32_t)(buf * BN);
@@ -235,6 +295,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
           if (++stage == stages) { stage = 0; phase ^= 1u; }
         }
         tc_commit_2sm(bar_tfull + 8u * buf);
+        V3_TRACE(0, n, 2);
         n++;
       }
     }
@@ -243,7 +304,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
     const int wq = warp & 3;
     const int et = (warp - 2) * 32 + lane;   // 0..127 among the epilogue threads
     uint32_t tphase[2] = {0, 0};
-    int64_t cur = lo;
     Piece pc;
     int n = 0;
     uint16_t* out16 = reinterpret_cast<uint16_t*>(p.out);
@@ -261,33 +321,51 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
       return *reinterpret_cast<uint16_t*>(&h);
     };
     const float cs0 = p.c_scale_vec ? 0.f : p.c_scale[0];
+    const int trow = wq * 32 + lane;        // row of this thread inside the CTA's 128
+    // fix-up buffers live in the pipeline smem, idle once the LAST piece's accumulator is complete
+    const int nbuf = min(MAX_STAGES, (int)((uint32_t)stages * STAGE_BYTES / FIX_BYTES));
     bool store_pending = false;
-    while (next_piece(p, cur, hi, &pc)) {
+    while (next_piece(p, sched, &pc)) {
       const int buf = n & 1;
-      const int rt = pc.tile % p.row_tiles, ct = pc.tile / p.row_tiles;
+      int rt, ct;
+      tile_coords(p, pc.tile, &rt, &ct);
       const int row0 = rt * 2 * BM + (int)cta * BM;   // this CTA's first row
       const int col0 = ct * BN;
+      if (cta == 0 && et == 0) { V3_TRACE(1, n, 0); }
       mbar_wait(bar_tfull + 8u * buf, tphase[buf]);
+      if (cta == 0 && et == 0) { V3_TRACE(1, n, 1); }
       tphase[buf] ^= 1u;
       tc_fence_after();
       const uint32_t tbase = tmem_base + (uint32_t)(buf * BN) + ((uint32_t)(wq * 32) << 16);
       const int ncols = min(BN, p.C - col0);
       const int nchunks = (ncols + 15) >> 4;
-      const int trow = wq * 32 + lane;        // row of this thread inside the CTA's 128
+      const int nbatch = (nchunks + 3) >> 2;
       if (pc.kb0 > 0) {
-        // ---------- not the owner of this tile: publish the fp32 partial, then raise the flag
-        float* slot = p.ws_partials + ((size_t)(pair * 2 + cta) * (BN / 16) * BM) * 16;
-        for (int ch = 0; ch < nchunks; ch++) {
-          uint32_t v[16];
-          tc_ld16(tbase + (uint32_t)(ch << 4), v);
-          tc_wait_ld();
-          uint4* dst = reinterpret_cast<uint4*>(slot + ((size_t)ch * BM + trow) * 16);
+        // ---------- not the owner of this tile: publish the fp32 partial, then raise the flag.
+        // Layout per CTA slot: [chunk][j = 0..3][row 0..127][4 floats]: a chunk is 8 KB contiguous (one bulk
+        // copy on the owner's side) and row-consecutive lanes are 16 bytes apart on both sides.
+        float4* slot = reinterpret_cast<float4*>(p.ws_partials + ((size_t)(pair * 2 + cta) * (BN / 16) * BM) * 16);
+        for (int b = 0; b < nbatch; b++) {
+          uint32_t v[4][16];
 #pragma unroll
-          for (int j = 0; j < 4; j++) dst[j] = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          for (int c = 0; c < 4; c++)
+            if (4 * b + c < nchunks) tc_ld16(tbase + (uint32_t)((4 * b + c) << 4), v[c]);
+          tc_wait_ld();
+#pragma unroll
+          for (int c = 0; c < 4; c++) {
+            if (4 * b + c < nchunks) {
+              float4* dst = slot + (size_t)(4 * b + c) * 4 * BM + trow;
+#pragma unroll
+              for (int j = 0; j < 4; j++)
+                dst[j * BM] = make_float4(__uint_as_float(v[c][4 * j]), __uint_as_float(v[c][4 * j + 1]),
+                                          __uint_as_float(v[c][4 * j + 2]), __uint_as_float(v[c][4 * j + 3]));
+            }
+          }
         }
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_leader(bar_tempty + 8u * buf);   // TMEM buffer free for the next piece
+        if (cta == 0 && et == 0) { V3_TRACE(1, n, 2); }
         __threadfence();
         asm volatile("bar.sync 1, 128;" ::: "memory");
         if (et == 0) atomicAdd(p.ws_flags + 2 * pair, 1u);
@@ -308,98 +386,163 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
             if (qlo >= tile_end) break;
             q_end++;
           }
+        }
+        const int qn = q_end - pair - 1;        // contributors (their partials are added in pair order)
+        const int total = ((nchunks + 1) >> 1) * qn;   // fix-up item i = (chunk pair i / qn, contributor i % qn)
+        auto issue = [&](int i) {               // et == 0 only
+          const int b = i / qn, q = pair + 1 + i % qn;
+          const int nch = min(2, nchunks - 2 * b);
+          const uint32_t bytes = (uint32_t)nch * CHUNK_BYTES;
+          const float* src = p.ws_partials + ((size_t)(q * 2 + cta) * (BN / 16) + 2 * b) * (BM * 16);
+          const uint32_t bar = bar_fix + 8u * (uint32_t)(i % nbuf);
+          mbar_arrive_expect_tx(bar, bytes);
+          bulk_g2s(base + (uint32_t)(i % nbuf) * FIX_BYTES, src, bytes, bar);
+        };
+        if (qn > 0 && et == 0) {
+          // the contributors published first thing in their ranges; this pair got here last
           for (int q = pair + 1; q < q_end; q++) {
             const uint32_t* f = p.ws_flags + 2 * q;
             while (ld_acquire_gpu(f) < 2u) {
             }
           }
+          asm volatile("fence.proxy.async;" ::: "memory");   // acquired generic writes -> async-proxy reads
+          for (int i = 0; i < total && i < nbuf; i++) issue(i);
         }
-        if (p.swap && p.tma_store) {
-          if (store_pending) {   // the previous tile's TMA store must have read the staging tile
-            if (et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-            asm volatile("bar.sync 1, 128;" ::: "memory");
-          }
+        if (p.swap && p.tma_store && store_pending) {
+          // the previous tile's TMA store must have read the staging tile
+          if (et == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+          asm volatile("bar.sync 1, 128;" ::: "memory");
         }
-        for (int ch = 0; ch < nchunks; ch++) {
-          uint32_t v[16];
-          tc_ld16(tbase + (uint32_t)(ch << 4), v);
-          tc_wait_ld();
-          float acc[16];
-#pragma unroll
-          for (int j = 0; j < 16; j++) acc[j] = __uint_as_float(v[j]);
-          for (int q = pair + 1; q < q_end; q++) {
-            const float* slot = p.ws_partials + ((size_t)(q * 2 + cta) * (BN / 16) * BM) * 16;
-            const float4* src = reinterpret_cast<const float4*>(slot + ((size_t)ch * BM + trow) * 16);
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-              const float4 t = __ldcg(src + j);
-              acc[4 * j] += t.x; acc[4 * j + 1] += t.y; acc[4 * j + 2] += t.z; acc[4 * j + 3] += t.w;
-            }
-          }
-          if (ch == nchunks - 1) {   // all TMEM reads of this buffer are done
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive_leader(bar_tempty + 8u * buf);
-          }
+        // One chunk = 16 accumulator columns. Two chunks per iteration in a ROLLED loop, one store flavour per
+        // instantiation: the unrolled 4-chunk / 3-flavour version was ~8000 SASS instructions of straight-line
+        // code and ran at instruction-fetch speed (30k cycles per tile vs 16k of MMAs, profiles/r1c).
+        auto emit = [&](auto mode_tag, const float (&a)[16], int ch) {
+          constexpr int MODE = decltype(mode_tag)::value;   // 0 = out[r][c] direct, 1 = swap via staging, 2 = swap direct
           const int c0 = ch << 4;
-          if (p.swap) {
-            if (p.tma_store) {
+          if constexpr (MODE == 1) {
 #pragma unroll
-              for (int j = 0; j < 16; j += 2) {
-                const int c = col0 + c0 + j;
-                const float cs_a = p.c_scale_vec ? (c < p.C ? p.c_scale[c] : 0.f) : cs0;
-                const float cs_b = p.c_scale_vec ? (c + 1 < p.C ? p.c_scale[c + 1] : 0.f) : cs0;
-                const float oa = cs_a * (rs * acc[j]) + bias_r;
-                const float ob = cs_b * (rs * acc[j + 1]) + bias_r;
-                const float send = (lane & 1) ? oa : ob;
-                const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
-                const float lo_ = (lane & 1) ? recv : oa;
-                const float hi_ = (lane & 1) ? ob : recv;
-                uint32_t packed;
-                if (p.out_bf16) {
-                  __nv_bfloat162 t = __floats2bfloat162_rn(lo_, hi_);
-                  packed = *reinterpret_cast<uint32_t*>(&t);
-                } else {
-                  __half2 t = __floats2half2_rn(lo_, hi_);
-                  packed = *reinterpret_cast<uint32_t*>(&t);
-                }
-                const int m_local = c0 + j + (lane & 1);
-                const uint32_t addr = staging + (uint32_t)m_local * (BM * 2) + (uint32_t)(wq * 32 + (lane & ~1)) * 2u;
-                asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(packed) : "memory");
+            for (int j = 0; j < 16; j += 2) {
+              const int cc = col0 + c0 + j;
+              const float cs_a = p.c_scale_vec ? (cc < p.C ? p.c_scale[cc] : 0.f) : cs0;
+              const float cs_b = p.c_scale_vec ? (cc + 1 < p.C ? p.c_scale[cc + 1] : 0.f) : cs0;
+              const float oa = cs_a * (rs * a[j]) + bias_r;
+              const float ob = cs_b * (rs * a[j + 1]) + bias_r;
+              const float send = (lane & 1) ? oa : ob;
+              const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
+              const float lo_ = (lane & 1) ? recv : oa;
+              const float hi_ = (lane & 1) ? ob : recv;
+              uint32_t packed;
+              if (p.out_bf16) {
+                __nv_bfloat162 t = __floats2bfloat162_rn(lo_, hi_);
+                packed = *reinterpret_cast<uint32_t*>(&t);
+              } else {
+                __half2 t = __floats2half2_rn(lo_, hi_);
+                packed = *reinterpret_cast<uint32_t*>(&t);
               }
-            } else if (r_ok) {
+              const int m_local = c0 + j + (lane & 1);
+              const uint32_t addr = staging + (uint32_t)m_local * (BM * 2) + (uint32_t)(wq * 32 + (lane & ~1)) * 2u;
+              asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(packed) : "memory");
+            }
+          } else if constexpr (MODE == 2) {
+            if (r_ok) {
 #pragma unroll
               for (int j = 0; j < 16; j++) {
-                const int c = col0 + c0 + j;
-                if (c < p.C) {
-                  const float cs = p.c_scale_vec ? p.c_scale[c] : cs0;
-                  out16[(int64_t)c * p.ldo + r] = from_f32(cs * (rs * acc[j]) + bias_r);
+                const int cc = col0 + c0 + j;
+                if (cc < p.C) {
+                  const float cs = p.c_scale_vec ? p.c_scale[cc] : cs0;
+                  out16[(int64_t)cc * p.ldo + r] = from_f32(cs * (rs * a[j]) + bias_r);
                 }
               }
             }
-          } else if (r_ok) {
-            uint16_t h[16];
+          } else {
+            if (r_ok) {
+              uint32_t h[8];
 #pragma unroll
-            for (int j = 0; j < 16; j++) {
-              const int c = col0 + c0 + j;
-              float o = 0.f;
-              if (c < p.C) {
-                const float cs = p.c_scale_vec ? p.c_scale[c] : cs0;
-                o = rs * (cs * acc[j]);
-                if (bias16) o += to_f32(bias16[c]);
+              for (int j = 0; j < 16; j += 2) {
+                float o[2];
+#pragma unroll
+                for (int e = 0; e < 2; e++) {
+                  const int cc = col0 + c0 + j + e;
+                  o[e] = 0.f;
+                  if (cc < p.C) {
+                    const float cs = p.c_scale_vec ? p.c_scale[cc] : cs0;
+                    o[e] = rs * (cs * a[j + e]);
+                    if (bias16) o[e] += to_f32(bias16[cc]);
+                  }
+                }
+                h[j >> 1] = (uint32_t)from_f32(o[0]) | ((uint32_t)from_f32(o[1]) << 16);
               }
-              h[j] = from_f32(o);
-            }
-            uint16_t* dst = out16 + (int64_t)r * p.ldo + col0 + c0;
-            if (col0 + c0 + 16 <= p.C && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
-              reinterpret_cast<uint4*>(dst)[0] = reinterpret_cast<const uint4*>(h)[0];
-              reinterpret_cast<uint4*>(dst)[1] = reinterpret_cast<const uint4*>(h)[1];
-            } else {
-              for (int j = 0; j < 16; j++)
-                if (col0 + c0 + j < p.C) dst[j] = h[j];
+              uint16_t* dst = out16 + (int64_t)r * p.ldo + col0 + c0;
+              if (col0 + c0 + 16 <= p.C && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+                reinterpret_cast<uint4*>(dst)[0] = make_uint4(h[0], h[1], h[2], h[3]);
+                reinterpret_cast<uint4*>(dst)[1] = make_uint4(h[4], h[5], h[6], h[7]);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 16; j++)
+                  if (col0 + c0 + j < p.C) dst[j] = (uint16_t)(h[j >> 1] >> ((j & 1) * 16));
+              }
             }
           }
-        }
+        };
+        auto drain = [&](auto mode_tag) {
+#pragma unroll 1
+          for (int ch = 0; ch < nchunks; ch += 2) {
+            const bool two = ch + 1 < nchunks;
+            float a0[16], a1[16];
+            {
+              uint32_t v0[16], v1[16];
+              tc_ld16(tbase + (uint32_t)(ch << 4), v0);
+              if (two) tc_ld16(tbase + (uint32_t)((ch + 1) << 4), v1);
+              tc_wait_ld();
+#pragma unroll
+              for (int j = 0; j < 16; j++) {
+                a0[j] = __uint_as_float(v0[j]);
+                a1[j] = two ? __uint_as_float(v1[j]) : 0.f;
+              }
+            }
+            if (ch + 2 >= nchunks) {   // all TMEM reads of this buffer are done
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive_leader(bar_tempty + 8u * buf);
+              if (cta == 0 && et == 0) { V3_TRACE(1, n, 2); }
+            }
+            if (qn > 0) {
+#pragma unroll 1
+              for (int qi = 0; qi < qn; qi++) {
+                const int i = (ch >> 1) * qn + qi;
+                mbar_wait(bar_fix + 8u * (uint32_t)(i % nbuf), (uint32_t)(i / nbuf) & 1u);
+                const uint32_t fb = base + (uint32_t)(i % nbuf) * FIX_BYTES + (uint32_t)trow * 16u;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                  float4 t;
+                  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                               : "=f"(t.x), "=f"(t.y), "=f"(t.z), "=f"(t.w)
+                               : "r"(fb + (uint32_t)(j * BM) * 16u));
+                  a0[4 * j] += t.x; a0[4 * j + 1] += t.y; a0[4 * j + 2] += t.z; a0[4 * j + 3] += t.w;
+                }
+                if (two) {
+#pragma unroll
+                  for (int j = 0; j < 4; j++) {
+                    float4 t;
+                    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];"
+                                 : "=f"(t.x), "=f"(t.y), "=f"(t.z), "=f"(t.w)
+                                 : "r"(fb + (uint32_t)((4 + j) * BM) * 16u));
+                    a1[4 * j] += t.x; a1[4 * j + 1] += t.y; a1[4 * j + 2] += t.z; a1[4 * j + 3] += t.w;
+                  }
+                }
+                if (i + nbuf < total) {   // recycle this buffer
+                  asm volatile("bar.sync 1, 128;" ::: "memory");
+                  if (et == 0) issue(i + nbuf);
+                }
+              }
+            }
+            emit(mode_tag, a0, ch);
+            if (two) emit(mode_tag, a1, ch + 1);
+          }
+        };
+        if (!p.swap) drain(std::integral_constant<int, 0>{});
+        else if (p.tma_store) drain(std::integral_constant<int, 1>{});
+        else drain(std::integral_constant<int, 2>{});
         if (p.swap && p.tma_store) {
           fence_proxy_async();
           asm volatile("bar.sync 1, 128;" ::: "memory");
@@ -412,7 +555,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
           store_pending = true;
         }
         // release the partial slots: the second of the pair's two CTAs to finish resets the flags
-        if (q_end > pair + 1) {
+        if (qn > 0) {
           asm volatile("bar.sync 1, 128;" ::: "memory");
           if (et == 0) {
             for (int q = pair + 1; q < q_end; q++) {
@@ -425,6 +568,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
           }
         }
       }
+      if (cta == 0 && et == 0) { V3_TRACE(1, n, 3); }
       n++;
     }
     if (store_pending && et == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
@@ -444,16 +588,17 @@ template <int BN>
 static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, const CUtensorMap& tmO, Params& p,
                   cudaStream_t stream) {
   constexpr uint32_t STAGE_BYTES = BM * BK + (BN / 2) * BK;
-  constexpr uint32_t STAGING_BYTES = BN * BM * 2;
+  const int staging = (p.swap && p.tma_store) ? BN * BM * 2 : 0;
+  p.staging_bytes = staging;
   const int smem_max = max_smem_optin();
-  int stages = (smem_max - 1024 - 256 - 64 - (int)STAGING_BYTES) / (int)STAGE_BYTES;
+  int stages = (smem_max - 1024 - 256 - 128 - staging) / (int)STAGE_BYTES;
   if (stages > MAX_STAGES) stages = MAX_STAGES;
   if (stages < 2) {
     set_last_error("fp8_gemm_v3: not enough shared memory");
     return B200_ERR_UNSUPPORTED;
   }
   p.stages = stages;
-  const int smem = stages * (int)STAGE_BYTES + (int)STAGING_BYTES + 16 * MAX_STAGES + 32 + 64 + 1024;
+  const int smem = stages * (int)STAGE_BYTES + staging + 24 * MAX_STAGES + 32 + 64 + 1024;
   static int max_pairs = 0;
   if (max_pairs == 0) {
     B200_CUDA(cudaFuncSetAttribute(gemm_fp8_v3_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
@@ -462,7 +607,7 @@ static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, const CUtensor
     memset(&cfg, 0, sizeof(cfg));
     cfg.gridDim = dim3(sm_count() / 2 * 2);
     cfg.blockDim = dim3(NTHREADS);
-    cfg.dynamicSmemBytes = smem;
+    cfg.dynamicSmemBytes = smem_max;
     int clusters = 0;
     cudaError_t e = cudaOccupancyMaxActiveClusters(&clusters, gemm_fp8_v3_kernel<BN>, &cfg);
     if (e != cudaSuccess || clusters <= 0) {
@@ -472,8 +617,13 @@ static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, const CUtensor
     max_pairs = clusters < sm_count() / 2 ? clusters : sm_count() / 2;
   }
   p.pairs = max_pairs;
-  const int64_t units = (int64_t)p.row_tiles * p.col_tiles * p.num_kb;
+  const int64_t tiles = (int64_t)p.row_tiles * p.col_tiles;
+  const int64_t units = tiles * p.num_kb;
   if (units < p.pairs) p.pairs = (int)units;
+  // many tiles per pair: whole tiles in a grouped raster (L2 locality; the tail wave costs < 1 / (tiles / pairs));
+  // few: stream-K so every pair streams the same number of k-blocks
+  p.interleave = (!p.swap && tiles >= 4 * (int64_t)p.pairs) ? 1 : 0;
+  p.raster_group = p.interleave ? 8 : 0;
   gemm_fp8_v3_kernel<BN><<<p.pairs * 2, NTHREADS, smem, stream>>>(tmR, tmC, tmO, p);
   B200_LAUNCH_CHECK();
   return B200_OK;
@@ -489,6 +639,12 @@ static int make_tmap_2d(CUtensorMap* tm, const void* base, int rows, int K, int6
 
 }  // namespace gemm8v3
 }  // namespace b200
+
+#ifdef B200_V3_TRACE
+extern "C" __attribute__((visibility("default"))) void b200_fp8_gemm_v3_set_trace(void* dev_ptr) {
+  b200::gemm8v3::g_trace = reinterpret_cast<unsigned long long*>(dev_ptr);
+}
+#endif
 
 extern "C" size_t b200_fp8_gemm_v3_workspace_bytes(void) {
   // flags + one fp32 partial tile (2 CTAs x 128 rows x 256 cols) per CTA pair
@@ -525,6 +681,9 @@ extern "C" int b200_fp8_gemm_v3(void* out, const void* a, const void* b, const f
   p.K = K;
   p.ldo = ldo;
   p.out_bf16 = out_dtype == B200_BF16;
+#ifdef B200_V3_TRACE
+  p.trace = g_trace;
+#endif
   p.ws_flags = reinterpret_cast<uint32_t*>(workspace);
   p.ws_partials = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(workspace) + WS_FLAG_BYTES);
   p.num_kb = (K + BK - 1) / BK;
