@@ -267,13 +267,23 @@ def cutlass_scaled_mm_supports_fp8(cuda_device_capability: int) -> bool:
 
 
 # which FP8 GEMM kernel cutlass_scaled_mm launches: "v2" = one CTA per tile (csrc/gemm_fp8.cu),
-# "v3" = persistent CTA pairs (cta_group::2) + stream-K (csrc/gemm_fp8_v3.cu). Both are tcgen05 kernels
-# with the same arithmetic and both are parity-green; this is a tuning switch (env B200_GEMM_IMPL), not a
-# fallback. Measured on B200 (gpurun_out/bench_gemm_v3.log): v3 ties v2 at large M (2.11 vs 2.22 PFLOP/s)
-# and loses at decode M (its stream-K fix-up reads fp32 partials from L2 latency-bound), so v2 is the
-# default until the fix-up is moved onto bulk copies.
-GEMM_IMPL = os.environ.get("B200_GEMM_IMPL", "v2")
+# "v3" = persistent CTA pairs (cta_group::2), whole-tile raster or stream-K (csrc/gemm_fp8_v3.cu). Both are
+# tcgen05 kernels with the same arithmetic and both are parity-green; this is a tuning switch (env
+# B200_GEMM_IMPL), not a fallback. "auto" (default) follows the measurements on B200
+# (gpurun_out/bg_v2.log, bg_v3.log): M > 256 -> v3 (8192^3: 3.05 vs 2.24 PFLOP/s; 4096^3: 2.29 vs 1.48),
+# decode batches (M <= 256, swap-AB) -> v2 (14.6 / 13.1 / 33.6 us vs 30.6 / 37.5 / 44.5 us on the Llama-8B qkv / o /
+# down shapes: the fp32 partial round trip of stream-K costs more than it balances there) except when N gives
+# every CTA pair at least one whole 256-row weight tile (gate_up: v3 34.4 us vs v2 38.7 us).
+GEMM_IMPL = os.environ.get("B200_GEMM_IMPL", "auto")
 _gemm_ws: dict[str, torch.Tensor] = {}
+_sms: dict[str, int] = {}
+
+
+def _sm_count(device: torch.device) -> int:
+    key = str(device)
+    if key not in _sms:
+        _sms[key] = torch.cuda.get_device_properties(device).multi_processor_count
+    return _sms[key]
 
 
 def _gemm_workspace(device: torch.device) -> torch.Tensor:
@@ -329,7 +339,12 @@ def cutlass_scaled_mm(
     common = (_p(out), _p(a), _p(b), _p(scale_a), _p(scale_b), _p(bias), M, N, K,
               a.stride(0) if M > 1 else K, b.stride(1), out.stride(0) if out.dim() > 1 else N,
               1 if scale_a.numel() > 1 else 0, 1 if scale_b.numel() > 1 else 0, _dt(out))
-    if (impl or GEMM_IMPL) == "v3":
+    which = impl or GEMM_IMPL
+    if which == "auto":
+        # decode batches go to v3 only when there are at least as many 256-row weight tiles as CTA pairs
+        # (gate_up: 34.4 vs 38.7 us at batch 256)
+        which = "v3" if (M > 256 or N >= 256 * (_sm_count(a.device) // 2)) else "v2"
+    if which == "v3":
         ws = _gemm_workspace(a.device)
         rc = lib.b200_fp8_gemm_v3(*common, _p(ws), ws.numel(), _stream())
     else:

@@ -416,73 +416,76 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
         // One chunk = 16 accumulator columns. Two chunks per iteration in a ROLLED loop, one store flavour per
         // instantiation: the unrolled 4-chunk / 3-flavour version was ~8000 SASS instructions of straight-line
         // code and ran at instruction-fetch speed (30k cycles per tile vs 16k of MMAs, profiles/r1c).
-        auto emit = [&](auto mode_tag, const float (&a)[16], int ch) {
+        auto pack2 = [&](float lo, float hi) -> uint32_t {
+          if (p.out_bf16) {
+            __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
+            return *reinterpret_cast<uint32_t*>(&t);
+          }
+          __half2 t = __floats2half2_rn(lo, hi);
+          return *reinterpret_cast<uint32_t*>(&t);
+        };
+        auto emit_body = [&](auto mode_tag, auto full_tag, float (&a)[16], int ch) {
           constexpr int MODE = decltype(mode_tag)::value;   // 0 = out[r][c] direct, 1 = swap via staging, 2 = swap direct
+          constexpr bool full = decltype(full_tag)::value;  // all 16 columns of the chunk exist: no per-element guards
           const int c0 = ch << 4;
-          if constexpr (MODE == 1) {
+          const int cbase = col0 + c0;
+          // column factors of this chunk (per-column scale vector or the scalar)
+          float cs[16];
+          if (p.c_scale_vec) {
 #pragma unroll
-            for (int j = 0; j < 16; j += 2) {
-              const int cc = col0 + c0 + j;
-              const float cs_a = p.c_scale_vec ? (cc < p.C ? p.c_scale[cc] : 0.f) : cs0;
-              const float cs_b = p.c_scale_vec ? (cc + 1 < p.C ? p.c_scale[cc + 1] : 0.f) : cs0;
-              const float oa = cs_a * (rs * a[j]) + bias_r;
-              const float ob = cs_b * (rs * a[j + 1]) + bias_r;
-              const float send = (lane & 1) ? oa : ob;
-              const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
-              const float lo_ = (lane & 1) ? recv : oa;
-              const float hi_ = (lane & 1) ? ob : recv;
-              uint32_t packed;
-              if (p.out_bf16) {
-                __nv_bfloat162 t = __floats2bfloat162_rn(lo_, hi_);
-                packed = *reinterpret_cast<uint32_t*>(&t);
-              } else {
-                __half2 t = __floats2half2_rn(lo_, hi_);
-                packed = *reinterpret_cast<uint32_t*>(&t);
-              }
-              const int m_local = c0 + j + (lane & 1);
-              const uint32_t addr = staging + (uint32_t)m_local * (BM * 2) + (uint32_t)(wq * 32 + (lane & ~1)) * 2u;
-              asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(packed) : "memory");
-            }
-          } else if constexpr (MODE == 2) {
-            if (r_ok) {
-#pragma unroll
-              for (int j = 0; j < 16; j++) {
-                const int cc = col0 + c0 + j;
-                if (cc < p.C) {
-                  const float cs = p.c_scale_vec ? p.c_scale[cc] : cs0;
-                  out16[(int64_t)cc * p.ldo + r] = from_f32(cs * (rs * a[j]) + bias_r);
-                }
-              }
-            }
+            for (int j = 0; j < 16; j++) cs[j] = (full || cbase + j < p.C) ? __ldg(p.c_scale + cbase + j) : 0.f;
           } else {
+#pragma unroll
+            for (int j = 0; j < 16; j++) cs[j] = cs0;
+          }
+          if constexpr (MODE == 0) {
+            // out[r][c] = a_s[r] * (b_s[c] * acc) (+ bias[c])
+#pragma unroll
+            for (int j = 0; j < 16; j++) a[j] = rs * (cs[j] * a[j]);
+            if (bias16) {
+#pragma unroll
+              for (int j = 0; j < 16; j++)
+                if (full || cbase + j < p.C) a[j] += to_f32(bias16[cbase + j]);
+            }
             if (r_ok) {
               uint32_t h[8];
 #pragma unroll
-              for (int j = 0; j < 16; j += 2) {
-                float o[2];
-#pragma unroll
-                for (int e = 0; e < 2; e++) {
-                  const int cc = col0 + c0 + j + e;
-                  o[e] = 0.f;
-                  if (cc < p.C) {
-                    const float cs = p.c_scale_vec ? p.c_scale[cc] : cs0;
-                    o[e] = rs * (cs * a[j + e]);
-                    if (bias16) o[e] += to_f32(bias16[cc]);
-                  }
-                }
-                h[j >> 1] = (uint32_t)from_f32(o[0]) | ((uint32_t)from_f32(o[1]) << 16);
-              }
-              uint16_t* dst = out16 + (int64_t)r * p.ldo + col0 + c0;
-              if (col0 + c0 + 16 <= p.C && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+              for (int j = 0; j < 8; j++) h[j] = pack2(a[2 * j], a[2 * j + 1]);
+              uint16_t* dst = out16 + (int64_t)r * p.ldo + cbase;
+              if (full && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
                 reinterpret_cast<uint4*>(dst)[0] = make_uint4(h[0], h[1], h[2], h[3]);
                 reinterpret_cast<uint4*>(dst)[1] = make_uint4(h[4], h[5], h[6], h[7]);
               } else {
 #pragma unroll
                 for (int j = 0; j < 16; j++)
-                  if (col0 + c0 + j < p.C) dst[j] = (uint16_t)(h[j >> 1] >> ((j & 1) * 16));
+                  if (cbase + j < p.C) dst[j] = (uint16_t)(h[j >> 1] >> ((j & 1) * 16));
               }
             }
+          } else {
+            // out[c][r] = a_s[c] * (b_s[r] * acc) + bias[r]
+#pragma unroll
+            for (int j = 0; j < 16; j++) a[j] = cs[j] * (rs * a[j]) + bias_r;
+            if constexpr (MODE == 1) {
+#pragma unroll
+              for (int j = 0; j < 16; j += 2) {
+                const float oa = a[j], ob = a[j + 1];
+                const float send = (lane & 1) ? oa : ob;
+                const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
+                const uint32_t packed = pack2((lane & 1) ? recv : oa, (lane & 1) ? ob : recv);
+                const int m_local = c0 + j + (lane & 1);
+                const uint32_t addr = staging + (uint32_t)m_local * (BM * 2) + (uint32_t)(wq * 32 + (lane & ~1)) * 2u;
+                asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(packed) : "memory");
+              }
+            } else if (r_ok) {
+#pragma unroll
+              for (int j = 0; j < 16; j++)
+                if (full || cbase + j < p.C) out16[(int64_t)(cbase + j) * p.ldo + r] = from_f32(a[j]);
+            }
           }
+        };
+        auto emit = [&](auto mode_tag, float (&a)[16], int ch) {
+          if (col0 + (ch << 4) + 16 <= p.C) emit_body(mode_tag, std::true_type{}, a, ch);
+          else emit_body(mode_tag, std::false_type{}, a, ch);
         };
         auto drain = [&](auto mode_tag) {
 #pragma unroll 1
@@ -622,8 +625,10 @@ static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, const CUtensor
   if (units < p.pairs) p.pairs = (int)units;
   // many tiles per pair: whole tiles in a grouped raster (L2 locality; the tail wave costs < 1 / (tiles / pairs));
   // few: stream-K so every pair streams the same number of k-blocks
-  p.interleave = (!p.swap && tiles >= 4 * (int64_t)p.pairs) ? 1 : 0;
-  p.raster_group = p.interleave ? 8 : 0;
+  // (decode with more weight tiles than pairs, e.g. gate_up: whole tiles too -- the fp32 partial round trip of
+  // a split tile costs more than the idle half wave, timeline in profiles/r1c_gemm_v3.md)
+  p.interleave = ((!p.swap && tiles >= 4 * (int64_t)p.pairs) || (p.swap && tiles >= (int64_t)p.pairs)) ? 1 : 0;
+  p.raster_group = (p.interleave && !p.swap) ? 8 : 0;
   gemm_fp8_v3_kernel<BN><<<p.pairs * 2, NTHREADS, smem, stream>>>(tmR, tmC, tmO, p);
   B200_LAUNCH_CHECK();
   return B200_OK;
