@@ -169,6 +169,49 @@ B200_API size_t b200_paged_attention_workspace_bytes(int num_seqs, int num_heads
 B200_API int b200_paged_attention_decode(const b200_paged_attn_args* args, b200_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Variable-length paged attention: prefill, chunked prefill and mixed batches (query_len >= 1).
+ * Replaces the query_len > 1 branch of AttentionImpl.forward (vllm/v1/attention/backend.py:895-934)
+ * as implemented by unified_attention (vllm/v1/attention/ops/triton_unified_attention.py:802-1140,
+ * kernel :179-683; reference semantics tests/kernels/attention/test_triton_unified_attention.py:33-88)
+ * and flash_attn_varlen_func(..., block_table=...) (vllm/v1/attention/backends/flash_attn.py:1084).
+ *   q:   [num_tokens, num_heads, head_size] bf16 / f16, packed; cu_seqlens_q: int32 [num_seqs + 1]
+ *   k_cache / v_cache: [num_blocks, block_size, num_kv_heads, head_size] (strided), q dtype or e4m3
+ *   seq_lens: int32 [num_seqs] = context length + query length; block_table: int32 [num_seqs, bt_stride]
+ *   query token i of sequence s (context c = seq_len - query_len) attends kv positions j <= c + i, and
+ *   with sliding_window W > 0 only those with (c + i - j) < W (W = 1 + window_size[0] of the reference).
+ *   softcap: s -> softcap * tanh(s / softcap) before masking; ALiBi adds slope * (j - c) (kernel :392-397).
+ *   out: [num_tokens, num_heads, head_size] q dtype, or e4m3 when output_scale is set;
+ *   lse: optional float [num_tokens, num_heads], natural log.
+ * Device-only inputs, no host sync, CUDA-graph safe. head_size 64 / 128, block_size % 16 == 0.
+ */
+typedef struct b200_varlen_attn_args {
+  void* out;
+  float* lse; /* nullable */
+  const void* q;
+  const void* k_cache;
+  const void* v_cache;
+  const int32_t* cu_seqlens_q;
+  const int32_t* seq_lens;
+  const int32_t* block_table;
+  const float* k_scale;      /* device scalar; nullable => 1.0 */
+  const float* v_scale;      /* device scalar; nullable => 1.0 */
+  const float* alibi_slopes; /* [num_heads] float, nullable */
+  const float* output_scale; /* nullable: fused static FP8 output */
+  int64_t q_stride_t, q_stride_h;     /* elements */
+  int64_t out_stride_t, out_stride_h; /* elements of the out dtype */
+  int64_t kv_block_stride, kv_token_stride, kv_head_stride; /* elements of the kv dtype */
+  int64_t bt_stride;
+  int32_t num_seqs, num_tokens, num_heads, num_kv_heads, head_size, block_size;
+  int32_t q_dtype, kv_dtype;
+  int32_t causal;         /* must be 1 */
+  int32_t sliding_window; /* <= 0: none */
+  float scale;
+  float softcap; /* <= 0: none */
+} b200_varlen_attn_args;
+
+B200_API int b200_paged_attention_varlen(const b200_varlen_attn_args* args, b200_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
  * FP8 W8A8 GEMM with scale epilogue (tcgen05 / TMEM / TMA).
  * Replaces torch.ops._C.cutlass_scaled_mm
  *   (csrc/libtorch_stable/quantization/w8a8/cutlass/scaled_mm_entry.cu:197-270; sm100 kernels

@@ -287,6 +287,61 @@ def paged_attention_decode(query, key_cache, value_cache, block_table, seq_lens,
 # FP8 GEMM.  Baseline of the reference's own test: tests/kernels/utils.py:1130-1173
 # (baseline_scaled_mm): torch.mm(scale_a * a.float(), scale_b * b.float()).to(out_dtype) + bias
 # --------------------------------------------------------------------------------------------
+def paged_attention_varlen(query, key_cache, value_cache, query_lens, kv_lens, block_table, scale,
+                           k_scale=None, v_scale=None, alibi_slopes=None, sliding_window=None,
+                           softcap=None, return_lse=False):
+    """Variable-length causal paged attention (prefill / chunked prefill / mixed batches).
+    Restates ref_paged_attn (tests/kernels/attention/test_triton_unified_attention.py:33-88): query
+    [T,Hq,D] packed, query_lens / kv_lens python lists, caches [nb,bs,Hkv,D]; query token i of a
+    sequence with context c = kv_len - query_len sees kv positions j <= c + i (triu diagonal
+    kv_len - query_len + 1), sliding window keeps (c + i - j) < sliding_window (:71-79), soft-cap
+    before masking (:80-81). FP8 dequant = fp8.float() * scale; ALiBi adds slope * (j - c)
+    (apply_alibi_to_score, triton_attention_helpers.py:396-397). Returns float32 [T,Hq,D]
+    (and natural-log LSE [T,Hq])."""
+    q = _f32(query)
+    T, Hq, D = q.shape
+    kc, vc = _cache_f32(key_cache), _cache_f32(value_cache)
+    nb, bs, Hkv, _ = kc.shape
+    g = Hq // Hkv
+    ks = 1.0 if k_scale is None else float(_f32(k_scale).reshape(-1)[0])
+    vs = 1.0 if v_scale is None else float(_f32(v_scale).reshape(-1)[0])
+    bt = block_table.cpu().numpy()
+    out = np.zeros((T, Hq, D), dtype=np.float32)
+    lse = np.full((T, Hq), -np.inf, dtype=np.float32)
+    start = 0
+    for s, (ql, L) in enumerate(zip(query_lens, kv_lens)):
+        ql, L = int(ql), int(L)
+        if ql == 0:
+            continue
+        ctx = L - ql
+        nblk = (L + bs - 1) // bs
+        idx = bt[s, :nblk]
+        k = kc[idx].reshape(-1, Hkv, D)[:L].astype(np.float64) * ks
+        v = vc[idx].reshape(-1, Hkv, D)[:L].astype(np.float64) * vs
+        k = np.repeat(k, g, axis=1)
+        v = np.repeat(v, g, axis=1)
+        att = np.einsum("qhd,khd->hqk", q[start:start + ql].astype(np.float64) * scale, k)
+        if softcap is not None and softcap > 0:
+            att = softcap * np.tanh(att / softcap)
+        qi = np.arange(ql)[:, None]
+        kj = np.arange(L)[None, :]
+        if alibi_slopes is not None:
+            att = att + _f32(alibi_slopes).astype(np.float64)[:, None, None] * (kj - ctx)[None, :, :]
+        mask = kj > ctx + qi
+        if sliding_window is not None and sliding_window > 0:
+            mask = mask | ((ctx + qi - kj) >= sliding_window)
+        att = np.where(mask[None, :, :], -np.inf, att)
+        m = att.max(axis=2, keepdims=True)
+        p = np.exp(att - m)
+        den = p.sum(axis=2, keepdims=True)
+        out[start:start + ql] = np.einsum("hqk,khd->qhd", p / den, v).astype(np.float32)
+        lse[start:start + ql] = (m[:, :, 0] + np.log(den[:, :, 0])).T.astype(np.float32)
+        start += ql
+    if return_lse:
+        return out, lse
+    return out
+
+
 def scaled_mm(a_bits, b_bits_nk, scale_a, scale_b, bias=None) -> np.ndarray:
     """a_bits uint8 [M,K] (e4m3), b_bits_nk uint8 [N,K] (the weight; b = weight.T), scales float32
     ([1] / [M] / [N]); returns float64-accumulated float32 [M,N] (no output rounding)."""

@@ -71,6 +71,47 @@ def test_attention_oracle_matches_reference_cpu_kernel(path):
     assert np.abs(out - golden).mean() < 5e-4
 
 
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "cpu_varlen_*.npz"))))
+def test_varlen_attention_oracle_matches_reference_cpu_kernel(path):
+    """oracle paged_attention_varlen (query_len > 1: prefill / chunked prefill / mixed batches) vs the
+    outputs of the reference's own CPU kernel cpu_attention_with_kv_cache on the same packed queries
+    (fixtures made by tests/golden/make_golden.py, VARLEN_CASES)."""
+    z = np.load(path)
+    Hq, Hkv, D, bs, nb, win = [int(v) for v in z["meta"]]
+    q = bits_to_bf16(z["query"])
+    key, value = bits_to_bf16(z["key"]), bits_to_bf16(z["value"])
+    _, kc, vc = make_kv_cache(nb, bs, Hkv, D, torch.bfloat16, "NHD")
+    one = torch.ones(1)
+    ref_ops.reshape_and_cache_flash(key, value, kc, vc, torch.from_numpy(z["slot_mapping"]), "auto", one, one)
+    out = ref_ops.paged_attention_varlen(
+        q, kc, vc, z["query_lens"].tolist(), z["seq_lens"].tolist(), torch.from_numpy(z["block_table"]),
+        float(z["scale"][0]), sliding_window=win or None, softcap=float(z["softcap"][0]) or None)
+    golden = bits_to_bf16(z["out"]).float().numpy()
+    np.testing.assert_allclose(out, golden, atol=4e-3, rtol=8e-3)
+    assert np.abs(out - golden).mean() < 5e-4
+
+
+def test_varlen_oracle_reduces_to_decode_oracle():
+    """query_len == 1 rows of the varlen oracle are the decode oracle (incl. LSE, ALiBi, FP8 scales)."""
+    g = torch.Generator().manual_seed(3)
+    lens = [77, 300, 16, 1]
+    Hq, Hkv, D, bs = 8, 2, 64, 16
+    nb = 4 * 19 + 3
+    bt = torch.randperm(nb, generator=g)[: 4 * 19].to(torch.int32).view(4, 19)
+    kc = torch.randint(0, 0x78, (nb, bs, Hkv, D), generator=g, dtype=torch.uint8)
+    vc = torch.randint(0, 0x78, (nb, bs, Hkv, D), generator=g, dtype=torch.uint8)
+    q = (torch.rand(4, Hq, D, generator=g) * 2 - 1).to(torch.bfloat16)
+    ks, vs = torch.tensor([0.01]), torch.tensor([0.02])
+    slopes = torch.tensor([0.5 ** (i + 1) for i in range(Hq)])
+    a, la = ref_ops.paged_attention_varlen(q, kc, vc, [1] * 4, lens, bt, 0.125, k_scale=ks, v_scale=vs,
+                                           alibi_slopes=slopes, sliding_window=100, return_lse=True)
+    b, lb = ref_ops.paged_attention_decode(q, kc, vc, bt, torch.tensor(lens, dtype=torch.int32), 0.125,
+                                           k_scale=ks, v_scale=vs, alibi_slopes=slopes, sliding_window=100,
+                                           return_lse=True)
+    np.testing.assert_allclose(a, b, atol=1e-6, rtol=1e-6)
+    np.testing.assert_allclose(la, lb, atol=1e-5, rtol=1e-6)
+
+
 @pytest.mark.parametrize("hidden", [17, 1024, 1025, 5137])
 @pytest.mark.parametrize("tokens", [1, 7, 33])
 def test_per_token_quant_restatement_vs_reference_python_oracle(hidden, tokens):

@@ -61,6 +61,45 @@ class PagedAttnArgs(C.Structure):
     ]
 
 
+class VarlenAttnArgs(C.Structure):
+    """struct b200_varlen_attn_args (include/b200ops.h)."""
+
+    _fields_ = [
+        ("out", c_void_p),
+        ("lse", c_void_p),
+        ("q", c_void_p),
+        ("k_cache", c_void_p),
+        ("v_cache", c_void_p),
+        ("cu_seqlens_q", c_void_p),
+        ("seq_lens", c_void_p),
+        ("block_table", c_void_p),
+        ("k_scale", c_void_p),
+        ("v_scale", c_void_p),
+        ("alibi_slopes", c_void_p),
+        ("output_scale", c_void_p),
+        ("q_stride_t", c_int64),
+        ("q_stride_h", c_int64),
+        ("out_stride_t", c_int64),
+        ("out_stride_h", c_int64),
+        ("kv_block_stride", c_int64),
+        ("kv_token_stride", c_int64),
+        ("kv_head_stride", c_int64),
+        ("bt_stride", c_int64),
+        ("num_seqs", C.c_int32),
+        ("num_tokens", C.c_int32),
+        ("num_heads", C.c_int32),
+        ("num_kv_heads", C.c_int32),
+        ("head_size", C.c_int32),
+        ("block_size", C.c_int32),
+        ("q_dtype", C.c_int32),
+        ("kv_dtype", C.c_int32),
+        ("causal", C.c_int32),
+        ("sliding_window", C.c_int32),
+        ("scale", c_float),
+        ("softcap", c_float),
+    ]
+
+
 # name -> (restype, argtypes); every symbol include/b200ops.h declares must be listed here
 # (tests/test_abi.py cross-checks this table against the header).
 SIGNATURES = {
@@ -175,6 +214,7 @@ SIGNATURES = {
                 c_void_p]),
     "b200_paged_attention_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200_paged_attention_decode": (c_int, [C.POINTER(PagedAttnArgs), c_void_p]),
+    "b200_paged_attention_varlen": (c_int, [C.POINTER(VarlenAttnArgs), c_void_p]),
 }
 
 _lib = None

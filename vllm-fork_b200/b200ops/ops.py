@@ -648,6 +648,95 @@ def paged_attention_workspace(num_seqs: int, num_heads: int, num_kv_heads: int, 
     return ws
 
 
+def unified_attention(
+    q: torch.Tensor,
+    k: torch.Tensor,
+    v: torch.Tensor,
+    out: torch.Tensor,
+    cu_seqlens_q: torch.Tensor,
+    max_seqlen_q: int,
+    seqused_k: torch.Tensor,
+    max_seqlen_k: int,
+    softmax_scale: float,
+    causal: bool,
+    window_size,
+    block_table: torch.Tensor,
+    softcap: float,
+    q_descale,
+    k_descale: torch.Tensor | None,
+    v_descale: torch.Tensor | None,
+    alibi_slopes: torch.Tensor | None = None,
+    output_scale: torch.Tensor | None = None,
+    sinks: torch.Tensor | None = None,
+    lse: torch.Tensor | None = None,
+) -> torch.Tensor:
+    """Variable-length (prefill / chunked-prefill / mixed) paged attention; same positional arguments as
+    the reference's unified_attention (vllm/v1/attention/ops/triton_unified_attention.py:802-826).
+
+    q / out [T, Hq, D] packed over sequences (cu_seqlens_q int32 [S+1]); k / v = key_cache / value_cache
+    [num_blocks, block_size, Hkv, D] views (strides forwarded); seqused_k int32 [S] = context + query
+    length; block_table int32 [S, max_blocks]; window_size = (left, right) as FlashAttention, (-1, -1) =
+    none (the kernel's SLIDING_WINDOW is 1 + left, :1128); k_descale / v_descale: device f32 scalars for
+    FP8 caches; output_scale: `out` is float8_e4m3fn and receives e4m3(attention / output_scale).
+    Semantics: ref_paged_attn, tests/kernels/attention/test_triton_unified_attention.py:33-88.
+    max_seqlen_q / max_seqlen_k are accepted for signature parity (the kernel reads lengths on device).
+    lse (extension): optional float32 [T, Hq] natural-log LSE."""
+    _cuda(q, k, v, out, cu_seqlens_q, seqused_k, block_table, k_descale, v_descale, alibi_slopes, output_scale, lse)
+    lib = _lib.load()
+    if not causal:
+        raise RuntimeError("unified_attention: only causal attention is supported")
+    if q_descale is not None:
+        raise RuntimeError("unified_attention: q_descale (FP8 query) is not supported")
+    if sinks is not None:
+        raise RuntimeError("unified_attention: attention sinks are not supported")
+    if (output_scale is not None) != (out.element_size() == 1):
+        raise RuntimeError("unified_attention: out must be fp8 exactly when output_scale is given")
+    if q.dim() != 3 or k.dim() != 4 or v.dim() != 4:
+        raise RuntimeError("unified_attention: q must be 3-D and the caches 4-D")
+    if q.stride(2) != 1 or out.stride(2) != 1 or k.stride(3) != 1:
+        raise RuntimeError("unified_attention: last dimension must be contiguous")
+    if k.stride() != v.stride() or k.shape != v.shape:
+        raise RuntimeError("unified_attention: key_cache and value_cache must share shape and strides")
+    if block_table.dtype != torch.int32 or seqused_k.dtype != torch.int32 or cu_seqlens_q.dtype != torch.int32:
+        raise RuntimeError("unified_attention: block_table, seqused_k and cu_seqlens_q must be int32")
+    if block_table.stride(1) != 1 or not cu_seqlens_q.is_contiguous() or not seqused_k.is_contiguous():
+        raise RuntimeError("unified_attention: index tensors must be contiguous")
+    T, Hq, D = q.shape
+    nb, bs, Hkv, Dk = k.shape
+    S = seqused_k.numel()
+    if Dk != D or out.shape != q.shape:
+        raise RuntimeError("unified_attention: shape mismatch between q, out and the cache")
+    if cu_seqlens_q.numel() != S + 1 or block_table.shape[0] < S:
+        raise RuntimeError("unified_attention: cu_seqlens_q must have num_seqs + 1 entries")
+    kv_fp8 = k.element_size() == 1
+    if kv_fp8 and (k_descale is None or v_descale is None):
+        raise RuntimeError("unified_attention: fp8 kv cache needs k_descale and v_descale")
+    if lse is not None and (lse.dtype != torch.float32 or lse.shape != (T, Hq) or not lse.is_contiguous()):
+        raise RuntimeError("unified_attention: lse must be contiguous float32 [num_tokens, num_heads]")
+    left = -1 if window_size is None else int(window_size[0])
+    a = _lib.VarlenAttnArgs()
+    a.out, a.lse, a.q = _p(out), _p(lse), _p(q)
+    a.k_cache, a.v_cache = _p(k), _p(v)
+    a.cu_seqlens_q, a.seq_lens, a.block_table = _p(cu_seqlens_q), _p(seqused_k), _p(block_table)
+    a.k_scale, a.v_scale = _p(k_descale), _p(v_descale)
+    a.alibi_slopes, a.output_scale = _p(alibi_slopes), _p(output_scale)
+    a.q_stride_t, a.q_stride_h = q.stride(0), q.stride(1)
+    a.out_stride_t, a.out_stride_h = out.stride(0), out.stride(1)
+    a.kv_block_stride, a.kv_token_stride, a.kv_head_stride = k.stride(0), k.stride(1), k.stride(2)
+    a.bt_stride = block_table.stride(0)
+    a.num_seqs, a.num_tokens, a.num_heads, a.num_kv_heads, a.head_size, a.block_size = S, T, Hq, Hkv, D, bs
+    a.q_dtype = _dt(q)
+    a.kv_dtype = FP8_E4M3 if kv_fp8 else _dt(k)
+    a.causal = 1
+    a.sliding_window = left + 1 if left >= 0 else 0
+    a.scale = float(softmax_scale)
+    a.softcap = float(softcap) if softcap else 0.0
+    import ctypes
+    rc = lib.b200_paged_attention_varlen(ctypes.byref(a), _stream())
+    _lib.check(rc, "unified_attention")
+    return out
+
+
 def paged_attention_decode(
     out: torch.Tensor,
     query: torch.Tensor,
