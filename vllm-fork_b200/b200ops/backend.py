@@ -9,9 +9,12 @@ Mirrors the plug point of vllm/v1/attention/backend.py (AttentionBackend :56-401
   dim, physical order NHD (stride order (0, 2, 1, 3)); views
   ``key_cache, value_cache = kv_cache.transpose(1, 2).split(head_size, dim=-1)``.
 * ``forward_includes_kv_cache_update = False``: the KV write is ``do_kv_cache_update`` ->
-  reshape_and_cache_flash; ``forward`` is the paged decode attention.
-* decode-only kernel => CUDA-graph support level UNIFORM_SINGLE_TOKEN_DECODE; the metadata builder
-  owns the persistent split-KV workspace.
+  reshape_and_cache_flash; ``forward`` is the paged attention: the split-KV decode kernel when every
+  request has one query token (max_query_len == 1), the variable-length kernel (unified_attention:
+  prefill / chunked prefill / mixed batches) otherwise - the same dispatch triton_attn.py makes between
+  its 2-D and 3-D kernels.
+* both kernels read lengths / tables on the device (no host sync) => CUDA-graph support level ALWAYS;
+  the metadata builder owns the persistent split-KV workspace.
 
 With B200OPS_VLLM_BASES=1 (set by the plugin before importing this module) the classes derive from
 vLLM's ABCs and `register()` installs the backend in the CUSTOM slot
@@ -50,8 +53,8 @@ if not _HAVE_VLLM:
 
 @dataclasses.dataclass
 class B200AttentionMetadata:
-    """Per-step decode metadata (the subset of TritonAttentionMetadata, triton_attn.py:59-131,
-    a decode-only kernel needs)."""
+    """Per-step metadata (the subset of TritonAttentionMetadata, triton_attn.py:59-131, the two kernels
+    need)."""
     num_actual_tokens: int
     max_query_len: int
     max_seq_len: int
@@ -65,8 +68,8 @@ class B200AttentionMetadata:
 class B200AttentionMetadataBuilder(_BuilderBase):
     """Builds B200AttentionMetadata from CommonAttentionMetadata (backend.py:404-600)."""
 
-    # AttentionCGSupport.UNIFORM_SINGLE_TOKEN_DECODE (decode-only kernel)
-    _cudagraph_support = "UNIFORM_SINGLE_TOKEN_DECODE"
+    # AttentionCGSupport.ALWAYS: decode and variable-length kernels are both graph-safe
+    _cudagraph_support = "ALWAYS"
 
     def __init__(self, kv_cache_spec=None, layer_names=None, vllm_config=None, device=None,
                  num_heads: int | None = None, num_kv_heads: int | None = None,
@@ -89,10 +92,6 @@ class B200AttentionMetadataBuilder(_BuilderBase):
 
     def build(self, common_prefix_len: int, common_attn_metadata, fast_build: bool = False):
         m = common_attn_metadata
-        if m.max_query_len > 1:
-            raise NotImplementedError(
-                "B200AttentionBackend is a decode-only backend (max_query_len must be 1); prefill "
-                "needs a second backend (SURVEY.md section 8f rank 3)")
         return B200AttentionMetadata(
             num_actual_tokens=m.num_actual_tokens, max_query_len=m.max_query_len,
             max_seq_len=m.max_seq_len, query_start_loc=m.query_start_loc, seq_lens=m.seq_lens,
@@ -172,6 +171,17 @@ class B200AttentionImpl(_ImplBase):
             self.alibi_slopes = self.alibi_slopes.to(query.device)
         q = query[:n].view(n, self.num_heads, self.head_size)
         o = output[:n].view(n, self.num_heads, self.head_size)
+        if attn_metadata.max_query_len > 1:
+            # prefill / chunked prefill / mixed batch (triton_attn.py:735-770 -> unified_attention)
+            S = attn_metadata.seq_lens.numel()
+            win = (self.sliding_window - 1, 0) if self.sliding_window else (-1, -1)
+            ops.unified_attention(
+                q, key_cache, value_cache, o, attn_metadata.query_start_loc[: S + 1], attn_metadata.max_query_len,
+                attn_metadata.seq_lens, attn_metadata.max_seq_len, self.scale, True, win,
+                attn_metadata.block_table, self.logits_soft_cap or 0.0, None,
+                layer._k_scale if fp8 else None, layer._v_scale if fp8 else None,
+                alibi_slopes=self.alibi_slopes, output_scale=output_scale, lse=lse)
+            return output
         ops.paged_attention_decode(
             o, q, key_cache, value_cache, attn_metadata.block_table[:n], attn_metadata.seq_lens[:n],
             self.scale, k_scale=layer._k_scale if fp8 else None, v_scale=layer._v_scale if fp8 else None,
