@@ -252,6 +252,16 @@ B200_API int b200_fp8_gemm_v3(void* out, const void* a, const void* b, const flo
                               int out_dtype, void* workspace, size_t workspace_bytes,
                               b200_stream_t stream);
 
+/* Same contract as b200_fp8_gemm for decode batches (M <= 256) whose N gives fewer 256-row weight tiles than the
+ * chip has CTA pairs: the K range of each tile is split over the `split` CTA pairs of one thread-block cluster
+ * (tcgen05.mma.cta_group::2 per pair), the fp32 partials are reduce-scattered through distributed shared memory
+ * and summed in pair order (deterministic). split = 0 picks the largest split (<= 4) that keeps all clusters
+ * co-resident. No workspace. out must be 16-byte aligned with ldo * 2 a multiple of 16. */
+B200_API int b200_fp8_gemm_splitk(void* out, const void* a, const void* b, const float* a_scale,
+                                  const float* b_scale, const void* bias, int M, int N, int K, int64_t lda,
+                                  int64_t ldb, int64_t ldo, int a_scale_per_row, int b_scale_per_col,
+                                  int out_dtype, int split, b200_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Gated activation between the MLP / MoE GEMMs.
  * Replaces torch.ops._C.silu_and_mul (csrc/libtorch_stable/activation_kernels.cu:102-160,291-296):

@@ -170,3 +170,61 @@ def test_scaled_mm_silu_and_mul_quant_validation():
     w2 = torch.zeros(192, 128, dtype=torch.uint8, device=DEV).view(torch.float8_e4m3fn)
     with pytest.raises(NotImplementedError, match="multiple of 128"):
         ops.scaled_mm_silu_and_mul_quant(torch.empty(8, 96, dtype=torch.float8_e4m3fn, device=DEV), a[:8], w2, one, one, one)
+
+
+# ------------------------------------------------------------------ v4: cluster split-K over DSMEM (decode batches)
+V4_MNK = [(1, 256, 128), (16, 4096, 4096), (33, 1024, 1024), (64, 4096, 14336), (100, 6144, 4096),
+          (128, 8192, 8192), (200, 272, 512), (256, 4096, 4096), (256, 6144, 4096), (256, 4096, 14336)]
+
+
+@pytest.mark.parametrize("split", [0, 1, 2, 3, 4])
+@pytest.mark.parametrize("mnk", V4_MNK)
+def test_splitk_shapes(mnk, split):
+    M, N, K = mnk
+    if split > (K + 127) // 128:
+        pytest.skip("more K slices than k-blocks")
+    run_case(M, N, K, False, False, torch.bfloat16, False, impl="v4" if split == 0 else f"v4:{split}")
+
+
+@pytest.mark.parametrize("mnk", [(33, 1024, 1024), (256, 4096, 4096)])
+@pytest.mark.parametrize("per_token,per_channel", [(True, False), (False, True), (True, True)])
+@pytest.mark.parametrize("out_dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("use_bias", [False, True])
+def test_splitk_scales_bias_dtypes(mnk, per_token, per_channel, out_dtype, use_bias):
+    run_case(*mnk, per_token, per_channel, out_dtype, use_bias, seed=1, impl="v4")
+
+
+def test_splitk_exact_and_equal_to_v2():
+    """(a) integer-valued operands: bit-exact whatever the split; (b) random operands: the K slices are summed
+    in a different order than the unsplit kernel, so only output-rounding-level differences vs v2 are allowed
+    and split = 1 must be bit-identical to v2."""
+    g = torch.Generator().manual_seed(3)
+    one = torch.tensor([0.5], device=DEV)
+    for M, N, K in [(7, 256, 128), (130, 384, 512), (256, 256, 1024), (256, 4096, 4096), (64, 1024, 14336)]:
+        a = torch.randint(-2, 3, (M, K), generator=g).float()
+        w = torch.randint(-2, 3, (N, K), generator=g).float()
+        ref = ((a.double() @ w.double().t()).float() * 0.25).to(torch.bfloat16).float()
+        ag = to_fp8_bits(a).to(DEV).view(torch.float8_e4m3fn)
+        wg = to_fp8_bits(w).to(DEV).view(torch.float8_e4m3fn).t()
+        for split in (0, 1, 2, 3, 4):
+            if split > K // 128:
+                continue
+            out = _ops().cutlass_scaled_mm(ag, wg, one, one, torch.bfloat16, impl="v4" if split == 0 else f"v4:{split}")
+            assert torch.equal(out.float().cpu(), ref), (M, N, K, split)
+    a8 = to_fp8_bits(torch.randn(256, 4096, generator=g)).to(DEV).view(torch.float8_e4m3fn)
+    w8 = to_fp8_bits(torch.randn(6144, 4096, generator=g)).to(DEV).view(torch.float8_e4m3fn).t()
+    sa, sb = torch.tensor([0.03], device=DEV), torch.tensor([0.02], device=DEV)
+    o2 = _ops().cutlass_scaled_mm(a8, w8, sa, sb, torch.bfloat16, impl="v2")
+    o1 = _ops().cutlass_scaled_mm(a8, w8, sa, sb, torch.bfloat16, impl="v4:1")
+    o3 = _ops().cutlass_scaled_mm(a8, w8, sa, sb, torch.bfloat16, impl="v4:3")
+    assert torch.equal(o1, o2)
+    assert (o3.float() - o2.float()).abs().max().item() <= 2 ** -7 * o2.float().abs().max().item()
+    assert (o3 == o2).float().mean().item() > 0.98
+
+
+def test_splitk_rejects_large_batches():
+    x = torch.zeros(300, 256, dtype=torch.uint8, device=DEV).view(torch.float8_e4m3fn)
+    w = torch.zeros(256, 256, dtype=torch.uint8, device=DEV).view(torch.float8_e4m3fn).t()
+    one = torch.ones(1, device=DEV)
+    with pytest.raises(RuntimeError, match="decode batches only"):
+        _ops().cutlass_scaled_mm(x, w, one, one, torch.bfloat16, impl="v4")

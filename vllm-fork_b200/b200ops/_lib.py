@@ -132,6 +132,11 @@ SIGNATURES = {
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64,
          c_int64, c_int64, c_int, c_int, c_int, c_void_p],
     ),
+    "b200_fp8_gemm_splitk": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64,
+         c_int64, c_int64, c_int, c_int, c_int, c_int, c_void_p],
+    ),
     "b200_fp8_gemm_silu_mul_fp8": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64,

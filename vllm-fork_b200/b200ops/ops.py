@@ -343,8 +343,21 @@ def cutlass_scaled_mm(
     if which == "auto":
         # decode batches go to v3 only when there are at least as many 256-row weight tiles as CTA pairs
         # (gate_up: 34.4 vs 38.7 us at batch 256)
-        which = "v3" if (M > 256 or N >= 256 * (_sm_count(a.device) // 2)) else "v2"
-    if which == "v3":
+        pairs = _sm_count(a.device) // 2
+        tiles = (N + 255) // 256
+        if M > 256 or tiles >= pairs:
+            which = "v3"
+        elif (tiles * 2 <= pairs and (M <= 64 or K >= 8192) and out.data_ptr() % 16 == 0
+              and (out.stride(0) * 2) % 16 == 0):
+            # few weight tiles and either a long K (down_proj: 24.5 vs 33.6 us at batch 256) or a small batch
+            # (9.3 vs 11.7 us at batch 16): split K over the CTA pairs of a cluster (csrc/gemm_fp8_v4.cu)
+            which = "v4"
+        else:
+            which = "v2"
+    if which.startswith("v4"):   # "v4" (auto split) or "v4:<split>"
+        split = int(which[3:]) if len(which) > 3 else 0
+        rc = lib.b200_fp8_gemm_splitk(*common, split, _stream())
+    elif which == "v3":
         ws = _gemm_workspace(a.device)
         rc = lib.b200_fp8_gemm_v3(*common, _p(ws), ws.numel(), _stream())
     else:
