@@ -183,6 +183,8 @@ B200_API int b200_paged_attention_decode(const b200_paged_attn_args* args, b200_
  *   out: [num_tokens, num_heads, head_size] q dtype, or e4m3 when output_scale is set;
  *   lse: optional float [num_tokens, num_heads], natural log.
  * Device-only inputs, no host sync, CUDA-graph safe. head_size 64 / 128, block_size % 16 == 0.
+ * Two kernels behind this entry point: tcgen05 / TMEM / TMA (bf16 / f16 caches, head_size 128; csrc/attention_prefill_tc.cuh)
+ * and mma.sync (FP8 caches, head_size 64; csrc/attention_prefill.cu). B200_PREFILL_IMPL=mma forces the second one.
  */
 typedef struct b200_varlen_attn_args {
   void* out;
@@ -201,6 +203,7 @@ typedef struct b200_varlen_attn_args {
   int64_t out_stride_t, out_stride_h; /* elements of the out dtype */
   int64_t kv_block_stride, kv_token_stride, kv_head_stride; /* elements of the kv dtype */
   int64_t bt_stride;
+  int64_t num_blocks; /* physical blocks in the cache (bounds the TMA descriptors of the tcgen05 kernel) */
   int32_t num_seqs, num_tokens, num_heads, num_kv_heads, head_size, block_size;
   int32_t q_dtype, kv_dtype;
   int32_t causal;         /* must be 1 */

@@ -22,6 +22,17 @@ def _ops():
     return ops
 
 
+@pytest.fixture(autouse=True, params=["auto", "mma"])
+def prefill_impl(request, monkeypatch):
+    """Every case runs twice: through the shape dispatch (tcgen05 kernel for 16-bit caches with head_size 128,
+    mma.sync kernel otherwise) and with the mma.sync kernel forced (B200_PREFILL_IMPL, read per call)."""
+    if request.param == "mma":
+        monkeypatch.setenv("B200_PREFILL_IMPL", "mma")
+    else:
+        monkeypatch.delenv("B200_PREFILL_IMPL", raising=False)
+    return request.param
+
+
 def build(seq_lens, Hq, Hkv, D, bs, dtype, kv_fp8, seed=0, layout="NHD", k_scale=0.5, v_scale=0.25):
     """seq_lens: list of (query_len, kv_len) as in the reference test."""
     g = torch.Generator().manual_seed(seed)

@@ -85,6 +85,7 @@ class VarlenAttnArgs(C.Structure):
         ("kv_token_stride", c_int64),
         ("kv_head_stride", c_int64),
         ("bt_stride", c_int64),
+        ("num_blocks", c_int64),
         ("num_seqs", C.c_int32),
         ("num_tokens", C.c_int32),
         ("num_heads", C.c_int32),

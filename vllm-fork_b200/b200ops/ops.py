@@ -737,6 +737,7 @@ def unified_attention(
     a.out_stride_t, a.out_stride_h = out.stride(0), out.stride(1)
     a.kv_block_stride, a.kv_token_stride, a.kv_head_stride = k.stride(0), k.stride(1), k.stride(2)
     a.bt_stride = block_table.stride(0)
+    a.num_blocks = nb
     a.num_seqs, a.num_tokens, a.num_heads, a.num_kv_heads, a.head_size, a.block_size = S, T, Hq, Hkv, D, bs
     a.q_dtype = _dt(q)
     a.kv_dtype = FP8_E4M3 if kv_fp8 else _dt(k)

@@ -439,6 +439,43 @@ __global__ void __launch_bounds__(NTHREADS) varlen_attn_kernel(const Params p) {
   }
 }
 
+}  // namespace attnp
+}  // namespace b200
+
+#include "attention_prefill_tc.cuh"
+
+#include <cstdlib>
+#include <cstring>
+
+namespace b200 {
+namespace attnp {
+
+// 5-D view of a paged K (or V) cache for the tcgen05 kernel: [64 elements = 128 B][token in block][128-B segment]
+// [head][block]; one box = 16 tokens x 128 B of one head
+static int make_kv_tmap(CUtensorMap* tm, const void* base, int64_t nb, int64_t sb, int64_t st, int64_t sh, int bs,
+                        int hkv) {
+  uint64_t dims[5] = {64, (uint64_t)bs, 2, (uint64_t)hkv, (uint64_t)nb};
+  uint64_t strides[4] = {(uint64_t)(st * 2), 128, (uint64_t)(sh * 2), (uint64_t)(sb * 2)};
+  uint32_t box[5] = {64, 16, 1, 1, 1};
+  return encode_tensor_map(tm, CU_TENSOR_MAP_DATA_TYPE_UINT16, 5, base, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B,
+                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+}
+
+template <bool BF16>
+static int launch_tc(const CUtensorMap& tmK, const CUtensorMap& tmV, const Params& p, cudaStream_t stream) {
+  constexpr int smem = 6 * (int)TC_TILE + 1024 + 256;
+  static bool configured = false;
+  auto kern = varlen_attn_tc_kernel<BF16>;
+  if (!configured) {
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  dim3 grid(p.T / p.block_q + p.S, p.Hkv);
+  kern<<<grid, TC_THREADS, smem, stream>>>(tmK, tmV, p);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
 template <int D, int MODE>
 static int launch(const Params& p, cudaStream_t stream) {
   constexpr int ES = (MODE == BF16_FP8 || MODE == F16_FP8) ? 1 : 2;
@@ -520,6 +557,21 @@ extern "C" int b200_paged_attention_varlen(const b200_varlen_attn_args* a, b200_
   p.scale = a->scale;
   p.softcap = a->softcap > 0.f ? a->softcap : 0.f;
 
+  // tcgen05 kernel: 16-bit caches, head_size 128 (B200_PREFILL_IMPL=mma forces the mma.sync kernel)
+  const char* impl = std::getenv("B200_PREFILL_IMPL");
+  const bool want_mma = impl && std::strcmp(impl, "mma") == 0;
+  if (!fp8 && D == TC_D && g <= TC_BM && a->num_blocks > 0 && !want_mma && (a->out_stride_t * oes) % 16 == 0 &&
+      (a->out_stride_h * oes) % 16 == 0) {
+    p.block_q = TC_BM / g;
+    CUtensorMap tmK, tmV;
+    int rc = make_kv_tmap(&tmK, a->k_cache, a->num_blocks, a->kv_block_stride, a->kv_token_stride, a->kv_head_stride,
+                          a->block_size, Hkv);
+    if (rc) return rc;
+    rc = make_kv_tmap(&tmV, a->v_cache, a->num_blocks, a->kv_block_stride, a->kv_token_stride, a->kv_head_stride,
+                      a->block_size, Hkv);
+    if (rc) return rc;
+    return a->q_dtype == B200_BF16 ? launch_tc<true>(tmK, tmV, p, stream) : launch_tc<false>(tmK, tmV, p, stream);
+  }
   const int mode = fp8 ? (a->q_dtype == B200_BF16 ? BF16_FP8 : F16_FP8)
                        : (a->q_dtype == B200_BF16 ? BF16_BF16 : F16_F16);
 #define B200_VARLEN_CASE(DD, MM) \
