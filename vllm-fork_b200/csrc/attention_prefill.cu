@@ -461,11 +461,11 @@ static int make_kv_tmap(CUtensorMap* tm, const void* base, int64_t nb, int64_t s
                            CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
 }
 
-template <bool BF16>
+template <bool BF16, bool GENERAL>
 static int launch_tc(const CUtensorMap& tmK, const CUtensorMap& tmV, const Params& p, cudaStream_t stream) {
   constexpr int smem = 6 * (int)TC_TILE + 1024 + 256;
   static bool configured = false;
-  auto kern = varlen_attn_tc_kernel<BF16>;
+  auto kern = varlen_attn_tc_kernel<BF16, GENERAL>;
   if (!configured) {
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
@@ -570,7 +570,10 @@ extern "C" int b200_paged_attention_varlen(const b200_varlen_attn_args* a, b200_
     rc = make_kv_tmap(&tmV, a->v_cache, a->num_blocks, a->kv_block_stride, a->kv_token_stride, a->kv_head_stride,
                       a->block_size, Hkv);
     if (rc) return rc;
-    return a->q_dtype == B200_BF16 ? launch_tc<true>(tmK, tmV, p, stream) : launch_tc<false>(tmK, tmV, p, stream);
+    const bool general = p.softcap > 0.f || p.alibi != nullptr;
+    if (a->q_dtype == B200_BF16)
+      return general ? launch_tc<true, true>(tmK, tmV, p, stream) : launch_tc<true, false>(tmK, tmV, p, stream);
+    return general ? launch_tc<false, true>(tmK, tmV, p, stream) : launch_tc<false, false>(tmK, tmV, p, stream);
   }
   const int mode = fp8 ? (a->q_dtype == B200_BF16 ? BF16_FP8 : F16_FP8)
                        : (a->q_dtype == B200_BF16 ? BF16_BF16 : F16_F16);

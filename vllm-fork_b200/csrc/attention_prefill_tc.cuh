@@ -70,7 +70,10 @@ __device__ __forceinline__ uint32_t kmajor_off(int r, int c) {
   return (uint32_t)((c >> 3) * TC_SEG + r * 128 + (((c & 7) ^ (r & 7)) << 4));
 }
 
-template <bool BF16>
+// GENERAL = soft-cap and / or ALiBi present (scores are transformed element by element); the plain kernel folds
+// scale * log2(e) into the exponent's FFMA. Both keep the per-tile softmax code small (< ~1000 SASS instructions):
+// the first version spent 38 k cycles per tile on a 3000-instruction unrolled loop, instruction-fetch bound.
+template <bool BF16, bool GENERAL>
 __global__ void __launch_bounds__(TC_THREADS, 1)
     varlen_attn_tc_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
                           const Params p) {
@@ -270,21 +273,31 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
       mbar_arrive(bar_s_free);
       const bool need_mask = (t0 + TC_BN - 1 > ctx + first_q) || (t0 + TC_BN > kv_hi) ||
                              (p.window > 0 && t0 < ctx + last_q - p.window + 1);
-      float mx = -INFINITY;
+      // visible columns of this row inside the tile: [lo_e, hi_e] (causal limit, sequence end, sliding window)
+      const int hi_e = min(limit, kv_hi - 1) - t0;
+      const int lo_e = (p.window > 0 ? limit - p.window + 1 : 0) - t0;
+      if constexpr (GENERAL) {
+        const float a0 = slope * (float)(t0 - ctx);
 #pragma unroll
-      for (int e = 0; e < TC_BN; e++) {
-        const int t = t0 + e;
-        float v = sv[e] * qk_scale;
-        if (softcap > 0.f) v = softcap * tanhf(v / softcap);
-        v += slope * (float)(t - ctx);
-        v *= LOG2E;
-        if (need_mask) {
-          const bool vis = t <= limit && t < kv_hi && (p.window <= 0 || limit - t < p.window);
-          if (!vis) v = -INFINITY;
+        for (int e = 0; e < TC_BN; e++) {
+          float v = sv[e] * qk_scale;
+          if (softcap > 0.f) v = softcap * tanhf(v / softcap);
+          sv[e] = (v + fmaf(slope, (float)e, a0)) * LOG2E;
         }
-        sv[e] = v;
-        mx = fmaxf(mx, v);
       }
+      float mx = -INFINITY;
+      if (need_mask) {
+#pragma unroll
+        for (int e = 0; e < TC_BN; e++) {
+          if (e > hi_e || e < lo_e) sv[e] = -INFINITY;
+          mx = fmaxf(mx, sv[e]);
+        }
+      } else {
+#pragma unroll
+        for (int e = 0; e < TC_BN; e++) mx = fmaxf(mx, sv[e]);
+      }
+      const float cexp = GENERAL ? 1.f : qk_scale * LOG2E;   // exp2 argument = sv * cexp - m_ref
+      mx *= cexp;                                            // cexp > 0: max commutes, -inf stays -inf
       if (i > 0) {
         mbar_wait(bar_pv_done, (uint32_t)(i - 1) & 1u);   // P smem free again, O complete up to tile i - 1
         tc_fence_after();
@@ -314,7 +327,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
         uint32_t w[4];
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-          const float e0 = ex2(sv[c * 8 + 2 * k] - mb), e1 = ex2(sv[c * 8 + 2 * k + 1] - mb);
+          const float e0 = ex2(fmaf(sv[c * 8 + 2 * k], cexp, -mb)), e1 = ex2(fmaf(sv[c * 8 + 2 * k + 1], cexp, -mb));
           l_sum += e0 + e1;
           w[k] = pack2<BF16>(e0, e1);
         }
