@@ -298,41 +298,39 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
       }
       const float cexp = GENERAL ? 1.f : qk_scale * LOG2E;   // exp2 argument = sv * cexp - m_ref
       mx *= cexp;                                            // cexp > 0: max commutes, -inf stays -inf
+      // lazy running max: re-base only when the row max grew by more than 2^8 (exp2 arguments stay <= 8)
+      const bool grow = i > 0 && mx > m_ref + TC_RESCALE;
+      const float f = grow ? ex2(m_ref - mx) : 1.f;    // m_ref = -inf -> 0
+      if (i == 0 || grow) m_ref = mx;
+      l_sum *= f;
+      const float mb = m_ref == -INFINITY ? 0.f : m_ref;
+      // exponentials first (they only need S): this overlaps P.V of the previous tile on the tensor pipe
+      uint32_t pw[TC_BN / 2];
+#pragma unroll
+      for (int k = 0; k < TC_BN / 2; k++) {
+        const float e0 = ex2(fmaf(sv[2 * k], cexp, -mb)), e1 = ex2(fmaf(sv[2 * k + 1], cexp, -mb));
+        l_sum += e0 + e1;
+        pw[k] = pack2<BF16>(e0, e1);
+      }
       if (i > 0) {
         mbar_wait(bar_pv_done, (uint32_t)(i - 1) & 1u);   // P smem free again, O complete up to tile i - 1
         tc_fence_after();
-      }
-      // lazy running max: re-base O only when the row max grew by more than 2^8 (exp2 arguments stay <= 8)
-      const bool grow = mx > m_ref + TC_RESCALE;
-      if (i == 0) {
-        m_ref = mx;
-      } else if (__any_sync(0xffffffffu, grow)) {
-        const float f = grow ? ex2(m_ref - mx) : 1.f;    // m_ref = -inf -> 0
-        if (grow) m_ref = mx;
-        l_sum *= f;
+        if (__any_sync(0xffffffffu, grow)) {
 #pragma unroll 1
-        for (int c = 0; c < TC_D / 16; c++) {
-          uint32_t o[16];
-          tc_ld16(tm_O + lane_base + (uint32_t)(c << 4), o);
-          tc_wait_ld();
+          for (int c = 0; c < TC_D / 16; c++) {
+            uint32_t o[16];
+            tc_ld16(tm_O + lane_base + (uint32_t)(c << 4), o);
+            tc_wait_ld();
 #pragma unroll
-          for (int e = 0; e < 16; e++) o[e] = __float_as_uint(__uint_as_float(o[e]) * f);
-          tc_st16(tm_O + lane_base + (uint32_t)(c << 4), o);
+            for (int e = 0; e < 16; e++) o[e] = __float_as_uint(__uint_as_float(o[e]) * f);
+            tc_st16(tm_O + lane_base + (uint32_t)(c << 4), o);
+          }
+          tc_wait_st();
         }
-        tc_wait_st();
       }
-      const float mb = m_ref == -INFINITY ? 0.f : m_ref;
 #pragma unroll
-      for (int c = 0; c < 16; c++) {
-        uint32_t w[4];
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-          const float e0 = ex2(fmaf(sv[c * 8 + 2 * k], cexp, -mb)), e1 = ex2(fmaf(sv[c * 8 + 2 * k + 1], cexp, -mb));
-          l_sum += e0 + e1;
-          w[k] = pack2<BF16>(e0, e1);
-        }
-        sts128(p_s + kmajor_off(row, c), make_uint4(w[0], w[1], w[2], w[3]));
-      }
+      for (int c = 0; c < 16; c++)
+        sts128(p_s + kmajor_off(row, c), make_uint4(pw[4 * c], pw[4 * c + 1], pw[4 * c + 2], pw[4 * c + 3]));
       fence_proxy_async();    // P (generic proxy) -> tensor core (async proxy)
       tc_fence_before();      // O re-base (tcgen05.st) ordered before the MMA that accumulates into it
       mbar_arrive(bar_p_full);
