@@ -443,6 +443,7 @@ __global__ void __launch_bounds__(NTHREADS) varlen_attn_kernel(const Params p) {
 }  // namespace b200
 
 #include "attention_prefill_tc.cuh"
+#include "attention_prefill_tc8.cuh"
 
 #include <cstdlib>
 #include <cstring>
@@ -459,6 +460,31 @@ static int make_kv_tmap(CUtensorMap* tm, const void* base, int64_t nb, int64_t s
   uint32_t box[5] = {64, 16, 1, 1, 1};
   return encode_tensor_map(tm, CU_TENSOR_MAP_DATA_TYPE_UINT16, 5, base, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B,
                            CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+}
+
+// FP8 cache: [128 bytes = the whole head][token in block][1][head][block]; one box = 16 tokens x 128 B
+static int make_kv8_tmap(CUtensorMap* tm, const void* base, int64_t nb, int64_t sb, int64_t st, int64_t sh, int bs,
+                         int hkv) {
+  uint64_t dims[5] = {128, (uint64_t)bs, 1, (uint64_t)hkv, (uint64_t)nb};
+  uint64_t strides[4] = {(uint64_t)st, 128, (uint64_t)sh, (uint64_t)sb};
+  uint32_t box[5] = {128, 16, 1, 1, 1};
+  return encode_tensor_map(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 5, base, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B,
+                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+}
+
+template <bool QBF16, bool GENERAL>
+static int launch_tc8(const CUtensorMap& tmK, const CUtensorMap& tmV, const Params& p, cudaStream_t stream) {
+  constexpr int smem = 4 * (int)TC_TILE + 4 * (int)TC8_RAW + 1024 + 256;
+  static bool configured = false;
+  auto kern = varlen_attn_tc8_kernel<QBF16, GENERAL>;
+  if (!configured) {
+    B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  dim3 grid(p.T / p.block_q + p.S, p.Hkv);
+  kern<<<grid, TC8_THREADS, smem, stream>>>(tmK, tmV, p);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
 }
 
 template <bool BF16, bool GENERAL>
@@ -560,8 +586,23 @@ extern "C" int b200_paged_attention_varlen(const b200_varlen_attn_args* a, b200_
   // tcgen05 kernel: 16-bit caches, head_size 128 (B200_PREFILL_IMPL=mma forces the mma.sync kernel)
   const char* impl = std::getenv("B200_PREFILL_IMPL");
   const bool want_mma = impl && std::strcmp(impl, "mma") == 0;
-  if (!fp8 && D == TC_D && g <= TC_BM && a->num_blocks > 0 && !want_mma && (a->out_stride_t * oes) % 16 == 0 &&
-      (a->out_stride_h * oes) % 16 == 0) {
+  const bool tc_ok = D == TC_D && g <= TC_BM && a->num_blocks > 0 && !want_mma && (a->out_stride_t * oes) % 16 == 0 &&
+                     (a->out_stride_h * oes) % 16 == 0;
+  if (fp8 && tc_ok) {
+    p.block_q = TC_BM / g;
+    CUtensorMap tmK, tmV;
+    int rc = make_kv8_tmap(&tmK, a->k_cache, a->num_blocks, a->kv_block_stride, a->kv_token_stride, a->kv_head_stride,
+                           a->block_size, Hkv);
+    if (rc) return rc;
+    rc = make_kv8_tmap(&tmV, a->v_cache, a->num_blocks, a->kv_block_stride, a->kv_token_stride, a->kv_head_stride,
+                       a->block_size, Hkv);
+    if (rc) return rc;
+    const bool general = p.softcap > 0.f || p.alibi != nullptr;
+    if (a->q_dtype == B200_BF16)
+      return general ? launch_tc8<true, true>(tmK, tmV, p, stream) : launch_tc8<true, false>(tmK, tmV, p, stream);
+    return general ? launch_tc8<false, true>(tmK, tmV, p, stream) : launch_tc8<false, false>(tmK, tmV, p, stream);
+  }
+  if (!fp8 && tc_ok) {
     p.block_q = TC_BM / g;
     CUtensorMap tmK, tmV;
     int rc = make_kv_tmap(&tmK, a->k_cache, a->num_blocks, a->kv_block_stride, a->kv_token_stride, a->kv_head_stride,

@@ -70,6 +70,145 @@ __device__ __forceinline__ uint32_t kmajor_off(int r, int c) {
   return (uint32_t)((c >> 3) * TC_SEG + r * 128 + (((c & 7) ^ (r & 7)) << 4));
 }
 
+// Everything the softmax warps need to know about their q block
+struct SoftmaxCtx {
+  uint32_t tm_S, tm_O, p_s, bar_s_full, bar_s_free, bar_p_full, bar_pv_done;
+  int ntiles, j_lo, ctx, first_q, last_q, kv_hi, limit, row, warp, head, q_start, qpos;
+  bool valid;
+  float qk_scale, v_scale;
+};
+
+// Softmax / correction / epilogue warps (4 warps, one thread per q row). PBF16: P is written as bf16 (else f16);
+// OBF16: output dtype; GENERAL: soft-cap and / or ALiBi.
+template <bool PBF16, bool OBF16, bool GENERAL>
+__device__ __forceinline__ void softmax_warps(const Params& p, const SoftmaxCtx& cx) {
+  const float slope = (p.alibi && cx.valid) ? p.alibi[cx.head] : 0.f;
+  const float qk_scale = cx.qk_scale;
+  const float softcap = p.softcap;
+  const uint32_t lane_base = (uint32_t)(cx.warp * 32) << 16;
+  float m_ref = -INFINITY, l_sum = 0.f;
+  for (int i = 0; i < cx.ntiles; i++) {
+    const int t0 = (cx.j_lo + i) * TC_BN;
+    mbar_wait(cx.bar_s_full, (uint32_t)i & 1u);
+    tc_fence_after();
+    float sv[TC_BN];
+    {
+      uint32_t v[8][16];
+#pragma unroll
+      for (int c = 0; c < 8; c++) tc_ld16(cx.tm_S + lane_base + (uint32_t)(c << 4), v[c]);
+      tc_wait_ld();
+#pragma unroll
+      for (int c = 0; c < 8; c++)
+#pragma unroll
+        for (int e = 0; e < 16; e++) sv[c * 16 + e] = __uint_as_float(v[c][e]);
+    }
+    tc_fence_before();
+    mbar_arrive(cx.bar_s_free);
+    const bool need_mask = (t0 + TC_BN - 1 > cx.ctx + cx.first_q) || (t0 + TC_BN > cx.kv_hi) ||
+                           (p.window > 0 && t0 < cx.ctx + cx.last_q - p.window + 1);
+    // visible columns of this cx.row inside the tile: [lo_e, hi_e] (causal cx.limit, sequence end, sliding window)
+    const int hi_e = min(cx.limit, cx.kv_hi - 1) - t0;
+    const int lo_e = (p.window > 0 ? cx.limit - p.window + 1 : 0) - t0;
+    if constexpr (GENERAL) {
+      const float a0 = slope * (float)(t0 - cx.ctx);
+#pragma unroll
+      for (int e = 0; e < TC_BN; e++) {
+        float v = sv[e] * qk_scale;
+        if (softcap > 0.f) v = softcap * tanhf(v / softcap);
+        sv[e] = (v + fmaf(slope, (float)e, a0)) * LOG2E;
+      }
+    }
+    float mx = -INFINITY;
+    if (need_mask) {
+#pragma unroll
+      for (int e = 0; e < TC_BN; e++) {
+        if (e > hi_e || e < lo_e) sv[e] = -INFINITY;
+        mx = fmaxf(mx, sv[e]);
+      }
+    } else {
+#pragma unroll
+      for (int e = 0; e < TC_BN; e++) mx = fmaxf(mx, sv[e]);
+    }
+    const float cexp = GENERAL ? 1.f : qk_scale * LOG2E;   // exp2 argument = sv * cexp - m_ref
+    mx *= cexp;                                            // cexp > 0: max commutes, -inf stays -inf
+    // lazy running max: re-base only when the cx.row max grew by more than 2^8 (exp2 arguments stay <= 8)
+    const bool grow = i > 0 && mx > m_ref + TC_RESCALE;
+    const float f = grow ? ex2(m_ref - mx) : 1.f;    // m_ref = -inf -> 0
+    if (i == 0 || grow) m_ref = mx;
+    l_sum *= f;
+    const float mb = m_ref == -INFINITY ? 0.f : m_ref;
+    // exponentials first (they only need S): this overlaps P.V of the previous tile on the tensor pipe
+    uint32_t pw[TC_BN / 2];
+#pragma unroll
+    for (int k = 0; k < TC_BN / 2; k++) {
+      const float e0 = ex2(fmaf(sv[2 * k], cexp, -mb)), e1 = ex2(fmaf(sv[2 * k + 1], cexp, -mb));
+      l_sum += e0 + e1;
+      pw[k] = pack2<PBF16>(e0, e1);
+    }
+    if (i > 0) {
+      mbar_wait(cx.bar_pv_done, (uint32_t)(i - 1) & 1u);   // P smem free again, O complete up to tile i - 1
+      tc_fence_after();
+      if (__any_sync(0xffffffffu, grow)) {
+#pragma unroll 1
+        for (int c = 0; c < TC_D / 16; c++) {
+          uint32_t o[16];
+          tc_ld16(cx.tm_O + lane_base + (uint32_t)(c << 4), o);
+          tc_wait_ld();
+#pragma unroll
+          for (int e = 0; e < 16; e++) o[e] = __float_as_uint(__uint_as_float(o[e]) * f);
+          tc_st16(cx.tm_O + lane_base + (uint32_t)(c << 4), o);
+        }
+        tc_wait_st();
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < 16; c++)
+      sts128(cx.p_s + kmajor_off(cx.row, c), make_uint4(pw[4 * c], pw[4 * c + 1], pw[4 * c + 2], pw[4 * c + 3]));
+    fence_proxy_async();    // P (generic proxy) -> tensor core (async proxy)
+    tc_fence_before();      // O re-base (tcgen05.st) ordered before the MMA that accumulates into it
+    mbar_arrive(cx.bar_p_full);
+  }
+  // ---- epilogue: O / l -> out
+  mbar_wait(cx.bar_pv_done, (uint32_t)(cx.ntiles - 1) & 1u);
+  tc_fence_after();
+  const bool fp8_out = p.out_scale != nullptr;
+  const float qinv = fp8_out ? __fdiv_rn(1.0f, *p.out_scale) : 1.f;
+  const float inv = l_sum > 0.f ? cx.v_scale / l_sum : 0.f;
+  const int64_t tok = cx.q_start + cx.qpos;
+  if (cx.valid && p.lse) p.lse[tok * p.Hq + cx.head] = l_sum > 0.f ? (m_ref + lg2(l_sum)) * LN2 : -INFINITY;
+  const int64_t obase = tok * p.out_stride_t + (int64_t)cx.head * p.out_stride_h;
+#pragma unroll 1
+  for (int c = 0; c < TC_D / 16; c++) {
+    uint32_t o[16];
+    tc_ld16(cx.tm_O + lane_base + (uint32_t)(c << 4), o);
+    tc_wait_ld();
+    if (!cx.valid) continue;
+    if (fp8_out) {
+      uint32_t w[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        uint32_t b4 = 0;
+#pragma unroll
+        for (int h2 = 0; h2 < 2; h2++) {
+          const float a = fmaxf(-448.f, fminf(__uint_as_float(o[4 * k + 2 * h2]) * inv * qinv, 448.f));
+          const float b = fmaxf(-448.f, fminf(__uint_as_float(o[4 * k + 2 * h2 + 1]) * inv * qinv, 448.f));
+          b4 |= (uint32_t)f32x2_to_e4m3x2(a, b) << (16 * h2);
+        }
+        w[k] = b4;
+      }
+      *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(p.out) + obase + 16 * c) = make_uint4(w[0], w[1], w[2], w[3]);
+    } else {
+      uint32_t w[8];
+#pragma unroll
+      for (int k = 0; k < 8; k++)
+        w[k] = pack2<OBF16>(__uint_as_float(o[2 * k]) * inv, __uint_as_float(o[2 * k + 1]) * inv);
+      uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.out) + obase + 16 * c);
+      dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
+      dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
+    }
+  }
+  }
+
 // GENERAL = soft-cap and / or ALiBi present (scores are transformed element by element); the plain kernel folds
 // scale * log2(e) into the exponent's FFMA. Both keep the per-tile softmax code small (< ~1000 SASS instructions):
 // the first version spent 38 k cycles per tile on a 3000-instruction unrolled loop, instruction-fetch bound.
@@ -249,131 +388,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
     }
   } else {
     // ================================================================ softmax / correction / epilogue
-    const float slope = (p.alibi && valid) ? p.alibi[head] : 0.f;
-    const float qk_scale = p.scale;
-    const float softcap = p.softcap;
-    const uint32_t lane_base = (uint32_t)(warp * 32) << 16;
-    float m_ref = -INFINITY, l_sum = 0.f;
-    for (int i = 0; i < ntiles; i++) {
-      const int t0 = (j_lo + i) * TC_BN;
-      mbar_wait(bar_s_full, (uint32_t)i & 1u);
-      tc_fence_after();
-      float sv[TC_BN];
-      {
-        uint32_t v[8][16];
-#pragma unroll
-        for (int c = 0; c < 8; c++) tc_ld16(tm_S + lane_base + (uint32_t)(c << 4), v[c]);
-        tc_wait_ld();
-#pragma unroll
-        for (int c = 0; c < 8; c++)
-#pragma unroll
-          for (int e = 0; e < 16; e++) sv[c * 16 + e] = __uint_as_float(v[c][e]);
-      }
-      tc_fence_before();
-      mbar_arrive(bar_s_free);
-      const bool need_mask = (t0 + TC_BN - 1 > ctx + first_q) || (t0 + TC_BN > kv_hi) ||
-                             (p.window > 0 && t0 < ctx + last_q - p.window + 1);
-      // visible columns of this row inside the tile: [lo_e, hi_e] (causal limit, sequence end, sliding window)
-      const int hi_e = min(limit, kv_hi - 1) - t0;
-      const int lo_e = (p.window > 0 ? limit - p.window + 1 : 0) - t0;
-      if constexpr (GENERAL) {
-        const float a0 = slope * (float)(t0 - ctx);
-#pragma unroll
-        for (int e = 0; e < TC_BN; e++) {
-          float v = sv[e] * qk_scale;
-          if (softcap > 0.f) v = softcap * tanhf(v / softcap);
-          sv[e] = (v + fmaf(slope, (float)e, a0)) * LOG2E;
-        }
-      }
-      float mx = -INFINITY;
-      if (need_mask) {
-#pragma unroll
-        for (int e = 0; e < TC_BN; e++) {
-          if (e > hi_e || e < lo_e) sv[e] = -INFINITY;
-          mx = fmaxf(mx, sv[e]);
-        }
-      } else {
-#pragma unroll
-        for (int e = 0; e < TC_BN; e++) mx = fmaxf(mx, sv[e]);
-      }
-      const float cexp = GENERAL ? 1.f : qk_scale * LOG2E;   // exp2 argument = sv * cexp - m_ref
-      mx *= cexp;                                            // cexp > 0: max commutes, -inf stays -inf
-      // lazy running max: re-base only when the row max grew by more than 2^8 (exp2 arguments stay <= 8)
-      const bool grow = i > 0 && mx > m_ref + TC_RESCALE;
-      const float f = grow ? ex2(m_ref - mx) : 1.f;    // m_ref = -inf -> 0
-      if (i == 0 || grow) m_ref = mx;
-      l_sum *= f;
-      const float mb = m_ref == -INFINITY ? 0.f : m_ref;
-      // exponentials first (they only need S): this overlaps P.V of the previous tile on the tensor pipe
-      uint32_t pw[TC_BN / 2];
-#pragma unroll
-      for (int k = 0; k < TC_BN / 2; k++) {
-        const float e0 = ex2(fmaf(sv[2 * k], cexp, -mb)), e1 = ex2(fmaf(sv[2 * k + 1], cexp, -mb));
-        l_sum += e0 + e1;
-        pw[k] = pack2<BF16>(e0, e1);
-      }
-      if (i > 0) {
-        mbar_wait(bar_pv_done, (uint32_t)(i - 1) & 1u);   // P smem free again, O complete up to tile i - 1
-        tc_fence_after();
-        if (__any_sync(0xffffffffu, grow)) {
-#pragma unroll 1
-          for (int c = 0; c < TC_D / 16; c++) {
-            uint32_t o[16];
-            tc_ld16(tm_O + lane_base + (uint32_t)(c << 4), o);
-            tc_wait_ld();
-#pragma unroll
-            for (int e = 0; e < 16; e++) o[e] = __float_as_uint(__uint_as_float(o[e]) * f);
-            tc_st16(tm_O + lane_base + (uint32_t)(c << 4), o);
-          }
-          tc_wait_st();
-        }
-      }
-#pragma unroll
-      for (int c = 0; c < 16; c++)
-        sts128(p_s + kmajor_off(row, c), make_uint4(pw[4 * c], pw[4 * c + 1], pw[4 * c + 2], pw[4 * c + 3]));
-      fence_proxy_async();    // P (generic proxy) -> tensor core (async proxy)
-      tc_fence_before();      // O re-base (tcgen05.st) ordered before the MMA that accumulates into it
-      mbar_arrive(bar_p_full);
-    }
-    // ---- epilogue: O / l -> out
-    mbar_wait(bar_pv_done, (uint32_t)(ntiles - 1) & 1u);
-    tc_fence_after();
-    const bool fp8_out = p.out_scale != nullptr;
-    const float qinv = fp8_out ? __fdiv_rn(1.0f, *p.out_scale) : 1.f;
-    const float inv = l_sum > 0.f ? 1.f / l_sum : 0.f;
-    const int64_t tok = q_start + qpos;
-    if (valid && p.lse) p.lse[tok * p.Hq + head] = l_sum > 0.f ? (m_ref + lg2(l_sum)) * LN2 : -INFINITY;
-    const int64_t obase = tok * p.out_stride_t + (int64_t)head * p.out_stride_h;
-#pragma unroll 1
-    for (int c = 0; c < TC_D / 16; c++) {
-      uint32_t o[16];
-      tc_ld16(tm_O + lane_base + (uint32_t)(c << 4), o);
-      tc_wait_ld();
-      if (!valid) continue;
-      if (fp8_out) {
-        uint32_t w[4];
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-          uint32_t b4 = 0;
-#pragma unroll
-          for (int h2 = 0; h2 < 2; h2++) {
-            const float a = fmaxf(-448.f, fminf(__uint_as_float(o[4 * k + 2 * h2]) * inv * qinv, 448.f));
-            const float b = fmaxf(-448.f, fminf(__uint_as_float(o[4 * k + 2 * h2 + 1]) * inv * qinv, 448.f));
-            b4 |= (uint32_t)f32x2_to_e4m3x2(a, b) << (16 * h2);
-          }
-          w[k] = b4;
-        }
-        *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(p.out) + obase + 16 * c) = make_uint4(w[0], w[1], w[2], w[3]);
-      } else {
-        uint32_t w[8];
-#pragma unroll
-        for (int k = 0; k < 8; k++)
-          w[k] = pack2<BF16>(__uint_as_float(o[2 * k]) * inv, __uint_as_float(o[2 * k + 1]) * inv);
-        uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.out) + obase + 16 * c);
-        dst[0] = make_uint4(w[0], w[1], w[2], w[3]);
-        dst[1] = make_uint4(w[4], w[5], w[6], w[7]);
-      }
-    }
+    SoftmaxCtx c;
+    c.tm_S = tm_S; c.tm_O = tm_O; c.p_s = p_s;
+    c.bar_s_full = bar_s_full; c.bar_s_free = bar_s_free; c.bar_p_full = bar_p_full; c.bar_pv_done = bar_pv_done;
+    c.ntiles = ntiles; c.j_lo = j_lo; c.ctx = ctx; c.first_q = first_q; c.last_q = last_q; c.kv_hi = kv_hi;
+    c.limit = limit; c.row = row; c.warp = warp; c.head = head; c.q_start = q_start; c.qpos = qpos;
+    c.valid = valid; c.qk_scale = p.scale; c.v_scale = 1.f;
+    softmax_warps<BF16, BF16, GENERAL>(p, c);
   }
   tc_fence_before();
   __syncthreads();
