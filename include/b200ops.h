@@ -112,6 +112,21 @@ B200_API int b200_fp8_quant_dynamic_token(void* out, const void* input, float* s
                                           int hidden, int64_t in_row_stride, int64_t out_row_stride,
                                           int in_dtype, b200_stream_t stream);
 
+/* Per-token-group quantiser (1 x group_size activation scales of block-scaled FP8 linears).
+ * Replaces torch.ops._C.per_token_group_fp8_quant
+ *   (csrc/libtorch_stable/quantization/w8a8/fp8/per_token_group_quant.cu:43-161,195-300;
+ *    vllm/model_executor/layers/quantization/utils/fp8_utils.py:533-616).
+ *   s = max(eps, max|x_group|) / fp8_max;  ue8m0: s = 2^ceil(log2(max(|s|, 1e-10)));
+ *   out = e4m3(min(max(x / s, fp8_min), fp8_max));  scales[r*scale_stride_row + g*scale_stride_col] = s.
+ * Row-major, column-major and TMA-aligned column-major scale tensors are stride choices (in floats).
+ * hidden % group_size == 0. */
+B200_API int b200_fp8_quant_token_group(void* out, float* scales, const void* input,
+                                        int64_t num_tokens, int hidden, int group_size,
+                                        int64_t in_row_stride, int64_t out_row_stride,
+                                        int64_t scale_stride_row, int64_t scale_stride_col, float eps,
+                                        float fp8_min, float fp8_max, int scale_ue8m0, int in_dtype,
+                                        b200_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Paged-attention decode (one query token per sequence).
  * Replaces the decode branch of AttentionImpl.forward (vllm/v1/attention/backend.py:895-934) as

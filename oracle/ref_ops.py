@@ -212,6 +212,68 @@ def ref_dynamic_per_token_quant(x: torch.Tensor, scale_ub: torch.Tensor | None =
     return out, scales
 
 
+def per_token_group_quant_fp8(x: torch.Tensor, group_size: int, eps: float = 1e-10,
+                              use_ue8m0: bool = False):
+    """csrc/libtorch_stable/quantization/w8a8/fp8/per_token_group_quant.cu:43-161.
+    absmax (from eps, fmaxf drops NaN) / 448 (fp32 division) [-> 2^ceil(log2(.)) in fp32];
+    q = fminf(fmaxf(x / y_s, -448), 448) -> e4m3.  Returns (uint8 bits like x, float32 [M, K/g])."""
+    xf = _f32(x).reshape(-1, x.shape[-1])
+    M, K = xf.shape
+    g = xf.reshape(M, K // group_size, group_size)
+    a = np.abs(g)
+    a = np.where(np.isnan(a), np.float32(0), a)
+    absmax = np.maximum(a.max(axis=2) if a.size else np.zeros((M, K // group_size), np.float32),
+                        np.float32(eps)).astype(np.float32)
+    ys = (absmax / np.float32(FP8_MAX)).astype(np.float32)
+    if use_ue8m0:
+        with np.errstate(all="ignore"):
+            lg = np.log2(np.maximum(np.abs(ys), np.float32(1e-10)).astype(np.float32)).astype(np.float32)
+        ys = np.exp2(np.ceil(lg).astype(np.float64)).astype(np.float32)
+    with np.errstate(all="ignore"):
+        q = (g / ys[:, :, None]).astype(np.float32)
+    r = _fminf(_fmaxf(q, np.float32(-FP8_MAX)), np.float32(FP8_MAX))
+    return f32_to_e4m3_bits(r).reshape(x.shape), ys
+
+
+def ue8m0_near_tie(absmax_over_448: np.ndarray, rel: float = 1e-6) -> np.ndarray:
+    """Groups whose scale sits within `rel` of a power of two: ceil(log2f(.)) may legitimately differ
+    between libm implementations there (tests exclude them from the bit-exact check)."""
+    m, _ = np.frexp(absmax_over_448.astype(np.float64))
+    return (np.abs(m - 0.5) < rel) | (np.abs(m - 1.0) < rel)
+
+
+def ref_native_per_token_group_quant_fp8(x: torch.Tensor, group_size: int, eps: float = 1e-10):
+    """The reference's own torch oracle, tests/kernels/quant_utils.py:157-180 (restated) -- used to
+    cross-check the restatement above."""
+    fi = torch.finfo(torch.float8_e4m3fn)
+    x_ = x.reshape(x.numel() // group_size, group_size)
+    amax = x_.abs().max(dim=-1, keepdim=True)[0].clamp(min=eps).to(torch.float32)
+    x_s = amax / fi.max
+    x_q = (x_ / x_s).clamp(min=fi.min, max=fi.max).to(torch.float8_e4m3fn)
+    return x_q.reshape(x.shape), x_s.reshape(x.shape[:-1] + (x.shape[-1] // group_size,))
+
+
+def w8a8_block_scaled_mm(a_bits, b_bits_nk, a_s, b_s, block=(128, 128)) -> np.ndarray:
+    """tests/kernels/quant_utils.py:91-155 (native_w8a8_block_matmul) restated in float64:
+    C[:, nblk] = sum_kblk (A_kblk . B[nblk, kblk]^T) * a_s[:, kblk] * b_s[nblk, kblk].
+    a_bits uint8 [M,K], b_bits_nk uint8 [N,K], a_s float32 [M, ceil(K/bk)], b_s float32
+    [ceil(N/bn), ceil(K/bk)]; returns float32 [M,N] (no output rounding)."""
+    a = e4m3_bits_to_f32(np.asarray(a_bits)).astype(np.float64)
+    w = e4m3_bits_to_f32(np.asarray(b_bits_nk)).astype(np.float64)
+    a_s = np.asarray(a_s, dtype=np.float64)
+    b_s = np.asarray(b_s, dtype=np.float64)
+    bn, bk = block
+    M, K = a.shape
+    N = w.shape[0]
+    out = np.zeros((M, N), np.float64)
+    for kb in range((K + bk - 1) // bk):
+        ks = slice(kb * bk, min(K, (kb + 1) * bk))
+        part = a[:, ks] @ w[:, ks].T
+        scale_n = np.repeat(b_s[:, kb], bn)[:N]
+        out += part * a_s[:, kb:kb + 1] * scale_n[None, :]
+    return out.astype(np.float32)
+
+
 # --------------------------------------------------------------------------------------------
 # Slot mapping.  vllm/v1/worker/block_table.py:182-211, 379-441 (no DCP)
 # --------------------------------------------------------------------------------------------

@@ -103,3 +103,60 @@ def test_saturation_zero_rows_and_min_scale():
     out, _ = _ops().scaled_fp8_quant(big.to(DEV), scale=s.to(DEV))
     assert out.view(torch.uint8).cpu().tolist() == [[0x7E, 0xFE, 0x30, 0x7E]]
     np.testing.assert_array_equal(ref_ops.static_scaled_fp8_quant(big, s), [[0x7E, 0xFE, 0x30, 0x7E]])
+
+
+# ------------------------------------------------------------------------------------------------
+# per_token_group_fp8_quant: grid of tests/kernels/quantization/test_block_fp8.py:40-79 (+ f16 / f32,
+# group sizes without a vector path, UE8M0 scales, the three scale layouts)
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("group_size", [64, 128, 512])
+@pytest.mark.parametrize("tokens,hidden", [(7, 512), (2050, 4096), (7, 5120), (33, 13824)])
+@pytest.mark.parametrize("layout", ["row", "col", "tma"])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+def test_per_token_group_quant(tokens, hidden, group_size, layout, dtype):
+    x = _x(tokens, hidden, dtype, seed=3)
+    x[0, :group_size] = 0  # eps path
+    bits, scales = ref_ops.per_token_group_quant_fp8(x, group_size)
+    out, sc = _ops().per_token_group_quant_fp8(x.to(DEV), group_size, column_major_scales=layout != "row",
+                                               tma_aligned_scales=layout == "tma")
+    assert sc.shape == (tokens, hidden // group_size) and out.dtype == torch.float8_e4m3fn
+    if layout == "col":
+        assert sc.stride() == (1, tokens)
+    if layout == "tma":
+        assert sc.stride() == (1, (tokens + 3) // 4 * 4)
+    np.testing.assert_array_equal(sc.cpu().numpy(), scales)
+    np.testing.assert_array_equal(out.view(torch.uint8).cpu().numpy(), bits)
+
+
+@pytest.mark.parametrize("group_size", [16, 24, 128, 1024, 2048])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_per_token_group_quant_ue8m0_and_odd_groups(group_size, dtype):
+    tokens, hidden = 19, group_size * 6
+    x = _x(tokens, hidden, dtype, seed=4) * 3
+    x[1, 5] = float("nan")  # absmax drops NaN; the element itself clamps to fp8_min
+    for ue in (False, True):
+        bits, scales = ref_ops.per_token_group_quant_fp8(x, group_size, use_ue8m0=ue)
+        out, sc = _ops().per_token_group_quant_fp8(x.to(DEV), group_size, use_ue8m0=ue)
+        got_s, got = sc.cpu().numpy(), out.view(torch.uint8).cpu().numpy()
+        if ue:  # ceil(log2f(.)) one ulp from a power of two may differ between libms: exclude those groups
+            _, plain = ref_ops.per_token_group_quant_fp8(x, group_size)
+            ok = ~ref_ops.ue8m0_near_tie(plain)
+            assert ok.mean() > 0.9
+            np.testing.assert_array_equal(got_s[ok], scales[ok])
+            okx = np.repeat(ok, group_size, axis=1)
+            np.testing.assert_array_equal(got[okx], bits[okx])
+        else:
+            np.testing.assert_array_equal(got_s, scales)
+            np.testing.assert_array_equal(got, bits)
+    assert got[1, 5] == 0xFE  # -448
+
+
+def test_per_token_group_quant_errors_and_empty():
+    ops = _ops()
+    x = torch.zeros(4, 100, dtype=torch.bfloat16, device=DEV)
+    with pytest.raises(AssertionError, match="divisible"):
+        ops.per_token_group_quant_fp8(x, 64)
+    q, s = ops.per_token_group_quant_fp8(torch.zeros(0, 128, dtype=torch.bfloat16, device=DEV), 128)
+    assert q.shape == (0, 128) and s.shape == (0, 1)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.per_token_group_quant_fp8(torch.zeros(4, 128, dtype=torch.bfloat16), 128)

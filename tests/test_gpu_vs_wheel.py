@@ -121,6 +121,43 @@ def test_fp8_quantisers_bytes_and_scales(shape, dtype):
         assert torch.equal(t1, t2) and torch.equal(bits(a), bits(b))
 
 
+def _wheel_group_quant(W, x, q, s, g, ue, col, tma):
+    fi = torch.finfo(torch.float8_e4m3fn)
+    try:
+        W._C.per_token_group_fp8_quant(x, q, s, g, 1e-10, fi.min, fi.max, ue, col, tma)
+    except (RuntimeError, TypeError) as e:
+        if "argument" not in str(e) and "schema" not in str(e):
+            raise
+        try:
+            W._C.per_token_group_fp8_quant(x, q, s, g, 1e-10, fi.min, fi.max, ue)
+        except (RuntimeError, TypeError, AttributeError) as e2:
+            pytest.skip(f"wheel per_token_group_fp8_quant has another schema: {e2!r}"[:200])
+    except AttributeError as e:
+        pytest.skip(f"wheel has no per_token_group_fp8_quant: {e!r}"[:200])
+
+
+@pytest.mark.parametrize("shape", [(7, 512), (256, 4096), (83, 14336), (2050, 7168)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("group", [64, 128])
+@pytest.mark.parametrize("ue8m0", [False, True])
+@pytest.mark.parametrize("col", [False, True])
+def test_per_token_group_fp8_quant_bytes_and_scales(shape, dtype, group, ue8m0, col):
+    W = wheel()
+    x = (torch.randn(*shape, device=DEV, generator=gen(5)) * 3).to(dtype)
+    f8 = torch.float8_e4m3fn
+    a, b = torch.empty(shape, dtype=f8, device=DEV), torch.empty(shape, dtype=f8, device=DEV)
+    G = shape[1] // group
+    if col:
+        s1 = torch.empty(G, shape[0], device=DEV).t()
+        s2 = torch.empty(G, shape[0], device=DEV).t()
+    else:
+        s1, s2 = torch.empty(shape[0], G, device=DEV), torch.empty(shape[0], G, device=DEV)
+    _wheel_group_quant(W, x, a, s1, group, ue8m0, col, False)
+    fi = torch.finfo(f8)
+    ours().per_token_group_fp8_quant(x, b, s2, group, 1e-10, fi.min, fi.max, ue8m0, col, False)
+    assert torch.equal(s1, s2) and torch.equal(bits(a), bits(b))
+
+
 # ------------------------------------------------------------------------------------------------ activation / norm / rope
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
 def test_silu_and_mul_and_quant(dtype):

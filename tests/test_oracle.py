@@ -177,3 +177,42 @@ def test_reshape_and_cache_flash_oracle_fp8_and_skip():
             exp = (key[t].float() / ks[:, None]).clamp(-448, 448).to(torch.float8_e4m3fn).view(torch.uint8)
             assert torch.equal(kc[s // bs, s % bs], exp)
         assert int((raw != 0).any(dim=-1).sum()) <= 7 * H  # only 7 valid tokens were written
+
+
+@pytest.mark.parametrize("group_size", [64, 128, 512])
+@pytest.mark.parametrize("tokens,hidden", [(7, 512), (33, 4096), (5, 5120)])
+def test_per_token_group_quant_restatement_vs_reference_python_oracle(tokens, hidden, group_size):
+    """tests/kernels/quantization/test_block_fp8.py:57-79 grid; the reference's torch oracle
+    (quant_utils.py:157-180) must give the same bytes and scales as the kernel restatement."""
+    torch.manual_seed(0)
+    x = torch.rand(tokens, hidden, dtype=torch.bfloat16) * 2 - 1
+    x[0, :group_size] = 0  # eps path
+    bits, scales = ref_ops.per_token_group_quant_fp8(x, group_size)
+    q_ref, s_ref = ref_ops.ref_native_per_token_group_quant_fp8(x.float(), group_size)
+    np.testing.assert_array_equal(scales, s_ref.numpy())
+    np.testing.assert_array_equal(bits, q_ref.view(torch.uint8).numpy())
+    assert scales[0, 0] == np.float32(1e-10) / np.float32(448.0)
+    b8, s8 = ref_ops.per_token_group_quant_fp8(x, group_size, use_ue8m0=True)
+    m, _ = np.frexp(s8)
+    lo = np.maximum(scales, np.float32(1e-10))  # the kernel clamps before log2f
+    assert np.all(m == 0.5) and np.all(s8 >= lo) and np.all(s8 < 2 * lo * (1 + 1e-6))
+
+
+def test_block_scaled_mm_restatement_vs_reference_python_oracle():
+    """native_w8a8_block_matmul (tests/kernels/quant_utils.py:91-155), restated with torch fp32 exactly as
+    the reference writes it, against the float64 oracle (test_block_fp8.py:161-201 shape, N % 128 != 0)."""
+    torch.manual_seed(0)
+    M, N, K, bn, bk = 32, 576, 1024, 128, 128
+    a = ((torch.rand(M, K) - 0.5) * 2 * 448).to(torch.float8_e4m3fn)
+    b = ((torch.rand(N, K) - 0.5) * 2 * 448).to(torch.float8_e4m3fn)
+    a_s = torch.rand(M, K // bk) * 1e-2
+    b_s = torch.rand((N + bn - 1) // bn, K // bk) * 1e-2
+    c = torch.zeros(M, N)
+    for i in range(K // bk):
+        for j in range((N + bn - 1) // bn):
+            ns = slice(j * bn, min(N, (j + 1) * bn))
+            c[:, ns] += (a[:, i * bk:(i + 1) * bk].float() @ b[ns, i * bk:(i + 1) * bk].float().t()) \
+                * (a_s[:, i:i + 1] * b_s[j, i])
+    got = ref_ops.w8a8_block_scaled_mm(a.view(torch.uint8).numpy(), b.view(torch.uint8).numpy(),
+                                       a_s.numpy(), b_s.numpy())
+    np.testing.assert_allclose(got, c.numpy(), rtol=2e-5, atol=1e-3)

@@ -128,6 +128,11 @@ SIGNATURES = {
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int64, c_int64, c_int, c_void_p],
     ),
+    "b200_fp8_quant_token_group": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int64, c_int64, c_int64, c_int64,
+         c_float, c_float, c_float, c_int, c_int, c_void_p],
+    ),
     "b200_fp8_gemm": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64,

@@ -258,6 +258,64 @@ def scaled_fp8_quant(
     return output, scale
 
 
+def per_token_group_fp8_quant(input: torch.Tensor, output_q: torch.Tensor, output_s: torch.Tensor,
+                              group_size: int, eps: float, fp8_min: float, fp8_max: float,
+                              scale_ue8m0: bool, dummy_is_scale_transposed: bool = False,
+                              dummy_is_tma_aligned: bool = False) -> None:
+    """torch.ops._C.per_token_group_fp8_quant (per_token_group_quant.cu:195-300): the scale layout is
+    taken from output_s' strides, exactly what the two dummy flags describe in the reference."""
+    _cuda(input, output_q, output_s)
+    if not input.is_contiguous() or not output_q.is_contiguous():
+        raise RuntimeError("per_token_group_fp8_quant: input and output_q must be contiguous")
+    if output_s.dtype != torch.float32:
+        raise RuntimeError("per_token_group_fp8_quant: output_s must be float32")
+    hidden = input.shape[-1]
+    if hidden % group_size != 0:
+        raise RuntimeError(f"per_token_group_fp8_quant: the last dimension of `x` {hidden} must be "
+                           f"divisible by `group_size` {group_size}")
+    tokens = input.numel() // hidden if hidden else 0
+    s2 = output_s if output_s.ndim == 2 else output_s.view(tokens, -1) if output_s.is_contiguous() else None
+    if s2 is None or s2.ndim != 2 or tuple(s2.shape) != (tokens, hidden // group_size):
+        raise RuntimeError("per_token_group_fp8_quant: output_s must be a 2-D [tokens, groups] view")
+    rc = _lib.load().b200_fp8_quant_token_group(
+        _p(output_q), _p(s2), _p(input), tokens, hidden, group_size, hidden, hidden,
+        s2.stride(0), s2.stride(1), float(eps), float(fp8_min), float(fp8_max), int(bool(scale_ue8m0)),
+        _dt(input), _stream())
+    _lib.check(rc, "per_token_group_fp8_quant")
+
+
+def per_token_group_quant_fp8(x: torch.Tensor, group_size: int, eps: float = 1e-10,
+                              dtype: torch.dtype | None = None, column_major_scales: bool = False,
+                              tma_aligned_scales: bool = False, out_q: torch.Tensor | None = None,
+                              use_ue8m0: bool = False) -> tuple[torch.Tensor, torch.Tensor]:
+    """Same contract as fp8_utils.per_token_group_quant_fp8 (fp8_utils.py:533-660): allocates the
+    scale tensor row-major, column-major or TMA-aligned column-major and runs the CUDA kernel."""
+    dtype = FP8_DTYPE if dtype is None else dtype
+    assert dtype == FP8_DTYPE, "only torch.float8_e4m3fn is supported"
+    assert x.shape[-1] % group_size == 0, (
+        f"the last dimension of `x` {x.shape[-1]} must be divisible by `group_size` {group_size}")
+    assert x.stride(-1) == 1, "`x` groups must be contiguous"
+    assert out_q is None or out_q.shape == x.shape
+    x_q = out_q if out_q is not None else torch.empty(x.shape, device=x.device, dtype=dtype)
+    if column_major_scales:
+        if tma_aligned_scales:
+            assert x.dim() == 2, "TMA-aligned scales: 2-D activations"
+            m, sf_k = x.shape[-2], x.shape[-1] // group_size
+            tma_m = (m + 3) // 4 * 4  # get_tma_aligned_size(m, 4): 16-byte aligned columns of floats
+            x_s = torch.empty_strided((m, sf_k), (1, tma_m), device=x.device, dtype=torch.float32)
+        else:
+            shape = x.shape[:-2] + (x.shape[-1] // group_size, x.shape[-2])
+            x_s = torch.empty(shape, device=x.device, dtype=torch.float32).permute(-1, -2)
+    else:
+        x_s = torch.empty(x.shape[:-1] + (x.shape[-1] // group_size,), device=x.device,
+                          dtype=torch.float32)
+    fi = torch.finfo(dtype)
+    xc = x if x.is_contiguous() else x.contiguous()
+    per_token_group_fp8_quant(xc, x_q, x_s, group_size, eps, fi.min, fi.max, use_ue8m0,
+                              column_major_scales, tma_aligned_scales)
+    return x_q, x_s
+
+
 # ------------------------------------------------------------------------------------------------
 # FP8 W8A8 GEMM                                        reference: vllm/_custom_ops.py:756-804
 # ------------------------------------------------------------------------------------------------
