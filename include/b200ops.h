@@ -244,6 +244,21 @@ B200_API int b200_fp8_gemm(void* out, const void* a, const void* b, const float*
                            int64_t ldb, int64_t ldo, int a_scale_per_row, int b_scale_per_col,
                            int out_dtype, b200_stream_t stream);
 
+/* Block-scaled FP8 GEMM (DeepSeek-style 1 x 128 activation scales, 128 x 128 weight scales).
+ * Replaces the blockwise branch of torch.ops._C.cutlass_scaled_mm
+ *   (csrc/libtorch_stable/quantization/w8a8/cutlass/c3x/scaled_mm_helper.hpp:40-60,
+ *    c3x/scaled_mm_blockwise_sm100_fp8_dispatch.cuh; oracle tests/kernels/quant_utils.py:91-155):
+ *   out[m,n] = sum_kb a_scales[m,kb] * b_scales[kb, n/128] * (a[m, 128 kb ..] . b[128 kb .., n]).
+ * a / b / out as b200_fp8_gemm. a_scales float [M, ceil(K/128)] with element strides
+ * (as_stride_m, as_stride_k) - row-major, column-major and TMA-aligned layouts all work;
+ * b_scales float [ceil(K/128), ceil(N/128)] with element strides (bs_stride_k, bs_stride_n). No bias
+ * (the reference rejects it). N and K need not be multiples of 128 (K % 16 == 0). */
+B200_API int b200_fp8_gemm_blockscaled(void* out, const void* a, const void* b, const float* a_scales,
+                                       const float* b_scales, int M, int N, int K, int64_t lda,
+                                       int64_t ldb, int64_t ldo, int64_t as_stride_m, int64_t as_stride_k,
+                                       int64_t bs_stride_k, int64_t bs_stride_n, int out_dtype,
+                                       b200_stream_t stream);
+
 /* gate_up GEMM + silu_and_mul + static FP8 quant in ONE kernel, decode batches (M <= 256).
  * Replaces the sequence cutlass_scaled_mm (gate_up_proj) -> torch.ops._C.silu_and_mul_quant
  * (csrc/libtorch_stable/quantization/activation_kernels.cu:33-104; the reference fuses the activation

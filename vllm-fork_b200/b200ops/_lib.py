@@ -133,6 +133,11 @@ SIGNATURES = {
         [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int64, c_int64, c_int64, c_int64,
          c_float, c_float, c_float, c_int, c_int, c_void_p],
     ),
+    "b200_fp8_gemm_blockscaled": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int64, c_int64,
+         c_int64, c_int64, c_int64, c_int64, c_int, c_void_p],
+    ),
     "b200_fp8_gemm": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64,

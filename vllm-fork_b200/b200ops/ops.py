@@ -355,6 +355,46 @@ def _gemm_workspace(device: torch.device) -> torch.Tensor:
     return ws
 
 
+def _cutlass_scaled_mm_blockwise(a, b, scale_a, scale_b, out_dtype, bias, out, target_shape):
+    """The blockwise branch of torch.ops._C.cutlass_scaled_mm (c3x/scaled_mm_helper.hpp:40-60; error text kept)."""
+    M, K = a.shape
+    N = b.shape[1]
+    if scale_a.dim() != 2:
+        raise RuntimeError("a scale must be 2d tensor.")
+    if scale_b.dim() != 2:
+        raise RuntimeError("b scale must be 2d tensor.")
+    kb, nb = (K + 127) // 128, (N + 127) // 128
+    if tuple(scale_a.shape) != (M, kb):
+        raise RuntimeError("a_scale_group_shape must be [1, 128].")
+    if tuple(scale_b.shape) != (kb, nb):
+        raise RuntimeError("b_scale_group_shape must be [128, 128].")
+    if bias is not None:
+        raise RuntimeError("Bias not yet supported blockwise scaled_mm")
+    if out is None:
+        out = torch.empty((M, N), dtype=out_dtype, device=a.device)
+    elif out.dtype != out_dtype or out.stride(-1) != 1:
+        raise RuntimeError("cutlass_scaled_mm: bad out tensor")
+    rc = _lib.load().b200_fp8_gemm_blockscaled(
+        _p(out), _p(a), _p(b), _p(scale_a), _p(scale_b), M, N, K, a.stride(0) if M > 1 else K, b.stride(1),
+        out.stride(0) if out.dim() > 1 else N, scale_a.stride(0), scale_a.stride(1), scale_b.stride(0),
+        scale_b.stride(1), _dt(out), _stream())
+    _lib.check(rc, "cutlass_scaled_mm")
+    return out.view(*target_shape)
+
+
+def cutlass_scaled_mm_supports_block_fp8(cuda_device_capability: int) -> bool:
+    """torch.ops._C.cutlass_scaled_mm_supports_block_fp8 (scaled_mm_entry.cu:161-180): sm_100a only here."""
+    return cuda_device_capability // 10 == 10
+
+
+def w8a8_block_fp8_cutlass_mm(A: torch.Tensor, B: torch.Tensor, As: torch.Tensor, Bs: torch.Tensor,
+                              block_size: list[int], output_dtype: torch.dtype = torch.float16) -> torch.Tensor:
+    """kernels/linear/scaled_mm/cutlass.py:329-343 (`cutlass_scaled_mm(A, B, As, Bs, block_size, dtype)`):
+    B is the weight [N, K], Bs its [N/128, K/128] scales."""
+    assert list(block_size) == [128, 128], "only 128 x 128 weight blocks"
+    return cutlass_scaled_mm(A, B.T, out_dtype=output_dtype, scale_a=As, scale_b=Bs.T)
+
+
 def cutlass_scaled_mm(
     a: torch.Tensor,
     b: torch.Tensor,
@@ -387,7 +427,8 @@ def cutlass_scaled_mm(
     if scale_a.dtype != torch.float32 or scale_b.dtype != torch.float32:
         raise RuntimeError("cutlass_scaled_mm: scales must be float32")
     if scale_a.numel() not in (1, M) or scale_b.numel() not in (1, N):
-        raise RuntimeError("cutlass_scaled_mm: scale_a must have 1 or M elements, scale_b 1 or N")
+        # blockwise scaling (scaled_mm_helper.hpp:40-60): a_s [M, ceil(K/128)], b_s [ceil(K/128), ceil(N/128)]
+        return _cutlass_scaled_mm_blockwise(a, b, scale_a, scale_b, out_dtype, bias, out, target_shape)
     if not (scale_a.is_contiguous() and scale_b.is_contiguous()):
         raise RuntimeError("cutlass_scaled_mm: scales must be contiguous")
     if out is None:
