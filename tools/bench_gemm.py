@@ -19,6 +19,7 @@ def main():
     ap.add_argument("--shapes", default=DEFAULT)
     ap.add_argument("--iters", type=int, default=30)
     ap.add_argument("--impl", default=None, help="v2 | v3 (default: ops.GEMM_IMPL)")
+    ap.add_argument("--block", action="store_true", help="block-scaled GEMM (1x128 / 128x128 scales, csrc/gemm_fp8_block.cu)")
     ap.add_argument("--eager", action="store_true", help="no CUDA graph, 3 launches per shape (for ncu)")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
@@ -30,6 +31,10 @@ def main():
         x = torch.randint(0, 0x70, (M, K), dtype=torch.uint8, device=dev).view(torch.float8_e4m3fn)
         sa = torch.ones(1, device=dev)
         sb = torch.ones(1, device=dev)
+        if a.block:
+            kb, nb = (K + 127) // 128, (N + 127) // 128
+            sa = (torch.rand(kb, M, device=dev) + 0.5).t()   # column-major, as the reference passes it
+            sb = torch.rand(kb, nb, device=dev) + 0.5
         out = torch.empty(M, N, dtype=torch.bfloat16, device=dev)
         for i in range(3):
             ops.cutlass_scaled_mm(x, ws[i % ncopy].t(), sa, sb, torch.bfloat16, out=out, impl=a.impl)
@@ -55,7 +60,7 @@ def main():
         us = e0.elapsed_time(e1) / a_iters * 1e3
         flops = 2.0 * M * N * K
         byts = M * K + N * K + 2 * M * N
-        print(json.dumps({"impl": a.impl or ops.GEMM_IMPL, "M": M, "N": N, "K": K, "us": round(us, 2), "TFLOPs": round(flops / us / 1e6, 1),
+        print(json.dumps({"impl": "block" if a.block else a.impl or ops.GEMM_IMPL, "M": M, "N": N, "K": K, "us": round(us, 2), "TFLOPs": round(flops / us / 1e6, 1),
                           "GBps": round(byts / us / 1e3, 1)}))
 
 
