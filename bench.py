@@ -111,7 +111,8 @@ class ClockSampler(threading.Thread):
 def model_shape(name):
     from b200ops import decoder
     return {"llama-3.1-8b": decoder.LLAMA_3_1_8B, "tiny": decoder.TINY,
-            "qwen2.5-0.5b": decoder.QWEN2_5_0_5B}[name]
+            "qwen2.5-0.5b": decoder.QWEN2_5_0_5B, "llama-3.1-70b": decoder.LLAMA_3_1_70B,
+            "mixtral-8x7b": decoder.MIXTRAL_8X7B, "tiny-moe": decoder.TINY_MOE}[name]
 
 
 # ------------------------------------------------------------------------------------------------
@@ -234,6 +235,8 @@ def main():
         # ranks where a one-shot pulls 14 MiB per rank and takes 32 us)
         a.comm = "nvlink" if world <= 2 else "fused"
     shape = model_shape(a.model)
+    if shape.experts > 0 and a.comm == "fused":
+        a.comm = "nvlink"   # MoE layers (expert parallel): the all-reduce follows fused_experts, no norm fusion
     S, ctx = a.batch, a.ctx
     model = decoder.DecoderModel(shape, S, ctx, BLOCK, dev, tp_rank=rank, tp_size=world, tp_group=group,
                                  comm=a.comm)
@@ -341,8 +344,11 @@ def main():
         "vs_baseline": None, "dtype": "fp8_e4m3 (W8A8 GEMMs, fp32 accumulate; FP8 KV; bf16 activations)",
         "data": "synthetic",
         "config": {"workload": f"{shape.name} decode step, FP8 W8A8 + FP8 KV cache, batch {S}, "
-                               f"context {ctx}, block_size {BLOCK} (BASELINE.json configs[1])",
-                   "parallelism": f"tp{world}", "tp_collective": (a.comm if world > 1 else None), "weights": "random init (dummy), per-tensor FP8 scales",
+                               f"context {ctx}, block_size {BLOCK} " +
+                               ("(BASELINE.json configs[3]: FP8 fused_moe, %d experts top-%d, expert parallel; "
+                                "context length not given there)" % (shape.experts, shape.topk)
+                                if shape.experts > 0 else "(BASELINE.json configs[1])"),
+                   "parallelism": (f"tp{world} attention + ep{world} experts" if shape.experts > 0 else f"tp{world}"), "tp_collective": (a.comm if world > 1 else None), "weights": "random init (dummy), per-tensor FP8 scales",
                    "cuda_graph": not a.no_graph,
                    "l2": "inputs larger than L2 (KV cache %.1f GB + weights per GPU)" %
                          (sum(L["kv"].numel() for L in model.layers) / 1e9),
@@ -359,7 +365,7 @@ def main():
                      "launches_per_step": shape.layers,
                      "share_of_step": attn_ms * shape.layers / step_ms},
     }
-    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+    if rank == 0 and world == 1 and not a.no_cpu_baseline and shape.experts == 0:
         try:
             from oracle import refcpu
             if refcpu.available():

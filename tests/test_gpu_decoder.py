@@ -32,6 +32,8 @@ def oracle_step(m, kv_cpu, token_ids, positions, slot_mapping, seq_lens, block_t
     residual = m.embed.cpu()[token_ids]
     x = None
     cos_sin = m.cos_sin.cpu()
+    fragile = np.zeros(S, dtype=bool)   # MoE: sequences whose routing decision sits on a near-tie of the router
+    oracle_step.fragile = fragile
     for li, L in enumerate(m.layers):
         c = {k: (v.cpu() if torch.is_tensor(v) else v) for k, v in L.items() if k != "kv"}
         if li == 0:
@@ -53,6 +55,16 @@ def oracle_step(m, kv_cpu, token_ids, positions, slot_mapping, seq_lens, block_t
         else:           # bf16 attention output, then static_scaled_fp8_quant
             a8 = ref_ops.static_scaled_fp8_quant(_bf(att.reshape(S, -1)), c["a_o"])
         x = _bf(ref_ops.scaled_mm(a8, c["wo"].view(torch.uint8).numpy(), c["a_o"].numpy(), c["wo_s"].numpy()))
+        if m.moe:
+            # MixtralMoE (models/mixtral.py:145-160): bf16 router -> topk_softmax (renormalised) -> fused_experts
+            normed, residual = ref_ops.rms_norm(x, c["post_norm"], s.eps, residual=residual)
+            rl = (normed.float() @ c["gate_w_t"].float()).to(torch.bfloat16)
+            tw, ids, _ = ref_ops.topk_softmax(rl, s.topk, True)
+            pr = torch.softmax(rl.float(), -1).sort(-1, descending=True).values
+            fragile |= ((pr[:, s.topk - 1] - pr[:, s.topk]) < 0.03 * pr[:, s.topk - 1]).numpy()
+            x = _bf(ref_ops.fused_experts_fp8(normed, c["w1"].view(torch.uint8), c["w2"].view(torch.uint8), tw, ids,
+                                              c["w1_s"], c["w2_s"], c["a_gu"], c["a_d"]).numpy())
+            continue
         x8, residual = ref_ops.rms_norm_static_fp8_quant(x, c["post_norm"], c["a_gu"], s.eps, residual=residual)
         gu = _bf(ref_ops.scaled_mm(x8, c["wgu"].view(torch.uint8).numpy(), c["a_gu"].numpy(), c["wgu_s"].numpy()))
         h8 = ref_ops.silu_and_mul_quant(gu, c["a_d"])
@@ -62,13 +74,14 @@ def oracle_step(m, kv_cpu, token_ids, positions, slot_mapping, seq_lens, block_t
     return logits
 
 
-def _run(env):
+def _run(env, shape_name="TINY"):
     old = {k: os.environ.get(k) for k in env}
     os.environ.update(env)
     try:
         from b200ops import decoder
         S, max_ctx, bs = 5, 96, 16
-        m = decoder.DecoderModel(decoder.TINY, S, max_ctx, bs, DEV, seed=7)
+        m = decoder.DecoderModel(getattr(decoder, shape_name), S, max_ctx, bs, DEV, seed=7)
+        fragile_steps = []
         g = torch.Generator().manual_seed(3)
         for L in m.layers:   # random (finite) fp8 context in every cache block
             kv = L["kv"]
@@ -93,6 +106,7 @@ def _run(env):
             logits = oracle_step(m, kv_cpu, tokens, pos, slots, lens, bt, fused_out=m.fuse_attn_quant)
             got.append(out)
             ref_logits.append(logits)
+            fragile_steps.append(oracle_step.fragile.copy())
             D = m.D
             for li, L in enumerate(m.layers):   # the KV cache written by the GPU step vs the oracle's
                 gk, ck = L["kv"].cpu(), kv_cpu[li]
@@ -102,6 +116,9 @@ def _run(env):
                 a = ref_ops.e4m3_bits_to_f32(gk[new].numpy()).astype(np.float64)
                 b = ref_ops.e4m3_bits_to_f32(ck[new].numpy()).astype(np.float64)
                 mism = float((gk[new] != ck[new]).float().mean())
+                if m.moe and (li > 0 and fragile_steps[-1].any()):
+                    kv_cpu[li].copy_(gk)
+                    continue   # a routing near-tie may legitimately pick another expert: no drift bound
                 if li == 0:
                     # layer 0 sees bit-identical inputs: only bf16 rounding ties of the qkv GEMM can differ
                     assert mism < 0.01, mism
@@ -114,6 +131,7 @@ def _run(env):
                 kv_cpu[li].copy_(gk)                # keep both sides on identical context for the next step
             tokens = out.clone()                    # feed the GPU's tokens to both
             lens = lens + 1
+        _run.fragile = fragile_steps
         return got, ref_logits
     finally:
         for k, v in old.items():
@@ -146,3 +164,23 @@ def test_graph_replay_equals_eager():
     b, _ = _run({"B200_FUSE_ATTN_QUANT": "1"})
     for x, y in zip(a, b):
         assert torch.equal(x, y)   # deterministic end to end (eager steps 0-1, graph steps 2-3)
+
+
+def test_moe_greedy_tokens_match_oracle():
+    """BASELINE configs[3] in miniature: tiny Mixtral-shaped model (4 experts, top-2, FP8 fused_experts) through
+    the decoder driver vs the operator-by-operator oracle (router, topk_softmax, fused_experts_fp8)."""
+    got, ref_logits = _run({"B200_FUSE_ATTN_QUANT": "1"}, "TINY_MOE")
+    total = match = 0
+    for out, logits, frag in zip(got, ref_logits, _run.fragile):
+        ref_tok = logits.argmax(-1)
+        for s in range(out.numel()):
+            if frag[s]:
+                continue
+            total += 1
+            if out[s].item() == ref_tok[s].item():
+                match += 1
+                continue
+            top = logits[s, ref_tok[s]].item()
+            alt = logits[s, out[s]].item()
+            assert top - alt <= 2.0 ** -6 * max(1.0, abs(top)), (s, top, alt)
+    assert total >= 10 and match >= total - 2, f"{match}/{total} greedy tokens match"

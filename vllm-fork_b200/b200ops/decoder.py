@@ -26,7 +26,7 @@ import os
 
 import torch
 
-from . import ops, tp
+from . import fused_moe, ops, tp
 
 
 @dataclasses.dataclass(frozen=True)
@@ -41,15 +41,21 @@ class ModelShape:
     vocab: int
     rope_theta: float = 500000.0
     eps: float = 1e-5
+    experts: int = 0   # > 0: sparse MoE MLP (Mixtral: models/mixtral.py:76-160 -> FusedMoE), `inter` per expert
+    topk: int = 0
 
 
 LLAMA_3_1_8B = ModelShape("Llama-3.1-8B-shaped", 4096, 32, 32, 8, 128, 14336, 128256)
 LLAMA_3_1_70B = ModelShape("Llama-3.1-70B-shaped", 8192, 80, 64, 8, 128, 28672, 128256)
 QWEN2_5_0_5B = ModelShape("Qwen2.5-0.5B-shaped", 896, 24, 14, 2, 64, 4864, 151936, 1000000.0, 1e-6)
+MIXTRAL_8X7B = ModelShape("Mixtral-8x7B-shaped", 4096, 32, 32, 8, 128, 14336, 32000, 1000000.0, 1e-5, 8, 2)
 TINY = ModelShape("tiny-llama-shaped", 512, 2, 8, 2, 128, 1024, 1024)
+TINY_MOE = ModelShape("tiny-mixtral-shaped", 512, 2, 8, 2, 128, 512, 1024, 1000000.0, 1e-5, 4, 2)
 
 # kernels launched per call of each op (our own kernels only), for the bench's gpu_launches claim
-LAUNCHES = {"quant_static": 1, "gemm": 1, "cache_write": 1, "attention": 2, "silu_quant": 1}
+LAUNCHES = {"quant_static": 1, "gemm": 1, "cache_write": 1, "attention": 2, "silu_quant": 1,
+            # moe_align + permute/quant + grouped GEMM + silu/quant + grouped GEMM + unpermute/reduce
+            "topk_softmax": 1, "fused_experts": 6}
 
 
 def _quant_weight(w: torch.Tensor):
@@ -68,8 +74,14 @@ class DecoderModel:
         self.dev = torch.device(device)
         self.tp_rank, self.tp_size, self.tp_group = tp_rank, tp_size, tp_group
         assert s.heads % tp_size == 0 and s.kv_heads % tp_size == 0 and s.inter % tp_size == 0
+        self.moe = s.experts > 0
+        if self.moe:
+            assert s.experts % tp_size == 0, "expert parallel: experts must divide over the ranks"
+            assert comm != "fused", "MoE layers: comm must be nccl or nvlink"
+            per = s.experts // tp_size
+            self.e_lo, self.e_hi = tp_rank * per, (tp_rank + 1) * per
         self.hq, self.hkv = s.heads // tp_size, s.kv_heads // tp_size
-        self.inter = s.inter // tp_size
+        self.inter = s.inter if s.experts > 0 else s.inter // tp_size
         self.D, self.bs = s.head_size, block_size
         self.max_seqs, self.max_ctx = max_seqs, max_ctx
         self.blocks_per_seq = (max_ctx + block_size - 1) // block_size
@@ -100,15 +112,32 @@ class DecoderModel:
             sq, sk, sv = tp.qkv_shard(s.heads, s.kv_heads, D, tp_rank, tp_size)
             wqkv = torch.cat([wq[sq], wk[sk], wv[sv]])
             wo = rnd(H, s.heads * D, fan_in=s.heads * D)[:, tp.row_shard(s.heads * D, tp_rank, tp_size)]
-            cs = tp.column_shard(s.inter, tp_rank, tp_size)
-            wg = rnd(s.inter, H, fan_in=H)[cs]
-            wu = rnd(s.inter, H, fan_in=H)[cs]
-            wd = rnd(H, s.inter, fan_in=s.inter)[:, tp.row_shard(s.inter, tp_rank, tp_size)]
             # per-tensor scales must be identical on all ranks: derive them from the full tensors
             L["wqkv"], L["wqkv_s"] = _quant_weight(wqkv.contiguous())
             L["wo"], L["wo_s"] = _quant_weight(wo.contiguous())
-            L["wgu"], L["wgu_s"] = _quant_weight(torch.cat([wg, wu]).contiguous())
-            L["wd"], L["wd_s"] = _quant_weight(wd.contiguous())
+            if self.moe:
+                # expert parallel: rank r owns experts [r*E/ep, (r+1)*E/ep) whole (no TP inside
+                # an expert); every rank draws all experts from the same generator and keeps its own
+                L["gate_w_t"] = rnd(s.experts, H, fan_in=H).to(torch.bfloat16).t().contiguous()
+                w1, w1s, w2, w2s = [], [], [], []
+                for e in range(s.experts):
+                    wg = rnd(2 * s.inter, H, fan_in=H)
+                    wd = rnd(H, s.inter, fan_in=s.inter)
+                    if self.e_lo <= e < self.e_hi:
+                        q1, s1 = _quant_weight(wg)
+                        q2, s2 = _quant_weight(wd)
+                        w1.append(q1); w1s.append(s1); w2.append(q2); w2s.append(s2)
+                    del wg, wd
+                L["w1"], L["w1_s"] = torch.stack(w1), torch.cat(w1s)
+                L["w2"], L["w2_s"] = torch.stack(w2), torch.cat(w2s)
+            else:
+                cs = tp.column_shard(s.inter, tp_rank, tp_size)
+                wg = rnd(s.inter, H, fan_in=H)[cs]
+                wu = rnd(s.inter, H, fan_in=H)[cs]
+                wd = rnd(H, s.inter, fan_in=s.inter)[:, tp.row_shard(s.inter, tp_rank, tp_size)]
+                L["wgu"], L["wgu_s"] = _quant_weight(torch.cat([wg, wu]).contiguous())
+                L["wd"], L["wd_s"] = _quant_weight(wd.contiguous())
+                del wg, wu, wd
             L["in_norm"] = torch.ones(H, device=self.dev, dtype=torch.bfloat16)
             L["post_norm"] = torch.ones(H, device=self.dev, dtype=torch.bfloat16)
             # static activation scales (FP8 "static" checkpoints carry input_scale per linear)
@@ -118,7 +147,7 @@ class DecoderModel:
             # reference layout: (num_blocks, block_size, kv_heads, 2*head_size), K|V packed (NHD)
             L["kv"] = torch.zeros(self.num_blocks, block_size, self.hkv, 2 * D, dtype=cdt, device=self.dev)
             self.layers.append(L)
-            del wq, wk, wv, wqkv, wo, wg, wu, wd
+            del wq, wk, wv, wqkv, wo
         # rotary cache [max_pos, D] (cos | sin), neox style (rotary_embedding/base.py)
         inv = 1.0 / (s.rope_theta ** (torch.arange(0, D, 2, device=self.dev).float() / D))
         t = torch.arange(max_ctx + 1, device=self.dev).float()
@@ -155,12 +184,23 @@ class DecoderModel:
                 lo, hi = self.ar.rows_of_rank(S)
                 self.row_lo, self.row_hi = lo, hi
                 self.res_shard = torch.zeros((S + tp_size - 1) // tp_size, H, dtype=torch.bfloat16, device=self.dev)
-        self.gu = torch.empty(S, 2 * self.inter, dtype=torch.bfloat16, device=self.dev)
+        self.gu = None if self.moe else torch.empty(S, 2 * self.inter, dtype=torch.bfloat16, device=self.dev)
+        if self.moe:
+            E, k = s.experts, s.topk
+            self.router_logits = torch.empty(S, E, dtype=torch.bfloat16, device=self.dev)
+            self.topk_w = torch.empty(S, k, dtype=torch.float32, device=self.dev)
+            self.topk_ids = torch.empty(S, k, dtype=torch.int32, device=self.dev)
+            self.tok_exp_idx = torch.empty(S, k, dtype=torch.int32, device=self.dev)
+            self.expert_map = None
+            if tp_size > 1:   # global expert id -> local id or -1 (fused_moe/layer.py determine_expert_map)
+                em = torch.full((E,), -1, dtype=torch.int32)
+                em[self.e_lo:self.e_hi] = torch.arange(self.e_hi - self.e_lo, dtype=torch.int32)
+                self.expert_map = em.to(self.dev)
         # gate_up GEMM + silu_and_mul + FP8 quant in one kernel. Measured (gpurun_out/bench4.json): at
         # batch 256 the GEMM is tensor-bound and the fused epilogue (silu on 4 warps of 112 CTAs, not
         # overlapped) costs more than the separate full-GPU activation kernel: 16.55 vs 15.95 ms/step.
         # It pays only while the GEMM is a weight stream (small batches).
-        self.fuse_gate_up = max_seqs <= 64 and self.inter % 128 == 0
+        self.fuse_gate_up = max_seqs <= 64 and self.inter % 128 == 0 and not self.moe
         self.fuse_attn_quant = os.environ.get("B200_FUSE_ATTN_QUANT", "1") == "1"
         self.attn_hook = None  # bench instrumentation: called around the attention launch
         self.graph = None
@@ -232,6 +272,24 @@ class DecoderModel:
             if not self.fuse_attn_quant:
                 ops.static_scaled_fp8_quant(a8, self.attn_out.view(S, self.hq * D), L["a_o"]); n += 1
             ops.cutlass_scaled_mm(a8, L["wo"].t(), L["a_o"], L["wo_s"], torch.bfloat16, out=pa); n += 1
+            if self.moe:
+                # MixtralMoE.forward (models/mixtral.py:145-160): router logits (bf16 replicated linear: library
+                # GEMM) -> topk_softmax (renormalised) -> fused_experts on the local experts -> all-reduce
+                red = self._all_reduce(pa)
+                n += 1 if self.ar is not None else 0
+                ops.fused_add_rms_norm(red, self.residual, L["post_norm"], s.eps); n += 1
+                torch.matmul(red, L["gate_w_t"], out=self.router_logits)
+                fused_moe.topk_softmax(self.topk_w, self.topk_ids, self.tok_exp_idx, self.router_logits, True)
+                n += LAUNCHES["topk_softmax"]
+                mo = fused_moe.fused_experts(red, L["w1"], L["w2"], self.topk_w, self.topk_ids, use_fp8_w8a8=True,
+                                             global_num_experts=s.experts, expert_map=self.expert_map,
+                                             w1_scale=L["w1_s"], w2_scale=L["w2_s"], a1_scale=L["a_gu"],
+                                             a2_scale=L["a_d"])
+                n += LAUNCHES["fused_experts"]
+                pb.copy_(mo)
+                red = self._all_reduce(pb)
+                n += 1 if self.ar is not None else 0
+                continue
             if fused:
                 self.ar.fused_add_rms_norm(x8, pa, self.res_shard, L["post_norm"], s.eps, L["a_gu"]); n += 1
             else:
