@@ -47,6 +47,8 @@ def parse():
                     help="TP collective (N>1): NCCL all-reduce, own NVLink all-reduce, or the fused "
                          "reduce-scatter+add+RMSNorm+FP8-quant+all-gather kernel")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--quant", default="fp8", choices=["fp8", "nvfp4"],
+                    help="linear layers: FP8 W8A8 (configs[1]) or NVFP4 W4A4 (configs[4]); the KV cache stays FP8")
     return ap.parse_args()
 
 
@@ -235,11 +237,11 @@ def main():
         # ranks where a one-shot pulls 14 MiB per rank and takes 32 us)
         a.comm = "nvlink" if world <= 2 else "fused"
     shape = model_shape(a.model)
-    if shape.experts > 0 and a.comm == "fused":
+    if (shape.experts > 0 or a.quant == "nvfp4") and a.comm == "fused":
         a.comm = "nvlink"   # MoE layers (expert parallel): the all-reduce follows fused_experts, no norm fusion
     S, ctx = a.batch, a.ctx
     model = decoder.DecoderModel(shape, S, ctx, BLOCK, dev, tp_rank=rank, tp_size=world, tp_group=group,
-                                 comm=a.comm)
+                                 comm=a.comm, quant=a.quant)
     D = shape.head_size
     # ---- synthetic state: KV caches full of random (non-NaN) fp8 codes; block table = random
     # permutation without repetition
@@ -341,13 +343,17 @@ def main():
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": step_ms, "higher_is_better": True, "scaling": "strong",
-        "vs_baseline": None, "dtype": "fp8_e4m3 (W8A8 GEMMs, fp32 accumulate; FP8 KV; bf16 activations)",
+        "vs_baseline": None,
+        "dtype": ("nvfp4 (W4A4 block-scaled GEMMs, fp32 accumulate; FP8 KV; bf16 activations)" if a.quant == "nvfp4"
+                  else "fp8_e4m3 (W8A8 GEMMs, fp32 accumulate; FP8 KV; bf16 activations)"),
         "data": "synthetic",
-        "config": {"workload": f"{shape.name} decode step, FP8 W8A8 + FP8 KV cache, batch {S}, "
+        "config": {"workload": f"{shape.name} decode step, " + ("NVFP4 W4A4" if a.quant == "nvfp4" else "FP8 W8A8") +
+                               f" + FP8 KV cache, batch {S}, "
                                f"context {ctx}, block_size {BLOCK} " +
                                ("(BASELINE.json configs[3]: FP8 fused_moe, %d experts top-%d, expert parallel; "
                                 "context length not given there)" % (shape.experts, shape.topk)
-                                if shape.experts > 0 else "(BASELINE.json configs[1])"),
+                                if shape.experts > 0 else
+                                "(BASELINE.json configs[4])" if a.quant == "nvfp4" else "(BASELINE.json configs[1])"),
                    "parallelism": (f"tp{world} attention + ep{world} experts" if shape.experts > 0 else f"tp{world}"), "tp_collective": (a.comm if world > 1 else None), "weights": "random init (dummy), per-tensor FP8 scales",
                    "cuda_graph": not a.no_graph,
                    "l2": "inputs larger than L2 (KV cache %.1f GB + weights per GPU)" %

@@ -74,13 +74,61 @@ def oracle_step(m, kv_cpu, token_ids, positions, slot_mapping, seq_lens, block_t
     return logits
 
 
-def _run(env, shape_name="TINY"):
+def _fp4_weights(L, name):
+    """GPU-quantised NVFP4 weight -> (codes [N,K], row-major scale bytes [N,K/16], alpha) for the oracle."""
+    w4 = L["w4_" + name].cpu().numpy()
+    N, K = w4.shape[0], w4.shape[1] * 2
+    sf = ref_ops.unswizzle_sf(L["wsf_" + name].cpu().view(torch.uint8).numpy().reshape(-1), N, K // 16)
+    return ref_ops.nvfp4_unpack(w4), sf, float(L["alpha_" + name].item())
+
+
+def oracle_step_nvfp4(m, kv_cpu, token_ids, positions, slot_mapping, seq_lens, block_table):
+    """The NVFP4 W4A4 layer loop on the CPU: scaled_fp4_quant -> cutlass_scaled_fp4_mm per linear
+    (oracle/ref_ops.py nvfp4_quant / nvfp4_scaled_mm), silu_and_mul_nvfp4_quant in the MLP."""
+    s, D = m.shape, m.D
+    S = token_ids.numel()
+    residual = m.embed.cpu()[token_ids]
+    cos_sin = m.cos_sin.cpu()
+    oracle_step.fragile = np.zeros(S, dtype=bool)
+
+    def linear(x, L, name):
+        codes, sf = ref_ops.nvfp4_quant(x, float(L["ags_" + name].item()))
+        wc, wsf, alpha = _fp4_weights(L, name)
+        return _bf(ref_ops.nvfp4_scaled_mm(codes, sf, wc, wsf, alpha))
+
+    x = None
+    for li, L in enumerate(m.layers):
+        c = {k: (v.cpu() if torch.is_tensor(v) else v) for k, v in L.items() if k != "kv"}
+        if li == 0:
+            xn, _ = ref_ops.rms_norm(residual, c["in_norm"], s.eps)
+        else:
+            xn, residual = ref_ops.rms_norm(x, c["in_norm"], s.eps, residual=residual)
+        qkv = linear(xn, L, "qkv")
+        q = qkv[:, : m.hq * D].view(S, m.hq, D)
+        k = qkv[:, m.hq * D:(m.hq + m.hkv) * D].view(S, m.hkv, D)
+        v = qkv[:, (m.hq + m.hkv) * D:].view(S, m.hkv, D)
+        q, k = ref_ops.rotary_embedding(positions, q, k, D, cos_sin, True)
+        kv = kv_cpu[li]
+        ref_ops.reshape_and_cache_flash(k, v, kv[..., :D], kv[..., D:], slot_mapping, "fp8", c["k_scale"], c["v_scale"])
+        att = ref_ops.paged_attention_decode(q, kv[..., :D], kv[..., D:], block_table, seq_lens, D ** -0.5,
+                                             k_scale=c["k_scale"], v_scale=c["v_scale"])
+        x = linear(_bf(att.reshape(S, -1)), L, "o")
+        xn, residual = ref_ops.rms_norm(x, c["post_norm"], s.eps, residual=residual)
+        gu = linear(xn, L, "gu")
+        hc, hsf = ref_ops.silu_and_mul_nvfp4_quant(gu, float(L["ags_d"].item()))
+        wc, wsf, alpha = _fp4_weights(L, "d")
+        x = _bf(ref_ops.nvfp4_scaled_mm(hc, hsf, wc, wsf, alpha))
+    out, _ = ref_ops.rms_norm(x, m.final_norm.cpu(), s.eps, residual=residual)
+    return out.float() @ m.lm_head.cpu().float().t()
+
+
+def _run(env, shape_name="TINY", quant="fp8"):
     old = {k: os.environ.get(k) for k in env}
     os.environ.update(env)
     try:
         from b200ops import decoder
         S, max_ctx, bs = 5, 96, 16
-        m = decoder.DecoderModel(getattr(decoder, shape_name), S, max_ctx, bs, DEV, seed=7)
+        m = decoder.DecoderModel(getattr(decoder, shape_name), S, max_ctx, bs, DEV, seed=7, quant=quant)
         fragile_steps = []
         g = torch.Generator().manual_seed(3)
         for L in m.layers:   # random (finite) fp8 context in every cache block
@@ -103,7 +151,10 @@ def _run(env, shape_name="TINY"):
             host = {"token_ids": tokens.pin_memory(), "positions": pos.pin_memory(), "slot_mapping": slots.pin_memory(),
                     "seq_lens": lens.pin_memory(), "block_table": bt.pin_memory()}
             out = m.step(host, host_out).clone()
-            logits = oracle_step(m, kv_cpu, tokens, pos, slots, lens, bt, fused_out=m.fuse_attn_quant)
+            if quant == "nvfp4":
+                logits = oracle_step_nvfp4(m, kv_cpu, tokens, pos, slots, lens, bt)
+            else:
+                logits = oracle_step(m, kv_cpu, tokens, pos, slots, lens, bt, fused_out=m.fuse_attn_quant)
             got.append(out)
             ref_logits.append(logits)
             fragile_steps.append(oracle_step.fragile.copy())
@@ -184,3 +235,21 @@ def test_moe_greedy_tokens_match_oracle():
             alt = logits[s, out[s]].item()
             assert top - alt <= 2.0 ** -6 * max(1.0, abs(top)), (s, top, alt)
     assert total >= 10 and match >= total - 2, f"{match}/{total} greedy tokens match"
+
+
+def test_nvfp4_greedy_tokens_match_oracle():
+    """BASELINE configs[4] in miniature: NVFP4 W4A4 linears + FP8 KV cache through the decoder driver vs the
+    operator-by-operator oracle (nvfp4_quant, nvfp4_scaled_mm, silu_and_mul_nvfp4_quant)."""
+    got, ref_logits = _run({}, "TINY", quant="nvfp4")
+    total = match = 0
+    for out, logits in zip(got, ref_logits):
+        ref_tok = logits.argmax(-1)
+        for s in range(out.numel()):
+            total += 1
+            if out[s].item() == ref_tok[s].item():
+                match += 1
+                continue
+            top = logits[s, ref_tok[s]].item()
+            alt = logits[s, out[s]].item()
+            assert top - alt <= 2.0 ** -5 * max(1.0, abs(top)), (s, top, alt)
+    assert match >= total - 3, f"{match}/{total} greedy tokens match"

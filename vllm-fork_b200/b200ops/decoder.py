@@ -69,8 +69,10 @@ class DecoderModel:
     def __init__(self, shape: ModelShape, max_seqs: int, max_ctx: int, block_size: int = 16,
                  device: str | torch.device = "cuda:0", tp_rank: int = 0, tp_size: int = 1,
                  tp_group=None, seed: int = 1234, kv_fp8: bool = True, num_blocks: int | None = None,
-                 comm: str = "nccl"):
+                 comm: str = "nccl", quant: str = "fp8"):
         self.shape = s = shape
+        assert quant in ("fp8", "nvfp4")
+        self.quant = quant   # "nvfp4": W4A4 linears (scaled_fp4_quant -> cutlass_scaled_fp4_mm), FP8 KV cache
         self.dev = torch.device(device)
         self.tp_rank, self.tp_size, self.tp_group = tp_rank, tp_size, tp_group
         assert s.heads % tp_size == 0 and s.kv_heads % tp_size == 0 and s.inter % tp_size == 0
@@ -78,6 +80,7 @@ class DecoderModel:
         if self.moe:
             assert s.experts % tp_size == 0, "expert parallel: experts must divide over the ranks"
             assert comm != "fused", "MoE layers: comm must be nccl or nvlink"
+            assert quant == "fp8", "MoE layers: FP8 fused_experts only"
             per = s.experts // tp_size
             self.e_lo, self.e_hi = tp_rank * per, (tp_rank + 1) * per
         self.hq, self.hkv = s.heads // tp_size, s.kv_heads // tp_size
@@ -113,6 +116,16 @@ class DecoderModel:
             wqkv = torch.cat([wq[sq], wk[sk], wv[sv]])
             wo = rnd(H, s.heads * D, fan_in=s.heads * D)[:, tp.row_shard(s.heads * D, tp_rank, tp_size)]
             # per-tensor scales must be identical on all ranks: derive them from the full tensors
+            if quant == "nvfp4":
+                self._init_nvfp4_layer(L, wqkv, wo, rnd, one)
+                L["in_norm"] = torch.ones(H, device=self.dev, dtype=torch.bfloat16)
+                L["post_norm"] = torch.ones(H, device=self.dev, dtype=torch.bfloat16)
+                L["k_scale"], L["v_scale"] = one(4.0 / 448), one(4.0 / 448)
+                cdt = torch.uint8 if kv_fp8 else torch.bfloat16
+                L["kv"] = torch.zeros(self.num_blocks, block_size, self.hkv, 2 * D, dtype=cdt, device=self.dev)
+                self.layers.append(L)
+                del wq, wk, wv, wqkv, wo
+                continue
             L["wqkv"], L["wqkv_s"] = _quant_weight(wqkv.contiguous())
             L["wo"], L["wo_s"] = _quant_weight(wo.contiguous())
             if self.moe:
@@ -200,10 +213,90 @@ class DecoderModel:
         # batch 256 the GEMM is tensor-bound and the fused epilogue (silu on 4 warps of 112 CTAs, not
         # overlapped) costs more than the separate full-GPU activation kernel: 16.55 vs 15.95 ms/step.
         # It pays only while the GEMM is a weight stream (small batches).
+        if quant == "nvfp4":
+            assert comm != "fused", "NVFP4 linears: comm must be nccl or nvlink"
+            self.xn = torch.empty(S, H, dtype=torch.bfloat16, device=self.dev)
+            self.h4 = torch.empty(S, self.inter // 2, dtype=torch.uint8, device=self.dev)
+            self.h_sf = ops.create_fp4_scale_tensor(S, self.inter, self.dev, True)
         self.fuse_gate_up = max_seqs <= 64 and self.inter % 128 == 0 and not self.moe
         self.fuse_attn_quant = os.environ.get("B200_FUSE_ATTN_QUANT", "1") == "1"
         self.attn_hook = None  # bench instrumentation: called around the attention launch
         self.graph = None
+
+    def _init_nvfp4_layer(self, L, wqkv, wo, rnd, one):
+        """NVFP4 (W4A4) linears, ModelOpt convention (quantization/modelopt.py ModelOptNvFp4LinearMethod):
+        weight_global_scale = 448*6/amax(w), input_global_scale = 448*6/amax(x) (static), block scales e4m3 per
+        16 elements in the swizzled layout, alpha = 1/(input_gs * weight_gs). Weights are quantised with this
+        package's own scaled_fp4_quant (bit-identical to the reference's kernel, tests/test_gpu_vs_wheel.py)."""
+        s, H = self.shape, self.shape.hidden
+        cs = tp.column_shard(s.inter, self.tp_rank, self.tp_size)
+        wg = rnd(s.inter, H, fan_in=H)[cs]
+        wu = rnd(s.inter, H, fan_in=H)[cs]
+        wd = rnd(H, s.inter, fan_in=s.inter)[:, tp.row_shard(s.inter, self.tp_rank, self.tp_size)]
+        amax_x = {"qkv": 4.0, "o": 2.0, "gu": 4.0, "d": 8.0}
+        for name, w in (("qkv", wqkv), ("o", wo), ("gu", torch.cat([wg, wu])), ("d", wd)):
+            w = w.contiguous()
+            w_gs = (448.0 * 6.0 / w.abs().amax().float().clamp(min=1e-12)).reshape(1)
+            q, sf = ops.scaled_fp4_quant(w.to(torch.bfloat16), w_gs)
+            a_gs = one(448.0 * 6.0 / amax_x[name])
+            L["w4_" + name], L["wsf_" + name], L["wgs_" + name] = q, sf, w_gs
+            L["ags_" + name] = a_gs
+            L["alpha_" + name] = (1.0 / (a_gs * w_gs)).to(torch.float32)
+        del wg, wu, wd
+
+    def _fp4_linear(self, x, L, name, out):
+        x4, x_sf = ops.scaled_fp4_quant(x, L["ags_" + name])
+        ops.cutlass_scaled_fp4_mm(x4, L["w4_" + name], x_sf, L["wsf_" + name], L["alpha_" + name],
+                                  torch.bfloat16, out=out)
+        return 2
+
+    def _forward_nvfp4(self) -> None:
+        """The same layer loop with NVFP4 W4A4 linears (BASELINE configs[4]): norms emit bf16, every linear is
+        scaled_fp4_quant -> cutlass_scaled_fp4_mm, the MLP activation is silu_and_mul_nvfp4_quant."""
+        s, D, S = self.shape, self.D, self.max_seqs
+        n = 0
+        q = self.qkv[:, : self.hq * D].view(S, self.hq, D)
+        k = self.qkv[:, self.hq * D:(self.hq + self.hkv) * D].view(S, self.hkv, D)
+        v = self.qkv[:, (self.hq + self.hkv) * D:].view(S, self.hkv, D)
+        pa, pb = self.proj_in
+        red = self.proj
+        torch.index_select(self.embed, 0, self.token_ids, out=self.residual)
+        for li, L in enumerate(self.layers):
+            if li == 0:
+                ops.rms_norm(self.xn, self.residual, L["in_norm"], s.eps); n += 1
+                xin = self.xn
+            else:
+                ops.fused_add_rms_norm(red, self.residual, L["in_norm"], s.eps); n += 1
+                xin = red
+            n += self._fp4_linear(xin, L, "qkv", self.qkv)
+            kc, vc = L["kv"][..., :D], L["kv"][..., D:]
+            ops.rope_and_reshape_and_cache_flash(self.positions, q, k, v, D, self.cos_sin, True, kc, vc,
+                                                 self.slot_mapping, "fp8" if self.kv_fp8 else "auto",
+                                                 L["k_scale"], L["v_scale"])
+            n += 1
+            if self.attn_hook:
+                self.attn_hook(0)
+            ops.paged_attention_decode(self.attn_out, q, kc, vc, self.block_table, self.seq_lens, D ** -0.5,
+                                       k_scale=L["k_scale"] if self.kv_fp8 else None,
+                                       v_scale=L["v_scale"] if self.kv_fp8 else None,
+                                       max_seq_len=self.max_ctx, workspace=self.workspace)
+            n += LAUNCHES["attention"]
+            if self.attn_hook:
+                self.attn_hook(1)
+            n += self._fp4_linear(self.attn_out.view(S, self.hq * D), L, "o", pa)
+            red = self._all_reduce(pa)
+            n += 1 if self.ar is not None else 0
+            ops.fused_add_rms_norm(red, self.residual, L["post_norm"], s.eps); n += 1
+            n += self._fp4_linear(red, L, "gu", self.gu)
+            ops.silu_and_mul_nvfp4_quant(self.h4, self.h_sf, self.gu, L["ags_d"]); n += 1
+            ops.cutlass_scaled_fp4_mm(self.h4, L["w4_d"], self.h_sf.view(torch.float8_e4m3fn), L["wsf_d"],
+                                      L["alpha_d"], torch.bfloat16, out=pb); n += 1
+            red = self._all_reduce(pb)
+            n += 1 if self.ar is not None else 0
+        ops.fused_add_rms_norm(red, self.residual, self.final_norm, s.eps); n += 1
+        logits = red @ self.lm_head.t()
+        self.next_tokens.copy_(logits.argmax(-1))
+        self.launches_per_step = n
 
     def _all_reduce(self, t):
         """sum over the TP group; returns the tensor holding the result."""
@@ -216,6 +309,8 @@ class DecoderModel:
 
     # ---- one decode step over the persistent device buffers
     def forward_device(self) -> None:
+        if self.quant == "nvfp4":
+            return self._forward_nvfp4()
         s, D, S = self.shape, self.D, self.max_seqs
         H = s.hidden
         n = 0
