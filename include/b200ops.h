@@ -252,11 +252,14 @@ B200_API int b200_fp8_gemm(void* out, const void* a, const void* b, const float*
  * a / b / out as b200_fp8_gemm. a_scales float [M, ceil(K/128)] with element strides
  * (as_stride_m, as_stride_k) - row-major, column-major and TMA-aligned layouts all work;
  * b_scales float [ceil(K/128), ceil(N/128)] with element strides (bs_stride_k, bs_stride_n). No bias
- * (the reference rejects it). N and K need not be multiples of 128 (K % 16 == 0). */
+ * (the reference rejects it). N and K need not be multiples of 128 (K % 16 == 0).
+ * split: K slices over the CTAs of one thread-block cluster for batches of at most 128 tokens (partials
+ * reduced through distributed shared memory in slice order: deterministic, no workspace); 0 = auto,
+ * 1 = off, else an upper bound (powers of two up to 8). */
 B200_API int b200_fp8_gemm_blockscaled(void* out, const void* a, const void* b, const float* a_scales,
                                        const float* b_scales, int M, int N, int K, int64_t lda,
                                        int64_t ldb, int64_t ldo, int64_t as_stride_m, int64_t as_stride_k,
-                                       int64_t bs_stride_k, int64_t bs_stride_n, int out_dtype,
+                                       int64_t bs_stride_k, int64_t bs_stride_n, int out_dtype, int split,
                                        b200_stream_t stream);
 
 /* gate_up GEMM + silu_and_mul + static FP8 quant in ONE kernel, decode batches (M <= 256).

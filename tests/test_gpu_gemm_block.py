@@ -56,8 +56,9 @@ def test_block_scaled_mm(mnk, a_layout, out_dtype):
     assert rel < 1e-3
 
 
-@pytest.mark.parametrize("mnk", [(16, 256, 512), (100, 384, 1024), (256, 1152, 768)])
-def test_block_scaled_mm_bit_exact_integers(mnk):
+@pytest.mark.parametrize("impl", [None, "split1", "split2", "split4", "split8"])
+@pytest.mark.parametrize("mnk", [(16, 256, 512), (100, 384, 1024), (256, 1152, 768), (32, 512, 2048), (64, 1280, 3584)])
+def test_block_scaled_mm_bit_exact_integers(mnk, impl):
     """Small-integer operands and power-of-two scales: every partial sum is exact in fp32, so the kernel
     must reproduce the float64 oracle bit for bit (catches any mis-indexed scale or k-block)."""
     M, N, K = mnk
@@ -69,7 +70,9 @@ def test_block_scaled_mm_bit_exact_integers(mnk):
     b_s = torch.exp2(torch.randint(-2, 2, (nb, kb), generator=g).float())
     ref = ref_ops.w8a8_block_scaled_mm(a8.view(torch.uint8).numpy(), w8.view(torch.uint8).numpy(),
                                        a_s.numpy(), b_s.numpy())
-    out = _ops().cutlass_scaled_mm(a8.to(DEV), w8.to(DEV).t(), a_s.to(DEV), b_s.to(DEV).t(), torch.float16)
+    # impl bounds the split-K of the kernel (K slices over a thread-block cluster, DSMEM reduction): every split
+    # must give the same bits
+    out = _ops().cutlass_scaled_mm(a8.to(DEV), w8.to(DEV).t(), a_s.to(DEV), b_s.to(DEV).t(), torch.float16, impl=impl)
     assert np.abs(ref).max() < 2048 * 16   # representable range check for the exactness argument
     want = torch.from_numpy(ref).to(torch.float16)
     assert torch.equal(out.cpu(), want)

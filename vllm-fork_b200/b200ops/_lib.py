@@ -136,7 +136,7 @@ SIGNATURES = {
     "b200_fp8_gemm_blockscaled": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int64, c_int64,
-         c_int64, c_int64, c_int64, c_int64, c_int, c_void_p],
+         c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_void_p],
     ),
     "b200_fp8_gemm": (
         c_int,

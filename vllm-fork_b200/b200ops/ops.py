@@ -355,7 +355,7 @@ def _gemm_workspace(device: torch.device) -> torch.Tensor:
     return ws
 
 
-def _cutlass_scaled_mm_blockwise(a, b, scale_a, scale_b, out_dtype, bias, out, target_shape):
+def _cutlass_scaled_mm_blockwise(a, b, scale_a, scale_b, out_dtype, bias, out, target_shape, split=0):
     """The blockwise branch of torch.ops._C.cutlass_scaled_mm (c3x/scaled_mm_helper.hpp:40-60; error text kept)."""
     M, K = a.shape
     N = b.shape[1]
@@ -377,7 +377,7 @@ def _cutlass_scaled_mm_blockwise(a, b, scale_a, scale_b, out_dtype, bias, out, t
     rc = _lib.load().b200_fp8_gemm_blockscaled(
         _p(out), _p(a), _p(b), _p(scale_a), _p(scale_b), M, N, K, a.stride(0) if M > 1 else K, b.stride(1),
         out.stride(0) if out.dim() > 1 else N, scale_a.stride(0), scale_a.stride(1), scale_b.stride(0),
-        scale_b.stride(1), _dt(out), _stream())
+        scale_b.stride(1), _dt(out), split, _stream())
     _lib.check(rc, "cutlass_scaled_mm")
     return out.view(*target_shape)
 
@@ -428,7 +428,9 @@ def cutlass_scaled_mm(
         raise RuntimeError("cutlass_scaled_mm: scales must be float32")
     if scale_a.numel() not in (1, M) or scale_b.numel() not in (1, N):
         # blockwise scaling (scaled_mm_helper.hpp:40-60): a_s [M, ceil(K/128)], b_s [ceil(K/128), ceil(N/128)]
-        return _cutlass_scaled_mm_blockwise(a, b, scale_a, scale_b, out_dtype, bias, out, target_shape)
+        # impl="split<n>" bounds the K split of the blockwise kernel (tests); default auto
+        split = int(impl[5:]) if impl and impl.startswith("split") else 0
+        return _cutlass_scaled_mm_blockwise(a, b, scale_a, scale_b, out_dtype, bias, out, target_shape, split)
     if not (scale_a.is_contiguous() and scale_b.is_contiguous()):
         raise RuntimeError("cutlass_scaled_mm: scales must be contiguous")
     if out is None:

@@ -43,7 +43,23 @@ struct Params {
   int out_bf16;
   int stages;
   int tma_store;
+  int split;   // K slices = CTAs per thread-block cluster (1, 1, split); 1 = no cluster
 };
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t mapa(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
 
 using namespace b200::tc;
 
@@ -77,7 +93,11 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row0 = blockIdx.x * BM;   // weight rows (output columns)
   const int col0 = blockIdx.y * BN;   // tokens (output rows)
-  const int num_kb = (p.K + BK - 1) / BK;
+  // split-K: CTA `ks` of the cluster contracts k-blocks [kb0, kb0 + num_kb) of the tile
+  const int total_kb = (p.K + BK - 1) / BK;
+  const int ks = p.split > 1 ? (int)cluster_ctarank() : 0;
+  const int kb0 = (int)((int64_t)ks * total_kb / p.split);
+  const int num_kb = (int)((int64_t)(ks + 1) * total_kb / p.split) - kb0;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < stages; i++) {
@@ -109,8 +129,8 @@ __global__ void __launch_bounds__(NTHREADS, 1)
         mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
         const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES;
         mbar_arrive_expect_tx(bar_full + 8u * stage, STAGE_BYTES);
-        tma_load_2d(dst, &tmW, bar_full + 8u * stage, kb * BK, row0, pol_w);
-        tma_load_2d(dst + W_BYTES, &tmA, bar_full + 8u * stage, kb * BK, col0, pol_a);
+        tma_load_2d(dst, &tmW, bar_full + 8u * stage, (kb0 + kb) * BK, row0, pol_w);
+        tma_load_2d(dst + W_BYTES, &tmA, bar_full + 8u * stage, (kb0 + kb) * BK, col0, pol_a);
         if (++stage == stages) { stage = 0; phase ^= 1u; }
       }
     }
@@ -152,13 +172,15 @@ __global__ void __launch_bounds__(NTHREADS, 1)
     for (int i = 0; i < BN; i++) acc[i] = 0.f;
     const uint32_t tlane = tmem_d + ((uint32_t)(wq * 32) << 16);
     float s_next = 0.f;
-    if (stage_it && num_kb > 0) s_next = (my_m < p.M ? as_row[0] : 0.f) * bs_col[0];
+    if (stage_it && num_kb > 0)
+      s_next = (my_m < p.M ? as_row[(int64_t)kb0 * p.as_k] : 0.f) * bs_col[(int64_t)kb0 * p.bs_k];
     for (int kb = 0; kb < num_kb; kb++) {
       const int slot = kb & 1;
       float* scs = sc + slot * BN;
       if (stage_it) scs[et] = s_next;
       if (stage_it && kb + 1 < num_kb)
-        s_next = (my_m < p.M ? as_row[(int64_t)(kb + 1) * p.as_k] : 0.f) * bs_col[(int64_t)(kb + 1) * p.bs_k];
+        s_next = (my_m < p.M ? as_row[(int64_t)(kb0 + kb + 1) * p.as_k] : 0.f) *
+                 bs_col[(int64_t)(kb0 + kb + 1) * p.bs_k];
       asm volatile("bar.sync 1, 128;" ::: "memory");
       mbar_wait(bar_acc_full + 8u * slot, ((uint32_t)kb >> 1) & 1u);
       tc_fence_after();
@@ -193,6 +215,31 @@ __global__ void __launch_bounds__(NTHREADS, 1)
       tc_fence_before();
       mbar_arrive(bar_acc_empty + 8u * slot);   // TMEM slot may be overwritten
     }
+    if (p.split > 1) {
+      // ---- split-K reduction over distributed shared memory: slices 1.. push their fp32 tiles into slice 0's
+      // idle pipeline smem ([slice-1][m][128 n] floats, lanes -> consecutive words), slice 0 adds them in slice
+      // order (deterministic) and runs the epilogue alone.
+      cluster_sync();   // A: every CTA of the cluster is past its main loop (its MMAs have all completed)
+      if (ks > 0) {
+        const uint32_t remote = mapa(base + (uint32_t)((ks - 1) * BN) * (BM * 4) + (uint32_t)et * 4u, 0);
+#pragma unroll
+        for (int j = 0; j < BN; j++)
+          asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote + (uint32_t)j * (BM * 4)), "f"(acc[j])
+                       : "memory");
+      }
+      cluster_sync();   // B: partial tiles have landed (release / acquire at cluster scope)
+      for (int z = 1; ks == 0 && z < p.split; z++) {
+        const uint32_t src = base + (uint32_t)((z - 1) * BN) * (BM * 4) + (uint32_t)et * 4u;
+#pragma unroll
+        for (int j = 0; j < BN; j++) {
+          float v;
+          asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(src + (uint32_t)j * (BM * 4)) : "memory");
+          acc[j] += v;
+        }
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");   // the staging below overwrites the partial tiles
+    }
+    if (ks == 0) {
     // ---- epilogue: out[m][n] = T(acc); lane = n, register index = m
     auto pack2 = [&](float lo, float hi) -> uint32_t {
       if (p.out_bf16) {
@@ -229,6 +276,11 @@ __global__ void __launch_bounds__(NTHREADS, 1)
         if (m < p.M) out16[(int64_t)m * p.ldo + r] = (uint16_t)(pack2(acc[j], 0.f) & 0xffffu);
       }
     }
+    }  // ks == 0
+  }
+  if (warp < 2 && p.split > 1) {   // producer / MMA warps take part in the two cluster barriers
+    cluster_sync();
+    cluster_sync();
   }
   tc_fence_before();
   __syncthreads();
@@ -258,8 +310,39 @@ static int launch(const CUtensorMap& tmW, const CUtensorMap& tmA, const CUtensor
                                    smem_max));
     configured = true;
   }
-  gemm_fp8_block_kernel<BN><<<grid, NTHREADS, smem, stream>>>(tmW, tmA, tmO, p);
-  B200_LAUNCH_CHECK();
+  // split-K (decode batches: one token tile, few weight tiles): K slices over the CTAs of a (1, 1, split)
+  // cluster so that tiles x split approaches the SM count; every slice keeps >= 4 k-blocks and the
+  // (split - 1) fp32 partial tiles must fit slice 0's pipeline smem.
+  const int total_kb = (p.K + BK - 1) / BK;
+  int split = 1;
+  if (grid.y == 1) {
+    const int want = p.split;   // 0 = auto
+    for (int sp = 8; sp >= 2; sp >>= 1) {
+      const bool fits = (sp - 1) * BN * BM * 4 <= stages * (int)STAGE_BYTES && sp <= total_kb;
+      if (!fits) continue;
+      if (want > 0 ? sp <= want : ((int)grid.x * sp <= sm_count() && total_kb / sp >= 4)) { split = sp; break; }
+    }
+  }
+  p.split = split;
+  if (split == 1) {
+    gemm_fp8_block_kernel<BN><<<grid, NTHREADS, smem, stream>>>(tmW, tmA, tmO, p);
+    B200_LAUNCH_CHECK();
+    return B200_OK;
+  }
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(grid.x, 1, split);
+  cfg.blockDim = dim3(NTHREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 1;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = split;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  B200_CUDA(cudaLaunchKernelEx(&cfg, gemm_fp8_block_kernel<BN>, tmW, tmA, tmO, p));
   return B200_OK;
 }
 
@@ -277,7 +360,7 @@ static int make_tmap_2d(CUtensorMap* tm, const void* base, int rows, int K, int6
 extern "C" int b200_fp8_gemm_blockscaled(void* out, const void* a, const void* b, const float* a_scales,
                                          const float* b_scales, int M, int N, int K, int64_t lda,
                                          int64_t ldb, int64_t ldo, int64_t as_stride_m, int64_t as_stride_k,
-                                         int64_t bs_stride_k, int64_t bs_stride_n, int out_dtype,
+                                         int64_t bs_stride_k, int64_t bs_stride_n, int out_dtype, int split,
                                          b200_stream_t stream_) {
   using namespace b200;
   using namespace b200::gemm8b;
@@ -303,6 +386,8 @@ extern "C" int b200_fp8_gemm_blockscaled(void* out, const void* a, const void* b
   p.M = M; p.N = N; p.K = K;
   p.ldo = ldo;
   p.out_bf16 = out_dtype == B200_BF16;
+  B200_CHECK(split >= 0 && split <= 8, B200_ERR_INVALID, "cutlass_scaled_mm (blockwise): split must be 0 (auto) .. 8");
+  p.split = split;
   const int bn = M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : 128;
   CUtensorMap tmW, tmA, tmO;
   memset(&tmO, 0, sizeof(tmO));
