@@ -540,6 +540,25 @@ B200_API int b200_allreduce_fused_add_rms_norm(void* ctx, void* out, const void*
                                                int64_t num_tokens, int hidden, int dtype,
                                                b200_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Sampler-side kernels of the decode step.
+ * b200_argmax: greedy sampling, out[r] = argmax_v logits[r, v] (vllm/v1/sample/sampler.py greedy_sample =
+ *   logits.argmax(dim=-1)); ties -> lowest index, NaN is the maximum; logits bf16 / f16 / f32.
+ * b200_top_k_top_p: apply_top_k_top_p (vllm/v1/sample/ops/topk_topp_sampler.py:349-408) on fp32 logits, in
+ *   place: values below the k[r]-th largest become -inf (ties kept; k[r] >= vocab or <= 0: no top-k), then
+ *   the tokens whose ascending cumulative softmax mass is <= 1 - p[r] become -inf; the largest always stays.
+ *   k (int32 / int64, k_dtype) and p (float) are device arrays [rows], either may be NULL.
+ * b200_apply_repetition_penalties: torch.ops._C.apply_repetition_penalties_
+ *   (csrc/libtorch_stable/sampler.cu:14-45,618-657): masks are bool [rows, vocab], penalties [rows] in the
+ *   logits dtype; contiguous. */
+B200_API int b200_argmax(int64_t* out, const void* logits, int64_t rows, int vocab, int64_t row_stride,
+                         int dtype, b200_stream_t stream);
+B200_API int b200_top_k_top_p(float* logits, const void* k, int k_dtype, const float* p, int64_t rows,
+                              int vocab, int64_t row_stride, b200_stream_t stream);
+B200_API int b200_apply_repetition_penalties(void* logits, const void* prompt_mask, const void* output_mask,
+                                             const void* penalties, int64_t rows, int vocab, int dtype,
+                                             b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

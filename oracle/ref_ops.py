@@ -770,3 +770,44 @@ def silu_and_mul_nvfp4_quant(x: torch.Tensor, global_scale: float, return_scaled
     g, u = x[..., :d].float(), x[..., d:].float()
     act = ((g / (1.0 + torch.exp(-g))) * u).to(x.dtype)
     return nvfp4_quant(act, global_scale, return_scaled=return_scaled)
+
+
+# --------------------------------------------------------------------------------------------
+# Sampler-side ops.  vllm/v1/sample/ops/topk_topp_sampler.py:367-408 (apply_top_k_top_p_pytorch, the
+# sort-based definition every other implementation in the reference is tested against) and
+# vllm/_custom_ops.py:309-322 (apply_repetition_penalties_torch), restated with the same torch ops.
+# --------------------------------------------------------------------------------------------
+def apply_top_k_top_p(logits: torch.Tensor, k: torch.Tensor | None, p: torch.Tensor | None):
+    """Returns (masked logits, info) where info carries what a test needs to exclude legitimate boundary
+    cases: `kth` = the k-th largest value per row (ties of it are kept), `cum` = the ascending cumulative
+    softmax mass at every token's sorted position scattered back to vocabulary order."""
+    logits = logits.clone().float()
+    info = {}
+    if k is None and p is None:
+        return logits, info
+    logits_sort, logits_idx = logits.sort(dim=-1, descending=False, stable=True)
+    if k is not None:
+        top_k_mask = logits_sort.size(1) - k.to(torch.long)
+        top_k_mask = logits_sort.gather(1, top_k_mask.clamp(min=0).unsqueeze(dim=1))
+        info["kth"] = top_k_mask.squeeze(1).clone()
+        no_k = (k.to(torch.long) >= logits_sort.size(1)) | (k.to(torch.long) <= 0)
+        top_k_mask = torch.where(no_k.unsqueeze(1), torch.full_like(top_k_mask, -float("inf")), top_k_mask)
+        logits_sort.masked_fill_(logits_sort < top_k_mask, -float("inf"))
+    if p is not None:
+        probs_sort = logits_sort.softmax(dim=-1)
+        probs_sum = torch.cumsum(probs_sort, dim=-1)
+        info["cum"] = torch.empty_like(probs_sum).scatter_(dim=-1, index=logits_idx, src=probs_sum)
+        top_p_mask = probs_sum <= 1 - p.unsqueeze(dim=1)
+        top_p_mask[:, -1] = False
+        logits_sort.masked_fill_(top_p_mask, -float("inf"))
+    return logits.scatter_(dim=-1, index=logits_idx, src=logits_sort), info
+
+
+def apply_repetition_penalties(logits: torch.Tensor, prompt_mask: torch.Tensor, output_mask: torch.Tensor,
+                               repetition_penalties: torch.Tensor) -> torch.Tensor:
+    """csrc/libtorch_stable/sampler.cu:14-45: logit > 0 ? logit / penalty : logit * penalty in the logits dtype
+    (fp32 operation, one rounding) on tokens of the prompt or the output."""
+    pen = repetition_penalties.to(logits.dtype).float().unsqueeze(1)
+    x = logits.float()
+    y = torch.where(x > 0, x / pen, x * pen).to(logits.dtype)
+    return torch.where(prompt_mask | output_mask, y, logits)

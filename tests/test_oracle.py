@@ -216,3 +216,28 @@ def test_block_scaled_mm_restatement_vs_reference_python_oracle():
     got = ref_ops.w8a8_block_scaled_mm(a.view(torch.uint8).numpy(), b.view(torch.uint8).numpy(),
                                        a_s.numpy(), b_s.numpy())
     np.testing.assert_allclose(got, c.numpy(), rtol=2e-5, atol=1e-3)
+
+
+@pytest.mark.parametrize("mode", ["k", "p", "kp"])
+def test_top_k_top_p_restatement_vs_reference_golden(mode):
+    """tests/golden/topk_topp_ref.npz = outputs of the reference's apply_top_k_top_p_pytorch
+    (topk_topp_sampler.py:367-408), generated by tests/golden/make_sampler_golden.py."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "topk_topp_ref.npz"))
+    x, k, p = torch.from_numpy(z["x"]), torch.from_numpy(z["k"]), torch.from_numpy(z["p"])
+    got, _ = ref_ops.apply_top_k_top_p(x, k if "k" in mode else None, p if "p" in mode else None)
+    np.testing.assert_array_equal(got.numpy(), z["out_" + mode])
+
+
+def test_repetition_penalties_restatement_vs_reference_python():
+    """apply_repetition_penalties_torch (vllm/_custom_ops.py:309-322), restated literally, vs the kernel restatement
+    (fp32 logits: the two definitions agree bit for bit)."""
+    torch.manual_seed(0)
+    x = torch.randn(6, 500) * 4
+    pm, om = torch.rand(6, 500) < 0.2, torch.rand(6, 500) < 0.2
+    pen = torch.rand(6) + 0.7
+    rp = pen.unsqueeze(1).repeat(1, 500)
+    penalties = torch.where(pm | om, rp, 1.0)
+    want = x * torch.where(x > 0, 1.0 / penalties, penalties)
+    got = ref_ops.apply_repetition_penalties(x, pm, om, pen)
+    np.testing.assert_allclose(got.numpy(), want.numpy(), rtol=2e-7, atol=0)

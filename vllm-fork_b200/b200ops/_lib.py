@@ -138,6 +138,10 @@ SIGNATURES = {
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int64, c_int64,
          c_int64, c_int64, c_int64, c_int64, c_int, c_int, c_void_p],
     ),
+    "b200_argmax": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int64, c_int, c_void_p]),
+    "b200_top_k_top_p": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_int64, c_int, c_int64, c_void_p]),
+    "b200_apply_repetition_penalties": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     "b200_fp8_gemm": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64,

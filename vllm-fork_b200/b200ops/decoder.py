@@ -9,8 +9,8 @@ Per layer:
     silu_and_mul_quant -> down GEMM (-> all-reduce)
 then final norm -> bf16 lm_head -> greedy argmax.
 
-Embedding lookup / bf16 lm_head / argmax are outside the path named by north_star and use plain torch
-ops (a library GEMM for lm_head); everything else - including the SURVEY.md section 8f rank-1 rows
+Embedding lookup / bf16 lm_head are outside the path named by north_star and use plain torch ops (a library
+GEMM for lm_head); greedy sampling is this package's argmax kernel; everything else - including the SURVEY.md section 8f rank-1 rows
 RMSNorm(+residual)+FP8-quant and RoPE - is libb200ops.so.
 Tensor parallelism: attention heads and GEMM N/K are sharded over the ranks
 of `tp_group`, one all-reduce after o_proj and down_proj (linear.py:1766-1767). `comm` picks the rung
@@ -295,7 +295,7 @@ class DecoderModel:
             n += 1 if self.ar is not None else 0
         ops.fused_add_rms_norm(red, self.residual, self.final_norm, s.eps); n += 1
         logits = red @ self.lm_head.t()
-        self.next_tokens.copy_(logits.argmax(-1))
+        ops.greedy_sample(logits, out=self.next_tokens); n += 1   # Sampler.greedy_sample
         self.launches_per_step = n
 
     def _all_reduce(self, t):
@@ -408,7 +408,7 @@ class DecoderModel:
         else:
             ops.fused_add_rms_norm(red, self.residual, self.final_norm, s.eps); n += 1
         logits = red @ self.lm_head.t()
-        self.next_tokens.copy_(logits.argmax(-1))
+        ops.greedy_sample(logits, out=self.next_tokens); n += 1   # Sampler.greedy_sample
         self.launches_per_step = n
 
     def capture(self) -> None:

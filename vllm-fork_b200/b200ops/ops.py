@@ -1046,3 +1046,64 @@ def merge_attn_states(output: torch.Tensor, prefix_output: torch.Tensor, prefix_
         -1 if prefill_tokens_with_context is None else int(prefill_tokens_with_context),
         _dt(prefix_output), _lib.FP8_E4M3 if fp8_out else _dt(output), _stream())
     _lib.check(rc, "merge_attn_states")
+
+
+# ------------------------------------------------------------------------------------------------
+# Sampler-side ops      reference: vllm/v1/sample/sampler.py (greedy_sample),
+# vllm/v1/sample/ops/topk_topp_sampler.py:349-408 (apply_top_k_top_p), vllm/_custom_ops.py:309-357
+# ------------------------------------------------------------------------------------------------
+def greedy_sample(logits: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """logits.argmax(dim=-1).view(-1) (Sampler.greedy_sample): int64 [rows]; ties -> lowest index."""
+    _cuda(logits, out)
+    if logits.dim() != 2 or logits.stride(1) != 1:
+        raise RuntimeError("greedy_sample: logits must be [rows, vocab] with a contiguous last dim")
+    rows, vocab = logits.shape
+    if out is None:
+        out = torch.empty(rows, dtype=torch.int64, device=logits.device)
+    elif out.dtype != torch.int64 or out.numel() != rows or not out.is_contiguous():
+        raise RuntimeError("greedy_sample: out must be a contiguous int64 [rows] tensor")
+    rc = _lib.load().b200_argmax(_p(out), _p(logits), rows, vocab, logits.stride(0) if rows > 1 else vocab,
+                                 _dt(logits), _stream())
+    _lib.check(rc, "greedy_sample")
+    return out
+
+
+def apply_top_k_top_p(logits: torch.Tensor, k: torch.Tensor | None, p: torch.Tensor | None) -> torch.Tensor:
+    """Same contract as topk_topp_sampler.apply_top_k_top_p: fp32 logits [rows, vocab] masked in place with -inf
+    (top-k keeps ties of the k-th value, top-p drops the ascending prefix whose softmax mass is <= 1 - p and always
+    keeps the largest token) and returned. k int32 / int64 [rows], p float32 [rows]."""
+    if p is None and k is None:
+        return logits
+    _cuda(logits, k, p)
+    if logits.dim() != 2 or logits.dtype != torch.float32 or logits.stride(1) != 1:
+        raise RuntimeError("apply_top_k_top_p: logits must be float32 [rows, vocab] with a contiguous last dim")
+    rows, vocab = logits.shape
+    kd = 0
+    if k is not None:
+        if k.dtype not in (torch.int32, torch.int64) or k.numel() != rows or not k.is_contiguous():
+            raise RuntimeError("apply_top_k_top_p: k must be a contiguous int32 / int64 [rows] tensor")
+        kd = _lib.I32 if k.dtype == torch.int32 else _lib.I64
+    if p is not None and (p.dtype != torch.float32 or p.numel() != rows or not p.is_contiguous()):
+        raise RuntimeError("apply_top_k_top_p: p must be a contiguous float32 [rows] tensor")
+    rc = _lib.load().b200_top_k_top_p(_p(logits), _p(k), kd, _p(p), rows, vocab,
+                                      logits.stride(0) if rows > 1 else vocab, _stream())
+    _lib.check(rc, "apply_top_k_top_p")
+    return logits
+
+
+def apply_repetition_penalties(logits: torch.Tensor, prompt_mask: torch.Tensor, output_mask: torch.Tensor,
+                               repetition_penalties: torch.Tensor) -> None:
+    """torch.ops._C.apply_repetition_penalties_ (vllm/_custom_ops.py:325-357), in place."""
+    _cuda(logits, prompt_mask, output_mask, repetition_penalties)
+    if not (logits.is_contiguous() and prompt_mask.is_contiguous() and output_mask.is_contiguous()
+            and repetition_penalties.is_contiguous()):
+        raise RuntimeError("apply_repetition_penalties_: tensors must be contiguous")
+    if prompt_mask.dtype != torch.bool or output_mask.dtype != torch.bool:
+        raise RuntimeError("apply_repetition_penalties_: masks must be bool")
+    if prompt_mask.shape != logits.shape or output_mask.shape != logits.shape:
+        raise RuntimeError("apply_repetition_penalties_: masks must have the shape of logits")
+    rows, vocab = logits.shape
+    pen = repetition_penalties.to(logits.dtype)
+    rc = _lib.load().b200_apply_repetition_penalties(_p(logits), _p(prompt_mask), _p(output_mask), _p(pen),
+                                                     rows, vocab, _dt(logits), _stream())
+    _lib.check(rc, "apply_repetition_penalties_")
