@@ -5,7 +5,8 @@
     RMSNorm + FP8 quant on the owner, all-gather - equals all-reduce followed by
     fused_add_rms_norm_static_fp8_quant on every rank, BIT-exactly (oracle/ref_ops.py arithmetic),
     including a token count that does not divide by the world size;
-(3) B200AllReduce refuses to come up without CUDA (no CPU fallback)."""
+(3) B200AllReduce refuses to come up without CUDA (no CPU fallback);
+(4) expert parallelism: per-rank fused_experts through expert_map + one all-reduce equals the full MoE block."""
 import os
 import socket
 import sys
@@ -89,6 +90,25 @@ def _worker(rank, world, port, q):
                                           torch.as_tensor(ref_res).float().numpy()[lo:hi])
         los = [tp.rows_of_rank(5, r, 2) for r in range(2)]
         assert los == [(0, 3), (3, 5)] and tp.rows_of_rank(1, 1, 2) == (1, 1)
+        # ---- (4) expert parallel (BASELINE configs[3]): every rank holds all tokens, runs fused_experts on its
+        # own experts through expert_map (non-local slots contribute zero) and one all-reduce restores the full
+        # MoE output (fused_moe.py:1821-1822) - oracle arithmetic, bit-identical FP8 inputs on both ranks
+        E, topk, Hm, Im, Mm = 4, 2, 64, 32, 7
+        xm = (torch.randn(Mm, Hm, generator=g) * 0.5).to(torch.bfloat16)
+        w1 = torch.randint(0, 0x60, (E, 2 * Im, Hm), generator=g, dtype=torch.uint8)
+        w2 = torch.randint(0, 0x60, (E, Hm, Im), generator=g, dtype=torch.uint8)
+        w1s, w2s = torch.rand(E, generator=g) * 0.01 + 0.005, torch.rand(E, generator=g) * 0.01 + 0.005
+        a1, a2 = torch.tensor([0.02]), torch.tensor([0.05])
+        tw, ids, _ = ref_ops.topk_softmax(torch.randn(Mm, E, generator=g), topk, True)
+        lo, hi = tp.expert_shard(E, rank, world)
+        em = tp.expert_map(E, rank, world)
+        assert em.tolist() == [i - lo if lo <= i < hi else -1 for i in range(E)]
+        part = ref_ops.fused_experts_fp8(xm, w1[lo:hi], w2[lo:hi], tw, ids, w1s[lo:hi], w2s[lo:hi], a1, a2,
+                                         expert_map=em).double()
+        dist.all_reduce(part)
+        full = ref_ops.fused_experts_fp8(xm, w1, w2, tw, ids, w1s, w2s, a1, a2).double()
+        np.testing.assert_allclose(part.numpy(), full.numpy(), rtol=1e-6, atol=1e-6)
+        assert tp.expert_map(E, 0, 1) is None
         # ---- (3) no CPU fallback for the NVLink collective
         from b200ops.all_reduce import B200AllReduce
         try:

@@ -81,8 +81,7 @@ class DecoderModel:
             assert s.experts % tp_size == 0, "expert parallel: experts must divide over the ranks"
             assert comm != "fused", "MoE layers: comm must be nccl or nvlink"
             assert quant == "fp8", "MoE layers: FP8 fused_experts only"
-            per = s.experts // tp_size
-            self.e_lo, self.e_hi = tp_rank * per, (tp_rank + 1) * per
+            self.e_lo, self.e_hi = tp.expert_shard(s.experts, tp_rank, tp_size)
         self.hq, self.hkv = s.heads // tp_size, s.kv_heads // tp_size
         self.inter = s.inter if s.experts > 0 else s.inter // tp_size
         self.D, self.bs = s.head_size, block_size
@@ -204,11 +203,9 @@ class DecoderModel:
             self.topk_w = torch.empty(S, k, dtype=torch.float32, device=self.dev)
             self.topk_ids = torch.empty(S, k, dtype=torch.int32, device=self.dev)
             self.tok_exp_idx = torch.empty(S, k, dtype=torch.int32, device=self.dev)
-            self.expert_map = None
-            if tp_size > 1:   # global expert id -> local id or -1 (fused_moe/layer.py determine_expert_map)
-                em = torch.full((E,), -1, dtype=torch.int32)
-                em[self.e_lo:self.e_hi] = torch.arange(self.e_hi - self.e_lo, dtype=torch.int32)
-                self.expert_map = em.to(self.dev)
+            # global expert id -> local id or -1 (fused_moe/layer.py determine_expert_map)
+            em = tp.expert_map(E, tp_rank, tp_size)
+            self.expert_map = None if em is None else em.to(self.dev)
         # gate_up GEMM + silu_and_mul + FP8 quant in one kernel. Measured (gpurun_out/bench4.json): at
         # batch 256 the GEMM is tensor-bound and the fused epilogue (silu on 4 warps of 112 CTAs, not
         # overlapped) costs more than the separate full-GPU activation kernel: 16.55 vs 15.95 ms/step.

@@ -40,3 +40,24 @@ def rows_of_rank(num_tokens: int, rank: int, world: int) -> tuple[int, int]:
     """[lo, hi) token rows that `rank` normalises in the fused reduce-scatter epilogue."""
     per = (num_tokens + world - 1) // world
     return min(num_tokens, rank * per), min(num_tokens, (rank + 1) * per)
+
+
+def expert_shard(num_experts: int, rank: int, world: int) -> tuple[int, int]:
+    """Expert parallelism: rank r owns the contiguous experts [lo, hi) whole (linear placement of
+    fused_moe/layer.py determine_expert_map)."""
+    if num_experts % world != 0:
+        raise ValueError(f"expert parallel: {num_experts} experts do not divide over {world} ranks")
+    per = num_experts // world
+    return rank * per, (rank + 1) * per
+
+
+def expert_map(num_experts: int, rank: int, world: int):
+    """int32 [num_experts]: global expert id -> local id on this rank, or -1 (the `expert_map` argument of
+    fused_experts / moe_align_block_size). None when there is one rank."""
+    import torch
+    if world == 1:
+        return None
+    lo, hi = expert_shard(num_experts, rank, world)
+    em = torch.full((num_experts,), -1, dtype=torch.int32)
+    em[lo:hi] = torch.arange(hi - lo, dtype=torch.int32)
+    return em
