@@ -13,9 +13,21 @@ from b200ops import ops  # noqa: E402
 
 
 def timeit(fn, iters=20):
+    """CUDA-graph replay of `fn` (10 calls per graph): python / ctypes launch cost (~30 us per call) must not be
+    part of a kernel number."""
     for _ in range(3):
         fn()
     torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(10):
+            fn()
+    g.replay()
+    torch.cuda.synchronize()
+    return _time(g.replay, max(1, iters // 10)) / 10
+
+
+def _time(fn, iters):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(iters):

@@ -153,7 +153,9 @@ def fused_experts(
     rc = lib.b200_moe_permute_fp8(_p(a8), _p(hidden_states), _p(sorted_ids), _p(npp), _p(a1_scale), P,
                                   topk, numel, H, hidden_states.stride(0), _dt(hidden_states), _stream())
     _lib.check(rc, "moe_permute")
-    inter = torch.zeros(P, N1, dtype=dt, device=dev)
+    # blocks past num_tokens_post_pad are skipped by the GEMMs and never gathered: zero-fill only when a
+    # dynamic activation scale will reduce over the whole buffer
+    inter = (torch.zeros if a2_scale is None else torch.empty)(P, N1, dtype=dt, device=dev)
     rc = lib.b200_moe_grouped_gemm_fp8(_p(inter), _p(a8), _p(w1), _p(expert_ids), _p(npp),
                                        _p(a1_scale), _p(w1_scale), None, P, E, N1, H, bs,
                                        1 if per_channel_quant else 0, _dt(inter), _stream())
@@ -166,7 +168,7 @@ def fused_experts(
     else:
         ops.silu_and_mul_quant(h8, inter, a2_scale)
     # row weights in sorted order: w_sorted[inv[t*k + j]] = topk_weights[t, j]
-    out2 = torch.zeros(P, H, dtype=dt, device=dev)
+    out2 = torch.empty(P, H, dtype=dt, device=dev)
     rc = lib.b200_moe_grouped_gemm_fp8(_p(out2), _p(h8), _p(w2), _p(expert_ids), _p(npp),
                                        _p(a2_scale), _p(w2_scale), None, P, E, H, I, bs,
                                        1 if per_channel_quant else 0, _dt(out2), _stream())

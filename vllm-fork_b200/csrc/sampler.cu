@@ -46,13 +46,35 @@ __global__ void __launch_bounds__(512)
   int bi = 0x7fffffff;
   const bool vec = (reinterpret_cast<uintptr_t>(row) & 15) == 0;
   const int nvec = vec ? vocab / N : 0;
-  for (int v = threadIdx.x; v < nvec; v += blockDim.x) {
-    const uint4 raw = ld_nc_v4(row + (int64_t)v * N);
-    const in_t* e = reinterpret_cast<const in_t*>(&raw);
+  // 4 independent 16-byte loads in flight per thread; a vector enters the exact (tie / NaN aware) comparison only
+  // when its fmaxf-tree maximum beats the running best or its sum is NaN (a NaN element, or +inf with -inf)
+  constexpr int U = 4;
+  for (int v0 = threadIdx.x; v0 < nvec; v0 += blockDim.x * U) {
+    uint4 raw[U];
 #pragma unroll
-    for (int j = 0; j < N; j++) {
-      const float x = Cvt<in_t>::to_f32(e[j]);
-      if (better<in_t>(x, v * N + j, bv, bi)) { bv = x; bi = v * N + j; }
+    for (int u = 0; u < U; u++) {
+      const int v = v0 + u * blockDim.x;
+      if (v < nvec) raw[u] = ld_nc_v4(row + (int64_t)v * N);
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int v = v0 + u * blockDim.x;
+      if (v >= nvec) break;
+      const in_t* e = reinterpret_cast<const in_t*>(&raw[u]);
+      float m = -INFINITY, sum = 0.f;
+#pragma unroll
+      for (int j = 0; j < N; j++) {
+        const float x = Cvt<in_t>::to_f32(e[j]);
+        m = fmaxf(m, x);
+        sum += x;
+      }
+      if (m > bv || sum != sum || bi == 0x7fffffff) {
+#pragma unroll
+        for (int j = 0; j < N; j++) {
+          const float x = Cvt<in_t>::to_f32(e[j]);
+          if (better<in_t>(x, v * N + j, bv, bi)) { bv = x; bi = v * N + j; }
+        }
+      }
     }
   }
   for (int i = nvec * N + threadIdx.x; i < vocab; i += blockDim.x) {
