@@ -13,6 +13,7 @@
 // store. Routing tables are read on the device: no host sync, CUDA-graph safe.
 #include "tcgen05.cuh"
 
+#include <cstdlib>
 #include <cstring>
 
 namespace b200 {
@@ -176,6 +177,13 @@ static int launch(const CUtensorMap& tmW, const CUtensorMap& tmA, const CUtensor
   const int smem_max = max_smem_optin();
   int stages = (smem_max - 1024 - 256 - 64) / (int)STAGE_BYTES;
   if (stages > MAX_STAGES) stages = MAX_STAGES;
+  // many short CTAs (one token block x one weight slab each): a pipeline that fills the SM alone leaves its
+  // prologue and epilogue uncovered (ncu r1k: DRAM traffic == algorithmic bytes but 4.4 TB/s). Half the ring lets
+  // two CTAs share an SM so one streams while the other drains. B200_MOE_STAGES overrides (tuning).
+  const int two_cta = ((228 * 1024) / 2 - 1024 - (16 * MAX_STAGES + 64 + 1024)) / (int)STAGE_BYTES;
+  if ((int64_t)grid.x * grid.y >= 2 * (int64_t)sm_count() && two_cta >= 3 && two_cta < stages) stages = two_cta;
+  static const int forced = [] { const char* e = getenv("B200_MOE_STAGES"); return e ? atoi(e) : 0; }();
+  if (forced >= 2 && forced <= MAX_STAGES && forced * (int)STAGE_BYTES + 2048 <= smem_max) stages = forced;
   p.stages = stages;
   const int smem = stages * (int)STAGE_BYTES + 16 * MAX_STAGES + 64 + 1024;
   static bool configured = false;
