@@ -567,6 +567,7 @@ def fused_experts_fp8(x: torch.Tensor, w1_bits: torch.Tensor, w2_bits: torch.Ten
     x8 = torch.from_numpy(e4m3_bits_to_f32(static_scaled_fp8_quant(x, a1_scale)))
     a1 = float(a1_scale.reshape(-1)[0]); a2 = float(a2_scale.reshape(-1)[0])
     out = torch.zeros(M, H, dtype=torch.float32)
+    deq = {}
     for t in range(M):
         for k in range(topk_ids.shape[1]):
             e = int(topk_ids[t, k])
@@ -576,8 +577,10 @@ def fused_experts_fp8(x: torch.Tensor, w1_bits: torch.Tensor, w2_bits: torch.Ten
                 e = int(expert_map[e])
                 if e < 0:
                     continue
-            w1 = torch.from_numpy(e4m3_bits_to_f32(w1_bits[e].numpy()))
-            w2 = torch.from_numpy(e4m3_bits_to_f32(w2_bits[e].numpy()))
+            if e not in deq:   # dequantise each expert once (same values, test run time only)
+                deq[e] = (torch.from_numpy(e4m3_bits_to_f32(w1_bits[e].numpy())),
+                          torch.from_numpy(e4m3_bits_to_f32(w2_bits[e].numpy())))
+            w1, w2 = deq[e]
             h = (x8[t] @ w1.t()) * (a1 * float(w1_scale[e]))
             h = h.to(x.dtype)
             act = silu_and_mul(h[None, :])
