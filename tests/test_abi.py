@@ -77,3 +77,34 @@ def test_argument_validation_before_launch(lib):
     assert rc == _lib.ERR_INVALID
     with pytest.raises(RuntimeError):
         _lib.check(rc, "reshape_and_cache_flash")
+
+
+def test_no_cpu_fallback_round1_next_rows():
+    """The operators added for the SURVEY 8f rows refuse CPU tensors like the rest (no CPU fallback), and their
+    argument checks run before any launch (validation through the C ABI works without a device)."""
+    from b200ops import _lib, ops
+    lib = _lib.load()
+    x = torch.randn(4, 256)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.per_token_group_quant_fp8(x.to(torch.bfloat16), 128)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.apply_top_k_top_p(x, torch.ones(4, dtype=torch.int32), None)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.greedy_sample(x)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.apply_repetition_penalties(x, x > 0, x < 0, torch.ones(4))
+    a8 = torch.zeros(4, 256, dtype=torch.float8_e4m3fn)
+    w8 = torch.zeros(128, 256, dtype=torch.float8_e4m3fn)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.cutlass_scaled_mm(a8, w8.t(), torch.ones(4, 2), torch.ones(2, 1), torch.bfloat16)
+    # C-ABI validation before launch
+    rc = lib.b200_fp8_quant_token_group(None, None, None, 4, 100, 64, 100, 100, 1, 1, 1e-10, -448.0, 448.0, 0,
+                                        _lib.BF16, None)
+    assert rc == _lib.ERR_INVALID and "divisible" in _lib.last_error()
+    rc = lib.b200_fp8_gemm_blockscaled(None, None, None, None, None, 4, 128, 256, 256, 256, 128, 2, 1, 1, 2,
+                                       _lib.BF16, 0, None)
+    assert rc == _lib.ERR_INVALID and "null pointer" in _lib.last_error()
+    rc = lib.b200_top_k_top_p(None, None, 0, None, 4, 0, 0, None)
+    assert rc == _lib.ERR_INVALID
+    rc = lib.b200_argmax(None, None, 4, 100, 100, _lib.I32, None)
+    assert rc == _lib.ERR_INVALID and "bf16 / f16 / f32" in _lib.last_error()
