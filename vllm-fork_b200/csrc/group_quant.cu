@@ -19,6 +19,20 @@
 
 namespace b200 {
 
+// x / y, correctly rounded, from the correctly rounded reciprocal r = RN(1 / y): q0 = RN(x r) is a faithful quotient,
+// the remainder x - q0 y is exact in one FMA, and RN(q0 + rem r) is the correctly rounded quotient (Markstein's
+// division theorem; no overflow / underflow can occur here: |x| <= 448 y up to the clamp, y >= eps / 448, and
+// quotients small enough for the remainder to underflow round to e4m3 zero either way). 3 issue slots instead of
+// the ~12 of __fdiv_rn, which made the kernel issue-bound (2.6 TB/s); bit-exactness vs the oracle's IEEE division
+// and vs the wheel's kernel is what tests/test_gpu_fp8_quant.py and test_gpu_vs_wheel.py check.
+__device__ __forceinline__ float div_by(float x, float y, float r) {
+  const float q0 = __fmul_rn(x, r);
+  const float rem = __fmaf_rn(-q0, y, x);
+  const float q1 = __fmaf_rn(rem, r, q0);
+  // inf / nan inputs: fall back to the plain quotient semantics (inf * r = inf, rem = nan)
+  return (q0 - q0 == 0.f) ? q1 : __fdiv_rn(x, y);
+}
+
 template <typename in_t, int VPL /* 16-byte vectors per lane */, int LANES>
 __global__ void __launch_bounds__(256)
     fp8_quant_token_group_kernel(uint8_t* __restrict__ out, float* __restrict__ scales,
@@ -53,6 +67,7 @@ __global__ void __launch_bounds__(256)
   float y_s = __fdiv_rn(m, fp8_max);
   if (ue8m0) y_s = exp2f(ceilf(log2f(fmaxf(fabsf(y_s), 1e-10f))));
   if (live && lane == 0) scales[row * s_stride_row + (int64_t)gcol * s_stride_col] = y_s;
+  const float r_s = __frcp_rn(y_s);
 #pragma unroll
   for (int i = 0; i < VPL; i++) {
     const int vi = lane + i * LANES;
@@ -61,8 +76,8 @@ __global__ void __launch_bounds__(256)
       uint16_t o[N / 2];
 #pragma unroll
       for (int j = 0; j < N / 2; j++) {
-        float a = fminf(fmaxf(__fdiv_rn(Cvt<in_t>::to_f32(e[2 * j]), y_s), fp8_min), fp8_max);
-        float b = fminf(fmaxf(__fdiv_rn(Cvt<in_t>::to_f32(e[2 * j + 1]), y_s), fp8_min), fp8_max);
+        float a = fminf(fmaxf(div_by(Cvt<in_t>::to_f32(e[2 * j]), y_s, r_s), fp8_min), fp8_max);
+        float b = fminf(fmaxf(div_by(Cvt<in_t>::to_f32(e[2 * j + 1]), y_s, r_s), fp8_min), fp8_max);
         o[j] = f32x2_to_e4m3x2(a, b);
       }
       if constexpr (N == 8)
