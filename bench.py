@@ -23,6 +23,12 @@ for _p in (ROOT, os.path.join(ROOT, "vllm-fork_b200")):
     if _p not in sys.path:
         sys.path.insert(0, _p)
 
+if "reference" in sys.argv and any(a == "--impl" or a.startswith("--impl=") for a in sys.argv):
+    # torch.distributed.run exports OMP_NUM_THREADS=1 to every rank; the reference arm is a CPU run that
+    # must use all the host threads it can, and the OpenMP runtimes read the variable when they load
+    for _v in ("OMP_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ.pop(_v, None)
+
 import torch  # noqa: E402
 
 METRIC = "decode_tokens_per_s"
@@ -47,6 +53,8 @@ def parse():
                     help="TP collective (N>1): NCCL all-reduce, own NVLink all-reduce, or the fused "
                          "reduce-scatter+add+RMSNorm+FP8-quant+all-gather kernel")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-tp-check", action="store_true",
+                    help="skip the multi-GPU correctness self-check that runs before the timed region at N>1")
     ap.add_argument("--quant", default="fp8", choices=["fp8", "nvfp4"],
                     help="linear layers: FP8 W8A8 (configs[1]) or NVFP4 W4A4 (configs[4]); the KV cache stays FP8")
     return ap.parse_args()
@@ -60,6 +68,16 @@ def peaks():
         except Exception:
             pass
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def measured_traffic(key):
+    """(bytes per launch, source) of the dominant kernel from profiles/traffic.json, or (None, None)."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        e = json.load(open(p))[key]
+        return int(e["dram_bytes_read"]) + int(e["dram_bytes_write"]), e["source"]
+    except Exception:
+        return None, None
 
 
 class ClockSampler(threading.Thread):
@@ -174,22 +192,51 @@ class CpuReferenceDecoder:
         return time.perf_counter() - t0
 
 
-def cpu_reference_run(shape, steps, warmup, ctx):
+def host_threads() -> int:
+    """Threads the CPU arm uses: the physical cores this process may run on (what torch picks by itself when
+    OMP_NUM_THREADS is unset; set explicitly so a launcher's OMP_NUM_THREADS=1 cannot shrink it)."""
+    try:
+        avail = len(os.sched_getaffinity(0))
+    except AttributeError:
+        avail = os.cpu_count() or 1
+    try:
+        import psutil
+        phys = psutil.cpu_count(logical=False) or avail
+    except Exception:
+        phys = avail
+    return max(1, min(avail, phys))
+
+
+def cpu_reference_run(shape, steps, warmup, ctx, sample_seqs=32, sample_layers=4, batch=BATCH):
     """Times the reference CPU path on a bounded sample and extrapolates to the full layer count."""
-    sample_seqs, sample_layers = 8, 2
+    cores = host_threads()
+    torch.set_num_threads(cores)   # ATen intra-op pool + omp_set_num_threads of the shared OpenMP runtime
+    sample_seqs = min(sample_seqs, batch)
+    sample_layers = min(sample_layers, shape.layers)
     dec = CpuReferenceDecoder(shape, sample_seqs, ctx, sample_layers)
     for _ in range(warmup):
         dec.step()
     ts = [dec.step() for _ in range(steps)]
-    t_layer = (sum(ts) / len(ts)) / sample_layers
+    t_sample = sum(ts) / len(ts)           # one timed sample step (what the wall clock saw)
+    t_layer = t_sample / sample_layers
     t_step = t_layer * shape.layers  # embedding / lm_head excluded (in favour of the CPU)
     cores = torch.get_num_threads()
     return {"value": sample_seqs / t_step, "unit": UNIT, "cores": cores, "kind": "reference",
-            "sample": f"{sample_seqs} of {BATCH} sequences x {ctx}-token context, {sample_layers} of "
+            "timed_ms_per_sample_step": t_sample * 1e3, "extrapolated_ms_per_step": t_step * 1e3,
+            "sample": f"{sample_seqs} of {batch} sequences x {ctx}-token context, {sample_layers} of "
                       f"{shape.layers} layers timed (reference csrc/cpu attention ISA {dec.isa}, bf16 KV, "
                       f"+ torch CPU bf16 linears), extrapolated to {shape.layers} layers; "
                       f"{steps} steps after {warmup} warm-up",
             "ms_per_step": t_step * 1e3}
+
+
+def baseline_config_tag(shape, quant):
+    if shape.experts > 0:
+        return "BASELINE.json configs[3]"
+    if quant == "nvfp4":
+        return "BASELINE.json configs[4]"
+    return {"Llama-3.1-8B-shaped": "BASELINE.json configs[1]", "Llama-3.1-70B-shaped": "BASELINE.json configs[2]",
+            "Qwen2.5-0.5B-shaped": "BASELINE.json configs[0]"}.get(shape.name, "not a BASELINE.json config")
 
 
 def reference_arm(a):
@@ -202,17 +249,203 @@ def reference_arm(a):
         print(json.dumps({"impl": "reference", "unavailable":
                           "oracle/_ref/refcpu.so not built (needs /root/reference at build time)"}))
         return
-    cb = cpu_reference_run(shape, max(1, a.steps), max(1, a.warmup), a.ctx)
+    cb = cpu_reference_run(shape, max(1, a.steps), max(1, a.warmup), a.ctx, batch=a.batch)
+    # ms_per_step = what was actually timed (one sample step); the full-workload figure the value is derived
+    # from is reported separately, so steps x ms_per_step is the wall time of the timed region
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT,
-            "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": cb["ms_per_step"],
+            "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": cb["timed_ms_per_sample_step"],
+            "extrapolated_ms_per_step": cb["extrapolated_ms_per_step"],
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16",
             "data": "synthetic",
             "config": {"workload": f"{shape.name} decode, batch {a.batch}, ctx {a.ctx}, block {BLOCK} "
-                                   "(BASELINE.json configs[1]); CPU sample, see cpu_baseline.sample"},
+                                   f"({baseline_config_tag(shape, a.quant)}); CPU sample, see cpu_baseline.sample"},
             "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
+
+
+def tp_self_check(rank, world, dev, group):
+    """Correctness of the multi-GPU data plane, run before the timed region at world > 1 (the driver's GPU test
+    box has one GPU, so this is where the NVLink collectives are verified under the driver's eyes):
+    (1) B200AllReduce one-shot / two-shot / auto, zero-copy (symmetric heap) and staged inputs, launched while a
+        GEMM on a side stream keeps the SMs busy (CTAs of the collective start at different times), against the
+        exact definition: fp32 sum in rank order of the NCCL-all-gathered inputs, rounded once -> bit-exact;
+    (2) the fused reduce-scatter + add + RMSNorm + FP8-quant + all-gather kernel against
+        torch.distributed.all_gather -> rank-order sum -> ops.fused_add_rms_norm_static_fp8_quant -> bit-exact;
+    (3) two decode steps of a tiny Llama-shaped model at TP=world (every comm rung this world size supports)
+        against the same model at TP=1 on rank 0 (every rank draws the full weights from one generator):
+        greedy tokens must match, except where the TP=1 logits of the two candidates are within 4 bf16 ulps.
+    Raises on mismatch; returns the dict printed as "tp_check"."""
+    import torch.distributed as dist
+    from b200ops import decoder, ops
+    from b200ops.all_reduce import B200AllReduce
+    res = {}
+    ar = B200AllReduce(group, dev, max_size=8 << 20, heap_size=32 << 20)
+    busy_a = torch.randn(4096, 4096, device=dev, dtype=torch.bfloat16)
+    side = torch.cuda.Stream(device=dev)
+
+    def keep_sms_busy():
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                torch.matmul(busy_a, busy_a)
+
+    def rank_input(numel, dtype, seed):
+        g = torch.Generator(device=dev).manual_seed(seed * 64 + rank)
+        return (torch.rand(numel, device=dev, generator=g) * 2 - 1).to(dtype)
+
+    def exact_sum(x):
+        parts = [torch.empty_like(x) for _ in range(world)]
+        dist.all_gather(parts, x, group=group)
+        acc = torch.zeros(x.numel(), dtype=torch.float32, device=dev)
+        for p in parts:                      # rank order 0..N-1, the kernels' order
+            acc = acc + p.float().view(-1)
+        return acc.to(x.dtype).view(x.shape)
+
+    seed, cases = 0, 0
+    for dtype in (torch.bfloat16, torch.float16, torch.float32):
+        for numel in (4096, 256 * 4096, 1024 * 1024 + 8):
+            for algo in (1, 2, 0):
+                for zero_copy in (False, True):
+                    seed += 1
+                    x = rank_input(numel, dtype, seed)
+                    used = ar._heap_used
+                    if zero_copy:
+                        buf = ar.alloc(numel, dtype)
+                        buf.copy_(x)
+                        x = buf
+                    exp = exact_sum(x)
+                    torch.cuda.synchronize(dev)
+                    keep_sms_busy()
+                    out = ar.all_reduce(x, algo=algo)
+                    torch.cuda.synchronize(dev)
+                    if not torch.equal(out, exp):
+                        raise AssertionError(f"tp_check: all_reduce mismatch {dtype} n={numel} algo={algo} "
+                                             f"zero_copy={zero_copy} rank={rank}")
+                    ar._heap_used = used
+                    cases += 1
+    res["allreduce"] = "bit-exact"
+    res["allreduce_cases"] = cases
+    if world in (2, 4, 8):
+        cases = 0
+        for dtype in (torch.bfloat16, torch.float16):
+            for (M, H) in ((256, 4096), (128, 8192), (33, 2048), (1, 4096)):
+                for quant in (True, False):
+                    for staged in (True, False):
+                        seed += 1
+                        used = ar._heap_used
+                        x = rank_input(M * H, dtype, seed).view(M, H)
+                        if not staged:
+                            buf = ar.alloc((M, H), dtype)
+                            buf.copy_(x)
+                            x = buf
+                        g = torch.Generator(device=dev).manual_seed(seed)    # same on every rank
+                        res_full = (torch.rand(M, H, device=dev, generator=g) * 2 - 1).to(dtype)
+                        w = (torch.rand(H, device=dev, generator=g) + 0.5).to(dtype)
+                        scale = torch.tensor([0.02], device=dev) if quant else None
+                        summed = exact_sum(x)
+                        res_ref = res_full.clone()
+                        if quant:
+                            out_ref = torch.empty(M, H, dtype=torch.float8_e4m3fn, device=dev)
+                            ops.fused_add_rms_norm_static_fp8_quant(out_ref, summed, res_ref, w, scale, 1e-5)
+                        else:
+                            ops.fused_add_rms_norm(summed, res_ref, w, 1e-5)
+                            out_ref = summed
+                        lo, hi = ar.rows_of_rank(M)
+                        shard = torch.zeros((M + world - 1) // world, H, dtype=dtype, device=dev)
+                        shard[: hi - lo] = res_full[lo:hi]
+                        out = ar.alloc((M, H), torch.float8_e4m3fn if quant else dtype)
+                        out.view(torch.uint8).fill_(0x55)
+                        torch.cuda.synchronize(dev)
+                        dist.barrier(group=group)
+                        keep_sms_busy()
+                        ar.fused_add_rms_norm(out, x, shard, w, 1e-5, scale)
+                        torch.cuda.synchronize(dev)
+                        dist.barrier(group=group)
+                        if not torch.equal(out.view(torch.uint8), out_ref.view(torch.uint8)) or \
+                                not torch.equal(shard[: hi - lo], res_ref[lo:hi]):
+                            raise AssertionError(f"tp_check: fused all-reduce+norm mismatch {dtype} {(M, H)} "
+                                                 f"quant={quant} staged={staged} rank={rank}")
+                        ar._heap_used = used
+                        cases += 1
+        res["fused_allreduce_rmsnorm"] = "bit-exact"
+        res["fused_cases"] = cases
+    torch.cuda.synchronize(dev)
+    ar.close()
+    del busy_a
+
+    # ---- (3) tiny model, TP=world vs TP=1
+    shape = decoder.TINY_TP
+    S, ctx, bs = 48, 64, BLOCK
+    cg = torch.Generator().manual_seed(5)
+    nblk = (ctx + bs - 1) // bs
+    nb = S * nblk + 8
+    bt = torch.randperm(nb, generator=cg)[: S * nblk].to(torch.int32).view(S, nblk)
+    tok0 = torch.randint(0, shape.vocab, (S,), generator=cg)
+    lens0 = torch.randint(1, ctx - 2, (S,), generator=cg)
+    # one global FP8 KV prefix per layer (random non-NaN e4m3 codes); a TP rank keeps its contiguous kv heads
+    kv_gen = torch.Generator().manual_seed(9)
+    kv_full = [(torch.randint(0, 0x70, (nb, bs, shape.kv_heads, 2 * shape.head_size), generator=kv_gen) |
+                (torch.randint(0, 2, (nb, bs, shape.kv_heads, 2 * shape.head_size), generator=kv_gen) << 7)
+                ).to(torch.uint8) for _ in range(shape.layers)]
+
+    def run(model, tokens_forced=None):
+        """two eager decode steps from the same synthetic state; returns (tokens[2, S], logits[2, S, V])"""
+        for li, L in enumerate(model.layers):
+            lo = model.tp_rank * model.hkv
+            L["kv"].copy_(kv_full[li][:, :, lo:lo + model.hkv])
+        toks, logs = [], []
+        tok = tok0.clone()
+        for step in range(2):
+            lens = lens0 + step
+            pos = lens - 1
+            model.token_ids.copy_(tok)
+            model.positions.copy_(pos)
+            model.seq_lens.copy_(lens.to(torch.int32))
+            model.block_table.copy_(bt)
+            model.slot_mapping.copy_(bt[torch.arange(S), pos // bs].long() * bs + pos % bs)
+            model.forward_device()
+            torch.cuda.synchronize(dev)
+            toks.append(model.next_tokens.cpu().clone())
+            logs.append(model.last_logits.float().cpu().clone())
+            tok = toks[-1] if tokens_forced is None else tokens_forced[step]
+        return torch.stack(toks), torch.stack(logs)
+
+    ref_t = ref_l = None
+    if rank == 0:
+        m1 = decoder.DecoderModel(shape, S, ctx, bs, dev, num_blocks=nb)
+        ref_t, ref_l = run(m1)
+        del m1
+    forced = [torch.empty(S, dtype=torch.int64, device=dev) for _ in range(2)]
+    if rank == 0:
+        for i in range(2):
+            forced[i].copy_(ref_t[i])
+    for i in range(2):
+        dist.broadcast(forced[i], 0, group=group)
+    forced = [f.cpu() for f in forced]
+    comms = ["nccl", "nvlink"] + (["fused"] if world in (2, 4, 8) else [])
+    near_ties = 0
+    for comm in comms:
+        mN = decoder.DecoderModel(shape, S, ctx, bs, dev, tp_rank=rank, tp_size=world, tp_group=group,
+                                  comm=comm, num_blocks=nb)
+        t, _ = run(mN, forced)      # teacher-forced with the TP=1 tokens so step 2 sees the same context
+        if mN.ar is not None:
+            torch.cuda.synchronize(dev)
+            mN.ar.close()
+        del mN
+        if rank == 0:
+            for step in range(2):
+                bad = (t[step] != ref_t[step]).nonzero().flatten().tolist()
+                for sidx in bad:
+                    a, b = ref_l[step, sidx, ref_t[step, sidx]], ref_l[step, sidx, t[step, sidx]]
+                    if abs(float(a - b)) > 2 ** -6 * max(abs(float(a)), 1e-3):
+                        raise AssertionError(f"tp_check: tiny model TP={world} comm={comm} step {step} seq {sidx}: "
+                                             f"token {int(t[step, sidx])} vs TP=1 {int(ref_t[step, sidx])} "
+                                             f"(TP=1 logits {float(a):.5f} vs {float(b):.5f})")
+                    near_ties += 1
+    res["tiny_tokens"] = "match"
+    res["tiny_model"] = f"{shape.name}, {S} seqs x 2 steps, comm {'/'.join(comms)}, {near_ties} near-tie exceptions"
+    return res
 
 
 def main():
@@ -237,6 +470,16 @@ def main():
         # ranks where a one-shot pulls 14 MiB per rank and takes 32 us)
         a.comm = "nvlink" if world <= 2 else "fused"
     shape = model_shape(a.model)
+    tp_check = None
+    if world > 1 and not a.no_tp_check:
+        try:
+            tp_check = tp_self_check(rank, world, dev, group)
+        except Exception as e:
+            import traceback
+            traceback.print_exc()
+            print(json.dumps({"tp_check": {"failed": repr(e)}, "rank": rank}), flush=True)
+            sys.stderr.flush()
+            os._exit(3)
     if (shape.experts > 0 or a.quant == "nvfp4") and a.comm == "fused":
         a.comm = "nvlink"   # MoE layers (expert parallel): the all-reduce follows fused_experts, no norm fusion
     S, ctx = a.batch, a.ctx
@@ -309,34 +552,41 @@ def main():
     ms_e2e = timed(lambda i: model.step(host[i % len(host)], host_out), a.steps)
     clocks = sampler.stop()
 
-    # ---- (3) roofline of the dominant kernel: CUDA events around every paged-attention launch of an
-    # eager (non-graph) pass over the same steps, on the launching stream
-    evs = []
-
-    def hook(which):
-        e = torch.cuda.Event(enable_timing=True)
-        e.record()
-        evs.append(e)
-
-    model.attn_hook = hook
-    saved_graph, model.graph = model.graph, None
-    barrier()
-    for i in range(min(a.steps, 5)):
-        model.run_device()
+    # ---- (3) roofline of the dominant kernel: a CUDA graph holding ONLY the paged-attention launches of the
+    # step (one per layer, each over that layer's own KV cache: 2.1 GB per launch, nothing survives in L2),
+    # replayed and timed with CUDA events on the launching stream. Device time per launch without host launch
+    # overhead (eager events around a ~70 us kernel at TP=8 would mostly measure Python).
+    side = torch.cuda.Stream(device=dev)
+    side.wait_stream(torch.cuda.current_stream(dev))
+    with torch.cuda.stream(side):
+        for L in model.layers[:2]:
+            model.attention_layer(L)
+    torch.cuda.current_stream(dev).wait_stream(side)
     torch.cuda.synchronize(dev)
-    model.attn_hook, model.graph = None, saved_graph
-    durs = [evs[i].elapsed_time(evs[i + 1]) for i in range(0, len(evs), 2)]
-    attn_ms = sum(durs) / len(durs)
+    attn_graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(attn_graph):
+        for L in model.layers:
+            model.attention_layer(L)
+    attn_graph.replay()
+    torch.cuda.synchronize(dev)
+    reps = max(1, min(a.steps, 5))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        attn_graph.replay()
+    e1.record()
+    torch.cuda.synchronize(dev)
+    attn_ms = e0.elapsed_time(e1) / (reps * shape.layers)
+    del attn_graph
     es = 1  # fp8 KV
     alg_bytes = (S * 2 * ctx * model.hkv * D * es + S * model.hq * D * (2 + 2) + S * nblk * 4 + 4 * S)
     peak, peak_src = peaks()
     achieved = alg_bytes / (attn_ms * 1e-3) / 1e9
-    # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this kernel on this exact workload, from
-    # the ncu --set full capture summarised in profiles/r1b_ncu_full.md (a number taken under the profiler is
-    # only used for the byte count, never for time)
-    traffic, traffic_src = None, None
-    if world == 1 and S == 256 and ctx == 4096 and shape.name.startswith("Llama-3.1-8B"):
-        traffic, traffic_src = 2149912000 + 5132544, "profiles/r1b_ncu_full.md (ncu, per launch)"
+    # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this kernel on this exact workload: parsed at
+    # run time from the committed ncu --set full summary (profiles/traffic.json names the .md it was extracted
+    # from); a number taken under the profiler is only used for the byte count, never for time. null when no
+    # capture of this workload is committed.
+    traffic, traffic_src = measured_traffic(f"{shape.name}|tp{world}|batch{S}|ctx{ctx}|{a.quant}")
     step_ms = ms_dev / a.steps
     value = S / (step_ms * 1e-3)
     e2e_value = S / (ms_e2e / a.steps * 1e-3)
@@ -353,7 +603,7 @@ def main():
                                ("(BASELINE.json configs[3]: FP8 fused_moe, %d experts top-%d, expert parallel; "
                                 "context length not given there)" % (shape.experts, shape.topk)
                                 if shape.experts > 0 else
-                                "(BASELINE.json configs[4])" if a.quant == "nvfp4" else "(BASELINE.json configs[1])"),
+                                f"({baseline_config_tag(shape, a.quant)})"),
                    "parallelism": (f"tp{world} attention + ep{world} experts" if shape.experts > 0 else f"tp{world}"), "tp_collective": (a.comm if world > 1 else None), "weights": "random init (dummy), per-tensor FP8 scales",
                    "cuda_graph": not a.no_graph,
                    "l2": "inputs larger than L2 (KV cache %.1f GB + weights per GPU)" %
@@ -366,16 +616,20 @@ def main():
         "clocks": clocks,
         "roofline": {"kernel": "paged_attn_decode_kernel<128,1,BF16_FP8>", "bound": "hbm",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "timing": "CUDA graph of the step's attention launches (one per layer, each on its own "
+                               "KV cache), CUDA events, per launch",
                      "peak_source": peak_src, "traffic": traffic, "traffic_source": traffic_src,
                      "algorithmic_bytes_per_launch": alg_bytes, "ms_per_launch": attn_ms,
                      "launches_per_step": shape.layers,
                      "share_of_step": attn_ms * shape.layers / step_ms},
     }
+    if tp_check is not None:
+        line["tp_check"] = tp_check
     if rank == 0 and world == 1 and not a.no_cpu_baseline and shape.experts == 0:
         try:
             from oracle import refcpu
             if refcpu.available():
-                cb = cpu_reference_run(shape, 3, 1, ctx)
+                cb = cpu_reference_run(shape, 3, 1, ctx, batch=S)
                 line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
             else:
                 line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference",

@@ -69,6 +69,28 @@ def _worker(rank: int, world: int, port: int, q):
                             torch.cuda.synchronize()
                             ar._heap_used = start  # bump allocator: release (same on every rank)
         log.append("all_reduce bit-exact")
+        # ---- 1b. STAGED inputs while a GEMM on another stream keeps most SMs busy: the CTAs of the collective
+        # start at different times, so a CTA must only read packs its peer counterpart staged (the barriers
+        # order same-index CTAs across ranks, nothing else); part = 65537 packs is not a multiple of the stride
+        busy = torch.randn(4096, 4096, device=dev, dtype=torch.bfloat16)
+        side0 = torch.cuda.Stream()
+        for it in range(6):
+            for algo, numel in ((2, 1024 * 1024 + 8), (1, 1024 * 1024 + 8), (2, 3 * 4096 + 8)):
+                seed += 1
+                x = _rank_input(rank, numel, torch.bfloat16, seed).to(dev)
+                exp = _expected_sum(world, numel, torch.bfloat16, seed)
+                torch.cuda.synchronize(); dist.barrier()
+                with torch.cuda.stream(side0):
+                    for _ in range(2 + (rank + it) % 3):   # ranks are busy for different lengths
+                        torch.matmul(busy, busy)
+                out = ar.all_reduce(x, algo=algo)
+                # a second staged collective right behind the first, asking to skip the end barrier: the
+                # library must keep it (the staging area is reused)
+                out2 = ar.all_reduce(x, algo=1, skip_end_barrier=True)
+                out3 = ar.all_reduce(out2 * 0 + x, algo=1)
+                assert torch.equal(out.cpu(), exp), f"staged all_reduce under load mismatch algo={algo} n={numel}"
+                assert torch.equal(out2.cpu(), exp) and torch.equal(out3.cpu(), exp), "staged skip_end mismatch"
+        log.append("staged all_reduce under SM contention bit-exact")
         # ---- 2. CUDA graph: capture several calls, replay many times with changing inputs
         numel = 256 * 4096
         xg = ar.alloc(numel, torch.bfloat16)

@@ -31,13 +31,16 @@ from . import ops
 import os
 
 _HAVE_VLLM = False
-if os.environ.get("B200OPS_VLLM_BASES", "0") == "1":  # pragma: no cover - set by the vLLM plugin
+_CG_ALWAYS = "ALWAYS"
+if os.environ.get("B200OPS_VLLM_BASES", "0") == "1":  # set by b200ops.vllm_plugin.register()
     # derive from the reference's ABCs only when asked to (importing vLLM is slow and its ABCs
     # differ between vLLM generations)
     from vllm.v1.attention.backend import (AttentionBackend as _BackendBase,
+                                           AttentionCGSupport as _CGSupport,
                                            AttentionImpl as _ImplBase,
                                            AttentionMetadataBuilder as _BuilderBase)
     _HAVE_VLLM = True
+    _CG_ALWAYS = _CGSupport.ALWAYS   # the enum member the reference compares against (backend.py:606-626)
 if not _HAVE_VLLM:
 
     class _BackendBase:  # type: ignore[no-redef]
@@ -68,18 +71,18 @@ class B200AttentionMetadata:
 class B200AttentionMetadataBuilder(_BuilderBase):
     """Builds B200AttentionMetadata from CommonAttentionMetadata (backend.py:404-600)."""
 
-    # AttentionCGSupport.ALWAYS: decode and variable-length kernels are both graph-safe
-    _cudagraph_support = "ALWAYS"
+    # AttentionCGSupport.ALWAYS: decode and variable-length kernels are both graph-safe (the enum member when
+    # the vLLM ABCs are in use, its name otherwise)
+    _cudagraph_support = _CG_ALWAYS
 
     def __init__(self, kv_cache_spec=None, layer_names=None, vllm_config=None, device=None,
                  num_heads: int | None = None, num_kv_heads: int | None = None,
                  head_size: int | None = None, max_num_seqs: int = 1024):
-        try:
-            super().__init__(kv_cache_spec, layer_names, vllm_config, device)
-        except Exception:
-            pass
+        # the vLLM base keeps kv_cache_spec / layer_names / vllm_config / device (backend.py:640-651)
+        self.kv_cache_spec, self.layer_names = kv_cache_spec, layer_names
+        self.vllm_config = vllm_config
         self.device = torch.device(device) if device is not None else torch.device("cuda")
-        if vllm_config is not None and num_heads is None:  # pragma: no cover
+        if vllm_config is not None and num_heads is None:
             mc, pc = vllm_config.model_config, vllm_config.parallel_config
             num_heads = mc.get_num_attention_heads(pc)
             num_kv_heads = mc.get_num_kv_heads(pc)
@@ -231,13 +234,16 @@ class B200AttentionBackend(_BackendBase):
             return (1, 0, 3, 2, 4)
         return (0, 2, 1, 3)
 
+    # head sizes BOTH kernels serve: the decode kernel also takes 256, but the variable-length (prefill) kernel
+    # that forward() routes every max_query_len > 1 batch to handles 64 and 128 only (attention_prefill.cu),
+    # so 256 must not be accepted at backend selection
     @classmethod
     def supports_head_size(cls, head_size: int) -> bool:
-        return head_size in (64, 128, 256)
+        return head_size in (64, 128)
 
     @classmethod
     def get_supported_head_sizes(cls) -> list[int]:
-        return [64, 128, 256]
+        return [64, 128]
 
     @classmethod
     def supports_compute_capability(cls, capability) -> bool:

@@ -50,6 +50,8 @@ LLAMA_3_1_70B = ModelShape("Llama-3.1-70B-shaped", 8192, 80, 64, 8, 128, 28672, 
 QWEN2_5_0_5B = ModelShape("Qwen2.5-0.5B-shaped", 896, 24, 14, 2, 64, 4864, 151936, 1000000.0, 1e-6)
 MIXTRAL_8X7B = ModelShape("Mixtral-8x7B-shaped", 4096, 32, 32, 8, 128, 14336, 32000, 1000000.0, 1e-5, 8, 2)
 TINY = ModelShape("tiny-llama-shaped", 512, 2, 8, 2, 128, 1024, 1024)
+# tiny shape whose heads / kv heads / inter divide by 8 ranks (bench.py's TP=N vs TP=1 self-check)
+TINY_TP = ModelShape("tiny-llama-shaped-tp8", 1024, 2, 16, 8, 128, 2048, 1024)
 TINY_MOE = ModelShape("tiny-mixtral-shaped", 512, 2, 8, 2, 128, 512, 1024, 1000000.0, 1e-5, 4, 2)
 
 # kernels launched per call of each op (our own kernels only), for the bench's gpu_launches claim
@@ -273,11 +275,7 @@ class DecoderModel:
             n += 1
             if self.attn_hook:
                 self.attn_hook(0)
-            ops.paged_attention_decode(self.attn_out, q, kc, vc, self.block_table, self.seq_lens, D ** -0.5,
-                                       k_scale=L["k_scale"] if self.kv_fp8 else None,
-                                       v_scale=L["v_scale"] if self.kv_fp8 else None,
-                                       max_seq_len=self.max_ctx, workspace=self.workspace)
-            n += LAUNCHES["attention"]
+            n += self.attention_layer(L)
             if self.attn_hook:
                 self.attn_hook(1)
             n += self._fp4_linear(self.attn_out.view(S, self.hq * D), L, "o", pa)
@@ -292,6 +290,7 @@ class DecoderModel:
             n += 1 if self.ar is not None else 0
         ops.fused_add_rms_norm(red, self.residual, self.final_norm, s.eps); n += 1
         logits = red @ self.lm_head.t()
+        self.last_logits = logits
         ops.greedy_sample(logits, out=self.next_tokens); n += 1   # Sampler.greedy_sample
         self.launches_per_step = n
 
@@ -345,20 +344,7 @@ class DecoderModel:
             n += 1
             if self.attn_hook:
                 self.attn_hook(0)
-            if self.fuse_attn_quant:
-                # the attention kernel writes the statically quantised o_proj input itself (fused FP8 output)
-                ops.paged_attention_decode(a8.view(S, self.hq, D), q, kc, vc, self.block_table, self.seq_lens,
-                                           D ** -0.5, k_scale=L["k_scale"] if self.kv_fp8 else None,
-                                           v_scale=L["v_scale"] if self.kv_fp8 else None,
-                                           max_seq_len=self.max_ctx, workspace=self.workspace,
-                                           output_scale=L["a_o"])
-                n += LAUNCHES["attention"]
-            else:
-                ops.paged_attention_decode(self.attn_out, q, kc, vc, self.block_table, self.seq_lens,
-                                           D ** -0.5, k_scale=L["k_scale"] if self.kv_fp8 else None,
-                                           v_scale=L["v_scale"] if self.kv_fp8 else None,
-                                           max_seq_len=self.max_ctx, workspace=self.workspace)
-                n += LAUNCHES["attention"]
+            n += self.attention_layer(L)
             if self.attn_hook:
                 self.attn_hook(1)
             if not self.fuse_attn_quant:
@@ -405,8 +391,25 @@ class DecoderModel:
         else:
             ops.fused_add_rms_norm(red, self.residual, self.final_norm, s.eps); n += 1
         logits = red @ self.lm_head.t()
+        self.last_logits = logits
         ops.greedy_sample(logits, out=self.next_tokens); n += 1   # Sampler.greedy_sample
         self.launches_per_step = n
+
+    def attention_layer(self, L) -> int:
+        """The paged-attention decode call of one layer over the persistent buffers (q from self.qkv, the
+        layer's KV cache); forward_device() and bench.py's roofline timing share it. Returns launches."""
+        S, D = self.max_seqs, self.D
+        q = self.qkv[:, : self.hq * D].view(S, self.hq, D)
+        kc, vc = L["kv"][..., :D], L["kv"][..., D:]
+        fp8_out = self.quant == "fp8" and self.fuse_attn_quant
+        # fp8_out: the attention kernel writes the statically quantised o_proj input itself (fused FP8 output)
+        ops.paged_attention_decode(self.a8.view(S, self.hq, D) if fp8_out else self.attn_out, q, kc, vc,
+                                   self.block_table, self.seq_lens, D ** -0.5,
+                                   k_scale=L["k_scale"] if self.kv_fp8 else None,
+                                   v_scale=L["v_scale"] if self.kv_fp8 else None,
+                                   max_seq_len=self.max_ctx, workspace=self.workspace,
+                                   output_scale=L["a_o"] if fp8_out else None)
+        return LAUNCHES["attention"]
 
     def capture(self) -> None:
         """Capture forward_device() in a CUDA graph (decode steps are launch-bound otherwise)."""

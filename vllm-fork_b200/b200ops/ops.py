@@ -536,9 +536,11 @@ def create_fp4_scale_tensor(m: int, n: int, device, is_sf_swizzled_layout: bool)
 
 
 def scaled_fp4_quant(input: torch.Tensor, input_global_scale: torch.Tensor,
-                     is_sf_swizzled_layout: bool = True) -> tuple[torch.Tensor, torch.Tensor]:
-    """Returns (uint8 [m, n/2] packed e2m1, float8_e4m3fn scales in the swizzled / row-major layout)."""
-    _cuda(input, input_global_scale)
+                     is_sf_swizzled_layout: bool = True, output: torch.Tensor | None = None,
+                     output_scale: torch.Tensor | None = None) -> tuple[torch.Tensor, torch.Tensor]:
+    """Returns (uint8 [m, n/2] packed e2m1, float8_e4m3fn scales in the swizzled / row-major layout).
+    output / output_scale: caller-allocated results (the `scaled_fp4_quant.out` overload, torch_bindings.cpp:218)."""
+    _cuda(input, input_global_scale, output, output_scale)
     assert input.ndim >= 1, f"input.ndim needs to be >= 1, but got {input.ndim}."
     other_dims = 1 if input.ndim == 1 else -1
     input = input.reshape(other_dims, input.shape[-1])
@@ -548,8 +550,17 @@ def scaled_fp4_quant(input: torch.Tensor, input_global_scale: torch.Tensor,
         f"input.dtype needs to be fp16 or bf16 but got {input.dtype}.")
     if input.stride(1) != 1:
         input = input.contiguous()
-    output = torch.empty((m, n // 2), device=input.device, dtype=torch.uint8)
-    output_scale = create_fp4_scale_tensor(m, n, input.device, is_sf_swizzled_layout)
+    if output is None:
+        output = torch.empty((m, n // 2), device=input.device, dtype=torch.uint8)
+    elif tuple(output.shape) != (m, n // 2) or output.element_size() != 1 or not output.is_contiguous():
+        raise RuntimeError(f"scaled_fp4_quant: output must be a contiguous 1-byte tensor [{m}, {n // 2}]")
+    if output_scale is None:
+        output_scale = create_fp4_scale_tensor(m, n, input.device, is_sf_swizzled_layout)
+    else:
+        need = create_fp4_scale_tensor(m, n, "meta", is_sf_swizzled_layout)
+        if output_scale.numel() * output_scale.element_size() != need.numel() * need.element_size() or \
+                not output_scale.is_contiguous():
+            raise RuntimeError("scaled_fp4_quant: output_scale has the wrong size for this layout")
     rc = _lib.load().b200_nvfp4_quant(_p(output), _p(output_scale), _p(input), _p(input_global_scale),
                                       m, n, input.stride(0), 1 if is_sf_swizzled_layout else 0,
                                       _dt(input), _stream())

@@ -78,6 +78,23 @@ __device__ __forceinline__ uint4 ld_peer_v4(const void* p) {
   return r;
 }
 
+// A dead or wedged peer must not hang the GPU (SURVEY section 5 "never hang"): every flag wait is
+// bounded by wall time (%globaltimer, checked every 1024 polls) and traps with a message, which turns a
+// hang into a CUDA error on the stream (the reference's barriers spin forever, custom_all_reduce.cuh:236-305).
+constexpr unsigned long long SPIN_TIMEOUT_NS = 20ull * 1000ull * 1000ull * 1000ull;  // 20 s
+
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+__device__ __noinline__ void spin_timeout(int rank, int peer, uint32_t want, uint32_t got) {
+  printf("b200ops all-reduce: rank %d CTA %d waited > 20 s for rank %d (flag %u, want %u): peer dead or "
+         "collective call order differs between ranks\n", rank, (int)blockIdx.x, peer, got, want);
+  __trap();
+}
+
 // All CTAs with the same blockIdx.x on all ranks meet. `epoch` is the CTA's running barrier count
 // (register copy of Signal::epoch[cta]); consecutive barriers alternate between two flag arrays, and
 // a rank can be at most one barrier ahead of a peer, so a flag is never overwritten before it is read.
@@ -94,17 +111,23 @@ __device__ __forceinline__ void barrier(const Peers& pe, int rank, uint32_t& epo
   if (threadIdx.x < N) {
     uint32_t* theirs = &pe.sig[threadIdx.x]->arrive[epoch & 1][blockIdx.x][rank];
     const uint32_t* mine = &pe.sig[rank]->arrive[epoch & 1][blockIdx.x][threadIdx.x];
+    uint32_t v;
     if constexpr (ORDER) {
       __threadfence_system();
       st_release_sys(theirs, epoch);
-      while (ld_acquire_sys(mine) != epoch) {
-      }
     } else {
       asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(theirs), "r"(epoch) : "memory");
-      uint32_t v;
-      do {
-        asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
-      } while (v != epoch);
+    }
+    unsigned long long t0 = 0;
+    for (uint32_t polls = 1;; polls++) {
+      if constexpr (ORDER) v = ld_acquire_sys(mine);
+      else asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+      if (v == epoch) break;
+      if ((polls & 1023u) == 0) {
+        const unsigned long long now = global_timer_ns();
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > SPIN_TIMEOUT_NS) spin_timeout(rank, (int)threadIdx.x, epoch, v);
+      }
     }
   }
   __syncthreads();
@@ -172,14 +195,37 @@ __device__ __forceinline__ uint4 reduce_pack(const Peers& pe, int64_t idx) {
 }
 
 // If `stage_src` is set the input is outside the symmetric heap: copy it into this rank's staging
-// area (pe.in[rank]) first; the start barrier then publishes it.
+// area (pe.in[rank]) first; the start barrier then publishes it. The barrier only orders CTAs with the
+// SAME blockIdx.x across ranks, so CTA b must stage exactly the packs the peers' CTA b will read: for
+// every slice [s*part, (s+1)*part) the packs s*part + tid + k*stride - the index walk of reduce_range
+// (one-shot: one slice = the whole message; two-shot: one slice per rank).
 template <int N>
-__device__ __forceinline__ void stage_input(const Peers& pe, int rank, const uint8_t* stage_src, int64_t packs) {
+__device__ __forceinline__ void stage_input(const Peers& pe, int rank, const uint8_t* stage_src, int64_t packs,
+                                            int64_t part) {
   if (stage_src) {
     uint4* dst = reinterpret_cast<uint4*>(const_cast<uint8_t*>(pe.in[rank]));
     const uint4* src = reinterpret_cast<const uint4*>(stage_src);
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < packs; i += (int64_t)gridDim.x * blockDim.x)
-      dst[i] = src[i];
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t lo = 0; lo < packs; lo += part) {
+      const int64_t hi = min(packs, lo + part);
+      for (int64_t i = lo + tid; i < hi; i += stride) dst[i] = src[i];
+    }
+  }
+}
+
+// Row-wise variant for the fused kernel: its CTA b reads whole rows row_lo(s) + b + k*gridDim.x of slice s.
+template <int N>
+__device__ __forceinline__ void stage_rows(const Peers& pe, int rank, const uint8_t* stage_src, int M, int nv,
+                                           int rows_per_rank) {
+  if (stage_src) {
+    uint4* dst = reinterpret_cast<uint4*>(const_cast<uint8_t*>(pe.in[rank]));
+    const uint4* src = reinterpret_cast<const uint4*>(stage_src);
+    for (int lo = 0; lo < M; lo += rows_per_rank) {
+      const int hi = min(M, lo + rows_per_rank);
+      for (int row = lo + blockIdx.x; row < hi; row += gridDim.x)
+        for (int v = threadIdx.x; v < nv; v += blockDim.x) dst[(int64_t)row * nv + v] = src[(int64_t)row * nv + v];
+    }
   }
 }
 
@@ -217,14 +263,15 @@ __global__ void __launch_bounds__(NTHREADS, 1)
     allreduce_one_shot_kernel(Peers pe, uint8_t* __restrict__ out, const uint8_t* stage_src, int rank,
                               int64_t packs, int skip_end) {
   uint32_t epoch = pe.sig[rank]->epoch[blockIdx.x];
-  stage_input<N>(pe, rank, stage_src, packs);
+  stage_input<N>(pe, rank, stage_src, packs, packs);
   if (stage_src) barrier<N, true>(pe, rank, epoch);
   else barrier<N, false>(pe, rank, epoch);
   reduce_range<T, N, (N <= 4 ? 4 : 2)>(pe, 0, packs, [&](int64_t i, uint4 v) { reinterpret_cast<uint4*>(out)[i] = v; });
   // peers may overwrite their inputs only after everyone has read them. skip_end: the caller promises
   // not to touch the input before the NEXT collective of this context (e.g. alternating buffers), whose
-  // start barrier then plays this role.
-  if (!skip_end) barrier<N, false>(pe, rank, epoch);
+  // start barrier then plays this role. A STAGED input lives in the library-owned staging area, which the
+  // next collective overwrites before its start barrier: the promise cannot cover it, so never skip then.
+  if (!skip_end || stage_src) barrier<N, false>(pe, rank, epoch);
   if (threadIdx.x == 0) pe.sig[rank]->epoch[blockIdx.x] = epoch;
 }
 
@@ -236,7 +283,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   const int64_t part = (packs + N - 1) / N;          // packs per rank slice
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  stage_input<N>(pe, rank, stage_src, packs);
+  stage_input<N>(pe, rank, stage_src, packs, part);
   if (stage_src) barrier<N, true>(pe, rank, epoch);
   else barrier<N, false>(pe, rank, epoch);
   {  // stage 1: reduce my slice into my scratch

@@ -34,7 +34,7 @@ __global__ void __launch_bounds__(256, 1)
   __shared__ float red[32];
   uint32_t epoch = pe.sig[rank]->epoch[blockIdx.x];
   const int nv = fp.hidden / NP;            // packs per row
-  stage_input<N>(pe, rank, stage_src, (int64_t)fp.M * nv);
+  stage_rows<N>(pe, rank, stage_src, fp.M, nv, fp.rows_per_rank);
   if (stage_src) barrier<N, true>(pe, rank, epoch);
   else barrier<N, false>(pe, rank, epoch);
   const int row_lo = rank * fp.rows_per_rank;
