@@ -370,6 +370,40 @@ def tp_self_check(rank, world, dev, group):
                         cases += 1
         res["fused_allreduce_rmsnorm"] = "bit-exact"
         res["fused_cases"] = cases
+    # ---- (2b) decode-context-parallel merge (one NVLink kernel) vs all_gather + the definition in torch fp32
+    cases = 0
+    for dtype, tol in ((torch.bfloat16, 2 ** -7), (torch.float16, 2 ** -10)):
+        for (B, H, D) in ((256, 32, 128), (7, 8, 64)):
+            seed += 1
+            g = torch.Generator(device=dev).manual_seed(seed * 64 + rank)
+            o = (torch.rand(B, H, D, device=dev, generator=g) * 2 - 1).to(dtype)
+            l = torch.randn(B, H, device=dev, generator=g) * 4
+            if rank == 0:
+                l[0, 0] = float("-inf")
+            outs = [torch.empty_like(o) for _ in range(world)]
+            lses = [torch.empty_like(l) for _ in range(world)]
+            dist.all_gather(outs, o, group=group)
+            dist.all_gather(lses, l, group=group)
+            L = torch.stack(lses)
+            lse = torch.logsumexp(L, dim=0)
+            acc = torch.zeros(B, H, D, device=dev)
+            for r in range(world):
+                f = torch.exp(L[r] - lse)
+                acc = acc + (outs[r].float() * f[..., None]).to(dtype).float()
+            exp = acc.to(dtype)
+            torch.cuda.synchronize(dev)
+            dist.barrier(group=group)
+            keep_sms_busy()
+            got, got_lse = ar.dcp_lse_merge(o, l, reduce_scatter=True, return_lse=True)
+            torch.cuda.synchronize(dev)
+            hs = H // world
+            sl = slice(rank * hs, (rank + 1) * hs)
+            if not torch.allclose(got.float(), exp[:, sl].float(), rtol=2 * tol, atol=2 * tol) or \
+                    not torch.allclose(got_lse, lse[:, sl], rtol=1e-5, atol=1e-5):
+                raise AssertionError(f"tp_check: dcp_lse_merge mismatch {dtype} {(B, H, D)} rank={rank}")
+            cases += 1
+    res["dcp_lse_merge"] = "within output rounding of the definition"
+    res["dcp_cases"] = cases
     torch.cuda.synchronize(dev)
     ar.close()
     del busy_a

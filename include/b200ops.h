@@ -540,6 +540,20 @@ B200_API int b200_allreduce_fused_add_rms_norm(void* ctx, void* out, const void*
                                                int64_t num_tokens, int hidden, int dtype,
                                                b200_stream_t stream);
 
+/* Decode-context-parallel attention merge across ranks: cp_lse_ag_out_rs / cp_lse_ag_out_ar
+ * (vllm/v1/attention/ops/common.py:185-258; correction kernel :13-93) as ONE NVLink kernel instead of
+ * all_gather(lse) -> Triton correction -> reduce_scatter / all_reduce(out):
+ *   lse = log(sum_r exp(lse_r)) (NaN / +inf partial LSEs count as -inf; all -inf -> lse = -inf),
+ *   out = T(sum_r T(out_r * exp(lse_r - lse))) in rank order with fp32 accumulation.
+ * attn_out [num_tokens, num_heads, head_size] (dtype) and attn_lse [num_tokens, num_heads] (f32) must live in the
+ * symmetric heap at the same offset on every rank. mode 0: out [num_tokens, num_heads/world, head_size] and
+ * lse_out [num_tokens, num_heads/world] hold heads [rank*H/world, (rank+1)*H/world); mode 1: all heads on every
+ * rank (bit-identical). out / lse_out are ordinary device memory; lse_out may be NULL.
+ * is_lse_base_on_e: 1 natural-log LSEs, 0 log2 LSEs. */
+B200_API int b200_dcp_lse_merge(void* ctx, void* out, float* lse_out, const void* attn_out, const float* attn_lse,
+                                int64_t num_tokens, int num_heads, int head_size, int dtype, int mode,
+                                int is_lse_base_on_e, b200_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Sampler-side kernels of the decode step.
  * b200_argmax: greedy sampling, out[r] = argmax_v logits[r, v] (vllm/v1/sample/sampler.py greedy_sample =

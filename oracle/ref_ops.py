@@ -814,3 +814,46 @@ def apply_repetition_penalties(logits: torch.Tensor, prompt_mask: torch.Tensor, 
     x = logits.float()
     y = torch.where(x > 0, x / pen, x * pen).to(logits.dtype)
     return torch.where(prompt_mask | output_mask, y, logits)
+
+
+# --------------------------------------------------------------------------------------------
+# Decode-context-parallel merge across ranks: vllm/v1/attention/ops/common.py
+#   _correct_attn_cp_out_kernel :13-93, correct_attn_out :110-183, cp_lse_ag_out_rs :185-232,
+#   cp_lse_ag_out_ar :235-258. No golden vectors exist in the reference for this path (its only implementation is
+#   a Triton kernel); the restatement is pinned by the domain property tests/test_oracle_dcp.py checks:
+#   attention over a context split across N ranks, merged, equals attention over the whole context
+#   (the attention oracle itself is pinned to the reference CPU kernels).
+# --------------------------------------------------------------------------------------------
+def dcp_correct_attn_out(out, lses, cp_rank, is_lse_base_on_e=True):
+    """out f32 [B,H,D] (this rank's partial), lses f32 [N,B,H] (all ranks). Returns (corrected out f32, lse f32 [B,H])
+    in the kernel's operation order (fp32)."""
+    out = _f32(out) if torch.is_tensor(out) else np.asarray(out, dtype=np.float32)
+    l = _f32(lses) if torch.is_tensor(lses) else np.asarray(lses, dtype=np.float32)
+    exp, log = (np.exp, np.log) if is_lse_base_on_e else (np.exp2, np.log2)
+    with np.errstate(all="ignore"):
+        ls = np.where(np.isnan(l) | (l == np.inf), -np.inf, l).astype(np.float32)
+        mx = ls.max(axis=0)
+        mx = np.where(mx == -np.inf, np.float32(0), mx).astype(np.float32)
+        acc = exp((ls - mx).astype(np.float32)).astype(np.float32).sum(axis=0, dtype=np.float32)
+        lse = (log(acc).astype(np.float32) + mx).astype(np.float32)
+        fin = (l[cp_rank] - lse).astype(np.float32)
+        fin = np.where(np.isnan(fin) | (fin == np.inf), -np.inf, fin).astype(np.float32)
+        factor = exp(fin).astype(np.float32)
+        o = (out * factor[..., None]).astype(np.float32)
+        o = np.where(factor[..., None] == 0, np.float32(0), o)
+    return o.astype(np.float32), lse
+
+
+def dcp_lse_merge(outs, lses, dtype=torch.bfloat16, is_lse_base_on_e=True):
+    """cp_lse_ag_out_ar on one host: outs list of N torch [B,H,D] partials (dtype), lses list of N f32 [B,H].
+    Every corrected partial is rounded to `dtype` (the reference's kernel stores it in the output dtype before the
+    collective), then summed in rank order with fp32 accumulation and rounded once. Returns (out torch dtype
+    [B,H,D], lse f32 numpy [B,H]); the reduce-scatter form keeps heads [r*H/N, (r+1)*H/N) on rank r."""
+    N = len(outs)
+    L = np.stack([_f32(x) for x in lses])
+    acc, lse = None, None
+    for r in range(N):
+        o, lse = dcp_correct_attn_out(outs[r], L, r, is_lse_base_on_e)
+        o = torch.from_numpy(o).to(dtype).float().numpy()
+        acc = o if acc is None else (acc + o).astype(np.float32)
+    return torch.from_numpy(acc).to(dtype), lse

@@ -153,6 +153,52 @@ def _worker(rank: int, world: int, port: int, q):
                     assert torch.equal(shard[: hi - lo].cpu(), res_ref[lo:hi].cpu()), "fused norm residual mismatch"
                     ar._heap_used = start
         log.append("fused add+rmsnorm(+fp8) == unfused, bit-exact")
+        # ---- 3b. decode-context-parallel merge (cp_lse_ag_out_rs / _ar) in one NVLink kernel vs the oracle
+        from oracle import ref_ops
+        for dtype, tol in ((torch.bfloat16, 2 ** -7), (torch.float16, 2 ** -10), (torch.float32, 1e-5)):
+            for (B, H, D) in ((256, 32, 128), (5, 8, 64), (1, 16, 128), (33, 8, 256)):
+                for base_e in (True, False):
+                    seed += 1
+                    outs = [(torch.rand(B, H, D, generator=torch.Generator().manual_seed(seed * 16 + r)) * 2 - 1).to(dtype)
+                            for r in range(world)]
+                    lses = [torch.randn(B, H, generator=torch.Generator().manual_seed(seed * 16 + 8 + r)) * 4
+                            for r in range(world)]
+                    lses[0][0, 0] = float("-inf")
+                    lses[world - 1][B - 1, H - 1] = float("nan")
+                    if B > 1:
+                        for r in range(world):
+                            lses[r][1, 2] = float("-inf")      # nobody holds a token of this (row, head)
+                    exp_out, exp_lse = ref_ops.dcp_lse_merge(outs, lses, dtype=dtype, is_lse_base_on_e=base_e)
+                    for in_heap in (False, True):
+                        start = ar._heap_used
+                        o, l = outs[rank].to(dev), lses[rank].to(dev)
+                        if in_heap:
+                            ob, lb = ar.alloc((B, H, D), dtype), ar.alloc((B, H), torch.float32)
+                            ob.copy_(o); lb.copy_(l)
+                            o, l = ob, lb
+                        torch.cuda.synchronize(); dist.barrier()
+                        full, lse_full = ar.dcp_lse_merge(o, l, reduce_scatter=False, return_lse=True,
+                                                          is_lse_base_on_e=base_e)
+                        part, lse_part = ar.dcp_lse_merge(o, l, reduce_scatter=True, return_lse=True,
+                                                          is_lse_base_on_e=base_e)
+                        torch.cuda.synchronize(); dist.barrier()
+                        hs = H // world
+                        sl = slice(rank * hs, (rank + 1) * hs)
+                        assert torch.equal(part, full[:, sl]) and torch.equal(lse_part, lse_full[:, sl])
+                        torch.testing.assert_close(full.float().cpu(), exp_out.float(), rtol=2 * tol, atol=2 * tol)
+                        el = torch.from_numpy(exp_lse)
+                        fin = torch.isfinite(el)
+                        assert torch.equal(torch.isfinite(lse_full.cpu()), fin)
+                        torch.testing.assert_close(lse_full.cpu()[fin], el[fin], rtol=1e-5, atol=1e-5)
+                        # all-reduce form: bit-identical on every rank
+                        mine = full.contiguous().view(torch.uint8).view(-1).to(torch.int32).sum().reshape(1)
+                        both = [torch.empty_like(mine) for _ in range(world)]
+                        dist.all_gather(both, mine)
+                        assert all(int(b) == int(mine) for b in both)
+                        if in_heap:
+                            torch.cuda.synchronize()
+                            ar._heap_used = start
+        log.append("dcp_lse_merge (rs / ar) == oracle within output rounding, identical on all ranks")
         # ---- 4. latency vs NCCL at the decode message size (2 MiB bf16)
         numel = 256 * 4096
         xz = ar.alloc(numel, torch.bfloat16)

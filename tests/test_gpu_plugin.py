@@ -113,9 +113,10 @@ def test_opcheck_three_ops():
     o = torch.empty(32, 256, device=DEV, dtype=torch.bfloat16)
     tests = ("test_schema", "test_faketensor")
     torch.library.opcheck(torch.ops.b200.silu_and_mul.default, (o, x), test_utils=tests)
-    o8 = torch.empty(32, 512, device=DEV, dtype=torch.float8_e4m3fn)
-    sc = torch.tensor([0.02], device=DEV)
-    torch.library.opcheck(torch.ops.b200.static_scaled_fp8_quant.default, (o8, x, sc), test_utils=tests)
+    # (ops with FP8 outputs cannot go through opcheck's test_schema: it clones and compares every argument with
+    # aten ops that have no Float8 kernels)
+    w0 = torch.ones(512, device=DEV, dtype=torch.bfloat16)
+    torch.library.opcheck(torch.ops.b200.rms_norm.default, (torch.empty_like(x), x, w0, 1e-5), test_utils=tests)
     res = torch.randn(32, 512, device=DEV, dtype=torch.bfloat16)
     w = torch.ones(512, device=DEV, dtype=torch.bfloat16)
     torch.library.opcheck(torch.ops.b200.fused_add_rms_norm.default, (x.clone(), res, w, 1e-5), test_utils=tests)

@@ -232,6 +232,8 @@ SIGNATURES = {
     "b200_allreduce_fused_add_rms_norm": (
         c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_int64, c_int, c_int,
                 c_void_p]),
+    "b200_dcp_lse_merge": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
+                                   c_int, c_int, c_void_p]),
     "b200_paged_attention_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200_paged_attention_decode": (c_int, [C.POINTER(PagedAttnArgs), c_void_p]),
     "b200_paged_attention_varlen": (c_int, [C.POINTER(VarlenAttnArgs), c_void_p]),

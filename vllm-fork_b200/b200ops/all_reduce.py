@@ -158,6 +158,57 @@ class B200AllReduce:
             _dt(inp), _stream())
         _lib.check(rc, "allreduce_fused_add_rms_norm")
 
+    def dcp_lse_merge(self, cp_attn_out: torch.Tensor, cp_attn_lse: torch.Tensor, *, reduce_scatter: bool = True,
+                      return_lse: bool = False, is_lse_base_on_e: bool = True):
+        """cp_lse_ag_out_rs (reduce_scatter=True) / cp_lse_ag_out_ar (False) of vllm/v1/attention/ops/common.py:185-258:
+        merge the partial attention outputs [B, H, D] that every rank of the (decode-)context-parallel group
+        computed over ITS shard of the KV cache, weighted by their log-sum-exps [B, H], in one NVLink kernel.
+        Inputs that already live in the symmetric heap (alloc()) are read in place by the peers; others are
+        copied into heap scratch first (one device copy). Returns out [B, H / world, D] (this rank's heads) or
+        [B, H, D], plus the merged LSE when return_lse."""
+        if self.disabled:
+            raise RuntimeError("B200AllReduce is disabled (world size 1)")
+        if cp_attn_out.dim() == 4 and cp_attn_out.shape[1] == 1:
+            cp_attn_out = cp_attn_out.squeeze(1)
+        if cp_attn_out.dim() != 3 or tuple(cp_attn_lse.shape) != tuple(cp_attn_out.shape[:2]):
+            raise RuntimeError(f"dcp_lse_merge: expected out [B,H,D] and lse [B,H], got {tuple(cp_attn_out.shape)} "
+                               f"and {tuple(cp_attn_lse.shape)}")
+        if not cp_attn_out.is_cuda:
+            raise RuntimeError("dcp_lse_merge: inputs must be CUDA tensors (no CPU fallback)")
+        B, H, D = cp_attn_out.shape
+        if reduce_scatter and H % self.world_size:
+            raise RuntimeError(f"dcp_lse_merge: {H} heads do not divide over {self.world_size} ranks")
+        o_in, l_in = cp_attn_out, cp_attn_lse
+        if not (self._in_heap(o_in) and o_in.is_contiguous()):
+            o_in = self._scratch("dcp_out", (B, H, D), cp_attn_out.dtype)
+            o_in.copy_(cp_attn_out)
+        if not (self._in_heap(l_in) and l_in.is_contiguous() and l_in.dtype == torch.float32):
+            l_in = self._scratch("dcp_lse", (B, H), torch.float32)
+            l_in.copy_(cp_attn_lse)
+        hs = H // self.world_size if reduce_scatter else H
+        out = torch.empty(B, hs, D, dtype=cp_attn_out.dtype, device=self.device)
+        lse = torch.empty(B, hs, dtype=torch.float32, device=self.device) if return_lse else None
+        rc = _lib.load().b200_dcp_lse_merge(self._ctx, _p(out), _p(lse), _p(o_in), _p(l_in), B, H, D, _dt(o_in),
+                                            0 if reduce_scatter else 1, 1 if is_lse_base_on_e else 0, _stream())
+        _lib.check(rc, "dcp_lse_merge")
+        return (out, lse) if return_lse else out
+
+    def _in_heap(self, t: torch.Tensor) -> bool:
+        lo = self._heap.data_ptr()
+        return lo <= t.data_ptr() and t.data_ptr() + t.numel() * t.element_size() <= lo + self._heap.numel()
+
+    def _scratch(self, name: str, shape, dtype: torch.dtype) -> torch.Tensor:
+        """persistent heap scratch by (name, bytes): allocated on first use, in the same order on every rank"""
+        n = 1
+        for s in shape:
+            n *= s
+        key = (name, n * torch.empty((), dtype=dtype).element_size())
+        if not hasattr(self, "_scratch_bufs"):
+            self._scratch_bufs = {}
+        if key not in self._scratch_bufs:
+            self._scratch_bufs[key] = self.alloc(key[1], torch.uint8)
+        return self._scratch_bufs[key].view(dtype).view(shape)
+
     def rows_of_rank(self, M: int) -> tuple[int, int]:
         return tp.rows_of_rank(M, self.rank, self.world_size)
 

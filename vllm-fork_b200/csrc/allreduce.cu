@@ -310,4 +310,5 @@ __global__ void __launch_bounds__(NTHREADS, 1)
 }  // namespace b200
 
 #include "allreduce_fused.cuh"
+#include "dcp_merge.cuh"
 #include "allreduce_host.cuh"

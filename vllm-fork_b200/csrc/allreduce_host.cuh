@@ -290,3 +290,76 @@ extern "C" int b200_allreduce_fused_add_rms_norm(void* ctx, void* out, const voi
   return scale ? dispatch_fused<__half, true>(c->world, pe, fp, stage_src, c->rank, stream)
                : dispatch_fused<__half, false>(c->world, pe, fp, stage_src, c->rank, stream);
 }
+
+// ---------------------------------------------------------------- DCP attention merge (csrc/dcp_merge.cuh)
+// cp_lse_ag_out_rs / cp_lse_ag_out_ar (vllm/v1/attention/ops/common.py:185-258) in one NVLink kernel.
+// attn_out [B, H, D] (dtype) and attn_lse [B, H] (f32): this rank's partial attention over its shard of the
+// context, BOTH inside a registered symmetric region at the same offset on every rank (peers read them in place).
+// mode 0 (reduce-scatter over heads): out [B, H / world, D], lse_out [B, H / world] = heads [rank*H/world, ...);
+// mode 1 (all-reduce): out [B, H, D], lse_out [B, H]. out / lse_out are local (any device memory), lse_out nullable.
+extern "C" int b200_dcp_lse_merge(void* ctx, void* out, float* lse_out, const void* attn_out, const float* attn_lse,
+                                  int64_t num_tokens, int num_heads, int head_size, int dtype, int mode,
+                                  int is_lse_base_on_e, b200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  B200_CHECK(ctx, B200_ERR_INVALID, "dcp_lse_merge: null context");
+  Context* c = reinterpret_cast<Context*>(ctx);
+  B200_CHECK(dtype == B200_F32 || dtype == B200_F16 || dtype == B200_BF16, B200_ERR_INVALID,
+             "dcp_lse_merge: dtype must be float32 / float16 / bfloat16");
+  B200_CHECK(mode == 0 || mode == 1, B200_ERR_INVALID, "dcp_lse_merge: mode must be 0 (reduce-scatter) or 1 (all-reduce)");
+  B200_CHECK(num_tokens >= 0 && num_tokens < (1 << 24) && num_heads > 0 && head_size > 0, B200_ERR_INVALID,
+             "dcp_lse_merge: bad sizes");
+  B200_CHECK((head_size * dtype_size(dtype)) % 16 == 0, B200_ERR_INVALID,
+             "dcp_lse_merge: head_size rows must be multiples of 16 bytes");
+  B200_CHECK(mode == 1 || num_heads % c->world == 0, B200_ERR_INVALID,
+             "dcp_lse_merge: num_heads (%d) must divide by the group size (%d) for reduce-scatter", num_heads, c->world);
+  if (num_tokens == 0) return B200_OK;
+  B200_CHECK(out && attn_out && attn_lse, B200_ERR_INVALID, "dcp_lse_merge: null pointer");
+  B200_CHECK(((uintptr_t)out & 15) == 0 && ((uintptr_t)attn_out & 15) == 0 && ((uintptr_t)attn_lse & 3) == 0,
+             B200_ERR_INVALID, "dcp_lse_merge: out / attn_out must be 16-byte aligned");
+  const size_t out_bytes = (size_t)num_tokens * num_heads * head_size * dtype_size(dtype);
+  const size_t lse_bytes = (size_t)num_tokens * num_heads * 4;
+  Peers pe;
+  DcpParams dp;
+  size_t off_o, off_l;
+  const int reg_o = find_region(c, attn_out, out_bytes, &off_o);
+  const int reg_l = find_region(c, attn_lse, lse_bytes, &off_l);
+  B200_CHECK(reg_o >= 0 && reg_l >= 0, B200_ERR_INVALID,
+             "dcp_lse_merge: attn_out and attn_lse must live in the symmetric heap (peers read them in place)");
+  for (int r = 0; r < c->world; r++) {
+    pe.sig[r] = reinterpret_cast<Signal*>(c->regions[0].base[r]);
+    pe.tmp[r] = nullptr;
+    pe.in[r] = c->regions[reg_o].base[r] + off_o;
+    dp.lse[r] = reinterpret_cast<const float*>(c->regions[reg_l].base[r] + off_l);
+  }
+  dp.out = out;
+  dp.lse_out = lse_out;
+  dp.B = (int)num_tokens;
+  dp.H = num_heads;
+  dp.D = head_size;
+  dp.Hs = mode == 0 ? num_heads / c->world : num_heads;
+  dp.head_lo = mode == 0 ? c->rank * dp.Hs : 0;
+  dp.base_e = is_lse_base_on_e ? 1 : 0;
+  const int64_t packs = (int64_t)dp.B * dp.Hs * (head_size * dtype_size(dtype) / 16);
+  int64_t blocks = (packs + 255) / 256;
+  const int cap = sm_count() < MAX_BLOCKS ? sm_count() : MAX_BLOCKS;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+#define B200_DCP(T, N) dcp_lse_merge_kernel<T, N><<<(int)blocks, 256, 0, stream>>>(pe, dp, c->rank)
+#define B200_DCP_T(T)                                                                      \
+  switch (c->world) {                                                                      \
+    case 2: B200_DCP(T, 2); break;                                                         \
+    case 4: B200_DCP(T, 4); break;                                                         \
+    case 6: B200_DCP(T, 6); break;                                                         \
+    case 8: B200_DCP(T, 8); break;                                                         \
+    default:                                                                               \
+      set_last_error("dcp_lse_merge supports 2, 4, 6 or 8 ranks, got %d", c->world);       \
+      return B200_ERR_UNSUPPORTED;                                                         \
+  }
+  if (dtype == B200_F32) { B200_DCP_T(float) }
+  else if (dtype == B200_F16) { B200_DCP_T(__half) }
+  else { B200_DCP_T(__nv_bfloat16) }
+#undef B200_DCP_T
+#undef B200_DCP
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
