@@ -458,27 +458,51 @@ def tp_self_check(rank, world, dev, group):
         dist.broadcast(forced[i], 0, group=group)
     forced = [f.cpu() for f in forced]
     comms = ["nccl", "nvlink"] + (["fused"] if world in (2, 4, 8) else [])
-    near_ties = 0
+    near_ties, identical, total, worst_rel = 0, 0, 0, 0.0
+    logits_by_comm = {}
     for comm in comms:
         mN = decoder.DecoderModel(shape, S, ctx, bs, dev, tp_rank=rank, tp_size=world, tp_group=group,
                                   comm=comm, num_blocks=nb)
-        t, _ = run(mN, forced)      # teacher-forced with the TP=1 tokens so step 2 sees the same context
+        t, lg = run(mN, forced)      # teacher-forced with the TP=1 tokens so step 2 sees the same context
+        logits_by_comm[comm] = lg
         if mN.ar is not None:
             torch.cuda.synchronize(dev)
             mN.ar.close()
         del mN
         if rank == 0:
+            # TP changes where the bf16 / FP8 roundings fall (per-rank partial sums are rounded before the
+            # all-reduce, and the next layer re-quantises to FP8), so logits agree to FP8 noise, not bit for bit:
+            # require a small relative error, and that a differing greedy token is explained by it (the TP=1
+            # margin between the two candidates is below twice that row's largest logit deviation)
             for step in range(2):
-                bad = (t[step] != ref_t[step]).nonzero().flatten().tolist()
-                for sidx in bad:
+                d = (lg[step] - ref_l[step]).abs()
+                rel = float(d.norm() / ref_l[step].norm())
+                worst_rel = max(worst_rel, rel)
+                if rel > 5e-2:
+                    raise AssertionError(f"tp_check: tiny model TP={world} comm={comm} step {step}: logits differ "
+                                         f"from TP=1 by {rel:.3e} (relative Frobenius)")
+                same = t[step] == ref_t[step]
+                identical += int(same.sum())
+                total += S
+                for sidx in (~same).nonzero().flatten().tolist():
                     a, b = ref_l[step, sidx, ref_t[step, sidx]], ref_l[step, sidx, t[step, sidx]]
-                    if abs(float(a - b)) > 2 ** -6 * max(abs(float(a)), 1e-3):
+                    if float(a - b) > 2.0 * float(d[sidx].max()):
                         raise AssertionError(f"tp_check: tiny model TP={world} comm={comm} step {step} seq {sidx}: "
-                                             f"token {int(t[step, sidx])} vs TP=1 {int(ref_t[step, sidx])} "
-                                             f"(TP=1 logits {float(a):.5f} vs {float(b):.5f})")
+                                             f"token {int(t[step, sidx])} vs TP=1 {int(ref_t[step, sidx])} (TP=1 logits "
+                                             f"{float(a):.5f} vs {float(b):.5f}, max logit deviation {float(d[sidx].max()):.5f})")
                     near_ties += 1
+    # the fused reduce-scatter+norm+quant+all-gather kernel is arithmetically identical to all-reduce -> norm+quant
+    # with the rank-order NVLink all-reduce: the two decoders must produce the same logits bit for bit
+    if "fused" in logits_by_comm and not torch.equal(logits_by_comm["fused"], logits_by_comm["nvlink"]):
+        raise AssertionError(f"tp_check: tiny model TP={world}: comm=fused and comm=nvlink logits are not bit-identical")
+    if world == 2 and not torch.equal(logits_by_comm["nccl"], logits_by_comm["nvlink"]):
+        raise AssertionError("tp_check: tiny model TP=2: NCCL and NVLink all-reduce decoders differ (a+b is order-free)")
+    if rank == 0 and identical < 0.9 * total:
+        raise AssertionError(f"tp_check: only {identical} of {total} greedy tokens equal TP=1")
     res["tiny_tokens"] = "match"
-    res["tiny_model"] = f"{shape.name}, {S} seqs x 2 steps, comm {'/'.join(comms)}, {near_ties} near-tie exceptions"
+    res["tiny_model"] = (f"{shape.name}, {S} seqs x 2 steps x comm {'/'.join(comms)}: {identical} of {total} greedy tokens "
+                         f"identical to TP=1, {near_ties} differ inside the measured logit deviation (near-ties); "
+                         f"logits vs TP=1 rel err <= {worst_rel:.2e}; fused == nvlink logits bit-identical")
     return res
 
 

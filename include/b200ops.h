@@ -573,6 +573,10 @@ B200_API int b200_apply_repetition_penalties(void* logits, const void* prompt_ma
                                              const void* penalties, int64_t rows, int vocab, int dtype,
                                              b200_stream_t stream);
 
+/* Development probe (tools/trace_gemm.py): device buffer receiving 8 x uint64 %globaltimer stamps per CTA of the
+ * v2 FP8 GEMM kernel; NULL (default) switches it off. Not part of the reference surface. */
+B200_API int b200_debug_set_trace(void* dev_ptr);
+
 #ifdef __cplusplus
 }
 #endif

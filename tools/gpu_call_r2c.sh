@@ -1,0 +1,5 @@
+# 2 GPUs: bench --gpus 2 with tp_check (tiny-model criterion fixed)
+set -x
+mkdir -p gpurun_out
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 10 --warmup 3 > gpurun_out/r2c_bench_tp2.json 2> gpurun_out/r2c_bench_tp2.err; echo "bench rc=$?"
+tail -c 1500 gpurun_out/r2c_bench_tp2.json

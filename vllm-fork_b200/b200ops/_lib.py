@@ -232,6 +232,7 @@ SIGNATURES = {
     "b200_allreduce_fused_add_rms_norm": (
         c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_int64, c_int, c_int,
                 c_void_p]),
+    "b200_debug_set_trace": (c_int, [c_void_p]),
     "b200_dcp_lse_merge": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int,
                                    c_int, c_int, c_void_p]),
     "b200_paged_attention_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),

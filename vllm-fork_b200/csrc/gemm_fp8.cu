@@ -19,6 +19,7 @@
 #include "tcgen05.cuh"
 
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 namespace b200 {
@@ -51,7 +52,18 @@ struct Params {
   // tiles (35 MB of operands at K = 8192) instead of all row tiles (ncu r1b: 649 MB DRAM reads for 134 MB
   // of operands with the row-major order). 0 = plain 2-D grid.
   int raster_group, row_tiles, col_tiles;
+  // development probe (b200_debug_set_trace): 8 x u64 %globaltimer stamps per CTA, null in production
+  unsigned long long* trace;
 };
+
+static unsigned long long* g_trace = nullptr;
+__device__ __forceinline__ void probe(const Params& p, int slot) {
+  if (p.trace) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    p.trace[((size_t)blockIdx.y * gridDim.x + blockIdx.x) * 8 + slot] = t;
+  }
+}
 
 using namespace b200::tc;
 
@@ -95,6 +107,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
       reinterpret_cast<volatile uint32_t*>(smem + (size_t)stages * STAGE_BYTES + 16 * MAX_STAGES + 8);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) probe(p, 0);
   int rt = blockIdx.x, ct = blockIdx.y;
   if (p.raster_group > 0) {
     const int per_group = p.raster_group * p.col_tiles;
@@ -126,6 +139,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_d = *tmem_holder;
+  if (threadIdx.x == 0) probe(p, 1);
 
   if (warp == 0) {
     // ============================== TMA producer
@@ -146,8 +160,10 @@ __global__ void __launch_bounds__(NTHREADS, 1)
         tma_load_2d(dst, &tmR, bar_full + 8u * stage, kb * BK, row0, pol_r);
         if constexpr (GATED) tma_load_2d(dst + BM * BK, &tmR, bar_full + 8u * stage, kb * BK, p.gate_rows + row0, pol_r);
         tma_load_2d(dst + R_BYTES, &tmC, bar_full + 8u * stage, kb * BK, col0, pol_c);
+        if (kb == 0) probe(p, 2);
         if (++stage == stages) { stage = 0; phase ^= 1u; }
       }
+      probe(p, 6);
     }
   } else if (warp == 1) {
     // ============================== MMA issuer (one thread)
@@ -157,6 +173,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
       for (int kb = 0; kb < num_kb; kb++) {
         mbar_wait(bar_full + 8u * stage, phase);
         tc_fence_after();
+        if (kb == 0) probe(p, 3);
         const uint32_t sa = base + (uint32_t)stage * STAGE_BYTES;
         const uint64_t da = make_smem_desc(sa);
         const uint64_t db = make_smem_desc(sa + R_BYTES);
@@ -177,12 +194,14 @@ __global__ void __launch_bounds__(NTHREADS, 1)
         if (++stage == stages) { stage = 0; phase ^= 1u; }
       }
       tc_commit(bar_tmem);  // accumulator complete
+      probe(p, 4);
     }
   } else {
     // ============================== epilogue (4 warps, one TMEM lane quarter each)
     const int wq = warp & 3;
     mbar_wait(bar_tmem, 0);
     tc_fence_after();
+    if (warp == 2 && lane == 0) probe(p, 5);
     const int r = row0 + wq * 32 + lane;  // rows-operand index of this thread
     const bool r_ok = r < p.R;
     const float rs = p.r_scale_vec ? (r_ok ? p.r_scale[r] : 0.f) : p.r_scale[0];
@@ -349,6 +368,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   }
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) probe(p, 7);
   if (warp == 1) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_d), "r"(TMEM_COLS)
@@ -367,7 +387,10 @@ static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, const CUtensor
     set_last_error("fp8_gemm: not enough shared memory");
     return B200_ERR_UNSUPPORTED;
   }
+  static const int forced_stages = [] { const char* e = getenv("B200_GEMM_STAGES"); return e ? atoi(e) : 0; }();
+  if (forced_stages >= 2 && forced_stages < stages) stages = forced_stages;
   p.stages = stages;
+  p.trace = g_trace;
   const int smem = stages * (int)STAGE_BYTES + 16 * MAX_STAGES + 64 + 1024;
   static bool configured = false;
   if (!configured) {
@@ -391,6 +414,12 @@ static int make_tmap_2d(CUtensorMap* tm, const void* base, int rows, int K, int6
 
 }  // namespace gemm8
 }  // namespace b200
+
+// development probe: device buffer of 8 x u64 per CTA receiving %globaltimer stamps of the v2 kernel (NULL = off)
+extern "C" int b200_debug_set_trace(void* dev_ptr) {
+  b200::gemm8::g_trace = reinterpret_cast<unsigned long long*>(dev_ptr);
+  return B200_OK;
+}
 
 extern "C" int b200_fp8_gemm(void* out, const void* a, const void* b, const float* a_scale,
                              const float* b_scale, const void* bias, int M, int N, int K,
@@ -448,6 +477,8 @@ extern "C" int b200_fp8_gemm(void* out, const void* a, const void* b, const floa
       const double t = waves * (num_kb * (mma > ingest ? mma : ingest) + 5000.0 + 12.0 * c);
       if (t < best) { best = t; bn = c; }
     }
+    static const int forced_bn = [] { const char* e = getenv("B200_GEMM_BN"); return e ? atoi(e) : 0; }();
+    if (forced_bn == 16 || forced_bn == 32 || forced_bn == 64 || forced_bn == 128 || forced_bn == 256) bn = forced_bn;
     p.R = N; p.C = M;
     p.r_scale = b_scale; p.r_scale_vec = b_scale_per_col;
     p.c_scale = a_scale; p.c_scale_vec = a_scale_per_row;
