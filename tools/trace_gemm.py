@@ -26,12 +26,13 @@ def run(shapes):
         for w in ws[:4]:
             ops.cutlass_scaled_mm(x, w.t(), one, one, torch.bfloat16, out=out, impl="v2")
         torch.cuda.synchronize()
-        trace = torch.zeros(4096 * 8, dtype=torch.int64, device=dev)
+        trace = torch.zeros(4096 * 8 + 4 * 64, dtype=torch.int64, device=dev)
         lib.b200_debug_set_trace(trace.data_ptr())
         ops.cutlass_scaled_mm(x, ws[5].t(), one, one, torch.bfloat16, out=out, impl="v2")
         torch.cuda.synchronize()
         lib.b200_debug_set_trace(None)
-        t = trace.cpu().view(-1, 8)
+        fine = trace.cpu()[32768:].view(4, 64)
+        t = trace.cpu()[:32768].view(-1, 8)
         t = t[t[:, 0] > 0].double()
         t0 = t[:, 0].min()
         print(f"== M={M} N={N} K={K}  BN={os.environ.get('B200_GEMM_BN', 'auto')} stages={os.environ.get('B200_GEMM_STAGES', 'auto')}"
@@ -39,6 +40,12 @@ def run(shapes):
         for i, n in enumerate(NAMES):
             c = (t[:, i] - t0) / 1e3
             print(f"   {n:28s} min {c.min():6.2f}  median {c.median():6.2f}  max {c.max():6.2f} us")
+        if os.environ.get("TRACE_FINE"):
+            nkb = min(64, (K + 127) // 128)
+            c0 = int(fine[0, 0])
+            print("   CTA(0,0) clock64 per k-block: producer got-empty / issued | MMA got-full / issued+committed (cycles since first)")
+            for kb in range(nkb):
+                print(f"     kb {kb:2d}: P {int(fine[0, kb]) - c0:7d} {int(fine[1, kb]) - c0:7d} | M {int(fine[2, kb]) - c0:7d} {int(fine[3, kb]) - c0:7d}")
         # graph-timed average over rotated weights
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):

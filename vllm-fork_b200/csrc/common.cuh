@@ -170,6 +170,21 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {
   }
 }
+// One lane of a CONVERGED warp. Single-thread roles (TMA producer, tcgen05.mma issuer) must be written as
+// warp-uniform loops with `if (elect_one())` around the issue instructions: under a divergent `if (lane == 0)`
+// ptxas cannot prove the operands of the uniform-datapath instructions (UTMALDG / UTCQMMA / UTCBAR) uniform and
+// wraps EVERY one of them in an ELECT ... BRA.U.ANY loop plus R2UR moves - measured on B200 as ~100 cycles per
+// TMA issue and ~65 cycles per MMA issue (profiles/r2f_trace_fine.txt), which bounds a k-block at ~480 cycles
+// whatever the tile width.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }

@@ -57,6 +57,10 @@ struct Params {
 };
 
 static unsigned long long* g_trace = nullptr;
+// fine probe: CTA (0,0) only, clock64 per k-block (< 64) into trace[32768 + role * 64 + kb]
+__device__ __forceinline__ void probe_kb(const Params& p, int role, int kb) {
+  if (p.trace && blockIdx.x == 0 && blockIdx.y == 0 && kb < 64) p.trace[32768 + role * 64 + kb] = clock64();
+}
 __device__ __forceinline__ void probe(const Params& p, int slot) {
   if (p.trace) {
     unsigned long long t;
@@ -142,38 +146,42 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   if (threadIdx.x == 0) probe(p, 1);
 
   if (warp == 0) {
-    // ============================== TMA producer
-    if (lane == 0) {
-      prefetch_tmap(&tmR);
-      prefetch_tmap(&tmC);
-      // weights are streamed once; activations are re-read by every CTA
-      const uint64_t pol_w = l2_policy_evict_first();
-      const uint64_t pol_a = l2_policy_evict_last();
-      const uint64_t pol_r = p.swap ? pol_w : pol_a;
-      const uint64_t pol_c = p.swap ? pol_a : pol_w;
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = 0; kb < num_kb; kb++) {
-        mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
+    // ============================== TMA producer (warp-uniform loop, one elected lane issues: see elect_one())
+    prefetch_tmap(&tmR);
+    prefetch_tmap(&tmC);
+    // weights are streamed once; activations are re-read by every CTA
+    const uint64_t pol_w = l2_policy_evict_first();
+    const uint64_t pol_a = l2_policy_evict_last();
+    const uint64_t pol_r = p.swap ? pol_w : pol_a;
+    const uint64_t pol_c = p.swap ? pol_a : pol_w;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = 0; kb < num_kb; kb++) {
+      mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
+      if (elect_one()) {
+        probe_kb(p, 0, kb);
         const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES;
         mbar_arrive_expect_tx(bar_full + 8u * stage, STAGE_BYTES);
         tma_load_2d(dst, &tmR, bar_full + 8u * stage, kb * BK, row0, pol_r);
         if constexpr (GATED) tma_load_2d(dst + BM * BK, &tmR, bar_full + 8u * stage, kb * BK, p.gate_rows + row0, pol_r);
         tma_load_2d(dst + R_BYTES, &tmC, bar_full + 8u * stage, kb * BK, col0, pol_c);
         if (kb == 0) probe(p, 2);
-        if (++stage == stages) { stage = 0; phase ^= 1u; }
+        probe_kb(p, 1, kb);
       }
-      probe(p, 6);
+      __syncwarp();
+      if (++stage == stages) { stage = 0; phase ^= 1u; }
     }
+    if (lane == 0) probe(p, 6);
   } else if (warp == 1) {
-    // ============================== MMA issuer (one thread)
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = 0; kb < num_kb; kb++) {
-        mbar_wait(bar_full + 8u * stage, phase);
-        tc_fence_after();
+    // ============================== MMA issuer (warp-uniform loop, one elected lane issues)
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = 0; kb < num_kb; kb++) {
+      mbar_wait(bar_full + 8u * stage, phase);
+      tc_fence_after();
+      if (elect_one()) {
         if (kb == 0) probe(p, 3);
+        probe_kb(p, 2, kb);
         const uint32_t sa = base + (uint32_t)stage * STAGE_BYTES;
         const uint64_t da = make_smem_desc(sa);
         const uint64_t db = make_smem_desc(sa + R_BYTES);
@@ -191,10 +199,14 @@ __global__ void __launch_bounds__(NTHREADS, 1)
                       (kb > 0 || k > 0) ? 1u : 0u);
         }
         tc_commit(bar_empty + 8u * stage);  // frees the smem slot when the MMAs have read it
-        if (++stage == stages) { stage = 0; phase ^= 1u; }
+        probe_kb(p, 3, kb);
+        if (kb == num_kb - 1) {
+          tc_commit(bar_tmem);  // accumulator complete
+          probe(p, 4);
+        }
       }
-      tc_commit(bar_tmem);  // accumulator complete
-      probe(p, 4);
+      __syncwarp();
+      if (++stage == stages) { stage = 0; phase ^= 1u; }
     }
   } else {
     // ============================== epilogue (4 warps, one TMEM lane quarter each)

@@ -117,33 +117,34 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   const uint32_t tmem_d = *tmem_holder;
 
   if (warp == 0) {
-    // ============================== TMA producer
-    if (lane == 0) {
-      prefetch_tmap(&tmW);
-      prefetch_tmap(&tmA);
-      const uint64_t pol_w = gridDim.y > 1 ? l2_policy_evict_last() : l2_policy_evict_first();
-      const uint64_t pol_a = l2_policy_evict_last();
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = 0; kb < num_kb; kb++) {
-        mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
+    // ============================== TMA producer (warp-uniform loop, one elected lane issues: common.cuh elect_one)
+    prefetch_tmap(&tmW);
+    prefetch_tmap(&tmA);
+    const uint64_t pol_w = gridDim.y > 1 ? l2_policy_evict_last() : l2_policy_evict_first();
+    const uint64_t pol_a = l2_policy_evict_last();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = 0; kb < num_kb; kb++) {
+      mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
+      if (elect_one()) {
         const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES;
         mbar_arrive_expect_tx(bar_full + 8u * stage, STAGE_BYTES);
         tma_load_2d(dst, &tmW, bar_full + 8u * stage, (kb0 + kb) * BK, row0, pol_w);
         tma_load_2d(dst + W_BYTES, &tmA, bar_full + 8u * stage, (kb0 + kb) * BK, col0, pol_a);
-        if (++stage == stages) { stage = 0; phase ^= 1u; }
       }
+      __syncwarp();
+      if (++stage == stages) { stage = 0; phase ^= 1u; }
     }
   } else if (warp == 1) {
-    // ============================== MMA issuer (one thread): one partial accumulator per k-block
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = 0; kb < num_kb; kb++) {
-        const int slot = kb & 1;
-        mbar_wait(bar_acc_empty + 8u * slot, (((uint32_t)kb >> 1) & 1u) ^ 1u);   // promotion of kb-2 done
-        mbar_wait(bar_full + 8u * stage, phase);
-        tc_fence_after();
+    // ============================== MMA issuer (one elected lane): one partial accumulator per k-block
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = 0; kb < num_kb; kb++) {
+      const int slot = kb & 1;
+      mbar_wait(bar_acc_empty + 8u * slot, (((uint32_t)kb >> 1) & 1u) ^ 1u);   // promotion of kb-2 done
+      mbar_wait(bar_full + 8u * stage, phase);
+      tc_fence_after();
+      if (elect_one()) {
         const uint32_t sa = base + (uint32_t)stage * STAGE_BYTES;
         const uint64_t dw = make_smem_desc(sa);
         const uint64_t da = make_smem_desc(sa + W_BYTES);
@@ -153,8 +154,9 @@ __global__ void __launch_bounds__(NTHREADS, 1)
                     da + (uint64_t)(k * UMMA_K >> 4), IDESC, k > 0 ? 1u : 0u);
         tc_commit(bar_empty + 8u * stage);        // smem slot free when the MMAs have read it
         tc_commit(bar_acc_full + 8u * slot);      // partial accumulator complete
-        if (++stage == stages) { stage = 0; phase ^= 1u; }
       }
+      __syncwarp();
+      if (++stage == stages) { stage = 0; phase ^= 1u; }
     }
   } else {
     // ============================== promotion + epilogue (4 warps, one TMEM lane quarter each)

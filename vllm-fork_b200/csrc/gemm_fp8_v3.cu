@@ -235,39 +235,40 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
   sched_init(p, pair, &sched);
 
   if (warp == 0) {
-    // ============================== TMA producer (one thread per CTA)
-    if (lane == 0) {
-      prefetch_tmap(&tmR);
-      prefetch_tmap(&tmC);
-      const uint64_t pol_w = l2_policy_evict_first();
-      const uint64_t pol_a = l2_policy_evict_last();
-      // decode: weights stream once (evict first), the batch is re-read by every pair (evict last);
-      // large M: both operands are re-read by other tiles of the raster block
-      const uint64_t pol_r = p.swap ? pol_w : pol_a;
-      const uint64_t pol_c = pol_a;
-      int stage = 0;
-      uint32_t phase = 0;
-      Piece pc;
-      while (next_piece(p, sched, &pc)) {
-        int rt, ct;
-        tile_coords(p, pc.tile, &rt, &ct);
-        const int row0 = rt * 2 * BM + (int)cta * BM;
-        const int col0 = ct * BN + (int)cta * (BN / 2);
-        for (int kb = pc.kb0; kb < pc.kb1; kb++) {
-          mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
+    // ============================== TMA producer (warp-uniform loops, one elected lane issues: common.cuh elect_one)
+    prefetch_tmap(&tmR);
+    prefetch_tmap(&tmC);
+    const uint64_t pol_w = l2_policy_evict_first();
+    const uint64_t pol_a = l2_policy_evict_last();
+    // decode: weights stream once (evict first), the batch is re-read by every pair (evict last);
+    // large M: both operands are re-read by other tiles of the raster block
+    const uint64_t pol_r = p.swap ? pol_w : pol_a;
+    const uint64_t pol_c = pol_a;
+    int stage = 0;
+    uint32_t phase = 0;
+    Piece pc;
+    while (next_piece(p, sched, &pc)) {
+      int rt, ct;
+      tile_coords(p, pc.tile, &rt, &ct);
+      const int row0 = rt * 2 * BM + (int)cta * BM;
+      const int col0 = ct * BN + (int)cta * (BN / 2);
+      for (int kb = pc.kb0; kb < pc.kb1; kb++) {
+        mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
+        if (elect_one()) {
           const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES;
           // the leader's barrier counts the bytes of BOTH CTAs (the peer's complete_tx may land first:
           // the tx-count simply goes negative until the leader's expect_tx)
           if (cta == 0) mbar_arrive_expect_tx(bar_full + 8u * stage, 2 * STAGE_BYTES);
           tma_load_2d_2sm(dst, &tmR, bar_full + 8u * stage, kb * BK, row0, pol_r);
           tma_load_2d_2sm(dst + R_BYTES, &tmC, bar_full + 8u * stage, kb * BK, col0, pol_c);
-          if (++stage == stages) { stage = 0; phase ^= 1u; }
         }
+        __syncwarp();
+        if (++stage == stages) { stage = 0; phase ^= 1u; }
       }
     }
   } else if (warp == 1) {
-    // ============================== MMA issuer: one thread of the LEADER CTA drives both tensor cores
-    if (cta == 0 && lane == 0) {
+    // ============================== MMA issuer: one elected lane of the LEADER CTA drives both tensor cores
+    if (cta == 0) {
       int stage = 0;
       uint32_t phase = 0;
       uint32_t tphase[2] = {0, 0};
@@ -275,27 +276,30 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
       int n = 0;
       while (next_piece(p, sched, &pc)) {
         const int buf = n & 1;
-        V3_TRACE(0, n, 0);
+        if (lane == 0) V3_TRACE(0, n, 0);
         mbar_wait(bar_tempty + 8u * buf, tphase[buf] ^ 1u);   // epilogues of both CTAs drained this buffer
-        V3_TRACE(0, n, 1);
+        if (lane == 0) V3_TRACE(0, n, 1);
         tphase[buf] ^= 1u;
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + (uint32_t)(buf * BN);
         for (int kb = pc.kb0; kb < pc.kb1; kb++) {
           mbar_wait(bar_full + 8u * stage, phase);
           tc_fence_after();
-          const uint32_t sa = base + (uint32_t)stage * STAGE_BYTES;
-          const uint64_t da = make_smem_desc(sa);
-          const uint64_t db = make_smem_desc(sa + R_BYTES);
+          if (elect_one()) {
+            const uint32_t sa = base + (uint32_t)stage * STAGE_BYTES;
+            const uint64_t da = make_smem_desc(sa);
+            const uint64_t db = make_smem_desc(sa + R_BYTES);
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; k++)
-            tc_mma_f8_2sm(tmem_d, da + (uint64_t)(k * UMMA_K >> 4), db + (uint64_t)(k * UMMA_K >> 4), IDESC,
-                          (kb > pc.kb0 || k > 0) ? 1u : 0u);
-          tc_commit_2sm(bar_empty + 8u * stage);
+            for (int k = 0; k < BK / UMMA_K; k++)
+              tc_mma_f8_2sm(tmem_d, da + (uint64_t)(k * UMMA_K >> 4), db + (uint64_t)(k * UMMA_K >> 4), IDESC,
+                            (kb > pc.kb0 || k > 0) ? 1u : 0u);
+            tc_commit_2sm(bar_empty + 8u * stage);
+            if (kb == pc.kb1 - 1) tc_commit_2sm(bar_tfull + 8u * buf);
+          }
+          __syncwarp();
           if (++stage == stages) { stage = 0; phase ^= 1u; }
         }
-        tc_commit_2sm(bar_tfull + 8u * buf);
-        V3_TRACE(0, n, 2);
+        if (lane == 0) V3_TRACE(0, n, 2);
         n++;
       }
     }

@@ -145,44 +145,47 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   const uint32_t tmem_base = *tmem_holder;
 
   if (warp == 0) {
-    // ============================== TMA producer (one thread per CTA)
-    if (lane == 0) {
-      prefetch_tmap(&tmR);
-      prefetch_tmap(&tmC);
-      const uint64_t pol_w = l2_policy_evict_first();   // weights stream once
-      const uint64_t pol_a = l2_policy_evict_last();    // the batch is re-read by every cluster
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = kb0; kb < kb1; kb++) {
-        mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
+    // ============================== TMA producer (warp-uniform loop, one elected lane issues: common.cuh elect_one)
+    prefetch_tmap(&tmR);
+    prefetch_tmap(&tmC);
+    const uint64_t pol_w = l2_policy_evict_first();   // weights stream once
+    const uint64_t pol_a = l2_policy_evict_last();    // the batch is re-read by every cluster
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = kb0; kb < kb1; kb++) {
+      mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
+      if (elect_one()) {
         const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES;
         if (h == 0) mbar_arrive_expect_tx(bar_full + 8u * stage, 2 * STAGE_BYTES);
         tma_load_2d_2sm(dst, &tmR, bar_full + 8u * stage, kb * BK, row0, pol_w);
         tma_load_2d_2sm(dst + R_BYTES, &tmC, bar_full + 8u * stage, kb * BK, (int)h * (BN / 2), pol_a);
-        if (++stage == stages) { stage = 0; phase ^= 1u; }
       }
+      __syncwarp();
+      if (++stage == stages) { stage = 0; phase ^= 1u; }
     }
-    __syncwarp();
   } else if (warp == 1) {
-    // ============================== MMA issuer: one thread of the even CTA drives both tensor cores
-    if (h == 0 && lane == 0) {
+    // ============================== MMA issuer: one elected lane of the even CTA drives both tensor cores
+    if (h == 0) {
       const uint16_t pair_mask = (uint16_t)(3u << (2 * s));
       int stage = 0;
       uint32_t phase = 0;
       for (int kb = kb0; kb < kb1; kb++) {
         mbar_wait(bar_full + 8u * stage, phase);
         tc_fence_after();
-        const uint32_t sa = base + (uint32_t)stage * STAGE_BYTES;
-        const uint64_t da = make_smem_desc(sa);
-        const uint64_t db = make_smem_desc(sa + R_BYTES);
+        if (elect_one()) {
+          const uint32_t sa = base + (uint32_t)stage * STAGE_BYTES;
+          const uint64_t da = make_smem_desc(sa);
+          const uint64_t db = make_smem_desc(sa + R_BYTES);
 #pragma unroll
-        for (int k = 0; k < BK / UMMA_K; k++)
-          tc_mma_f8_2sm(tmem_base, da + (uint64_t)(k * UMMA_K >> 4), db + (uint64_t)(k * UMMA_K >> 4), IDESC,
-                        (kb > kb0 || k > 0) ? 1u : 0u);
-        tc_commit_2sm(bar_empty + 8u * stage, pair_mask);
+          for (int k = 0; k < BK / UMMA_K; k++)
+            tc_mma_f8_2sm(tmem_base, da + (uint64_t)(k * UMMA_K >> 4), db + (uint64_t)(k * UMMA_K >> 4), IDESC,
+                          (kb > kb0 || k > 0) ? 1u : 0u);
+          tc_commit_2sm(bar_empty + 8u * stage, pair_mask);
+          if (kb == kb1 - 1) tc_commit_2sm(bar_tfull, pair_mask);
+        }
+        __syncwarp();
         if (++stage == stages) { stage = 0; phase ^= 1u; }
       }
-      tc_commit_2sm(bar_tfull, pair_mask);
     }
     __syncwarp();
   } else {

@@ -131,24 +131,25 @@ __global__ void __launch_bounds__(NTHREADS, 1)
 
   if (warp == 0) {
     // ============================== producer: TMA tiles of codes + bulk copies of scale tiles
-    if (lane == 0) {
-      prefetch_tmap(&tmR);
-      prefetch_tmap(&tmC);
-      const uint64_t pol_w = l2_policy_evict_first();
-      const uint64_t pol_a = l2_policy_evict_last();
-      const uint64_t pol_r = p.swap ? pol_w : pol_a;
-      const uint64_t pol_c = p.swap ? pol_a : pol_w;
-      const int c_rows_pad = (p.C + 127) / 128 * 128;
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = 0; kb < num_kb; kb++) {
-        mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
+    // (warp-uniform loop, one elected lane issues: common.cuh elect_one)
+    prefetch_tmap(&tmR);
+    prefetch_tmap(&tmC);
+    const uint64_t pol_w = l2_policy_evict_first();
+    const uint64_t pol_a = l2_policy_evict_last();
+    const uint64_t pol_r = p.swap ? pol_w : pol_a;
+    const uint64_t pol_c = p.swap ? pol_a : pol_w;
+    const int c_rows_pad = (p.C + 127) / 128 * 128;
+    int c_tiles = 0;
+    for (int t = 0; t < C_TILES; t++)
+      if (col0 + t * 128 < c_rows_pad) c_tiles++;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = 0; kb < num_kb; kb++) {
+      mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
+      if (elect_one()) {
         const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES;
         const int kt = min(4, k_tiles - kb * 4);  // scale tiles (= MMAs) in this k-block
         const uint32_t sf_bytes = (uint32_t)kt * SF_TILE;
-        int c_tiles = 0;
-        for (int t = 0; t < C_TILES; t++)
-          if (col0 + t * 128 < c_rows_pad) c_tiles++;
         mbar_arrive_expect_tx(bar_full + 8u * stage, R_BYTES + C_BYTES + sf_bytes * (1 + c_tiles));
         tma_load_2d(dst, &tmR, bar_full + 8u * stage, kb * BKB, row0, pol_r);
         tma_load_2d(dst + R_BYTES, &tmC, bar_full + 8u * stage, kb * BKB, col0, pol_c);
@@ -159,18 +160,19 @@ __global__ void __launch_bounds__(NTHREADS, 1)
           bulk_load_1d(dst + R_BYTES + C_BYTES + SFR_BYTES + (uint32_t)t * SF_KB,
                        p.c_sf + ((int64_t)((col0 >> 7) + t) * k_tiles + kb * 4) * SF_TILE, sf_bytes,
                        bar_full + 8u * stage);
-        if (++stage == stages) { stage = 0; phase ^= 1u; }
       }
+      __syncwarp();
+      if (++stage == stages) { stage = 0; phase ^= 1u; }
     }
   } else if (warp == 1) {
-    // ============================== MMA issuer (one thread): scales smem->TMEM, then the MMAs
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      const uint32_t sfb_col_off = BN < 128 ? (uint32_t)((col0 & 127) >> 5) : 0u;
-      for (int kb = 0; kb < num_kb; kb++) {
-        mbar_wait(bar_full + 8u * stage, phase);
-        tc_fence_after();
+    // ============================== MMA issuer (one elected lane): scales smem->TMEM, then the MMAs
+    int stage = 0;
+    uint32_t phase = 0;
+    const uint32_t sfb_col_off = BN < 128 ? (uint32_t)((col0 & 127) >> 5) : 0u;
+    for (int kb = 0; kb < num_kb; kb++) {
+      mbar_wait(bar_full + 8u * stage, phase);
+      tc_fence_after();
+      if (elect_one()) {
         const uint32_t sa = base + (uint32_t)stage * STAGE_BYTES;
         const uint32_t ssf_r = sa + R_BYTES + C_BYTES;
         const uint32_t ssf_c = ssf_r + SFR_BYTES;
@@ -191,9 +193,10 @@ __global__ void __launch_bounds__(NTHREADS, 1)
                       (kb > 0 || k > 0) ? 1u : 0u);
         }
         tc_commit(bar_empty + 8u * stage);
-        if (++stage == stages) { stage = 0; phase ^= 1u; }
+        if (kb == num_kb - 1) tc_commit(bar_tmem);
       }
-      tc_commit(bar_tmem);
+      __syncwarp();
+      if (++stage == stages) { stage = 0; phase ^= 1u; }
     }
   } else {
     // ============================== epilogue (4 warps, one TMEM lane quarter each): out = alpha * acc

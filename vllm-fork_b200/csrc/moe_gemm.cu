@@ -77,28 +77,31 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   const uint32_t tmem_d = *tmem_holder;
 
   if (warp == 0) {
-    if (lane == 0) {
-      prefetch_tmap(&tmW);
-      prefetch_tmap(&tmA);
-      const uint64_t pol_w = l2_policy_evict_first(), pol_a = l2_policy_evict_last();
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = 0; kb < num_kb; kb++) {
-        mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
+    // TMA producer: warp-uniform loop, one elected lane issues (common.cuh elect_one)
+    prefetch_tmap(&tmW);
+    prefetch_tmap(&tmA);
+    const uint64_t pol_w = l2_policy_evict_first(), pol_a = l2_policy_evict_last();
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = 0; kb < num_kb; kb++) {
+      mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
+      if (elect_one()) {
         const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES;
         mbar_arrive_expect_tx(bar_full + 8u * stage, STAGE_BYTES);
         tma_load_3d(dst, &tmW, bar_full + 8u * stage, kb * BK, row0, e, pol_w);
         tma_load_2d(dst + R_BYTES, &tmA, bar_full + 8u * stage, kb * BK, col0, pol_a);
-        if (++stage == stages) { stage = 0; phase ^= 1u; }
       }
+      __syncwarp();
+      if (++stage == stages) { stage = 0; phase ^= 1u; }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int kb = 0; kb < num_kb; kb++) {
-        mbar_wait(bar_full + 8u * stage, phase);
-        tc_fence_after();
+    // MMA issuer: warp-uniform loop, one elected lane issues
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int kb = 0; kb < num_kb; kb++) {
+      mbar_wait(bar_full + 8u * stage, phase);
+      tc_fence_after();
+      if (elect_one()) {
         const uint32_t sa = base + (uint32_t)stage * STAGE_BYTES;
         const uint64_t da = make_smem_desc(sa), db = make_smem_desc(sa + R_BYTES);
 #pragma unroll
@@ -106,9 +109,10 @@ __global__ void __launch_bounds__(NTHREADS, 1)
           tc_mma_f8(tmem_d, da + (uint64_t)(k * UMMA_K >> 4), db + (uint64_t)(k * UMMA_K >> 4), IDESC,
                     (kb > 0 || k > 0) ? 1u : 0u);
         tc_commit(bar_empty + 8u * stage);
-        if (++stage == stages) { stage = 0; phase ^= 1u; }
+        if (kb == num_kb - 1) tc_commit(bar_tmem);
       }
-      tc_commit(bar_tmem);
+      __syncwarp();
+      if (++stage == stages) { stage = 0; phase ^= 1u; }
     }
   } else {
     const int wq = warp & 3;
