@@ -49,9 +49,11 @@ def parse():
     ap.add_argument("--profile-step", action="store_true",
                     help="bracket ONE eager decode step with cudaProfilerStart/Stop and exit "
                          "(for `ncu --profile-from-start off`; prints no bench line)")
-    ap.add_argument("--comm", default="auto", choices=["auto", "nccl", "nvlink", "fused"],
-                    help="TP collective (N>1): NCCL all-reduce, own NVLink all-reduce, or the fused "
-                         "reduce-scatter+add+RMSNorm+FP8-quant+all-gather kernel")
+    ap.add_argument("--comm", default="auto", choices=["auto", "nccl", "nvlink", "nvls", "fused"],
+                    help="TP collective (N>1): NCCL all-reduce, own NVLink peer-pull all-reduce, own NVSwitch multimem "
+                         "all-reduce, or the fused reduce-scatter+add+RMSNorm+FP8-quant+all-gather kernel (in-switch "
+                         "reduction when a multicast mapping exists)")
+    ap.add_argument("--no-multicast", action="store_true", help="never use the NVSwitch multicast mapping")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-tp-check", action="store_true",
                     help="skip the multi-GPU correctness self-check that runs before the timed region at N>1")
@@ -326,6 +328,44 @@ def tp_self_check(rank, world, dev, group):
                     cases += 1
     res["allreduce"] = "bit-exact"
     res["allreduce_cases"] = cases
+    res["multicast"] = ar.multicast_note
+    if ar.multicast:
+        # (1b) NVSwitch in-network reduction (multimem.ld_reduce / multimem.st): the switch's accumulation order is
+        # not the rank order, so equality is within one rounding of the output dtype; with the output in the
+        # symmetric heap the switch broadcasts ONE result: bit-identical on every rank
+        cases = 0
+        for dtype, tol in ((torch.bfloat16, 2 ** -7), (torch.float16, 2 ** -10), (torch.float32, 2 ** -20)):
+            for numel in (4096, 256 * 4096, 1024 * 1024 + 8):
+                for zero_copy in (False, True):
+                    for out_in_heap in (False, True):
+                        seed += 1
+                        used = ar._heap_used
+                        x = rank_input(numel, dtype, seed)
+                        if zero_copy:
+                            buf = ar.alloc(numel, dtype)
+                            buf.copy_(x)
+                            x = buf
+                        out = ar.alloc(numel, dtype) if out_in_heap else torch.empty(numel, dtype=dtype, device=dev)
+                        exp = exact_sum(x)
+                        torch.cuda.synchronize(dev)
+                        dist.barrier(group=group)
+                        keep_sms_busy()
+                        ar.all_reduce(x, out=out, algo=3)
+                        torch.cuda.synchronize(dev)
+                        if not torch.allclose(out.float(), exp.float(), rtol=tol, atol=tol):
+                            raise AssertionError(f"tp_check: multimem all_reduce mismatch {dtype} n={numel} "
+                                                 f"zero_copy={zero_copy} out_in_heap={out_in_heap} rank={rank}")
+                        if out_in_heap:
+                            mine = out.view(torch.uint8).to(torch.int64).sum().reshape(1)
+                            alls = [torch.empty_like(mine) for _ in range(world)]
+                            dist.all_gather(alls, mine, group=group)
+                            if any(int(a_) != int(mine) for a_ in alls):
+                                raise AssertionError("tp_check: multimem all_reduce result differs between ranks")
+                        dist.barrier(group=group)
+                        ar._heap_used = used
+                        cases += 1
+        res["multimem_allreduce"] = "within one output rounding of the exact sum; identical on all ranks"
+        res["multimem_cases"] = cases
     if world in (2, 4, 8):
         cases = 0
         for dtype in (torch.bfloat16, torch.float16):
@@ -362,13 +402,24 @@ def tp_self_check(rank, world, dev, group):
                         ar.fused_add_rms_norm(out, x, shard, w, 1e-5, scale)
                         torch.cuda.synchronize(dev)
                         dist.barrier(group=group)
-                        if not torch.equal(out.view(torch.uint8), out_ref.view(torch.uint8)) or \
-                                not torch.equal(shard[: hi - lo], res_ref[lo:hi]):
+                        if ar.multicast:
+                            # in-switch sum: the residual stream may differ by one rounding of T, the FP8 codes by
+                            # one step on the few elements that sit on a rounding boundary
+                            o1 = out.view(torch.float8_e4m3fn).float() if quant else out.float()
+                            o2 = out_ref.float()
+                            bad = ((o1 - o2).abs() > (0.13 * o2.abs() + 1e-2 if quant else 2 ** -6 * o2.abs() + 1e-3))
+                            ok = float(bad.float().mean()) < 1e-3 and torch.allclose(
+                                shard[: hi - lo].float(), res_ref[lo:hi].float(), rtol=2 ** -7, atol=2 ** -7)
+                        else:
+                            ok = torch.equal(out.view(torch.uint8), out_ref.view(torch.uint8)) and \
+                                torch.equal(shard[: hi - lo], res_ref[lo:hi])
+                        if not ok:
                             raise AssertionError(f"tp_check: fused all-reduce+norm mismatch {dtype} {(M, H)} "
-                                                 f"quant={quant} staged={staged} rank={rank}")
+                                                 f"quant={quant} staged={staged} rank={rank} multicast={ar.multicast}")
                         ar._heap_used = used
                         cases += 1
-        res["fused_allreduce_rmsnorm"] = "bit-exact"
+        res["fused_allreduce_rmsnorm"] = ("in-switch reduction: within one rounding of the unfused pair"
+                                          if ar.multicast else "bit-exact")
         res["fused_cases"] = cases
     # ---- (2b) decode-context-parallel merge (one NVLink kernel) vs all_gather + the definition in torch fp32
     cases = 0
@@ -404,8 +455,39 @@ def tp_self_check(rank, world, dev, group):
             cases += 1
     res["dcp_lse_merge"] = "within output rounding of the definition"
     res["dcp_cases"] = cases
+    have_mc = ar.multicast
     torch.cuda.synchronize(dev)
     ar.close()
+    if have_mc and world in (2, 4, 8):
+        # the peer-pull data plane (no multicast) must still be bit-exact: the fused kernel against the unfused pair
+        ar = B200AllReduce(group, dev, max_size=8 << 20, heap_size=32 << 20, multicast=False)
+        for (M, H) in ((256, 4096), (33, 2048)):
+            seed += 1
+            x = ar.alloc((M, H), torch.bfloat16)
+            x.copy_(rank_input(M * H, torch.bfloat16, seed).view(M, H))
+            g = torch.Generator(device=dev).manual_seed(seed)
+            res_full = (torch.rand(M, H, device=dev, generator=g) * 2 - 1).to(torch.bfloat16)
+            w = (torch.rand(H, device=dev, generator=g) + 0.5).to(torch.bfloat16)
+            scale = torch.tensor([0.02], device=dev)
+            summed = exact_sum(x)
+            res_ref = res_full.clone()
+            out_ref = torch.empty(M, H, dtype=torch.float8_e4m3fn, device=dev)
+            ops.fused_add_rms_norm_static_fp8_quant(out_ref, summed, res_ref, w, scale, 1e-5)
+            lo, hi = ar.rows_of_rank(M)
+            shard = torch.zeros((M + world - 1) // world, H, dtype=torch.bfloat16, device=dev)
+            shard[: hi - lo] = res_full[lo:hi]
+            out = ar.alloc((M, H), torch.float8_e4m3fn)
+            torch.cuda.synchronize(dev)
+            dist.barrier(group=group)
+            ar.fused_add_rms_norm(out, x, shard, w, 1e-5, scale)
+            torch.cuda.synchronize(dev)
+            dist.barrier(group=group)
+            if not torch.equal(out.view(torch.uint8), out_ref.view(torch.uint8)) or \
+                    not torch.equal(shard[: hi - lo], res_ref[lo:hi]):
+                raise AssertionError(f"tp_check: peer-pull fused all-reduce+norm not bit-exact {(M, H)} rank={rank}")
+        res["fused_allreduce_rmsnorm_peer_pull"] = "bit-exact"
+        torch.cuda.synchronize(dev)
+        ar.close()
     del busy_a
 
     # ---- (3) tiny model, TP=world vs TP=1
@@ -457,14 +539,19 @@ def tp_self_check(rank, world, dev, group):
     for i in range(2):
         dist.broadcast(forced[i], 0, group=group)
     forced = [f.cpu() for f in forced]
-    comms = ["nccl", "nvlink"] + (["fused"] if world in (2, 4, 8) else [])
+    # (comm, multicast): the peer-pull data plane (multicast False) and, where the box has it, the NVLS one
+    cfgs = [("nccl", None), ("nvlink", False)] + ([("fused", False)] if world in (2, 4, 8) else [])
+    if have_mc:
+        cfgs += [("nvls", None)] + ([("fused", None)] if world in (2, 4, 8) else [])
+    comms = [c_ + ("+multimem" if (m_ is None and c_ != "nccl") else "") for c_, m_ in cfgs]
     near_ties, identical, total, worst_rel = 0, 0, 0, 0.0
     logits_by_comm = {}
-    for comm in comms:
+    for (comm, mcast), label in zip(cfgs, comms):
         mN = decoder.DecoderModel(shape, S, ctx, bs, dev, tp_rank=rank, tp_size=world, tp_group=group,
-                                  comm=comm, num_blocks=nb)
+                                  comm=comm, num_blocks=nb, multicast=mcast)
         t, lg = run(mN, forced)      # teacher-forced with the TP=1 tokens so step 2 sees the same context
-        logits_by_comm[comm] = lg
+        logits_by_comm[label] = lg
+        comm = label
         if mN.ar is not None:
             torch.cuda.synchronize(dev)
             mN.ar.close()
@@ -493,7 +580,7 @@ def tp_self_check(rank, world, dev, group):
                     near_ties += 1
     # the fused reduce-scatter+norm+quant+all-gather kernel is arithmetically identical to all-reduce -> norm+quant
     # with the rank-order NVLink all-reduce: the two decoders must produce the same logits bit for bit
-    if "fused" in logits_by_comm and not torch.equal(logits_by_comm["fused"], logits_by_comm["nvlink"]):
+    if "fused" in logits_by_comm and not torch.equal(logits_by_comm["fused"], logits_by_comm["nvlink"]):  # peer-pull
         raise AssertionError(f"tp_check: tiny model TP={world}: comm=fused and comm=nvlink logits are not bit-identical")
     if world == 2 and not torch.equal(logits_by_comm["nccl"], logits_by_comm["nvlink"]):
         raise AssertionError("tp_check: tiny model TP=2: NCCL and NVLink all-reduce decoders differ (a+b is order-free)")
@@ -502,7 +589,7 @@ def tp_self_check(rank, world, dev, group):
     res["tiny_tokens"] = "match"
     res["tiny_model"] = (f"{shape.name}, {S} seqs x 2 steps x comm {'/'.join(comms)}: {identical} of {total} greedy tokens "
                          f"identical to TP=1, {near_ties} differ inside the measured logit deviation (near-ties); "
-                         f"logits vs TP=1 rel err <= {worst_rel:.2e}; fused == nvlink logits bit-identical")
+                         f"logits vs TP=1 rel err <= {worst_rel:.2e}; peer-pull fused == nvlink logits bit-identical")
     return res
 
 
@@ -542,7 +629,7 @@ def main():
         a.comm = "nvlink"   # MoE layers (expert parallel): the all-reduce follows fused_experts, no norm fusion
     S, ctx = a.batch, a.ctx
     model = decoder.DecoderModel(shape, S, ctx, BLOCK, dev, tp_rank=rank, tp_size=world, tp_group=group,
-                                 comm=a.comm, quant=a.quant)
+                                 comm=a.comm, quant=a.quant, multicast=False if a.no_multicast else None)
     D = shape.head_size
     # ---- synthetic state: KV caches full of random (non-NaN) fp8 codes; block table = random
     # permutation without repetition
@@ -662,7 +749,8 @@ def main():
                                 "context length not given there)" % (shape.experts, shape.topk)
                                 if shape.experts > 0 else
                                 f"({baseline_config_tag(shape, a.quant)})"),
-                   "parallelism": (f"tp{world} attention + ep{world} experts" if shape.experts > 0 else f"tp{world}"), "tp_collective": (a.comm if world > 1 else None), "weights": "random init (dummy), per-tensor FP8 scales",
+                   "parallelism": (f"tp{world} attention + ep{world} experts" if shape.experts > 0 else f"tp{world}"), "tp_collective": (a.comm if world > 1 else None),
+                   "nvswitch_multicast": (bool(model.ar.multicast) if model.ar is not None else None), "weights": "random init (dummy), per-tensor FP8 scales",
                    "cuda_graph": not a.no_graph,
                    "l2": "inputs larger than L2 (KV cache %.1f GB + weights per GPU)" %
                          (sum(L["kv"].numel() for L in model.layers) / 1e9),

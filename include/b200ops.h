@@ -526,9 +526,18 @@ B200_API int b200_allreduce_init(void** ctx_out, int rank, int world, void* cons
 B200_API int b200_allreduce_heap(void* ctx, size_t* offset, size_t* bytes);
 B200_API int b200_allreduce_register(void* ctx, void* const* buffer_ptrs, size_t bytes);
 B200_API int b200_allreduce_destroy(void* ctx);
+/* NVSwitch multicast (NVLS) mapping of the symmetric buffer passed to b200_allreduce_init: one virtual address bound
+ * to the same allocation on every rank (cuMulticastBindMem; torch symmetric memory's multicast_ptr). With it
+ * b200_allreduce_run algo 3 and b200_allreduce_fused_add_rms_norm reduce INSIDE the switch (multimem.ld_reduce,
+ * fp32 accumulation) and broadcast with multimem.st - what the reference reaches through
+ * vllm/distributed/device_communicators/symm_mem.py:127-150 (multimem_all_reduce_). NULL = peer loads / stores. */
+B200_API int b200_allreduce_set_multicast(void* ctx, void* multicast_ptr);
+B200_API int b200_allreduce_has_multicast(void* ctx);
 /* out = sum over ranks of in (fp32 accumulate in rank order: bit-identical on all ranks), out-of-place
  * (in == out allowed only for staged inputs). numel * sizeof(dtype) % 16 == 0.
- * algo: 0 auto (reference thresholds), 1 one-shot, 2 two-shot. */
+ * algo: 0 auto (reference thresholds), 1 one-shot, 2 two-shot, 3 NVSwitch multimem (needs b200_allreduce_set_multicast
+ * and an input inside the first symmetric buffer; the switch's accumulation order is not the rank order: equal within
+ * one fp32 rounding, identical on all ranks when out also lives in the symmetric buffer); +4 skips the end barrier. */
 B200_API int b200_allreduce_run(void* ctx, const void* in, void* out, int64_t numel, int dtype, int algo,
                                 b200_stream_t stream);
 /* One kernel: z = T(T(sum_r in_r) + residual); residual = z; y = rmsnorm(z) * weight;

@@ -228,6 +228,8 @@ SIGNATURES = {
     "b200_allreduce_heap": (c_int, [c_void_p, C.POINTER(c_size_t), C.POINTER(c_size_t)]),
     "b200_allreduce_register": (c_int, [c_void_p, C.POINTER(c_void_p), c_size_t]),
     "b200_allreduce_destroy": (c_int, [c_void_p]),
+    "b200_allreduce_set_multicast": (c_int, [c_void_p, c_void_p]),
+    "b200_allreduce_has_multicast": (c_int, [c_void_p]),
     "b200_allreduce_run": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),
     "b200_allreduce_fused_add_rms_norm": (
         c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_int64, c_int, c_int,

@@ -9,7 +9,12 @@ the (CPU / NCCL) process group at construction, ``should_custom_ar`` / ``custom_
   rank, SPMD allocation order), which peers then reduce in place - no staging copy and no graph-buffer
   registration step (the reference's ``register_graph_buffers``);
 * ``fused_add_rms_norm(...)`` = reduce-scatter + residual add + RMSNorm (+ static FP8 quant) +
-  all-gather in one kernel (the reference's fuse_allreduce_rms target, docs/design/fusions.md:23).
+  all-gather in one kernel (the reference's fuse_allreduce_rms target, docs/design/fusions.md:23);
+* NVSwitch in-network reduction (NVLS): when torch symmetric memory can give the buffer a multicast mapping
+  (the plumbing the reference uses too: device_communicators/symm_mem.py:38-150), ``all_reduce(algo=3)`` and the
+  fused kernel reduce with ``multimem.ld_reduce`` inside the switch and broadcast with ``multimem.st`` - our own
+  kernels, torch only allocates and exchanges the handles. Without it the buffer is cudaMalloc + CUDA IPC and
+  the kernels use peer loads / stores.
 
 There is no fallback inside this class: the caller decides between this and NCCL with
 ``should_custom_ar`` exactly like ``CudaCommunicator.all_reduce`` (cuda_communicator.py:275-341).
@@ -17,6 +22,7 @@ There is no fallback inside this class: the caller decides between this and NCCL
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 import torch.distributed as dist
@@ -37,11 +43,17 @@ class _DevMem:
 
 class B200AllReduce:
     def __init__(self, group: dist.ProcessGroup | None, device: torch.device | int | str,
-                 max_size: int = 8 * 1024 * 1024, heap_size: int = 64 * 1024 * 1024):
-        """group: process group used ONLY to exchange the 64-byte IPC handles (any backend).
+                 max_size: int = 8 * 1024 * 1024, heap_size: int = 64 * 1024 * 1024,
+                 multicast: bool | None = None):
+        """group: process group used ONLY to exchange the memory handles (any backend for the IPC path).
         max_size: largest message (bytes) a single all_reduce may carry (staging + scratch size).
-        heap_size: bytes of symmetric heap for alloc()."""
+        heap_size: bytes of symmetric heap for alloc().
+        multicast: None = use an NVSwitch multicast mapping when torch symmetric memory provides one
+        (B200_AR_SYMM=0 disables), False = never (cudaMalloc + CUDA IPC), True = require it."""
         self.disabled = True
+        self.multicast = False
+        self.multicast_note = "not requested"
+        self._symm = None
         self._ctx = None
         self._own = None
         self._peers: list[int] = []
@@ -63,32 +75,76 @@ class B200AllReduce:
         meta = lib.b200_allreduce_meta_bytes()
         total = meta + 2 * self.max_size + (heap_size + 1023) // 1024 * 1024
         with torch.cuda.device(self.device):
-            own = C.c_void_p()
-            handle = (C.c_ubyte * 64)()
-            _lib.check(lib.b200_ipc_alloc(total, C.byref(own), handle), "b200_ipc_alloc")
-            self._own = own.value
-            handles: list[bytes | None] = [None] * self.world_size
-            dist.all_gather_object(handles, bytes(handle), group=group)
             ptrs = (C.c_void_p * self.world_size)()
-            for r, h in enumerate(handles):
-                if r == self.rank:
-                    ptrs[r] = self._own
-                else:
-                    p = C.c_void_p()
-                    buf = (C.c_ubyte * 64).from_buffer_copy(h)
-                    _lib.check(lib.b200_ipc_open(buf, C.byref(p)), "b200_ipc_open")
-                    ptrs[r] = p.value
-                    self._peers.append(p.value)
+            mc_ptr = 0
+            want_symm = multicast is not False and os.environ.get("B200_AR_SYMM", "1") == "1"
+            if want_symm:
+                mc_ptr = self._alloc_symmetric(group, total, ptrs)
+            if multicast is True and not mc_ptr:
+                raise RuntimeError(f"B200AllReduce: no NVSwitch multicast mapping ({self.multicast_note})")
+            if self._symm is None:
+                own = C.c_void_p()
+                handle = (C.c_ubyte * 64)()
+                _lib.check(lib.b200_ipc_alloc(total, C.byref(own), handle), "b200_ipc_alloc")
+                self._own = own.value
+                handles: list[bytes | None] = [None] * self.world_size
+                dist.all_gather_object(handles, bytes(handle), group=group)
+                for r, h in enumerate(handles):
+                    if r == self.rank:
+                        ptrs[r] = self._own
+                    else:
+                        p = C.c_void_p()
+                        buf = (C.c_ubyte * 64).from_buffer_copy(h)
+                        _lib.check(lib.b200_ipc_open(buf, C.byref(p)), "b200_ipc_open")
+                        ptrs[r] = p.value
+                        self._peers.append(p.value)
             ctx = C.c_void_p()
             _lib.check(lib.b200_allreduce_init(C.byref(ctx), self.rank, self.world_size, ptrs, total,
                                                self.max_size), "b200_allreduce_init")
             self._ctx = ctx.value
+            if mc_ptr:
+                _lib.check(lib.b200_allreduce_set_multicast(self._ctx, mc_ptr), "b200_allreduce_set_multicast")
+                self.multicast = True
             off, nbytes = C.c_size_t(), C.c_size_t()
             _lib.check(lib.b200_allreduce_heap(self._ctx, C.byref(off), C.byref(nbytes)), "b200_allreduce_heap")
             self._heap = torch.as_tensor(_DevMem(self._own + off.value, nbytes.value), device=self.device)
             self._heap_used = 0
         dist.barrier(group=group)  # every rank has zeroed its signals and opened its peers
         self.disabled = False
+
+    def _alloc_symmetric(self, group, total: int, ptrs) -> int:
+        """Allocate the symmetric buffer through torch symmetric memory (cuMemCreate + handle exchange + multicast
+        bind: plumbing) and fill `ptrs` with every rank's mapping. Returns the multicast address or 0; on any
+        failure leaves self._symm None so that the caller takes the cudaMalloc + CUDA-IPC path."""
+        try:
+            import warnings
+            import torch.distributed._symmetric_memory as symm
+            pg = group if group is not None else dist.group.WORLD
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
+                if hasattr(symm, "enable_symm_mem_for_group"):
+                    try:
+                        symm.enable_symm_mem_for_group(pg.group_name)
+                    except Exception:
+                        pass
+                t = symm.empty(total, dtype=torch.uint8, device=self.device)
+                hdl = symm.rendezvous(t, pg)
+            t.zero_()
+            torch.cuda.synchronize(self.device)
+            bufs = list(hdl.buffer_ptrs)
+            if len(bufs) != self.world_size or any(int(b) % 1024 for b in bufs):
+                raise RuntimeError("unexpected buffer_ptrs from symmetric memory")
+            for r in range(self.world_size):
+                ptrs[r] = int(bufs[r])
+            self._own = int(bufs[self.rank])
+            self._symm = (t, hdl)
+            mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+            self.multicast_note = "torch symmetric memory, multicast_ptr %s" % ("mapped" if mc else "unavailable")
+            return mc if mc % 1024 == 0 else 0
+        except Exception as e:  # noqa: BLE001
+            self._symm = None
+            self.multicast_note = f"torch symmetric memory unavailable: {e!r}"[:200]
+            return 0
 
     # ---- symmetric heap ---------------------------------------------------------------------
     def alloc(self, shape, dtype: torch.dtype) -> torch.Tensor:
@@ -117,7 +173,9 @@ class B200AllReduce:
 
     def all_reduce(self, inp: torch.Tensor, *, out: torch.Tensor | None = None, algo: int = 0,
                    skip_end_barrier: bool = False) -> torch.Tensor:
-        """out-of-place sum over the group; algo 0 = auto, 1 = one-shot, 2 = two-shot.
+        """out-of-place sum over the group; algo 0 = auto, 1 = one-shot, 2 = two-shot, 3 = NVSwitch multimem
+        (self.multicast must be True; `out` allocated with alloc() is broadcast by the switch and is then
+        bit-identical on every rank).
         skip_end_barrier: the caller promises not to overwrite `inp` before the next collective of this
         object has started on every rank (alternating input buffers) - saves one NVLink rendezvous."""
         if skip_end_barrier:
@@ -223,7 +281,9 @@ class B200AllReduce:
         for p in self._peers:
             lib.b200_ipc_close(p)
         self._heap = None
-        lib.b200_ipc_free(self._own)
+        if self._symm is None:
+            lib.b200_ipc_free(self._own)
+        self._symm = None   # torch frees the symmetric allocation with the last reference
         self._ctx, self._peers, self._own, self.disabled = None, [], None, True
 
     def __del__(self):

@@ -71,7 +71,7 @@ class DecoderModel:
     def __init__(self, shape: ModelShape, max_seqs: int, max_ctx: int, block_size: int = 16,
                  device: str | torch.device = "cuda:0", tp_rank: int = 0, tp_size: int = 1,
                  tp_group=None, seed: int = 1234, kv_fp8: bool = True, num_blocks: int | None = None,
-                 comm: str = "nccl", quant: str = "fp8"):
+                 comm: str = "nccl", quant: str = "fp8", multicast: bool | None = None):
         self.shape = s = shape
         assert quant in ("fp8", "nvfp4")
         self.quant = quant   # "nvfp4": W4A4 linears (scaled_fp4_quant -> cutlass_scaled_fp4_mm), FP8 KV cache
@@ -92,8 +92,9 @@ class DecoderModel:
         self.num_blocks = num_blocks or max_seqs * self.blocks_per_seq + 8
         self.kv_fp8 = kv_fp8
         self.launches_per_step = 0
-        assert comm in ("nccl", "nvlink", "fused")
+        assert comm in ("nccl", "nvlink", "nvls", "fused")
         self.comm = comm if tp_size > 1 else "nccl"
+        self.multicast = multicast
         self.ar = None
         g = torch.Generator(device=self.dev).manual_seed(seed)
 
@@ -188,7 +189,12 @@ class DecoderModel:
         if self.comm != "nccl":
             from .all_reduce import B200AllReduce
             self.ar = B200AllReduce(tp_group, self.dev, max_size=max(8 << 20, S * H * 2),
-                                    heap_size=4 * S * H * 2 + (1 << 20))
+                                    heap_size=6 * S * H * 2 + (1 << 20), multicast=self.multicast)
+            if self.comm == "nvls":
+                if not self.ar.multicast:
+                    raise RuntimeError(f"comm=nvls needs an NVSwitch multicast mapping: {self.ar.multicast_note}")
+                # the reduced activations are broadcast by the switch into every rank's copy of this buffer
+                self.proj = self.ar.alloc((S, H), torch.bfloat16)
             # alternating GEMM-output buffers in the symmetric heap: peers read them in place, and the
             # start barrier of the next collective doubles as the end barrier of this one
             self.proj_in = [self.ar.alloc((S, H), torch.bfloat16), self.ar.alloc((S, H), torch.bfloat16)]
@@ -301,6 +307,8 @@ class DecoderModel:
         if self.comm == "nccl":
             torch.distributed.all_reduce(t, group=self.tp_group)
             return t
+        if self.comm == "nvls":
+            return self.ar.all_reduce(t, out=self.proj, algo=3)
         return self.ar.all_reduce(t, out=self.proj, algo=1, skip_end_barrier=True)
 
     # ---- one decode step over the persistent device buffers

@@ -23,6 +23,7 @@
 // graph replays without any host-side state.
 #include "common.cuh"
 
+#include <cstdlib>
 #include <cstring>
 
 namespace b200 {
@@ -53,13 +54,52 @@ struct Context {
   size_t heap_bytes;      // data part of region 0 (after the signals)
   size_t staging_off;     // byte offset (from region 0 base) of the staging area = SIGNAL_BYTES
   size_t staging_bytes;   // the staging area covers the first half of the heap by convention
+  uint8_t* mc_base;       // NVSwitch multicast (NVLS) address of region 0, or null (b200_allreduce_set_multicast)
 };
 
 struct Peers {
   Signal* sig[MAX_RANKS];
   const uint8_t* in[MAX_RANKS];   // input of every rank (already offset)
   uint8_t* tmp[MAX_RANKS];        // scratch of every rank (two-shot result slices)
+  const uint8_t* mc_in;           // multicast address of the input (all ranks' copies at once), or null
 };
+
+// ---- NVSwitch in-network reduction (NVLS): one load from a multicast address returns the SUM over every rank's
+// copy, reduced inside the switch with fp32 accumulation; one store to it lands in every rank's copy. What the
+// reference reaches through symm_mem multimem_all_reduce_ (device_communicators/symm_mem.py:127-150).
+template <typename T> struct McRed;
+template <> struct McRed<float> {
+  static __device__ __forceinline__ uint4 ld(const void* p) {
+    uint4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+    return r;
+  }
+};
+template <> struct McRed<__half> {
+  static __device__ __forceinline__ uint4 ld(const void* p) {
+    uint4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+    return r;
+  }
+};
+template <> struct McRed<__nv_bfloat16> {
+  static __device__ __forceinline__ uint4 ld(const void* p) {
+    uint4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+    return r;
+  }
+};
+__device__ __forceinline__ void mc_st_v4(void* p, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(__uint_as_float(v.x)),
+               "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w)) : "memory");
+}
+__device__ __forceinline__ void mc_st_v2(void* p, const uint2& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1,%2};" ::"l"(p), "f"(__uint_as_float(v.x)),
+               "f"(__uint_as_float(v.y)) : "memory");
+}
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -303,6 +343,34 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   // the scratch slices are re-written by the next two-shot call: always rendezvous here
   (void)skip_end;
   barrier<N, false>(pe, rank, epoch);
+  if (threadIdx.x == 0) pe.sig[rank]->epoch[blockIdx.x] = epoch;
+}
+
+// NVLS all-reduce. mc_out != null (output inside the symmetric buffer): two-shot in the switch - rank r reduces
+// slice r with multimem.ld_reduce and broadcasts it with multimem.st, so every rank ends with the SAME bits and
+// receives the message once ((N-1)/N * bytes through its NVLink instead of (N-1) * bytes for the peer-pull
+// one-shot). mc_out == null: every rank reduces the whole message into its private output (still one message of
+// receive traffic). The switch's accumulation order is not the rank order of the peer-pull kernels: results agree
+// within the rounding of one fp32 accumulation (bit-exact for exactly representable sums).
+template <typename T, int N>
+__global__ void __launch_bounds__(NTHREADS, 1)
+    allreduce_multimem_kernel(Peers pe, uint8_t* __restrict__ out, uint8_t* mc_out, const uint8_t* stage_src, int rank,
+                              int64_t packs) {
+  uint32_t epoch = pe.sig[rank]->epoch[blockIdx.x];
+  const int64_t part = (packs + N - 1) / N;
+  stage_input<N>(pe, rank, stage_src, packs, mc_out ? part : packs);
+  if (stage_src) barrier<N, true>(pe, rank, epoch);
+  else barrier<N, false>(pe, rank, epoch);
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  if (mc_out) {
+    const int64_t lo = rank * part, hi = min(packs, lo + part);
+    for (int64_t i = lo + tid; i < hi; i += stride) mc_st_v4(mc_out + i * 16, McRed<T>::ld(pe.mc_in + i * 16));
+    barrier<N, true>(pe, rank, epoch);   // every rank's broadcast slice has landed everywhere
+  } else {
+    for (int64_t i = tid; i < packs; i += stride) reinterpret_cast<uint4*>(out)[i] = McRed<T>::ld(pe.mc_in + i * 16);
+    barrier<N, false>(pe, rank, epoch);  // inputs may be overwritten only after everyone has reduced them
+  }
   if (threadIdx.x == 0) pe.sig[rank]->epoch[blockIdx.x] = epoch;
 }
 

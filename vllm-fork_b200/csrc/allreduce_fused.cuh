@@ -19,6 +19,7 @@ namespace b200 {
 namespace ar {
 
 struct FusedParams {
+  uint8_t* mc_out;           // MC kernels: multicast address of the output buffer (one store reaches every rank)
   uint8_t* out[MAX_RANKS];   // output buffer of every rank ([M, hidden] e4m3 or T), symmetric heap
   void* residual;            // local [Mp, hidden] T: rows of this rank only (nullable: no add)
   const void* weight;        // [hidden] T
@@ -27,7 +28,11 @@ struct FusedParams {
   int M, hidden, rows_per_rank;
 };
 
-template <typename T, int N, bool QUANT, int R>
+// MC = true: the reduce leg is one multimem.ld_reduce per 16 bytes (sum over all ranks inside the NVSwitch, fp32
+// accumulation, rounded to T - the same rounding point as the peer-pull sum) and the gather leg one multimem.st
+// per finished 8 / 16 bytes instead of N posted stores. Per-rank NVLink traffic for [M, hidden]: M/N rows in
+// (once, not N-1 times) and M/N FP8 rows out (once, not N-1 times).
+template <typename T, int N, bool QUANT, int R, bool MC = false>
 __global__ void __launch_bounds__(256, 1)
     allreduce_fused_norm_kernel(Peers pe, FusedParams fp, const uint8_t* stage_src, int rank) {
   constexpr int NP = 16 / sizeof(T);
@@ -47,8 +52,16 @@ __global__ void __launch_bounds__(256, 1)
     float ss = 0.f;
     // issue every peer load of the row before the first add when the registers allow it: one NVLink
     // round trip per row instead of R
-    constexpr bool BATCH = R * N <= 16;
-    uint4 pv[BATCH ? R : 1][N];
+    constexpr bool BATCH = !MC && R * N <= 16;
+    uint4 pv[BATCH ? R : 1][MC ? 1 : N];
+    uint4 mv[MC ? R : 1];
+    if constexpr (MC) {   // all in-switch reductions of the row in flight before the first use
+#pragma unroll
+      for (int i = 0; i < R; i++) {
+        const int v = threadIdx.x + i * 256;
+        if (v < nv) mv[i] = McRed<T>::ld(pe.mc_in + ((int64_t)row * nv + v) * 16);
+      }
+    }
     if constexpr (BATCH) {
 #pragma unroll
       for (int i = 0; i < R; i++) {
@@ -63,8 +76,10 @@ __global__ void __launch_bounds__(256, 1)
     for (int i = 0; i < R; i++) {
       const int v = threadIdx.x + i * 256;
       if (v < nv) {
-        uint4 x;   // T(sum over ranks), rank order 0..N-1
-        if constexpr (BATCH) {
+        uint4 x;   // T(sum over ranks), rank order 0..N-1 (MC: the switch's order)
+        if constexpr (MC) {
+          x = mv[i];
+        } else if constexpr (BATCH) {
           float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
           for (int r = 0; r < N; r++) Pack<T>::add(a, pv[i][r]);
@@ -109,10 +124,16 @@ __global__ void __launch_bounds__(256, 1)
             o[j] = f32x2_to_e4m3x2(a, b);
           }
           const int64_t off = (int64_t)row * fp.hidden + (int64_t)v * NP;  // bytes (1 B / element)
+          if constexpr (MC) {
+            if constexpr (NP == 8) {
+              mc_st_v2(fp.mc_out + off, *reinterpret_cast<const uint2*>(o));
+            }
+          } else {
 #pragma unroll
-          for (int r = 0; r < N; r++) {
-            uint8_t* dst = fp.out[(rank + r) % N] + off;
-            *reinterpret_cast<uint2*>(dst) = *reinterpret_cast<const uint2*>(o);
+            for (int r = 0; r < N; r++) {
+              uint8_t* dst = fp.out[(rank + r) % N] + off;
+              *reinterpret_cast<uint2*>(dst) = *reinterpret_cast<const uint2*>(o);
+            }
           }
         } else {
           uint4 rr;
@@ -121,8 +142,12 @@ __global__ void __launch_bounds__(256, 1)
           for (int j = 0; j < NP; j++)
             re[j] = Cvt<T>::from_f32(Cvt<T>::to_f32(xe[j]) * s * Cvt<T>::to_f32(we[j]));
           const int64_t off = ((int64_t)row * fp.hidden + (int64_t)v * NP) * sizeof(T);
+          if constexpr (MC) {
+            mc_st_v4(fp.mc_out + off, rr);
+          } else {
 #pragma unroll
-          for (int r = 0; r < N; r++) *reinterpret_cast<uint4*>(fp.out[(rank + r) % N] + off) = rr;
+            for (int r = 0; r < N; r++) *reinterpret_cast<uint4*>(fp.out[(rank + r) % N] + off) = rr;
+          }
         }
       }
     }

@@ -28,6 +28,7 @@ static int resolve_input(const Context* c, const void* in, size_t bytes, Peers* 
     pe->tmp[r] = c->regions[0].base[r] + c->staging_off + c->staging_bytes;  // scratch follows staging
   }
   size_t off;
+  pe->mc_in = nullptr;
   const int reg = find_region(c, in, bytes, &off);
   if (reg >= 0) {
     // region 0: the user heap starts after signals + staging + scratch; staging/scratch themselves are
@@ -37,6 +38,7 @@ static int resolve_input(const Context* c, const void* in, size_t bytes, Peers* 
       return B200_ERR_INVALID;
     }
     for (int r = 0; r < c->world; r++) pe->in[r] = c->regions[reg].base[r] + off;
+    if (reg == 0 && c->mc_base) pe->mc_in = c->mc_base + off;
     *stage_src = nullptr;
   } else {
     if (bytes > c->staging_bytes) {
@@ -45,6 +47,7 @@ static int resolve_input(const Context* c, const void* in, size_t bytes, Peers* 
       return B200_ERR_WORKSPACE;
     }
     for (int r = 0; r < c->world; r++) pe->in[r] = c->regions[0].base[r] + c->staging_off;
+    if (c->mc_base) pe->mc_in = c->mc_base + c->staging_off;
     *stage_src = reinterpret_cast<const uint8_t*>(in);
   }
   return B200_OK;
@@ -82,14 +85,46 @@ static int dispatch_ar(int world, const Peers& pe, void* out, const uint8_t* sta
   }
 }
 
+template <typename T, int N>
+static int launch_mc(const Peers& pe, void* out, uint8_t* mc_out, const uint8_t* stage_src, int rank, int64_t packs,
+                     cudaStream_t stream) {
+  const int64_t mine = mc_out ? (packs + N - 1) / N : packs;
+  int64_t blocks = (mine + NTHREADS - 1) / NTHREADS;    // one 16-byte in-switch reduction per thread where possible
+  const int cap = sm_count() < MAX_BLOCKS ? sm_count() : MAX_BLOCKS;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  allreduce_multimem_kernel<T, N><<<(int)blocks, NTHREADS, 0, stream>>>(pe, (uint8_t*)out, mc_out, stage_src, rank, packs);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+template <typename T>
+static int dispatch_mc(int world, const Peers& pe, void* out, uint8_t* mc_out, const uint8_t* stage_src, int rank,
+                       int64_t packs, cudaStream_t stream) {
+  switch (world) {
+    case 2: return launch_mc<T, 2>(pe, out, mc_out, stage_src, rank, packs, stream);
+    case 4: return launch_mc<T, 4>(pe, out, mc_out, stage_src, rank, packs, stream);
+    case 6: return launch_mc<T, 6>(pe, out, mc_out, stage_src, rank, packs, stream);
+    case 8: return launch_mc<T, 8>(pe, out, mc_out, stage_src, rank, packs, stream);
+    default:
+      set_last_error("custom allreduce only supports num gpus in (2,4,6,8), got %d", world);
+      return B200_ERR_UNSUPPORTED;
+  }
+}
+
 template <typename T, int N, bool QUANT>
 static int launch_fused(const Peers& pe, const FusedParams& fp, const uint8_t* stage_src, int rank,
                         cudaStream_t stream) {
   const int nv = fp.hidden / (16 / (int)sizeof(T));
   int blocks = fp.rows_per_rank < 1 ? 1 : fp.rows_per_rank;
   if (blocks > MAX_BLOCKS) blocks = MAX_BLOCKS;
-#define B200_FUSED(RR) \
-  allreduce_fused_norm_kernel<T, N, QUANT, RR><<<blocks, 256, 0, stream>>>(pe, fp, stage_src, rank)
+#define B200_FUSED(RR)                                                                                   \
+  do {                                                                                                   \
+    if (fp.mc_out && pe.mc_in)                                                                           \
+      allreduce_fused_norm_kernel<T, N, QUANT, RR, true><<<blocks, 256, 0, stream>>>(pe, fp, stage_src, rank); \
+    else                                                                                                 \
+      allreduce_fused_norm_kernel<T, N, QUANT, RR, false><<<blocks, 256, 0, stream>>>(pe, fp, stage_src, rank); \
+  } while (0)
   if (nv <= 256) B200_FUSED(1);
   else if (nv <= 512) B200_FUSED(2);
   else if (nv <= 1024) B200_FUSED(4);
@@ -175,8 +210,24 @@ extern "C" int b200_allreduce_init(void** ctx_out, int rank, int world, void* co
   c->staging_off = SIGNAL_BYTES;
   c->staging_bytes = max_message_bytes;
   c->heap_bytes = buffer_bytes - SIGNAL_BYTES - 2 * max_message_bytes;
+  c->mc_base = nullptr;
   *ctx_out = c;
   return B200_OK;
+}
+
+// NVSwitch multicast (NVLS) address of the symmetric buffer given to b200_allreduce_init: a virtual address bound
+// (cuMulticastBindMem) to the SAME allocation on every rank, e.g. torch symmetric memory's multicast_ptr. With it
+// b200_allreduce_run algo 3 and the fused kernel reduce inside the switch (multimem.ld_reduce / multimem.st).
+// NULL switches back to peer loads / stores.
+extern "C" int b200_allreduce_set_multicast(void* ctx, void* multicast_ptr) {
+  B200_CHECK(ctx, B200_ERR_INVALID, "allreduce_set_multicast: null context");
+  B200_CHECK(((uintptr_t)multicast_ptr & 1023) == 0, B200_ERR_INVALID,
+             "allreduce_set_multicast: the multicast address must be 1024-byte aligned");
+  reinterpret_cast<Context*>(ctx)->mc_base = reinterpret_cast<uint8_t*>(multicast_ptr);
+  return B200_OK;
+}
+extern "C" int b200_allreduce_has_multicast(void* ctx) {
+  return ctx && reinterpret_cast<Context*>(ctx)->mc_base ? 1 : 0;
 }
 
 // byte offset of the user heap inside the symmetric buffer, and its size
@@ -212,7 +263,7 @@ extern "C" int b200_allreduce_destroy(void* ctx) {
 // ---------------------------------------------------------------- collectives
 // algo bit 2 (value 4) = skip the end barrier of the one-shot kernel (caller alternates input buffers).
 // algo (low 2 bits): 0 = auto (thresholds of custom_all_reduce.cuh: one-shot for world 2, < 512 KiB at world 4,
-// < 256 KiB at world 6/8; two-shot above), 1 = one-shot, 2 = two-shot.
+// < 256 KiB at world 6/8; two-shot above), 1 = one-shot, 2 = two-shot, 3 = NVSwitch multimem (in-switch reduction).
 extern "C" int b200_allreduce_run(void* ctx, const void* in, void* out, int64_t numel, int dtype, int algo,
                                   b200_stream_t stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
@@ -236,6 +287,20 @@ extern "C" int b200_allreduce_run(void* ctx, const void* in, void* out, int64_t 
   if (rc) return rc;
   const int skip_end = (algo & 4) ? 1 : 0;
   algo &= 3;
+  const int64_t packs_mc = (int64_t)(bytes / 16);
+  if (algo == 3) {
+    // in-switch reduction; the output is broadcast with multimem.st when it lives in the symmetric buffer too
+    B200_CHECK(c->mc_base && pe.mc_in, B200_ERR_UNSUPPORTED,
+               "all_reduce: algo 3 (NVSwitch multimem) needs a multicast mapping (b200_allreduce_set_multicast) and an "
+               "input inside the first symmetric buffer");
+    size_t off_o;
+    uint8_t* mc_out = nullptr;
+    if (find_region(c, out, bytes, &off_o) == 0 && off_o >= c->staging_off + 2 * c->staging_bytes)
+      mc_out = c->mc_base + off_o;
+    if (dtype == B200_F32) return dispatch_mc<float>(c->world, pe, out, mc_out, stage_src, c->rank, packs_mc, stream);
+    if (dtype == B200_F16) return dispatch_mc<__half>(c->world, pe, out, mc_out, stage_src, c->rank, packs_mc, stream);
+    return dispatch_mc<__nv_bfloat16>(c->world, pe, out, mc_out, stage_src, c->rank, packs_mc, stream);
+  }
   bool two_shot;
   if (algo == 1) two_shot = false;
   else if (algo == 2) two_shot = true;
@@ -277,6 +342,8 @@ extern "C" int b200_allreduce_fused_add_rms_norm(void* ctx, void* out, const voi
              "allreduce_fused_add_rms_norm: out must live in the symmetric heap (it is written by the peers)");
   FusedParams fp;
   for (int r = 0; r < c->world; r++) fp.out[r] = c->regions[reg].base[r] + off;
+  static const int mc_off = [] { const char* e = getenv("B200_AR_MULTIMEM"); return e && atoi(e) == 0; }();
+  fp.mc_out = (reg == 0 && c->mc_base && !mc_off && hidden % (16 / 2) == 0) ? c->mc_base + off : nullptr;
   fp.residual = residual;
   fp.weight = weight;
   fp.scale = scale;

@@ -59,6 +59,7 @@ struct Params {
   int window;
   float scale, softcap;
   uint32_t tile_bytes;   // hc * 16 * RB  (one K or V tile)
+  int kv_pair;           // 1: tmK's box carries the K tile and the V tile of a page (attention_host.cuh get_tmap)
   uint32_t off_merge, off_cum, off_bar;  // smem offsets
 };
 

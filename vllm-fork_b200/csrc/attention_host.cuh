@@ -12,27 +12,31 @@ constexpr int kMaxCtas = 192;  // workspace is sized for at most this many persi
 struct TmapKey {
   const void* base;
   int64_t nb, sb, st, sh;
-  int bs, hkv, hc, D, es;
+  int bs, hkv, hc, D, es, kv_pair;
   bool operator==(const TmapKey& o) const {
     return base == o.base && nb == o.nb && sb == o.sb && st == o.st && sh == o.sh && bs == o.bs &&
-           hkv == o.hkv && hc == o.hc && D == o.D && es == o.es;
+           hkv == o.hkv && hc == o.hc && D == o.D && es == o.es && kv_pair == o.kv_pair;
   }
 };
 struct TmapKeyHash {
   size_t operator()(const TmapKey& k) const {
     size_t h = (size_t)k.base * 1315423911u;
     h ^= (size_t)k.nb * 2654435761u + (size_t)k.sb * 40503u + (size_t)k.st * 7919u +
-         (size_t)k.sh * 104729u + (size_t)(k.bs * 31 + k.hkv * 17 + k.hc * 13 + k.D * 7 + k.es);
+         (size_t)k.sh * 104729u + (size_t)(k.bs * 31 + k.hkv * 17 + k.hc * 13 + k.D * 7 + k.es + k.kv_pair * 3);
     return h;
   }
 };
 static std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> g_tmaps;
 static std::mutex g_tmap_mu;
 
-// 5-D view of a paged K (or V) cache: [inner 128 B][token in block][128-B segment][head][block]
+// 5-D view of a paged K (or V) cache: [inner 128 B][token in block][128-B segment][head][block].
+// kv_pair (K|V packed per token and head, one 128-byte segment per row: the fork's NHD layout with FP8 D = 128):
+// the idle segment dimension becomes the K / V selector (stride = one row), so ONE box brings the K tile and the V
+// tile of a 16-token page: [128 B][token][K, V][head][block] lands as [K tile | V tile] - the same shared-memory
+// image as the two separate loads when the CTA handles one head (hc == 1).
 static int get_tmap(CUtensorMap* out, const void* base, int64_t nb, int64_t sb, int64_t st,
-                    int64_t sh, int bs, int hkv, int hc, int D, int es) {
-  TmapKey key{base, nb, sb, st, sh, bs, hkv, hc, D, es};
+                    int64_t sh, int bs, int hkv, int hc, int D, int es, int kv_pair = 0) {
+  TmapKey key{base, nb, sb, st, sh, bs, hkv, hc, D, es, kv_pair};
   std::lock_guard<std::mutex> lk(g_tmap_mu);
   auto it = g_tmaps.find(key);
   if (it != g_tmaps.end()) {
@@ -45,6 +49,11 @@ static int get_tmap(CUtensorMap* out, const void* base, int64_t nb, int64_t sb, 
   uint64_t dims[5] = {(uint64_t)(IB / es), (uint64_t)bs, (uint64_t)nseg, (uint64_t)hkv, (uint64_t)nb};
   uint64_t strides[4] = {(uint64_t)(st * es), (uint64_t)IB, (uint64_t)(sh * es), (uint64_t)(sb * es)};
   uint32_t box[5] = {(uint32_t)(IB / es), 16u, (uint32_t)nseg, (uint32_t)hc, 1u};
+  if (kv_pair) {   // nseg == 1: dimension 2 selects K (0) or V (1), one row = RB bytes apart
+    dims[2] = 2;
+    strides[1] = (uint64_t)RB;
+    box[2] = 2;
+  }
   CUtensorMap tm;
   int rc = encode_tensor_map(&tm, es == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_UINT16,
                              5, base, dims, strides, box,
@@ -187,8 +196,14 @@ extern "C" int b200_paged_attention_decode(const b200_paged_attn_args* a, b200_s
              "paged_attention_decode: workspace must be 256-byte aligned");
 
   CUtensorMap tmK, tmV;
+  // K|V packed per (token, head) with one 128-byte row each and a single head per CTA (TP shards with one kv head):
+  // one TMA box per page instead of two (the producer is bound by TMA issue there: 2 KB per instruction)
+  const int kv_pair = (pl.hc == 1 && D * es <= 128 &&
+                       reinterpret_cast<const uint8_t*>(a->v_cache) == reinterpret_cast<const uint8_t*>(a->k_cache) + D * es &&
+                       a->kv_head_stride >= 2 * D)
+                          ? 1 : 0;
   rc = get_tmap(&tmK, a->k_cache, a->num_blocks, a->kv_block_stride, a->kv_token_stride,
-                a->kv_head_stride, a->block_size, Hkv, pl.hc, D, es);
+                a->kv_head_stride, a->block_size, Hkv, pl.hc, D, es, kv_pair);
   if (rc) return rc;
   rc = get_tmap(&tmV, a->v_cache, a->num_blocks, a->kv_block_stride, a->kv_token_stride,
                 a->kv_head_stride, a->block_size, Hkv, pl.hc, D, es);
@@ -221,6 +236,7 @@ extern "C" int b200_paged_attention_decode(const b200_paged_attn_args* a, b200_s
   p.scale = a->scale;
   p.softcap = a->softcap > 0.f ? a->softcap : 0.f;
   p.tile_bytes = pl.tile_bytes;
+  p.kv_pair = kv_pair;
   p.off_merge = pl.off_merge; p.off_cum = pl.off_cum; p.off_bar = pl.off_bar;
 
   const int mode = fp8 ? (a->q_dtype == B200_BF16 ? BF16_FP8 : F16_FP8)

@@ -141,8 +141,8 @@ __global__ void __launch_bounds__(NTHREADS, 1)
         __syncwarp();
         if (lane < nt_) {
           const uint32_t dst = base + (uint32_t)stage * stage_bytes + (uint32_t)lane * 2u * TB;
-          tma_load_5d(dst, &tmK, bar_full + 8u * stage, 0, tok_in, 0, h0, blk, pol);
-          tma_load_5d(dst + TB, &tmV, bar_full + 8u * stage, 0, tok_in, 0, h0, blk, pol);
+          tma_load_5d(dst, &tmK, bar_full + 8u * stage, 0, tok_in, 0, h0, blk, pol);   // kv_pair: K and V in one box
+          if (!p.kv_pair) tma_load_5d(dst + TB, &tmV, bar_full + 8u * stage, 0, tok_in, 0, h0, blk, pol);
         }
         if (++stage == p.stages) { stage = 0; phase ^= 1u; }
       }

@@ -347,8 +347,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
       }
     }
   } else if (warp == 5) {
-    // ================================================================ MMA issuer (one thread)
-    if (lane == 0) {
+    // ================================================================ MMA issuer: warp-uniform control flow, one
+    // elected lane issues (common.cuh elect_one: under `if (lane == 0)` ptxas wraps each of the 16 UTCHMMA of a
+    // tile in an ELECT loop, ~65 cycles apiece - as much as the tensor work of the tile)
+    {
       constexpr uint32_t FMT = BF16 ? 1u : 0u;
       constexpr uint32_t IDESC_S = (1u << 4) | (FMT << 7) | (FMT << 10) | ((uint32_t)(TC_BN >> 3) << 17) |
                                    ((uint32_t)(TC_BM >> 4) << 24);
@@ -358,12 +360,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
         const uint32_t kb = kv_s + (uint32_t)(i & 1) * 2u * TC_TILE;
         mbar_wait(bar_k_full + 8u * (i & 1), (uint32_t)(i >> 1) & 1u);
         tc_fence_after();
+        if (elect_one()) {
 #pragma unroll
-        for (int ks = 0; ks < TC_D / 16; ks++) {
-          const uint32_t off = (uint32_t)(ks >> 2) * TC_SEG + (uint32_t)(ks & 3) * 32u;
-          tc_mma_f16(tm_S, desc_kmajor(q_s + off), desc_kmajor(kb + off), IDESC_S, ks > 0 ? 1u : 0u);
+          for (int ks = 0; ks < TC_D / 16; ks++) {
+            const uint32_t off = (uint32_t)(ks >> 2) * TC_SEG + (uint32_t)(ks & 3) * 32u;
+            tc_mma_f16(tm_S, desc_kmajor(q_s + off), desc_kmajor(kb + off), IDESC_S, ks > 0 ? 1u : 0u);
+          }
+          tc_commit(bar_s_full);
         }
-        tc_commit(bar_s_full);
+        __syncwarp();
       };
       issue_s(0);
       for (int i = 0; i < ntiles; i++) {
@@ -375,15 +380,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
         mbar_wait(bar_p_full, (uint32_t)i & 1u);
         mbar_wait(bar_v_full + 8u * stage, (uint32_t)(i >> 1) & 1u);
         tc_fence_after();
-        const uint32_t vb = kv_s + (uint32_t)stage * 2u * TC_TILE + TC_TILE;
+        if (elect_one()) {
+          const uint32_t vb = kv_s + (uint32_t)stage * 2u * TC_TILE + TC_TILE;
 #pragma unroll
-        for (int ks = 0; ks < TC_BN / 16; ks++) {
-          const uint32_t poff = (uint32_t)(ks >> 2) * TC_SEG + (uint32_t)(ks & 3) * 32u;
-          tc_mma_f16(tm_O, desc_kmajor(p_s + poff), desc_mnmajor(vb + (uint32_t)ks * 2048u, TC_SEG, 1024u), IDESC_O,
-                     (i > 0 || ks > 0) ? 1u : 0u);
+          for (int ks = 0; ks < TC_BN / 16; ks++) {
+            const uint32_t poff = (uint32_t)(ks >> 2) * TC_SEG + (uint32_t)(ks & 3) * 32u;
+            tc_mma_f16(tm_O, desc_kmajor(p_s + poff), desc_mnmajor(vb + (uint32_t)ks * 2048u, TC_SEG, 1024u), IDESC_O,
+                       (i > 0 || ks > 0) ? 1u : 0u);
+          }
+          tc_commit(bar_kv_empty + 8u * stage);
+          tc_commit(bar_pv_done);
         }
-        tc_commit(bar_kv_empty + 8u * stage);
-        tc_commit(bar_pv_done);
+        __syncwarp();
       }
     }
   } else {

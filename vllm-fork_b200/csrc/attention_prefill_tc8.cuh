@@ -138,20 +138,24 @@ __global__ void __launch_bounds__(TC8_THREADS, 1)
       }
     }
   } else if (warp == 5) {
-    // ================================================================ MMA issuer (one thread), kind::f16 / F16
-    if (lane == 0) {
+    // ================================================================ MMA issuer, kind::f16 / F16: warp-uniform
+    // control flow, one elected lane issues (common.cuh elect_one)
+    {
       constexpr uint32_t IDESC_S = (1u << 4) | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
       constexpr uint32_t IDESC_O = (1u << 4) | (1u << 16) | ((uint32_t)(TC_D >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
       auto issue_s = [&](int i) {
         mbar_wait(bar_k16_full, (uint32_t)i & 1u);
         tc_fence_after();
+        if (elect_one()) {
 #pragma unroll
-        for (int ks = 0; ks < TC_D / 16; ks++) {
-          const uint32_t off = (uint32_t)(ks >> 2) * TC_SEG + (uint32_t)(ks & 3) * 32u;
-          tc_mma_f16(tm_S, desc_kmajor(q_s + off), desc_kmajor(k16_s + off), IDESC_S, ks > 0 ? 1u : 0u);
+          for (int ks = 0; ks < TC_D / 16; ks++) {
+            const uint32_t off = (uint32_t)(ks >> 2) * TC_SEG + (uint32_t)(ks & 3) * 32u;
+            tc_mma_f16(tm_S, desc_kmajor(q_s + off), desc_kmajor(k16_s + off), IDESC_S, ks > 0 ? 1u : 0u);
+          }
+          tc_commit(bar_k16_free);   // the expanded K tile may be overwritten
+          tc_commit(bar_s_full);
         }
-        tc_commit(bar_k16_free);   // the expanded K tile may be overwritten
-        tc_commit(bar_s_full);
+        __syncwarp();
       };
       issue_s(0);
       for (int i = 0; i < ntiles; i++) {
@@ -162,14 +166,17 @@ __global__ void __launch_bounds__(TC8_THREADS, 1)
         mbar_wait(bar_p_full, (uint32_t)i & 1u);
         mbar_wait(bar_v16_full, (uint32_t)i & 1u);
         tc_fence_after();
+        if (elect_one()) {
 #pragma unroll
-        for (int ks = 0; ks < TC_BN / 16; ks++) {
-          const uint32_t poff = (uint32_t)(ks >> 2) * TC_SEG + (uint32_t)(ks & 3) * 32u;
-          tc_mma_f16(tm_O, desc_kmajor(p_s + poff), desc_mnmajor(v16_s + (uint32_t)ks * 2048u, TC_SEG, 1024u), IDESC_O,
-                     (i > 0 || ks > 0) ? 1u : 0u);
+          for (int ks = 0; ks < TC_BN / 16; ks++) {
+            const uint32_t poff = (uint32_t)(ks >> 2) * TC_SEG + (uint32_t)(ks & 3) * 32u;
+            tc_mma_f16(tm_O, desc_kmajor(p_s + poff), desc_mnmajor(v16_s + (uint32_t)ks * 2048u, TC_SEG, 1024u), IDESC_O,
+                       (i > 0 || ks > 0) ? 1u : 0u);
+          }
+          tc_commit(bar_v16_free);
+          tc_commit(bar_pv_done);
         }
-        tc_commit(bar_v16_free);
-        tc_commit(bar_pv_done);
+        __syncwarp();
       }
     }
   } else if (warp >= 6) {
