@@ -404,7 +404,8 @@ B200_API int b200_rotary_embedding(const int64_t* positions, void* query, void* 
  * b200_moe_sum replaces torch.ops._moe_C.moe_sum (moe_align_sum_kernels.cu:352-500, 757-930).
  * b200_moe_permute_fp8 / b200_moe_unpermute_reduce: moe_permute / moe_unpermute
  *   (csrc/libtorch_stable/moe/moe_permute_unpermute_op.cu) fused with the static FP8 quantisation
- *   of the GEMM input and with the topk-weighted sum respectively.
+ *   of the GEMM input and with the topk-weighted sum respectively. inv_perm entries < 0 or
+ *   >= *num_valid_rows (device int32, nullable) are skipped (dropped (token, k) pairs).
  * b200_moe_grouped_gemm_fp8: the grouped GEMM of fused_experts
  *   (vllm/model_executor/layers/fused_moe/fused_moe.py:299-612; cutlass_moe_mm,
  *   csrc/libtorch_stable/quantization/w8a8/cutlass/moe/grouped_mm_c3x_sm100.cu:16-115):
@@ -429,8 +430,9 @@ B200_API int b200_moe_permute_fp8(void* dst, const void* src, const int32_t* sor
                                   int64_t max_rows, int topk, int64_t numel, int hidden,
                                   int64_t src_stride, int src_dtype, b200_stream_t stream);
 B200_API int b200_moe_unpermute_reduce(void* out, const void* src, const int32_t* inv_perm,
-                                       const float* topk_weights, int64_t num_tokens, int topk,
-                                       int hidden, int64_t out_stride, int dtype, b200_stream_t stream);
+                                       const float* topk_weights, const int32_t* num_valid_rows,
+                                       int64_t num_tokens, int topk, int hidden, int64_t out_stride,
+                                       int dtype, b200_stream_t stream);
 B200_API int b200_moe_grouped_gemm_fp8(void* out, const void* a_sorted, const void* w,
                                        const int32_t* expert_ids, const int32_t* num_tokens_post_pad,
                                        const float* a_scale, const float* w_scale,
@@ -501,6 +503,55 @@ B200_API int b200_nvfp4_gemm(void* out, const void* a, const void* b, const void
                              const void* block_scale_b, const float* alpha, int M, int N, int K,
                              int64_t lda_bytes, int64_t ldb_bytes, int64_t ldo, int out_dtype,
                              b200_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * NVFP4 fused MoE (packed, expert-sorted rows without block padding: the CUTLASS-style layout).
+ * b200_moe_mm_data replaces torch.ops._C.get_cutlass_moe_mm_data
+ *   (csrc/libtorch_stable/quantization/w8a8/cutlass/moe/moe_data.cu:17-117,236-289; schema
+ *   csrc/libtorch_stable/torch_bindings.cpp get_cutlass_moe_mm_data; vllm/_custom_ops.py:847-899):
+ *   topk_ids int32 [numel] -> expert_offsets [E+1], problem_sizes1 / problem_sizes2 [E,3]
+ *   ((m_e, n1, k) / (m_e, k, n), n1 = is_gated ? 2n : n; (n1, m_e, k) / (k, m_e, n) when swap_ab),
+ *   input_permutation [numel] (source token of each packed row), output_permutation [numel] (packed row of
+ *   each flat (token, k) index; the packed row count for ids == -1; input_permutation rows past the packed
+ *   row count are -1), blockscale_offsets [E+1] (nullable;
+ *   running sum of m_e rounded up to 128). Rows of one expert keep ascending flat-index order.
+ * b200_shuffle_rows replaces torch.ops._moe_C.shuffle_rows (csrc/libtorch_stable/moe/
+ *   moe_permute_unpermute_op.cu; vllm/_custom_ops.py:919-931): dst[i,:] = src[dst2src_map[i],:], rows of
+ *   row_bytes (multiple of 16) bytes; a map entry outside [0, src_rows) gives a zero row.
+ * b200_nvfp4_experts_quant / b200_silu_and_mul_nvfp4_experts_quant replace
+ *   torch.ops._C.scaled_fp4_experts_quant / silu_and_mul_scaled_fp4_experts_quant
+ *   (csrc/libtorch_stable/quantization/fp4/nvfp4_experts_quant.cu:36-250, nvfp4_quant_entry.cu:120;
+ *   vllm/_custom_ops.py:1601-1725): input [m_topk, k] (or [m_topk, 2k] gate|up) f16/bf16 sorted by expert,
+ *   global_scale float [E] (nullable = 1), out uint8 [m_topk, k/2], out_scale e4m3 bytes: one swizzled
+ *   128x4-tile matrix per expert starting blockscale_offsets[e] rows (x round_up(k/16,4) bytes) in.
+ * b200_nvfp4_moe_gemm replaces torch.ops._C.cutlass_fp4_group_mm (csrc/libtorch_stable/quantization/fp4/
+ *   nvfp4_blockwise_moe_kernel.cu:676-746; vllm/_custom_ops.py:1010-1046):
+ *   out[r,:] = alphas[e] * (a[r,:] (.) sfa_e) (w[e] (.) sfw_e)^T for the problem_sizes[e][0] rows of expert e
+ *   starting at expert_offsets[e]; a uint8 [max_rows, K/2], w uint8 [E, N, K/2], a_blockscale as written by
+ *   b200_nvfp4_experts_quant at sf_offsets[e], w_blockscale [E, round_up(N,128), round_up(K/16,4)] swizzled
+ *   per expert, out bf16/f16 [max_rows, N] contiguous. K = e2m1 ELEMENTS (K % 32 == 0), N % 8 == 0.
+ */
+B200_API int b200_moe_mm_data(const int32_t* topk_ids, int32_t* expert_offsets, int32_t* problem_sizes1,
+                              int32_t* problem_sizes2, int32_t* input_permutation,
+                              int32_t* output_permutation, int32_t* blockscale_offsets, int num_experts,
+                              int64_t numel, int topk, int n, int k, int is_gated, int swap_ab,
+                              b200_stream_t stream);
+B200_API int b200_shuffle_rows(void* dst, const void* src, const int32_t* dst2src_map, int64_t dst_rows,
+                               int64_t src_rows, int64_t row_bytes, int64_t src_stride_bytes,
+                               b200_stream_t stream);
+B200_API int b200_nvfp4_experts_quant(void* out, void* out_scale, const void* input,
+                                      const float* global_scale, const int32_t* expert_offsets,
+                                      const int32_t* blockscale_offsets, int num_experts, int64_t m_topk, int k,
+                                      int64_t in_row_stride, int in_dtype, b200_stream_t stream);
+B200_API int b200_silu_and_mul_nvfp4_experts_quant(void* out, void* out_scale, const void* input,
+                                                   const float* global_scale, const int32_t* expert_offsets,
+                                                   const int32_t* blockscale_offsets, int num_experts,
+                                                   int64_t m_topk, int k, int64_t in_row_stride, int in_dtype,
+                                                   b200_stream_t stream);
+B200_API int b200_nvfp4_moe_gemm(void* out, const void* a, const void* w, const void* a_blockscale,
+                                 const void* w_blockscale, const float* alphas, const int32_t* problem_sizes,
+                                 const int32_t* expert_offsets, const int32_t* sf_offsets, int64_t max_rows,
+                                 int num_experts, int N, int K, int out_dtype, b200_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Tensor-parallel all-reduce over NVLink peer memory (one process per GPU).

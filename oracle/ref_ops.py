@@ -857,3 +857,117 @@ def dcp_lse_merge(outs, lses, dtype=torch.bfloat16, is_lse_base_on_e=True):
         o = torch.from_numpy(o).to(dtype).float().numpy()
         acc = o if acc is None else (acc + o).astype(np.float32)
     return torch.from_numpy(acc).to(dtype), lse
+
+
+# --------------------------------------------------------------------------------------------
+# NVFP4 fused MoE on packed expert-sorted rows.
+#   get_cutlass_moe_mm_data   csrc/libtorch_stable/quantization/w8a8/cutlass/moe/moe_data.cu:17-117,236-289
+#   scaled_fp4_experts_quant  csrc/libtorch_stable/quantization/fp4/nvfp4_experts_quant.cu:36-250
+#   cutlass_fp4_group_mm      csrc/libtorch_stable/quantization/fp4/nvfp4_blockwise_moe_kernel.cu:676-746
+#   run_cutlass_moe_fp4       vllm/model_executor/layers/fused_moe/experts/cutlass_moe.py:498-688
+# and the reference test's own model of the whole block: dequantise, then torch_moe
+# (tests/kernels/moe/test_nvfp4_moe.py:121-160, tests/kernels/utils.py torch_moe).
+# --------------------------------------------------------------------------------------------
+def cutlass_moe_mm_data(topk_ids: np.ndarray, num_experts: int, n: int, k: int, is_gated: bool = True,
+                        swap_ab: bool = False, with_blockscale: bool = True):
+    """Returns dict(expert_offsets [E+1], problem_sizes1/2 [E,3], a_map [numel] (-1 past the packed rows),
+    c_map [numel], blockscale_offsets [E+1]). Rows inside an expert are in ascending flat-index order (the
+    reference's compute_arg_sorts orders them by atomicAdd: only the per-expert SET is defined there)."""
+    ids = np.asarray(topk_ids).astype(np.int64)
+    topk = ids.shape[-1] if ids.ndim > 1 else 1
+    flat = ids.reshape(-1)
+    E = num_experts
+    counts = np.array([(flat == e).sum() for e in range(E)], dtype=np.int64)
+    off = np.concatenate([[0], np.cumsum(counts)]).astype(np.int32)
+    bso = np.concatenate([[0], np.cumsum((counts + 127) // 128 * 128)]).astype(np.int32)
+    n1 = 2 * n if is_gated else n
+    ps1 = np.zeros((E, 3), dtype=np.int32)
+    ps2 = np.zeros((E, 3), dtype=np.int32)
+    for e in range(E):
+        ps1[e] = (n1, counts[e], k) if swap_ab else (counts[e], n1, k)
+        ps2[e] = (k, counts[e], n) if swap_ab else (counts[e], k, n)
+    a_map = np.full(flat.size, -1, dtype=np.int32)
+    c_map = np.full(flat.size, off[E], dtype=np.int32)
+    fill = off[:-1].astype(np.int64).copy()
+    for i, e in enumerate(flat):
+        if 0 <= e < E:
+            a_map[fill[e]] = i // topk
+            c_map[i] = fill[e]
+            fill[e] += 1
+    return dict(expert_offsets=off, problem_sizes1=ps1, problem_sizes2=ps2, a_map=a_map, c_map=c_map,
+                blockscale_offsets=bso if with_blockscale else None)
+
+
+def nvfp4_experts_quant(x: torch.Tensor, global_scales: np.ndarray, expert_offsets: np.ndarray,
+                        blockscale_offsets: np.ndarray, gated: bool = False, return_scaled: bool = False):
+    """Per-expert nvfp4_quant of expert-sorted rows. Returns (codes uint8 [m, k] one per element, sf: flat uint8
+    buffer of blockscale_offsets[E] * round_up(k/16, 4) bytes holding one swizzled matrix per expert -- rows
+    past an expert's last row are zero here and UNDEFINED in the reference --, sf_rows: row-major scale bytes
+    [m, k/16] (, y))."""
+    E = len(expert_offsets) - 1
+    m = int(expert_offsets[E])
+    k = x.shape[1] // (2 if gated else 1)
+    C = k // 16
+    rc = (C + 3) // 4 * 4
+    codes = np.zeros((m, k), dtype=np.uint8)
+    sf_rows = np.zeros((m, C), dtype=np.uint8)
+    ys = np.zeros((m, k), dtype=np.float32)
+    sf = np.zeros(int(blockscale_offsets[E]) * rc, dtype=np.uint8)
+    for e in range(E):
+        lo, hi = int(expert_offsets[e]), int(expert_offsets[e + 1])
+        if hi == lo:
+            continue
+        gs = 1.0 if global_scales is None else float(global_scales[e])
+        fn = silu_and_mul_nvfp4_quant if gated else nvfp4_quant
+        c, s, y = fn(x[lo:hi], gs, return_scaled=True)
+        codes[lo:hi], sf_rows[lo:hi], ys[lo:hi] = c, s, y
+        sw = swizzle_sf(s)
+        base = int(blockscale_offsets[e]) * rc
+        sf[base:base + sw.size] = sw
+    if return_scaled:
+        return codes, sf, sf_rows, ys
+    return codes, sf, sf_rows
+
+
+def nvfp4_group_mm(a_codes: np.ndarray, a_sf_rows: np.ndarray, w_codes: np.ndarray, w_sf_rows: np.ndarray,
+                   alphas: np.ndarray, expert_offsets: np.ndarray) -> np.ndarray:
+    """out[rows of e] = alphas[e] * (a_e (.) sfa_e)(w[e] (.) sfw[e])^T (nvfp4_scaled_mm per expert).
+    a_codes [m, K], a_sf_rows [m, K/16], w_codes [E, N, K], w_sf_rows [E, N, K/16] (row-major scale bytes)."""
+    E = w_codes.shape[0]
+    out = np.zeros((a_codes.shape[0], w_codes.shape[1]), dtype=np.float32)
+    for e in range(E):
+        lo, hi = int(expert_offsets[e]), int(expert_offsets[e + 1])
+        if hi > lo:
+            out[lo:hi] = nvfp4_scaled_mm(a_codes[lo:hi], a_sf_rows[lo:hi], w_codes[e], w_sf_rows[e], float(alphas[e]))
+    return out
+
+
+def cutlass_moe_fp4(a: torch.Tensor, a1_gscale: np.ndarray, w1_codes: np.ndarray, w1_sf_rows: np.ndarray,
+                    w1_alphas: np.ndarray, a2_gscale: np.ndarray, w2_codes: np.ndarray, w2_sf_rows: np.ndarray,
+                    w2_alphas: np.ndarray, topk_weights: torch.Tensor, topk_ids: np.ndarray,
+                    return_stages: bool = False):
+    """run_cutlass_moe_fp4 operator by operator (cutlass_moe.py:587-688) with the GEMM outputs rounded to the
+    activation dtype where the kernels round them. w*_codes one e2m1 code per element, w*_sf_rows row-major."""
+    dt = a.dtype
+    E, n2, k = w1_codes.shape
+    n = n2 // 2
+    m, topk = topk_ids.shape
+    d = cutlass_moe_mm_data(topk_ids, E, n, k)
+    off, bso = d["expert_offsets"], d["blockscale_offsets"]
+    rows = int(off[E])
+    rep_a = a[torch.from_numpy(d["a_map"][:rows].astype(np.int64))]
+    c_a, _, s_a = nvfp4_experts_quant(rep_a, a1_gscale, off, bso)
+    c1 = torch.from_numpy(nvfp4_group_mm(c_a, s_a, w1_codes, w1_sf_rows, w1_alphas, off)).to(dt)
+    c_h, _, s_h = nvfp4_experts_quant(c1, a2_gscale, off, bso, gated=True)
+    c3 = torch.from_numpy(nvfp4_group_mm(c_h, s_h, w2_codes, w2_sf_rows, w2_alphas, off)).to(dt)
+    out = torch.zeros(m, k, dtype=torch.float32)
+    c3f = c3.float()
+    for t in range(m):
+        for j in range(topk):
+            r = int(d["c_map"][t * topk + j])
+            if r < rows:
+                out[t] += float(topk_weights[t, j]) * c3f[r]
+    out = out.to(dt)
+    if return_stages:
+        return out, dict(data=d, rep_a=rep_a, c1=c1, c3=c3, a_codes=c_a, h_codes=c_h)
+    return out

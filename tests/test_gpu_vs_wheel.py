@@ -461,3 +461,113 @@ def test_flash_layout_decode_vs_wheel_paged_attention(kv, heads, D):
     ours().paged_attention_decode(out, q, kf, vf, bt, sl, D ** -0.5, k_scale=ks if fp8 else None,
                                   v_scale=vs if fp8 else None, max_seq_len=max(lens))
     torch.testing.assert_close(out.float(), ref.float(), atol=2e-2, rtol=2e-2)
+
+
+# ------------------------------------------------------------------------------------------------ NVFP4 MoE
+def _wheel_fp4_moe_or_skip(W):
+    for name in ("get_cutlass_moe_mm_data", "scaled_fp4_experts_quant", "cutlass_fp4_group_mm"):
+        if not hasattr(W._C, name):
+            pytest.skip(f"wheel has no _C.{name}")
+
+
+@pytest.mark.parametrize("m,topk,E", [(64, 8, 64), (224, 6, 40), (256, 2, 8)])
+def test_get_cutlass_moe_mm_data_vs_wheel(m, topk, E):
+    """offsets and problem sizes exact; the permutations per-expert set-equal (the wheel orders by atomicAdd)."""
+    W = wheel()
+    _wheel_fp4_moe_or_skip(W)
+    ids = torch.stack([torch.randperm(E, device=DEV, generator=gen(m + i))[:topk] for i in range(m)]).to(torch.int32)
+    n, k = 1024, 1536
+
+    def run(fn):
+        eo = torch.zeros(E + 1, dtype=torch.int32, device=DEV)
+        bso = torch.zeros(E + 1, dtype=torch.int32, device=DEV)
+        ps1 = torch.zeros(E, 3, dtype=torch.int32, device=DEV)
+        ps2 = torch.zeros(E, 3, dtype=torch.int32, device=DEV)
+        am = torch.zeros(m * topk, dtype=torch.int32, device=DEV)
+        cm = torch.zeros(m * topk, dtype=torch.int32, device=DEV)
+        fn(ids, eo, ps1, ps2, am, cm, E, n, k, bso, True)
+        return [t.cpu().numpy() for t in (eo, bso, ps1, ps2, am, cm)]
+
+    a = run(W._C.get_cutlass_moe_mm_data)
+    b = run(ours().get_cutlass_moe_mm_data)
+    for x, y in zip(a[:4], b[:4]):
+        np.testing.assert_array_equal(x, y)
+    eo = a[0]
+    for e in range(E):
+        assert sorted(a[4][eo[e]:eo[e + 1]].tolist()) == sorted(b[4][eo[e]:eo[e + 1]].tolist())
+    flat = ids.cpu().numpy().reshape(-1)
+    for cm in (a[5], b[5]):
+        assert ((cm >= eo[flat]) & (cm < eo[flat + 1])).all()
+
+
+@pytest.mark.parametrize("gated", [False, True])
+@pytest.mark.parametrize("m,topk,E,k", [(64, 8, 64, 1024), (224, 6, 40, 1536), (256, 2, 8, 4096)])
+def test_scaled_fp4_experts_quant_bits_vs_wheel(m, topk, E, k, gated):
+    """codes of every packed row and scale bytes of every valid (row, column) bit-identical to the wheel's kernel."""
+    W = wheel()
+    _wheel_fp4_moe_or_skip(W)
+    name = "silu_and_mul_scaled_fp4_experts_quant" if gated else "scaled_fp4_experts_quant"
+    if not hasattr(W._C, name):
+        pytest.skip(f"wheel has no _C.{name}")
+    from oracle import ref_ops
+    ids = np.stack([np.random.default_rng(i).choice(E, topk, replace=False) for i in range(m)]).astype(np.int32)
+    d = ref_ops.cutlass_moe_mm_data(ids, E, 64, k)
+    eo = torch.from_numpy(d["expert_offsets"]).to(DEV)
+    bso = torch.from_numpy(d["blockscale_offsets"]).to(DEV)
+    rows = m * topk
+    x = torch.randn(rows, k * (2 if gated else 1), device=DEV, generator=gen(20)).to(torch.bfloat16)
+    gs = (torch.rand(E, device=DEV, generator=gen(21)) * 300 + 50).float()
+    rc = (k // 16 + 3) // 4 * 4
+    sf_rows = int(d["blockscale_offsets"][E])
+    o1 = torch.zeros(rows, k // 2, dtype=torch.uint8, device=DEV)
+    s1 = torch.zeros(sf_rows, rc // 4, dtype=torch.int32, device=DEV)
+    o2, s2 = torch.zeros_like(o1), torch.zeros_like(s1)
+    getattr(W._C, name)(o1, s1, x, gs, eo, bso)
+    fn = ours().silu_and_mul_scaled_fp4_experts_quant_out if gated else ours().scaled_fp4_experts_quant_out
+    fn(o2, s2, x, gs, eo, bso)
+    assert torch.equal(o1, o2)
+    f1, f2 = bits(s1).cpu().numpy().reshape(-1), bits(s2).cpu().numpy().reshape(-1)
+    for e in range(E):
+        lo, hi = int(d["expert_offsets"][e]), int(d["expert_offsets"][e + 1])
+        if hi == lo:
+            continue
+        mask = ref_ops.swizzle_sf(np.ones((hi - lo, k // 16), dtype=np.uint8)) != 0
+        base = int(d["blockscale_offsets"][e]) * rc
+        np.testing.assert_array_equal(f1[base:base + mask.size][mask], f2[base:base + mask.size][mask])
+
+
+@pytest.mark.parametrize("m,topk,E,n,k", [(64, 8, 64, 512, 1024), (224, 6, 40, 1024, 1536), (256, 2, 8, 2048, 1024)])
+def test_cutlass_fp4_group_mm_vs_wheel(m, topk, E, n, k):
+    W = wheel()
+    _wheel_fp4_moe_or_skip(W)
+    from oracle import ref_ops
+    ids = np.stack([np.random.default_rng(i).choice(E, topk, replace=False) for i in range(m)]).astype(np.int32)
+    d = ref_ops.cutlass_moe_mm_data(ids, E, n, k, is_gated=False)
+    eo = torch.from_numpy(d["expert_offsets"]).to(DEV)
+    bso = torch.from_numpy(d["blockscale_offsets"]).to(DEV)
+    ps = torch.from_numpy(d["problem_sizes1"]).to(DEV)
+    rows = m * topk
+    x = torch.randn(rows, k, device=DEV, generator=gen(30)).to(torch.bfloat16)
+    a_gs = (torch.rand(E, device=DEV, generator=gen(31)) * 300 + 50).float()
+    a4, a_sf = ours().scaled_fp4_experts_quant(x, a_gs, eo, bso, topk)
+    rn, rc = (n + 127) // 128 * 128, (k // 16 + 3) // 4 * 4
+    w4 = torch.empty(E, n, k // 2, dtype=torch.uint8, device=DEV)
+    w_sf = torch.empty(E, rn, rc, dtype=torch.uint8, device=DEV)
+    w_gs = torch.empty(E, device=DEV)
+    for e in range(E):
+        w = (torch.randn(n, k, device=DEV, generator=gen(40 + e)) / 8).to(torch.bfloat16)
+        w_gs[e] = 448.0 * 6.0 / w.float().abs().max()
+        q, s = ours().scaled_fp4_quant(w, w_gs[e:e + 1])
+        w4[e], w_sf[e] = q, bits(s).view(rn, rc)
+    w_sf = w_sf.view(torch.float8_e4m3fn)
+    alphas = 1.0 / (a_gs * w_gs)
+    ref = torch.zeros(rows, n, dtype=torch.bfloat16, device=DEV)
+    out = torch.zeros_like(ref)
+    try:
+        W._C.cutlass_fp4_group_mm(ref, a4, w4, a_sf, w_sf, alphas, ps, eo[:-1].contiguous(), bso[:-1].contiguous())
+        torch.cuda.synchronize()
+    except RuntimeError as e:   # the wheel's grouped kernel may be compiled out for this arch
+        pytest.skip(f"wheel cutlass_fp4_group_mm unavailable: {repr(e)[:120]}")
+    ours().cutlass_fp4_group_mm(out, a4, w4, a_sf, w_sf, alphas, ps, eo[:-1].contiguous(), bso[:-1].contiguous())
+    torch.testing.assert_close(out.float(), ref.float(), rtol=2 ** -7, atol=2e-3 * ref.float().abs().max().item())
+    assert (out == ref).float().mean().item() > 0.95

@@ -1,5 +1,6 @@
 """CPU tests: MoE routing oracle pinned to the reference's worked example and its golden properties."""
 import numpy as np
+import pytest
 import torch
 
 from oracle import ref_ops
@@ -69,3 +70,96 @@ def test_nvfp4_oracle_matches_reference_test_helpers():
     np.testing.assert_array_equal(ref_ops.unswizzle_sf(flat, 150, 10), sf)
     t = torch.from_numpy(flat.copy()).reshape(1, 2, 3, 32, 4, 4).permute(0, 1, 4, 3, 2, 5).reshape(256, 12)
     np.testing.assert_array_equal(t[:150, :10].numpy(), sf)
+
+
+# ------------------------------------------------------------------------------------------------
+# NVFP4 fused MoE oracle (packed expert-sorted rows): pinned by definition-level properties and by the
+# reference test's own model of the block (tests/kernels/moe/test_nvfp4_moe.py:121-160: dequantise, then a
+# dense per-token MoE, atol = rtol = 1e-1).
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("m,topk,E", [(1, 1, 4), (7, 3, 5), (64, 8, 64), (100, 2, 8)])
+def test_cutlass_moe_mm_data_oracle_definition(m, topk, E):
+    rng = np.random.default_rng(m * 31 + E)
+    ids = np.stack([rng.choice(E, size=topk, replace=False) for _ in range(m)]).astype(np.int32)
+    ids[rng.random(ids.shape) < 0.1] = -1
+    d = ref_ops.cutlass_moe_mm_data(ids, E, 96, 160)
+    flat = ids.reshape(-1)
+    off, bso = d["expert_offsets"], d["blockscale_offsets"]
+    rows = int(off[E])
+    assert rows == (flat >= 0).sum()
+    for e in range(E):
+        cnt = int((flat == e).sum())
+        assert off[e + 1] - off[e] == cnt                                   # moe_data.cu:17-52, 55-66
+        assert tuple(d["problem_sizes1"][e]) == (cnt, 192, 160)             # gated: 2n
+        assert tuple(d["problem_sizes2"][e]) == (cnt, 160, 96)
+        assert bso[e + 1] - bso[e] == (cnt + 127) // 128 * 128              # moe_data.cu:68-85
+        # the packed rows of expert e are exactly the tokens routed to it (compute_arg_sorts, :87-117)
+        toks = sorted(int(i) // topk for i in np.nonzero(flat == e)[0])
+        assert sorted(d["a_map"][off[e]:off[e + 1]].tolist()) == toks
+    for i, e in enumerate(flat):
+        if e < 0:
+            assert d["c_map"][i] == rows                                    # "invalid" pairs -> the packed row count
+        else:
+            assert off[e] <= d["c_map"][i] < off[e + 1]
+            assert d["a_map"][d["c_map"][i]] == i // topk                   # c_map inverts a_map
+    assert (d["a_map"][rows:] == -1).all()
+    sw = ref_ops.cutlass_moe_mm_data(ids, E, 96, 160, swap_ab=True, with_blockscale=False)
+    assert (sw["problem_sizes1"][:, [1, 0, 2]] == d["problem_sizes1"]).all()
+    assert (sw["problem_sizes2"][:, [1, 0, 2]] == d["problem_sizes2"]).all()
+
+
+def test_nvfp4_experts_quant_oracle_is_per_expert_quant():
+    g = torch.Generator().manual_seed(0)
+    off = np.array([0, 3, 3, 140, 141], dtype=np.int32)
+    bso = np.array([0, 128, 128, 384, 512], dtype=np.int32)
+    x = torch.randn(141, 96, generator=g).to(torch.bfloat16)
+    gs = np.array([100.0, 7.0, 300.0, 50.0], dtype=np.float32)
+    codes, sf, rows = ref_ops.nvfp4_experts_quant(x, gs, off, bso)
+    rc = 8   # round_up(96 / 16, 4)
+    assert sf.size == 512 * rc
+    for e in range(4):
+        lo, hi = off[e], off[e + 1]
+        if hi == lo:
+            continue
+        c, s = ref_ops.nvfp4_quant(x[lo:hi], gs[e])
+        np.testing.assert_array_equal(codes[lo:hi], c)
+        np.testing.assert_array_equal(rows[lo:hi], s)
+        n_pad = (hi - lo + 127) // 128 * 128
+        got = ref_ops.unswizzle_sf(sf[bso[e] * rc:bso[e] * rc + n_pad * rc], hi - lo, 6)
+        np.testing.assert_array_equal(got, s)
+
+
+def test_cutlass_moe_fp4_oracle_vs_reference_test_model():
+    m, n, k, E, topk = 24, 64, 128, 6, 2
+    g = torch.Generator().manual_seed(7)
+    a = (torch.randn(m, k, generator=g) / 10).to(torch.bfloat16)
+    w1 = (torch.randn(E, 2 * n, k, generator=g) / 8).to(torch.bfloat16)
+    w2 = (torch.randn(E, k, n, generator=g) / 8).to(torch.bfloat16)
+    score = torch.randn(m, E, generator=g)
+    tw, ti = torch.topk(torch.softmax(score, dim=-1), topk, dim=-1)
+
+    def quant(w):
+        gs = np.array([448.0 * 6.0 / w[e].float().abs().max().item() for e in range(E)], dtype=np.float32)
+        cs = [ref_ops.nvfp4_quant(w[e], gs[e]) for e in range(E)]
+        return np.stack([c for c, _ in cs]), np.stack([s for _, s in cs]), gs
+
+    w1c, w1s, w1gs = quant(w1)
+    w2c, w2s, w2gs = quant(w2)
+    one = np.ones(E, dtype=np.float32)
+    out = ref_ops.cutlass_moe_fp4(a, one, w1c, w1s, 1 / w1gs, one, w2c, w2s, 1 / w2gs, tw, ti.numpy().astype(np.int32))
+    # reference test model: dequantised weights, activations as given, dense per-token MoE in fp32
+    w1d = torch.from_numpy(np.stack([ref_ops.nvfp4_dequant(w1c[e], w1s[e], w1gs[e]) for e in range(E)]))
+    w2d = torch.from_numpy(np.stack([ref_ops.nvfp4_dequant(w2c[e], w2s[e], w2gs[e]) for e in range(E)]))
+    dense = torch.zeros(m, k)
+    for t in range(m):
+        for j in range(topk):
+            e = int(ti[t, j])
+            h = w1d[e] @ a[t].float()
+            dense[t] += tw[t, j] * (w2d[e] @ (torch.nn.functional.silu(h[:n]) * h[n:]))
+    torch.testing.assert_close(out.float(), dense, atol=1e-1, rtol=1e-1)
+    # and dropping a pair removes exactly its contribution
+    ti2 = ti.numpy().astype(np.int32).copy()
+    ti2[:, 1] = -1
+    out1 = ref_ops.cutlass_moe_fp4(a, one, w1c, w1s, 1 / w1gs, one, w2c, w2s, 1 / w2gs, tw, ti2)
+    outk1 = ref_ops.cutlass_moe_fp4(a, one, w1c, w1s, 1 / w1gs, one, w2c, w2s, 1 / w2gs, tw[:, :1], ti2[:, :1])
+    assert torch.equal(out1, outk1)

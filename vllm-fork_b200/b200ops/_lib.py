@@ -196,7 +196,7 @@ SIGNATURES = {
         c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int64, c_int,
                 c_int64, c_int, c_void_p]),
     "b200_moe_unpermute_reduce": (
-        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int64, c_int,
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int64, c_int,
                 c_void_p]),
     "b200_moe_grouped_gemm_fp8": (
         c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
@@ -206,6 +206,20 @@ SIGNATURES = {
     "b200_nvfp4_gemm": (
         c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64,
                 c_int64, c_int64, c_int, c_void_p]),
+    "b200_moe_mm_data": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int,
+                c_int, c_int, c_int, c_int, c_void_p]),
+    "b200_shuffle_rows": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p]),
+    "b200_nvfp4_experts_quant": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int, c_int64,
+                c_int, c_void_p]),
+    "b200_silu_and_mul_nvfp4_experts_quant": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int, c_int64,
+                c_int, c_void_p]),
+    "b200_nvfp4_moe_gemm": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                c_int64, c_int, c_int, c_int, c_int, c_void_p]),
     "b200_paged_attention_v1": (
         c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_void_p,
                 c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_void_p, c_void_p, c_int64, c_int64,

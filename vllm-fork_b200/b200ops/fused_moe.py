@@ -175,7 +175,87 @@ def fused_experts(
     _lib.check(rc, "moe_grouped_gemm_fp8")
     out = torch.empty(M, H, dtype=dt, device=dev)
     tw = topk_weights.to(torch.float32).contiguous()
-    rc = lib.b200_moe_unpermute_reduce(_p(out), _p(out2), _p(inv), _p(tw), M, topk, H, out.stride(0),
+    rc = lib.b200_moe_unpermute_reduce(_p(out), _p(out2), _p(inv), _p(tw), None, M, topk, H, out.stride(0),
                                        _dt(out), _stream())
     _lib.check(rc, "moe_unpermute")
     return out
+
+
+def cutlass_moe_fp4(
+    a: torch.Tensor,
+    a1_gscale: torch.Tensor,
+    w1_fp4: torch.Tensor,
+    w1_blockscale: torch.Tensor,
+    w1_alphas: torch.Tensor,
+    a2_gscale: torch.Tensor,
+    w2_fp4: torch.Tensor,
+    w2_blockscale: torch.Tensor,
+    w2_alphas: torch.Tensor,
+    topk_weights: torch.Tensor,
+    topk_ids: torch.Tensor,
+    apply_router_weight_on_input: bool = False,
+    output: torch.Tensor | None = None,
+) -> torch.Tensor:
+    """NVFP4 W4A4 fused MoE, the operator sequence of run_cutlass_moe_fp4 (fused_moe/experts/cutlass_moe.py:
+    498-688) with SiLU gating: get_cutlass_moe_mm_data -> shuffle_rows -> scaled_fp4_experts_quant ->
+    cutlass_fp4_group_mm (w1) -> silu_and_mul_scaled_fp4_experts_quant -> cutlass_fp4_group_mm (w2) ->
+    top-k weighted un-permute.
+
+    a [m, k] bf16/f16; a1_gscale / a2_gscale f32 [e] per-expert activation global scales; w1_fp4 uint8
+    [e, 2n, k/2], w1_blockscale float8_e4m3fn [e, 2n, k/16] swizzled per expert, w1_alphas f32 [e];
+    w2_fp4 uint8 [e, k, n/2], w2_blockscale [e, k, n/16], w2_alphas f32 [e]; topk_weights [m, topk];
+    topk_ids int32 [m, topk] (-1 = dropped)."""
+    _cuda(a, a1_gscale, w1_fp4, w1_blockscale, w1_alphas, a2_gscale, w2_fp4, w2_blockscale, w2_alphas,
+          topk_weights, topk_ids, output)
+    assert topk_weights.shape == topk_ids.shape, "topk shape mismatch"
+    assert w1_fp4.dtype == torch.uint8, "weight 1 must be uint8"
+    assert w2_fp4.dtype == torch.uint8, "weight 2 must be uint8"
+    assert w1_fp4.ndim == 3 and w2_fp4.ndim == 3 and w1_blockscale.ndim == 3 and w2_blockscale.ndim == 3, \
+        "All Weights must be of rank 3 for cutlass_moe_fp4"
+    m, k = a.shape
+    e, w1_n, half_k = w1_fp4.shape
+    e2, k_w2, half_n = w2_fp4.shape
+    n = half_n * 2
+    assert e == e2, f"Number of experts must match between weights. {e}, {e2}"
+    assert k == half_k * 2 and k == k_w2, "Hidden size mismatch between a, w1 and w2"
+    assert w1_n == 2 * n, "mismatch in expected `n`"
+    assert a.dtype in (torch.half, torch.bfloat16), "Invalid input dtype"
+    assert topk_weights.size(0) == m and topk_ids.size(0) == m, "topk must be provided for each row of a"
+    if topk_ids.dtype != torch.int32:
+        topk_ids = topk_ids.to(torch.int32)
+    topk_ids = topk_ids.contiguous()
+    topk = topk_ids.size(1)
+    dev, dt = a.device, a.dtype
+    numel = m * topk
+    expert_offsets = torch.empty(e + 1, dtype=torch.int32, device=dev)
+    blockscale_offsets = torch.empty(e + 1, dtype=torch.int32, device=dev)
+    problem_sizes1 = torch.empty((e, 3), dtype=torch.int32, device=dev)
+    problem_sizes2 = torch.empty((e, 3), dtype=torch.int32, device=dev)
+    a_map = torch.empty(numel, dtype=torch.int32, device=dev)
+    c_map = torch.empty(numel, dtype=torch.int32, device=dev)
+    if apply_router_weight_on_input:
+        assert topk == 1, "apply_router_weight_on_input is only implemented for topk=1"
+        a = a * topk_weights.to(dt)
+    ops.get_cutlass_moe_mm_data(topk_ids, expert_offsets, problem_sizes1, problem_sizes2, a_map, c_map, e, n, k,
+                                blockscale_offsets, is_gated=True)
+    # dropped pairs (topk_ids == -1) leave -1 in the tail of a_map: those packed rows are zero-filled
+    rep_a = ops.shuffle_rows(a, a_map)
+    rep_a_fp4, rep_a_blockscale = ops.scaled_fp4_experts_quant(rep_a, a1_gscale, expert_offsets,
+                                                               blockscale_offsets, topk)
+    c1 = torch.empty((numel, w1_n), dtype=dt, device=dev)
+    ops.cutlass_fp4_moe_mm(c1, rep_a_fp4, w1_fp4, rep_a_blockscale, w1_blockscale, w1_alphas, problem_sizes1,
+                           expert_offsets[:-1], blockscale_offsets[:-1])
+    int_fp4, int_blockscale = ops.silu_and_mul_scaled_fp4_experts_quant(c1, a2_gscale, expert_offsets,
+                                                                        blockscale_offsets, topk)
+    c3 = torch.empty((numel, k), dtype=dt, device=dev)
+    ops.cutlass_fp4_moe_mm(c3, int_fp4, w2_fp4, int_blockscale, w2_blockscale, w2_alphas, problem_sizes2,
+                           expert_offsets[:-1], blockscale_offsets[:-1])
+    if output is None:
+        output = torch.empty((m, k), dtype=dt, device=dev)
+    # c_map is exactly the inverse permutation b200_moe_unpermute_reduce consumes (packed row of each flat
+    # (token, j) pair); dropped pairs carry the packed row count expert_offsets[e] and are skipped
+    tw = None if apply_router_weight_on_input else topk_weights.to(torch.float32).contiguous()
+    rc = _lib.load().b200_moe_unpermute_reduce(_p(output), _p(c3), _p(c_map), _p(tw), _p(expert_offsets[e:]), m,
+                                               topk, k, output.stride(0), _dt(output), _stream())
+    _lib.check(rc, "moe_unpermute")
+    return output

@@ -634,6 +634,197 @@ def cutlass_scaled_fp4_mm(a: torch.Tensor, b: torch.Tensor, block_scale_a: torch
 
 
 # ------------------------------------------------------------------------------------------------
+# NVFP4 fused MoE operators (packed expert-sorted rows)     reference: vllm/_custom_ops.py:847-931,
+# 1010-1046, 1601-1725; caller run_cutlass_moe_fp4 (fused_moe/experts/cutlass_moe.py:498-688)
+# ------------------------------------------------------------------------------------------------
+MAX_TOKENS_PER_EXPERT_FP4_MOE = int(os.environ.get("VLLM_MAX_TOKENS_PER_EXPERT_FP4_MOE", "163840"))
+SWAP_AB_THRESHOLD = 64   # moe_data.cu:14
+
+
+def get_cutlass_moe_mm_data(topk_ids: torch.Tensor, expert_offsets: torch.Tensor, problem_sizes1: torch.Tensor,
+                            problem_sizes2: torch.Tensor, input_permutation: torch.Tensor,
+                            output_permutation: torch.Tensor, num_experts: int, n: int, k: int,
+                            blockscale_offsets: torch.Tensor | None = None, is_gated: bool = True) -> None:
+    """torch.ops._C.get_cutlass_moe_mm_data (vllm/_custom_ops.py:847-899, moe_data.cu:236-289): all outputs
+    int32, caller-allocated. Swap-AB problem sizes exactly when the reference would use them (FP8 path with
+    at most 64 (token, k) pairs, moe_data.cu:254-255)."""
+    _cuda(topk_ids, expert_offsets, problem_sizes1, problem_sizes2, input_permutation, output_permutation,
+          blockscale_offsets)
+    for name, t in (("topk_ids", topk_ids), ("expert_offsets", expert_offsets), ("problem_sizes1", problem_sizes1),
+                    ("problem_sizes2", problem_sizes2), ("input_permutation", input_permutation),
+                    ("output_permutation", output_permutation), ("blockscale_offsets", blockscale_offsets)):
+        if t is not None and (t.dtype != torch.int32 or not t.is_contiguous()):
+            raise RuntimeError(f"get_cutlass_moe_mm_data: {name} must be a contiguous int32 tensor")
+    numel = topk_ids.numel()
+    if expert_offsets.numel() < num_experts + 1 or problem_sizes1.numel() < 3 * num_experts or \
+            problem_sizes2.numel() < 3 * num_experts or input_permutation.numel() < numel or \
+            output_permutation.numel() < numel or \
+            (blockscale_offsets is not None and blockscale_offsets.numel() < num_experts + 1):
+        raise RuntimeError("get_cutlass_moe_mm_data: an output tensor is too small")
+    swap_ab = blockscale_offsets is None and numel <= SWAP_AB_THRESHOLD
+    topk = topk_ids.shape[-1] if topk_ids.dim() > 1 else 1
+    rc = _lib.load().b200_moe_mm_data(_p(topk_ids), _p(expert_offsets), _p(problem_sizes1), _p(problem_sizes2),
+                                      _p(input_permutation), _p(output_permutation), _p(blockscale_offsets),
+                                      num_experts, numel, topk, n, k, 1 if is_gated else 0, 1 if swap_ab else 0,
+                                      _stream())
+    _lib.check(rc, "get_cutlass_moe_mm_data")
+
+
+def shuffle_rows(input_tensor: torch.Tensor, dst2src_map: torch.Tensor,
+                 output_tensor: torch.Tensor | None = None) -> torch.Tensor:
+    """output[i, :] = input[dst2src_map[i], :] (vllm/_custom_ops.py:919-931, torch.ops._moe_C.shuffle_rows)."""
+    _cuda(input_tensor, dst2src_map, output_tensor)
+    if input_tensor.dim() != 2 or input_tensor.stride(1) != 1:
+        raise RuntimeError("shuffle_rows: input must be 2-D with a contiguous last dim")
+    if dst2src_map.dtype != torch.int32 or not dst2src_map.is_contiguous():
+        raise RuntimeError("shuffle_rows: dst2src_map must be a contiguous int32 tensor")
+    rows = dst2src_map.shape[0]
+    if output_tensor is None:
+        output_tensor = torch.empty((rows, input_tensor.shape[1]), device=input_tensor.device,
+                                    dtype=input_tensor.dtype)
+    elif tuple(output_tensor.shape) != (rows, input_tensor.shape[1]) or not output_tensor.is_contiguous() or \
+            output_tensor.dtype != input_tensor.dtype:
+        raise RuntimeError("shuffle_rows: bad output tensor")
+    es = input_tensor.element_size()
+    rc = _lib.load().b200_shuffle_rows(_p(output_tensor), _p(input_tensor), _p(dst2src_map), rows,
+                                       input_tensor.shape[0], input_tensor.shape[1] * es,
+                                       input_tensor.stride(0) * es, _stream())
+    _lib.check(rc, "shuffle_rows")
+    return output_tensor
+
+
+def _experts_quant_out(op: str, gated: bool, output, output_scale, input, input_global_scale,
+                       input_offset_by_experts, output_scale_offset_by_experts) -> None:
+    _cuda(output, output_scale, input, input_global_scale, input_offset_by_experts, output_scale_offset_by_experts)
+    if input.dim() != 2 or input.stride(1) != 1:
+        raise RuntimeError(f"{op}: input must be 2-D with a contiguous last dim")
+    if input.dtype not in (torch.float16, torch.bfloat16):
+        raise RuntimeError(f"{op}: input.dtype needs to be fp16 or bf16 but got {input.dtype}.")
+    m_topk, k = input.shape[0], input.shape[1] // (2 if gated else 1)
+    if k % 16 != 0:
+        raise RuntimeError(f"{op}: k must be a multiple of 16, but got {k}")
+    for name, t in (("input_offset_by_experts", input_offset_by_experts),
+                    ("output_scale_offset_by_experts", output_scale_offset_by_experts)):
+        if t.dtype != torch.int32 or not t.is_contiguous():
+            raise RuntimeError(f"{op}: {name} must be a contiguous int32 tensor")
+    n_experts = input_offset_by_experts.numel() - 1
+    if output_scale_offset_by_experts.numel() != n_experts + 1 or n_experts < 1:
+        raise RuntimeError(f"{op}: the two offset tensors must both have num_experts + 1 entries")
+    if input_global_scale is not None and (input_global_scale.dtype != torch.float32 or
+                                           input_global_scale.numel() < n_experts):
+        raise RuntimeError(f"{op}: input_global_scale must be float32 [num_experts]")
+    if output.element_size() != 1 or not output.is_contiguous() or tuple(output.shape) != (m_topk, k // 2):
+        raise RuntimeError(f"{op}: output must be a contiguous 1-byte tensor [{m_topk}, {k // 2}]")
+    padded_k = (k // 16 + 3) // 4 * 4
+    if not output_scale.is_contiguous() or (output_scale.numel() * output_scale.element_size()) % padded_k != 0:
+        raise RuntimeError(f"{op}: output_scale must be contiguous with rows of {padded_k} bytes")
+    fn = _lib.load().b200_silu_and_mul_nvfp4_experts_quant if gated else _lib.load().b200_nvfp4_experts_quant
+    rc = fn(_p(output), _p(output_scale), _p(input), _p(input_global_scale), _p(input_offset_by_experts),
+            _p(output_scale_offset_by_experts), n_experts, m_topk, k, input.stride(0), _dt(input), _stream())
+    _lib.check(rc, op)
+
+
+def scaled_fp4_experts_quant_out(output, output_scale, input, input_global_scale, input_offset_by_experts,
+                                 output_scale_offset_by_experts) -> None:
+    """torch.ops._C.scaled_fp4_experts_quant (torch_bindings.cpp:225-229): caller-allocated outputs."""
+    _experts_quant_out("scaled_fp4_experts_quant", False, output, output_scale, input, input_global_scale,
+                       input_offset_by_experts, output_scale_offset_by_experts)
+
+
+def silu_and_mul_scaled_fp4_experts_quant_out(output, output_scale, input, input_global_scale,
+                                              input_offset_by_experts, output_scale_offset_by_experts) -> None:
+    """torch.ops._C.silu_and_mul_scaled_fp4_experts_quant (torch_bindings.cpp:231-236)."""
+    _experts_quant_out("silu_and_mul_scaled_fp4_experts_quant", True, output, output_scale, input,
+                       input_global_scale, input_offset_by_experts, output_scale_offset_by_experts)
+
+
+def _experts_quant(gated: bool, input_tensor, input_global_scale, expert_offsets, blockscale_offsets, topk,
+                   max_scale_rows):
+    assert input_tensor.ndim == 2, f"input.ndim needs to be == 2, but got {input_tensor.ndim}."
+    m_numtopk = input_tensor.shape[0]
+    k = input_tensor.shape[1] // (2 if gated else 1)
+    assert m_numtopk <= MAX_TOKENS_PER_EXPERT_FP4_MOE * topk, (
+        f"m_numtopk must be less than MAX_TOKENS_PER_EXPERT({MAX_TOKENS_PER_EXPERT_FP4_MOE}) for cutlass_moe_fp4, "
+        f"observed m_numtopk = {m_numtopk}. Use VLLM_MAX_TOKENS_PER_EXPERT_FP4_MOE to set this value.")
+    padded_k = (k // 16 + 3) // 4
+    n_experts = expert_offsets.numel() - 1
+    # The reference allocates MAX_TOKENS_PER_EXPERT * topk scale rows (160 k rows: ~tens of MB of address space it
+    # never touches); the rows an expert-sorted batch can reach are bounded by m_numtopk + 127 per expert.
+    rows = max_scale_rows if max_scale_rows is not None else \
+        min(MAX_TOKENS_PER_EXPERT_FP4_MOE * topk, (m_numtopk + 127 * n_experts + 127) // 128 * 128)
+    output = torch.empty(m_numtopk, k // 2, device=input_tensor.device, dtype=torch.uint8)
+    output_scales = torch.empty(rows, padded_k, dtype=torch.int32, device=input_tensor.device)
+    _experts_quant_out("silu_and_mul_scaled_fp4_experts_quant" if gated else "scaled_fp4_experts_quant", gated,
+                       output, output_scales, input_tensor, input_global_scale, expert_offsets, blockscale_offsets)
+    return output, output_scales.view(torch.float8_e4m3fn)
+
+
+def scaled_fp4_experts_quant(input_tensor: torch.Tensor, input_global_scale: torch.Tensor,
+                             expert_offsets: torch.Tensor, blockscale_offsets: torch.Tensor, topk: int,
+                             max_scale_rows: int | None = None) -> tuple[torch.Tensor, torch.Tensor]:
+    """vllm/_custom_ops.py:1601-1660: NVFP4 quantisation of expert-sorted rows with one global scale and one
+    swizzled scale-factor matrix per expert. Returns (uint8 [m_topk, k/2], float8_e4m3fn scales)."""
+    return _experts_quant(False, input_tensor, input_global_scale, expert_offsets, blockscale_offsets, topk,
+                          max_scale_rows)
+
+
+def silu_and_mul_scaled_fp4_experts_quant(input_tensor: torch.Tensor, input_global_scale: torch.Tensor,
+                                          expert_offsets: torch.Tensor, blockscale_offsets: torch.Tensor,
+                                          topk: int, max_scale_rows: int | None = None):
+    """vllm/_custom_ops.py:1663-1725: input [m_topk, 2k] gate || up; quantises silu(gate) * up."""
+    return _experts_quant(True, input_tensor, input_global_scale, expert_offsets, blockscale_offsets, topk,
+                          max_scale_rows)
+
+
+def cutlass_fp4_group_mm(out: torch.Tensor, a: torch.Tensor, b: torch.Tensor, a_blockscale: torch.Tensor,
+                         b_blockscales: torch.Tensor, alphas: torch.Tensor, problem_sizes: torch.Tensor,
+                         expert_offsets: torch.Tensor, sf_offsets: torch.Tensor) -> None:
+    """torch.ops._C.cutlass_fp4_group_mm (torch_bindings.cpp:193-197; checks of nvfp4_blockwise_moe_kernel.cu:
+    676-746): a uint8 [m_topk, k/2] expert-sorted, b uint8 [E, n, k/2], a_blockscale / b_blockscales
+    float8_e4m3fn swizzled per expert, alphas f32 [E], problem_sizes int32 [E, 3] (m_e, n, k),
+    expert_offsets / sf_offsets int32 [E], out bf16 / f16 [m_topk, n]."""
+    _cuda(out, a, b, a_blockscale, b_blockscales, alphas, problem_sizes, expert_offsets, sf_offsets)
+    if a.dtype != torch.uint8 or b.dtype != torch.uint8:
+        raise RuntimeError("cutlass_fp4_group_mm: a and b must be uint8 (packed fp4)")
+    if a.dim() != 2 or b.dim() != 3 or not a.is_contiguous() or not b.is_contiguous():
+        raise RuntimeError("cutlass_fp4_group_mm: a must be a contiguous 2-D and b a contiguous 3-D tensor")
+    if a_blockscale.element_size() not in (1, 4) or b_blockscales.element_size() not in (1, 4):
+        raise RuntimeError("cutlass_fp4_group_mm: block scales must be float8_e4m3fn")
+    if alphas.dtype != torch.float32:
+        raise RuntimeError("cutlass_fp4_group_mm: alphas must be float32")
+    for name, t in (("problem_sizes", problem_sizes), ("expert_offsets", expert_offsets), ("sf_offsets", sf_offsets)):
+        if t.dtype != torch.int32 or not t.is_contiguous():
+            raise RuntimeError(f"cutlass_fp4_group_mm: {name} must be a contiguous int32 tensor")
+    E, n, half_k = b.shape
+    m_topk = a.shape[0]
+    if a.shape[1] != half_k:
+        raise RuntimeError("cutlass_fp4_group_mm: a and b disagree on k")
+    if problem_sizes.dim() != 2 or tuple(problem_sizes.shape) != (E, 3):
+        raise RuntimeError("cutlass_fp4_group_mm: problem_sizes must be [num_experts, 3]")
+    if expert_offsets.numel() < E or sf_offsets.numel() < E or alphas.numel() < E:
+        raise RuntimeError("cutlass_fp4_group_mm: expert_offsets / sf_offsets / alphas need num_experts entries")
+    k = half_k * 2
+    ru = lambda x, y: (x + y - 1) // y * y
+    if not b_blockscales.is_contiguous() or \
+            b_blockscales.numel() * b_blockscales.element_size() != E * ru(n, 128) * ru(k // 16, 4):
+        raise RuntimeError(f"cutlass_fp4_group_mm: b_blockscales must be padded and swizzled per expert to "
+                           f"({E}x{ru(n, 128)}x{ru(k // 16, 4)})")
+    if out.dtype not in (torch.bfloat16, torch.float16) or tuple(out.shape) != (m_topk, n) or not out.is_contiguous():
+        raise RuntimeError("cutlass_fp4_group_mm: out must be a contiguous bf16 / f16 [m_topk, n] tensor")
+    rc = _lib.load().b200_nvfp4_moe_gemm(_p(out), _p(a), _p(b), _p(a_blockscale), _p(b_blockscales), _p(alphas),
+                                         _p(problem_sizes), _p(expert_offsets), _p(sf_offsets), m_topk, E, n, k,
+                                         _dt(out), _stream())
+    _lib.check(rc, "cutlass_fp4_group_mm")
+
+
+def cutlass_fp4_moe_mm(out_tensors, a_tensors, b_tensors, a_scales, b_scales, alphas, problem_sizes,
+                       expert_offsets, sf_offsets) -> None:
+    """vllm/_custom_ops.py:1010-1046 (same argument order as the reference wrapper)."""
+    cutlass_fp4_group_mm(out_tensors, a_tensors, b_tensors, a_scales, b_scales, alphas, problem_sizes,
+                         expert_offsets, sf_offsets)
+
+
+# ------------------------------------------------------------------------------------------------
 # RMSNorm (+ residual, + static FP8 quant) and RoPE     reference: vllm/_custom_ops.py rms_norm,
 # fused_add_rms_norm, rms_norm_static_fp8_quant, fused_add_rms_norm_static_fp8_quant, rotary_embedding
 # ------------------------------------------------------------------------------------------------

@@ -62,6 +62,15 @@ SCHEMAS: dict[str, tuple[str, str]] = {
     "cutlass_fp4_group_mm": (
         "(Tensor! out, Tensor a, Tensor b, Tensor a_blockscale, Tensor b_blockscales, Tensor alphas, "
         "Tensor problem_sizes, Tensor expert_offsets, Tensor sf_offsets) -> ()", "torch_bindings.cpp:193-197"),
+    "silu_and_mul_scaled_fp4_experts_quant": (
+        "(Tensor! output, Tensor! output_scale, Tensor input, Tensor input_global_scale, "
+        "Tensor input_offset_by_experts, Tensor output_scale_offset_by_experts) -> ()", "torch_bindings.cpp:231-236"),
+    "get_cutlass_moe_mm_data": (
+        "(Tensor topk_ids, Tensor! expert_offsets, Tensor! problem_sizes1, Tensor! problem_sizes2, "
+        "Tensor! input_permutation, Tensor! output_permutation, int num_experts, int n, int k, "
+        "Tensor? blockscale_offsets, bool is_gated) -> ()", "torch_bindings.cpp:151-157"),
+    "shuffle_rows": (
+        "(Tensor input_tensor, Tensor dst2src_map, Tensor! output_tensor) -> ()", "moe/torch_bindings.cpp:119-121"),
     "silu_and_mul": ("(Tensor! result, Tensor input) -> ()", "torch_bindings.cpp:571"),
     "silu_and_mul_quant": ("(Tensor! result, Tensor input, Tensor scale) -> ()", "torch_bindings.cpp:583-584"),
     "merge_attn_states": (
@@ -179,6 +188,22 @@ def _cutlass_fp4_group_mm(out, a, b, a_blockscale, b_blockscales, alphas, proble
                              sf_offsets)
 
 
+def _silu_and_mul_scaled_fp4_experts_quant(output, output_scale, input, input_global_scale,
+                                           input_offset_by_experts, output_scale_offset_by_experts):
+    ops.silu_and_mul_scaled_fp4_experts_quant_out(output, output_scale, input, input_global_scale,
+                                                  input_offset_by_experts, output_scale_offset_by_experts)
+
+
+def _get_cutlass_moe_mm_data(topk_ids, expert_offsets, problem_sizes1, problem_sizes2, input_permutation,
+                             output_permutation, num_experts, n, k, blockscale_offsets, is_gated):
+    ops.get_cutlass_moe_mm_data(topk_ids, expert_offsets, problem_sizes1, problem_sizes2, input_permutation,
+                                output_permutation, num_experts, n, k, blockscale_offsets, is_gated)
+
+
+def _shuffle_rows(input_tensor, dst2src_map, output_tensor):
+    ops.shuffle_rows(input_tensor, dst2src_map, output_tensor)
+
+
 def _silu_and_mul(result, input):
     ops.silu_and_mul(result, input)
 
@@ -288,6 +313,8 @@ _IMPLS = {
     "cutlass_scaled_fp4_mm": _cutlass_scaled_fp4_mm, "scaled_fp4_quant.out": _scaled_fp4_quant_out,
     "silu_and_mul_nvfp4_quant": _silu_and_mul_nvfp4_quant, "scaled_fp4_experts_quant": _scaled_fp4_experts_quant,
     "cutlass_fp4_group_mm": _cutlass_fp4_group_mm, "silu_and_mul": _silu_and_mul,
+    "silu_and_mul_scaled_fp4_experts_quant": _silu_and_mul_scaled_fp4_experts_quant,
+    "get_cutlass_moe_mm_data": _get_cutlass_moe_mm_data, "shuffle_rows": _shuffle_rows,
     "silu_and_mul_quant": _silu_and_mul_quant, "merge_attn_states": _merge_attn_states, "rms_norm": _rms_norm,
     "fused_add_rms_norm": _fused_add_rms_norm, "rms_norm_static_fp8_quant": _rms_norm_static_fp8_quant,
     "fused_add_rms_norm_static_fp8_quant": _fused_add_rms_norm_static_fp8_quant,

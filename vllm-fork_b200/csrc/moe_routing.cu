@@ -258,17 +258,19 @@ template <typename T>
 __global__ void __launch_bounds__(256)
     moe_unpermute_reduce_kernel(T* __restrict__ out, const T* __restrict__ src,
                                 const int32_t* __restrict__ inv_perm,
-                                const float* __restrict__ topk_weights /* nullable */, int topk,
+                                const float* __restrict__ topk_weights /* nullable */,
+                                const int32_t* __restrict__ num_valid_rows /* nullable */, int topk,
                                 int hidden, int64_t out_stride) {
   constexpr int N = 16 / sizeof(T);
   const int64_t t = blockIdx.x;
+  const int valid = num_valid_rows ? *num_valid_rows : 0x7fffffff;
   for (int v = threadIdx.x; v < hidden / N; v += blockDim.x) {
     float acc[N];
 #pragma unroll
     for (int j = 0; j < N; j++) acc[j] = 0.f;
     for (int kk = 0; kk < topk; kk++) {
       const int pos = inv_perm[t * topk + kk];
-      if (pos < 0) continue;
+      if (pos < 0 || pos >= valid) continue;
       const float w = topk_weights ? topk_weights[t * topk + kk] : 1.f;
       const uint4 x = *reinterpret_cast<const uint4*>(src + (int64_t)pos * hidden + v * N);
       const T* xe = reinterpret_cast<const T*>(&x);
@@ -280,6 +282,119 @@ __global__ void __launch_bounds__(256)
 #pragma unroll
     for (int j = 0; j < N; j++) re[j] = Cvt<T>::from_f32(acc[j]);
     *reinterpret_cast<uint4*>(out + t * out_stride + v * N) = r;
+  }
+}
+
+
+// ------------------------------------------------------------- get_cutlass_moe_mm_data / shuffle_rows
+// torch.ops._C.get_cutlass_moe_mm_data (csrc/libtorch_stable/quantization/w8a8/cutlass/moe/moe_data.cu:17-117,
+// 236-289): the tightly packed (no block padding) expert sort used by the CUTLASS-style grouped GEMMs:
+//   expert_offsets[e]      first packed row of expert e (E + 1 entries),
+//   problem_sizes1/2[e]    (m_e, n1, k) and (m_e, k, n) -- (n1, m_e, k) / (k, m_e, n) when swap_ab,
+//   input_permutation[r]   source token of packed row r,  output_permutation[t*topk+j] packed row of (t, j)
+//                          (= expert_offsets[E] for topk_ids == -1),
+//   blockscale_offsets[e]  sum of the previous experts' rows rounded up to 128 (NVFP4 scale-factor rows).
+// One deterministic single-CTA kernel (the reference's four kernels order an expert's rows by atomicAdd):
+// rows of an expert keep ascending flat-index order.
+__global__ void __launch_bounds__(ALIGN_THREADS)
+    moe_mm_data_kernel(const int32_t* __restrict__ topk_ids, int32_t* __restrict__ expert_offsets,
+                       int32_t* __restrict__ problem_sizes1, int32_t* __restrict__ problem_sizes2,
+                       int32_t* __restrict__ input_permutation, int32_t* __restrict__ output_permutation,
+                       int32_t* __restrict__ blockscale_offsets, int E, int64_t numel, int topk, int n, int k,
+                       int n1, int swap_ab, int W) {
+  extern __shared__ int32_t sm[];
+  int32_t* hist = sm;               // [W][E]
+  int32_t* cum = sm + W * E;        // [E + 1]
+  __shared__ int32_t s_warp_tot[ALIGN_WARPS], s_warp_tot_r[ALIGN_WARPS];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int i = tid; i < W * E; i += ALIGN_THREADS) hist[i] = 0;
+  __syncthreads();
+  const int64_t strip = ((numel + W - 1) / W + 31) / 32 * 32;
+  const int64_t s0 = (int64_t)warp * strip, s1 = s0 + strip < numel ? s0 + strip : numel;
+  if (warp < W) {
+    for (int64_t i = s0 + lane; i < s1; i += 32) {
+      const int e = topk_ids[i];
+      if (e >= 0 && e < E) atomicAdd(&hist[warp * E + e], 1);
+    }
+  }
+  __syncthreads();
+  int tot = 0;
+  if (tid < E)
+    for (int w = 0; w < W; w++) tot += hist[w * E + tid];
+  const int rounded = (tot + 127) / 128 * 128;
+  int inc = tot, inc_r = rounded;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int a = __shfl_up_sync(0xffffffffu, inc, o);
+    const int b = __shfl_up_sync(0xffffffffu, inc_r, o);
+    if (lane >= o) { inc += a; inc_r += b; }
+  }
+  if (lane == 31) { s_warp_tot[warp] = inc; s_warp_tot_r[warp] = inc_r; }
+  __syncthreads();
+  int woff = 0, woff_r = 0;
+  for (int w = 0; w < warp; w++) { woff += s_warp_tot[w]; woff_r += s_warp_tot_r[w]; }
+  const int excl = woff + inc - tot, excl_r = woff_r + inc_r - rounded;
+  if (tid < E) {
+    cum[tid] = excl;
+    expert_offsets[tid] = excl;
+    if (blockscale_offsets) blockscale_offsets[tid] = excl_r;
+    int32_t* p1 = problem_sizes1 + tid * 3;
+    int32_t* p2 = problem_sizes2 + tid * 3;
+    if (swap_ab) { p1[0] = n1; p1[1] = tot; p1[2] = k; p2[0] = k; p2[1] = tot; p2[2] = n; }
+    else { p1[0] = tot; p1[1] = n1; p1[2] = k; p2[0] = tot; p2[1] = k; p2[2] = n; }
+    if (tid == E - 1) {
+      cum[E] = excl + tot;
+      expert_offsets[E] = excl + tot;
+      if (blockscale_offsets) blockscale_offsets[E] = excl_r + rounded;
+    }
+    int run = excl;
+    for (int w = 0; w < W; w++) {
+      const int c = hist[w * E + tid];
+      hist[w * E + tid] = run;
+      run += c;
+    }
+  }
+  __syncthreads();
+  const int num_rows = cum[E];
+  // packed rows past the last expert exist only when pairs were dropped: no source token
+  for (int64_t i = num_rows + tid; i < numel; i += ALIGN_THREADS) input_permutation[i] = -1;
+  if (warp < W) {
+    for (int64_t i0 = s0; i0 < s1; i0 += 32) {
+      const int64_t i = i0 + lane;
+      int e = i < s1 ? topk_ids[i] : -2;
+      if (e >= E) e = -2;   // out-of-range ids are dropped without an output row
+      if (i < s1 && e < 0) output_permutation[i] = num_rows;
+      const unsigned active = __ballot_sync(0xffffffffu, e >= 0);
+      if (e >= 0) {
+        const unsigned peers = __match_any_sync(active, e);
+        const int rank = __popc(peers & ((1u << lane) - 1u));
+        const int pos = hist[warp * E + e] + rank;
+        input_permutation[pos] = (int32_t)(i / topk);
+        output_permutation[i] = pos;
+        __syncwarp(active);
+        if (rank == 0) hist[warp * E + e] += __popc(peers);
+      }
+      __syncwarp();
+    }
+  }
+}
+
+// torch.ops._moe_C.shuffle_rows (csrc/libtorch_stable/moe/moe_permute_unpermute_op.cu shuffle_rows):
+// dst[i, :] = src[dst2src_map[i], :]; a map entry outside [0, src_rows) yields a zero row (the reference's
+// output_permutation marks dropped (token, k) pairs with the packed row count).
+__global__ void __launch_bounds__(256)
+    shuffle_rows_kernel(uint8_t* __restrict__ dst, const uint8_t* __restrict__ src,
+                        const int32_t* __restrict__ map, int64_t dst_rows, int64_t src_rows, int row_vecs,
+                        int64_t src_stride_bytes) {
+  for (int64_t row = blockIdx.x; row < dst_rows; row += gridDim.x) {
+    const int32_t s = map[row];
+    uint4* d = reinterpret_cast<uint4*>(dst) + row * row_vecs;
+    if (s < 0 || s >= src_rows) {
+      for (int v = threadIdx.x; v < row_vecs; v += blockDim.x) d[v] = make_uint4(0u, 0u, 0u, 0u);
+    } else {
+      const uint4* sp = reinterpret_cast<const uint4*>(src + (int64_t)s * src_stride_bytes);
+      for (int v = threadIdx.x; v < row_vecs; v += blockDim.x) d[v] = ld_nc_v4(sp + v);
+    }
   }
 }
 
@@ -418,7 +533,8 @@ extern "C" int b200_moe_permute_fp8(void* dst, const void* src, const int32_t* s
 }
 
 extern "C" int b200_moe_unpermute_reduce(void* out, const void* src, const int32_t* inv_perm,
-                                         const float* topk_weights, int64_t num_tokens, int topk,
+                                         const float* topk_weights, const int32_t* num_valid_rows,
+                                         int64_t num_tokens, int topk,
                                          int hidden, int64_t out_stride, int dtype,
                                          b200_stream_t stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
@@ -429,14 +545,64 @@ extern "C" int b200_moe_unpermute_reduce(void* out, const void* src, const int32
              "moe_unpermute: hidden must be a multiple of 8");
   if (dtype == B200_BF16)
     moe_unpermute_reduce_kernel<__nv_bfloat16><<<(unsigned)num_tokens, 256, 0, stream>>>(
-        (__nv_bfloat16*)out, (const __nv_bfloat16*)src, inv_perm, topk_weights, topk, hidden, out_stride);
+        (__nv_bfloat16*)out, (const __nv_bfloat16*)src, inv_perm, topk_weights, num_valid_rows, topk, hidden, out_stride);
   else if (dtype == B200_F16)
     moe_unpermute_reduce_kernel<__half><<<(unsigned)num_tokens, 256, 0, stream>>>(
-        (__half*)out, (const __half*)src, inv_perm, topk_weights, topk, hidden, out_stride);
+        (__half*)out, (const __half*)src, inv_perm, topk_weights, num_valid_rows, topk, hidden, out_stride);
   else {
     set_last_error("moe_unpermute: dtype must be half or bfloat16");
     return B200_ERR_INVALID;
   }
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+extern "C" int b200_moe_mm_data(const int32_t* topk_ids, int32_t* expert_offsets, int32_t* problem_sizes1,
+                                int32_t* problem_sizes2, int32_t* input_permutation,
+                                int32_t* output_permutation, int32_t* blockscale_offsets, int num_experts,
+                                int64_t numel, int topk, int n, int k, int is_gated, int swap_ab,
+                                b200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  B200_CHECK(numel >= 0 && num_experts > 0 && topk > 0 && n > 0 && k > 0, B200_ERR_INVALID,
+             "get_cutlass_moe_mm_data: bad sizes");
+  B200_CHECK(num_experts <= 1024, B200_ERR_UNSUPPORTED, "get_cutlass_moe_mm_data: at most 1024 experts");
+  B200_CHECK(expert_offsets && problem_sizes1 && problem_sizes2 && (numel == 0 || (topk_ids && input_permutation &&
+                                                                                   output_permutation)),
+             B200_ERR_INVALID, "get_cutlass_moe_mm_data: null pointer");
+  B200_CHECK(numel < (1LL << 31), B200_ERR_UNSUPPORTED, "get_cutlass_moe_mm_data: numel too large");
+  const int smem_max = max_smem_optin();
+  B200_CHECK(smem_max > 0, B200_ERR_CUDA, "get_cutlass_moe_mm_data: no CUDA device (no CPU fallback)");
+  int W = ALIGN_WARPS;
+  while (W > 1 && (size_t)(W * num_experts + num_experts + 1) * 4 > (size_t)smem_max - 2048) W >>= 1;
+  const size_t smem = (size_t)(W * num_experts + num_experts + 1) * 4;
+  static size_t cfg = 48 * 1024;
+  if (smem > cfg) {
+    B200_CUDA(cudaFuncSetAttribute(moe_mm_data_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cfg = smem;
+  }
+  moe_mm_data_kernel<<<1, ALIGN_THREADS, smem, stream>>>(topk_ids, expert_offsets, problem_sizes1, problem_sizes2,
+                                                         input_permutation, output_permutation, blockscale_offsets,
+                                                         num_experts, numel, topk, n, k, is_gated ? 2 * n : n,
+                                                         swap_ab, W);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+extern "C" int b200_shuffle_rows(void* dst, const void* src, const int32_t* dst2src_map, int64_t dst_rows,
+                                 int64_t src_rows, int64_t row_bytes, int64_t src_stride_bytes,
+                                 b200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  B200_CHECK(dst_rows >= 0 && src_rows >= 0 && row_bytes > 0, B200_ERR_INVALID, "shuffle_rows: bad sizes");
+  if (dst_rows == 0) return B200_OK;
+  B200_CHECK(dst && dst2src_map && (src || src_rows == 0), B200_ERR_INVALID, "shuffle_rows: null pointer");
+  B200_CHECK(row_bytes % 16 == 0 && src_stride_bytes % 16 == 0 && ((uintptr_t)src & 15) == 0 &&
+                 ((uintptr_t)dst & 15) == 0 && row_bytes / 16 < (1LL << 31),
+             B200_ERR_UNSUPPORTED, "shuffle_rows: rows must be 16-byte aligned multiples of 16 bytes");
+  B200_CHECK(sm_count() > 0, B200_ERR_CUDA, "shuffle_rows: no CUDA device (no CPU fallback)");
+  const int64_t cap = (int64_t)sm_count() * 16;
+  const unsigned blocks = (unsigned)(dst_rows < cap ? dst_rows : cap);
+  shuffle_rows_kernel<<<blocks, 256, 0, stream>>>((uint8_t*)dst, (const uint8_t*)src, dst2src_map, dst_rows,
+                                                  src_rows, (int)(row_bytes / 16), src_stride_bytes);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -74,5 +74,31 @@ __device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src, int
   asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
 
+
+// ---- block-scaled (NVFP4) helpers shared by gemm_nvfp4.cu and moe_gemm_nvfp4.cu
+// 1-D bulk copy global -> shared, completion on an mbarrier
+__device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+      "l"(src), "r"(bytes), "r"(bar)
+      : "memory");
+}
+// 32 rows x 16 bytes of smem -> 32 lanes x 4 columns of TMEM, replicated to the 4 lane quarters
+__device__ __forceinline__ void tc_cp_sf(uint32_t tmem_dst, uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)(128 >> 4) << 32;  // SBO: 8 rows x 16 B
+  d |= (uint64_t)1 << 46;           // SWIZZLE_NONE, LBO unused (one 128-bit atom along K)
+  asm volatile("tcgen05.cp.cta_group::1.32x128b.warpx4 [%0], %1;" ::"r"(tmem_dst), "l"(d) : "memory");
+}
+__device__ __forceinline__ void tc_mma_nvf4(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc,
+                                            uint32_t tsfa, uint32_t tsfb, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::mxf4nvf4.block_scale.block16 [%0], %1, %2, %3, [%5], [%6], p;\n\t}"
+      ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate), "r"(tsfa), "r"(tsfb)
+      : "memory");
+}
+
 }  // namespace tc
 }  // namespace b200
