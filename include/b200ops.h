@@ -409,7 +409,8 @@ B200_API int b200_rotary_embedding(const int64_t* positions, void* query, void* 
  * b200_moe_grouped_gemm_fp8: the grouped GEMM of fused_experts
  *   (vllm/model_executor/layers/fused_moe/fused_moe.py:299-612; cutlass_moe_mm,
  *   csrc/libtorch_stable/quantization/w8a8/cutlass/moe/grouped_mm_c3x_sm100.cu:16-115):
- *   out[i,:] = a_scale * w_scale[e] * (a_sorted[i,:] . w[e]^T) (* row_weight[i]) for every block of
+ *   out[i,:] = a_scale * w_scale[e] * (a_sorted[i,:] . w[e]^T) (* row_weight[i]) (a_scale: one float, or one per
+ *   sorted row when a_scale_per_row) for every block of
  *   block_size sorted rows with expert e = expert_ids[block] >= 0. w: e4m3 [E, N, K] contiguous.
  */
 B200_API int b200_moe_align_block_size(const void* topk_ids, int topk_ids_dtype, int64_t numel,
@@ -438,7 +439,25 @@ B200_API int b200_moe_grouped_gemm_fp8(void* out, const void* a_sorted, const vo
                                        const float* a_scale, const float* w_scale,
                                        const float* row_weight, int64_t max_rows, int num_experts,
                                        int N, int K, int block_size, int w_scale_per_channel,
-                                       int out_dtype, b200_stream_t stream);
+                                       int a_scale_per_row, int out_dtype, b200_stream_t stream);
+/* Per-token / block-scaled activation quantisation happens in TOKEN order (scaled_fp8_quant with
+ * use_per_token_if_dynamic, per_token_group_quant_fp8: fused_moe/utils.py:138-161), then
+ * b200_moe_permute_rows gathers the quantised rows and their scale rows into sorted order:
+ * dst[i,:] = src[sorted_token_ids[i] / topk, :], scale_dst[i, 0..scale_cols) likewise (pad rows: zeros).
+ * b200_moe_grouped_gemm_fp8_blockscaled: fused_experts with block_shape = [128, 128] (fused_moe.py:478-560):
+ * out[i,n] = sum_kb a_scales[i,kb] * w_scales[e, n/128, kb] * (a_sorted[i, kb-th 128 columns] . w[e, n, same]),
+ * a_scales float [max_rows, ceil(K/128)] row-major, w_scales float [E, ceil(N/128), ceil(K/128)]. */
+B200_API int b200_moe_permute_rows(void* dst, const void* src, const int32_t* sorted_token_ids,
+                                   const int32_t* num_tokens_post_pad, float* scale_dst, const float* scale_src,
+                                   int scale_cols, int64_t scale_src_stride, int64_t max_rows, int topk,
+                                   int64_t numel, int64_t row_bytes, int64_t src_stride_bytes,
+                                   b200_stream_t stream);
+B200_API int b200_moe_grouped_gemm_fp8_blockscaled(void* out, const void* a_sorted, const void* w,
+                                                   const int32_t* expert_ids,
+                                                   const int32_t* num_tokens_post_pad, const float* a_scales,
+                                                   const float* w_scales, int64_t max_rows, int num_experts,
+                                                   int N, int K, int block_size, int out_dtype,
+                                                   b200_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Legacy-layout paged attention. Replaces torch.ops._C.paged_attention_v1 / paged_attention_v2

@@ -971,3 +971,83 @@ def cutlass_moe_fp4(a: torch.Tensor, a1_gscale: np.ndarray, w1_codes: np.ndarray
     if return_stages:
         return out, dict(data=d, rep_a=rep_a, c1=c1, c3=c3, a_codes=c_a, h_codes=c_h)
     return out
+
+
+# --------------------------------------------------------------------------------------------
+# fused_experts, the other FP8 quantisation schemes of fused_experts_impl (fused_moe.py:1764-1770, 1813-1819
+# through moe_kernel_quantize_input / _fp8_quantize, fused_moe/utils.py:138-161):
+#   "channel": per_channel_quant=True -> dynamic PER-TOKEN activation scales, weight scales [E, N];
+#   "block":   block_shape=[128,128]  -> per-token-group (1x128) activation scales, weight scales [E, N/128, K/128];
+#   "tensor":  per-tensor (the function above, kept for its callers).
+# apply_router_weight_on_input (fused_moe.py:1757-1762, topk = 1): x * w rounded to the activation dtype first.
+# Vectorised per expert; GEMM results rounded to the activation dtype where the kernels round them.
+# --------------------------------------------------------------------------------------------
+def fused_experts_fp8_scheme(x: torch.Tensor, w1_bits: torch.Tensor, w2_bits: torch.Tensor,
+                             topk_weights: torch.Tensor, topk_ids: torch.Tensor, w1_scale: torch.Tensor,
+                             w2_scale: torch.Tensor, scheme: str, a1_scale=None, a2_scale=None,
+                             apply_router_weight_on_input: bool = False) -> torch.Tensor:
+    assert scheme in ("tensor", "channel", "block")
+    dt = x.dtype
+    M, H = x.shape
+    E, N1, _ = w1_bits.shape
+    I = N1 // 2
+    topk = topk_ids.shape[1]
+    if apply_router_weight_on_input:
+        assert topk == 1
+        x = x * topk_weights.to(dt)
+
+    def quant(t, static):
+        """-> (dequantisable values fp64 [rows, K], scale array broadcastable per (row, k-block))"""
+        if scheme == "block":
+            bits, s = per_token_group_quant_fp8(t, 128)
+            return e4m3_bits_to_f32(bits).astype(np.float64), s.astype(np.float64)
+        if static is not None:
+            return e4m3_bits_to_f32(static_scaled_fp8_quant(t, static)).astype(np.float64), \
+                np.full((t.shape[0], 1), float(static.reshape(-1)[0]))
+        if scheme == "channel":
+            bits, s = dynamic_per_token_scaled_fp8_quant(t)
+            return e4m3_bits_to_f32(bits).astype(np.float64), s.astype(np.float64)
+        bits, s = dynamic_scaled_fp8_quant(t)
+        return e4m3_bits_to_f32(bits).astype(np.float64), np.full((t.shape[0], 1), float(s[0]))
+
+    def mm(a, a_s, wb, w_s):
+        """a fp64 [r, K] with scales a_s; wb uint8 [N, K]; w_s per scheme -> fp32 [r, N] rounded to dt"""
+        w = e4m3_bits_to_f32(wb.numpy()).astype(np.float64)
+        if scheme == "block":
+            K = a.shape[1]
+            out = np.zeros((a.shape[0], w.shape[0]))
+            ws = np.asarray(w_s, dtype=np.float64)            # [N/128, K/128]
+            for kb in range((K + 127) // 128):
+                ks = slice(kb * 128, min(K, (kb + 1) * 128))
+                out += (a[:, ks] @ w[:, ks].T) * a_s[:, kb:kb + 1] * np.repeat(ws[:, kb], 128)[None, :w.shape[0]]
+        else:
+            ws = np.asarray(w_s, dtype=np.float64).reshape(1, -1)   # [1, 1] or [1, N]
+            out = (a @ w.T) * a_s * ws
+        return torch.from_numpy(out.astype(np.float32)).to(dt)
+
+    x8, x_s = quant(x, a1_scale)
+    flat = topk_ids.reshape(-1).numpy()
+    inter = torch.zeros(M * topk, N1, dtype=dt)
+    for e in range(E):
+        rows = np.nonzero(flat == e)[0]
+        if rows.size:
+            tok = rows // topk
+            inter[torch.from_numpy(rows)] = mm(x8[tok], x_s[tok], w1_bits[e], w1_scale[e].numpy())
+    valid = flat >= 0
+    act = torch.zeros(M * topk, I, dtype=dt)
+    act[torch.from_numpy(valid)] = silu_and_mul(inter[torch.from_numpy(valid)])
+    # the dynamic per-tensor scale reduces over the rows that exist (dropped pairs never enter the buffer)
+    h8 = np.zeros((M * topk, I))
+    h_s = np.zeros((M * topk, max(1, I // 128 if scheme == "block" else 1)))
+    vi = np.nonzero(valid)[0]
+    q, s = quant(act[torch.from_numpy(vi)], a2_scale)
+    h8[vi], h_s[vi] = q, s
+    out2 = torch.zeros(M * topk, H, dtype=dt)
+    for e in range(E):
+        rows = np.nonzero(flat == e)[0]
+        if rows.size:
+            out2[torch.from_numpy(rows)] = mm(h8[rows], h_s[rows], w2_bits[e], w2_scale[e].numpy())
+    o = out2.float().view(M, topk, H)
+    if not apply_router_weight_on_input:
+        o = o * topk_weights.float().view(M, topk, 1)
+    return o.sum(dim=1)

@@ -163,3 +163,36 @@ def test_cutlass_moe_fp4_oracle_vs_reference_test_model():
     out1 = ref_ops.cutlass_moe_fp4(a, one, w1c, w1s, 1 / w1gs, one, w2c, w2s, 1 / w2gs, tw, ti2)
     outk1 = ref_ops.cutlass_moe_fp4(a, one, w1c, w1s, 1 / w1gs, one, w2c, w2s, 1 / w2gs, tw[:, :1], ti2[:, :1])
     assert torch.equal(out1, outk1)
+
+
+def _bits(t):
+    return t.clamp(-448, 448).to(torch.float8_e4m3fn).view(torch.uint8)
+
+
+def test_fused_experts_scheme_oracle_consistency():
+    """the vectorised multi-scheme oracle equals the original per-token loop on the per-tensor scheme, and its
+    block scheme equals w8a8_block_scaled_mm (native_w8a8_block_matmul restated) composed by hand."""
+    g = torch.Generator().manual_seed(2)
+    M, E, topk, H, I = 12, 4, 2, 256, 128
+    x = (torch.randn(M, H, generator=g) * 0.5).to(torch.bfloat16)
+    w1, w2 = _bits(torch.randn(E, 2 * I, H, generator=g)), _bits(torch.randn(E, H, I, generator=g))
+    w1s, w2s = torch.rand(E, generator=g) * 0.05 + 0.01, torch.rand(E, generator=g) * 0.05 + 0.01
+    tw, ti, _ = ref_ops.topk_softmax(torch.randn(M, E, generator=g), topk, True)
+    a1, a2 = torch.tensor([0.01]), torch.tensor([0.02])
+    old = ref_ops.fused_experts_fp8(x, w1, w2, tw, ti, w1s, w2s, a1, a2)
+    new = ref_ops.fused_experts_fp8_scheme(x, w1, w2, tw, ti, w1s, w2s, "tensor", a1_scale=a1, a2_scale=a2)
+    torch.testing.assert_close(new, old, rtol=1e-6, atol=1e-6)
+    # block scheme, one token through one expert by hand
+    w1b = torch.rand(E, 2 * I // 128, H // 128, generator=g) * 0.05 + 0.01
+    w2b = torch.rand(E, H // 128, I // 128, generator=g) * 0.05 + 0.01
+    ti1 = ti[:, :1].contiguous()
+    tw1 = torch.ones(M, 1)
+    got = ref_ops.fused_experts_fp8_scheme(x, w1, w2, tw1, ti1, w1b, w2b, "block")
+    t = 5
+    e = int(ti1[t, 0])
+    q, s = ref_ops.per_token_group_quant_fp8(x[t:t + 1], 128)
+    h = torch.from_numpy(ref_ops.w8a8_block_scaled_mm(q, w1[e].numpy(), s, w1b[e].numpy())).to(torch.bfloat16)
+    act = ref_ops.silu_and_mul(h)
+    q2, s2 = ref_ops.per_token_group_quant_fp8(act, 128)
+    o = torch.from_numpy(ref_ops.w8a8_block_scaled_mm(q2, w2[e].numpy(), s2, w2b[e].numpy())).to(torch.bfloat16)
+    torch.testing.assert_close(got[t], o[0].float(), rtol=1e-6, atol=1e-6)

@@ -265,9 +265,9 @@ def bench_moe(W):
 
         def ours_pair(i):
             lib.b200_moe_grouped_gemm_fp8(_p(o1), _p(a8), _p(w1), _p(expert_ids), _p(npp), _p(a1), _p(w1s), None, P, E,
-                                          2 * I, H, bs, 0, _dt(o1), _stream())
+                                          2 * I, H, bs, 0, 0, _dt(o1), _stream())
             lib.b200_moe_grouped_gemm_fp8(_p(o2), _p(h8), _p(w2), _p(expert_ids), _p(npp), _p(a2), _p(w2s), None, P, E,
-                                          H, I, bs, 0, _dt(o2), _stream())
+                                          H, I, bs, 0, 0, _dt(o2), _stream())
 
         t_p = graph_time(ours_pair, 1, iters=6)
         report("grouped GEMM pair vs cutlass_moe_mm x2", f"C4 M={M} E={E} top{k}", t_p, t_w,

@@ -200,7 +200,13 @@ SIGNATURES = {
                 c_void_p]),
     "b200_moe_grouped_gemm_fp8": (
         c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
-                c_int64, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+                c_int64, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "b200_moe_permute_rows": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int64, c_int,
+                c_int64, c_int64, c_int64, c_void_p]),
+    "b200_moe_grouped_gemm_fp8_blockscaled": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int,
+                c_int, c_int, c_int, c_void_p]),
     "b200_nvfp4_quant": (
         c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int64, c_int, c_int, c_void_p]),
     "b200_nvfp4_gemm": (

@@ -120,15 +120,23 @@ def fused_experts(
     block_shape=None,
     **unsupported,
 ) -> torch.Tensor:
-    """out[t] = sum_k w[t,k] * W2[e] . silu_and_mul(W1[e] . x_t), FP8 W8A8 with per-tensor activation
-    scales (static if given, dynamic per-tensor otherwise) and per-expert (or per-channel) weight
-    scales. hidden_states [M,H] bf16/f16; w1 [E, 2I, H], w2 [E, H, I] e4m3; topk_weights f32 [M,k];
-    topk_ids int [M,k]; expert_map int32 [E_global] -> local id or -1 (expert parallel)."""
+    """out[t] = sum_k w[t,k] * W2[e] . silu_and_mul(W1[e] . x_t), FP8 W8A8 (fused_moe.py:1448-1535, 1587-1853).
+
+    hidden_states [M,H] bf16/f16; w1 [E, 2I, H], w2 [E, H, I] e4m3; topk_weights [M,k]; topk_ids int [M,k];
+    expert_map int32 [E_global] -> local id or -1 (expert parallel). Quantisation schemes, as the reference's
+    moe_kernel_quantize_input selects them (fused_moe/utils.py:138-161, call sites fused_moe.py:1764-1770,1813-1819):
+      * per-tensor: a*_scale given -> static, else dynamic over the whole batch; w*_scale [E] (or [E, N] with
+        per_channel_quant);
+      * per_channel_quant=True and a*_scale None: dynamic PER-TOKEN activation scales, w*_scale [E, N];
+      * block_shape=[128, 128]: per-token-group (1 x 128) activation scales, w*_scale [E, N/128, K/128].
+    apply_router_weight_on_input (topk == 1): the router weight multiplies the input, not the output
+    (fused_moe.py:1757-1762)."""
     if not use_fp8_w8a8:
-        raise NotImplementedError("b200ops.fused_experts: only use_fp8_w8a8=True is built")
-    if activation != "silu" or apply_router_weight_on_input or block_shape is not None or \
-            any(v not in (None, False) for v in unsupported.values()):
+        raise NotImplementedError("b200ops.fused_experts: only use_fp8_w8a8=True is built (NVFP4: cutlass_moe_fp4)")
+    if activation != "silu" or any(v not in (None, False) for v in unsupported.values()):
         raise NotImplementedError("b200ops.fused_experts: unsupported option")
+    if block_shape is not None and (list(block_shape) != [128, 128] or per_channel_quant):
+        raise NotImplementedError("b200ops.fused_experts: block_shape must be [128, 128] without per_channel_quant")
     _cuda(hidden_states, w1, w2, topk_weights, topk_ids, expert_map, w1_scale, w2_scale, a1_scale, a2_scale)
     lib = _lib.load()
     M, H = hidden_states.shape
@@ -142,39 +150,83 @@ def fused_experts(
     numel = M * topk
     Eg = global_num_experts if global_num_experts > 0 else E
     dev, dt = hidden_states.device, hidden_states.dtype
+    if apply_router_weight_on_input:
+        if topk != 1:
+            raise RuntimeError("apply_router_weight_on_input is only implemented for topk=1")
+        hidden_states = hidden_states * topk_weights.to(dt)
     bs = _block_size_for(numel / max(E, 1))
     sorted_ids, expert_ids, npp, inv = moe_align_block_size(
         topk_ids, bs, Eg, expert_map, pad_sorted_ids=True, ignore_invalid_experts=True,
         return_inv_perm=True)
     P = sorted_ids.numel()
-    if a1_scale is None:  # dynamic per-tensor: scale = max|x| / 448 (same kernel as scaled_fp8_quant)
-        _, a1_scale = ops.scaled_fp8_quant(hidden_states)
-    a8 = torch.zeros(P, H, dtype=torch.uint8, device=dev)
-    rc = lib.b200_moe_permute_fp8(_p(a8), _p(hidden_states), _p(sorted_ids), _p(npp), _p(a1_scale), P,
-                                  topk, numel, H, hidden_states.stride(0), _dt(hidden_states), _stream())
-    _lib.check(rc, "moe_permute")
+    blockwise = block_shape is not None
+    per_token = per_channel_quant and not blockwise
+
+    def permute_rows(q, scales):
+        """token-order quantised rows [M, K] (+ scale rows [M, C]) -> sorted order [P, K] (+ [P, C])"""
+        K = q.shape[1]
+        dst = torch.empty(P, K, dtype=torch.uint8, device=dev)
+        C = scales.shape[1]
+        sdst = torch.empty(P, C, dtype=torch.float32, device=dev)
+        rc = lib.b200_moe_permute_rows(_p(dst), _p(q), _p(sorted_ids), _p(npp), _p(sdst), _p(scales), C,
+                                       scales.stride(0), P, topk, numel, K, q.stride(0), _stream())
+        _lib.check(rc, "moe_permute_rows")
+        return dst, sdst
+
+    def grouped(out, a8, w, a_s, w_s, N, K, a_rows):
+        if blockwise:
+            rc = lib.b200_moe_grouped_gemm_fp8_blockscaled(_p(out), _p(a8), _p(w), _p(expert_ids), _p(npp), _p(a_s),
+                                                           _p(w_s), P, E, N, K, bs, _dt(out), _stream())
+        else:
+            rc = lib.b200_moe_grouped_gemm_fp8(_p(out), _p(a8), _p(w), _p(expert_ids), _p(npp), _p(a_s), _p(w_s),
+                                               None, P, E, N, K, bs, 1 if per_channel_quant else 0,
+                                               1 if a_rows else 0, _dt(out), _stream())
+        _lib.check(rc, "moe_grouped_gemm_fp8")
+
+    if blockwise:
+        if w1_scale is None or w2_scale is None or not w1_scale.is_contiguous() or not w2_scale.is_contiguous():
+            raise RuntimeError("fused_experts: block_shape needs contiguous w1_scale / w2_scale")
+        q, s = ops.per_token_group_quant_fp8(hidden_states, 128)
+        a8, a1_rows = permute_rows(q.view(torch.uint8), s)
+        a1_s = a1_rows
+    elif per_token and a1_scale is None:
+        q, s = ops.scaled_fp8_quant(hidden_states, None, use_per_token_if_dynamic=True)
+        a8, a1_rows = permute_rows(q.view(torch.uint8), s.view(M, 1))
+        a1_s = a1_rows
+    else:
+        if a1_scale is None:  # dynamic per-tensor: scale = max|x| / 448 (same kernel as scaled_fp8_quant)
+            _, a1_scale = ops.scaled_fp8_quant(hidden_states)
+        a8 = torch.empty(P, H, dtype=torch.uint8, device=dev)
+        rc = lib.b200_moe_permute_fp8(_p(a8), _p(hidden_states), _p(sorted_ids), _p(npp), _p(a1_scale), P,
+                                      topk, numel, H, hidden_states.stride(0), _dt(hidden_states), _stream())
+        _lib.check(rc, "moe_permute")
+        a1_s = a1_scale
     # blocks past num_tokens_post_pad are skipped by the GEMMs and never gathered: zero-fill only when a
     # dynamic activation scale will reduce over the whole buffer
-    inter = (torch.zeros if a2_scale is None else torch.empty)(P, N1, dtype=dt, device=dev)
-    rc = lib.b200_moe_grouped_gemm_fp8(_p(inter), _p(a8), _p(w1), _p(expert_ids), _p(npp),
-                                       _p(a1_scale), _p(w1_scale), None, P, E, N1, H, bs,
-                                       1 if per_channel_quant else 0, _dt(inter), _stream())
-    _lib.check(rc, "moe_grouped_gemm_fp8")
+    dynamic2 = a2_scale is None
+    inter = (torch.zeros if dynamic2 else torch.empty)(P, N1, dtype=dt, device=dev)
+    grouped(inter, a8, w1, a1_s, w1_scale, N1, H, a_rows=(per_token and a1_scale is None))
     h8 = torch.empty(P, I, dtype=torch.float8_e4m3fn, device=dev)
-    if a2_scale is None:
+    a2_rows = False
+    if blockwise:
         act = torch.empty(P, I, dtype=dt, device=dev)
         ops.silu_and_mul(act, inter)
-        _, a2_scale = ops.scaled_fp8_quant(act, output=h8)
+        h8, a2_s = ops.per_token_group_quant_fp8(act, 128)
+    elif dynamic2:
+        act = torch.empty(P, I, dtype=dt, device=dev)
+        ops.silu_and_mul(act, inter)
+        if per_token:
+            _, a2_s = ops.scaled_fp8_quant(act, None, use_per_token_if_dynamic=True, output=h8)
+            a2_rows = True
+        else:
+            _, a2_s = ops.scaled_fp8_quant(act, output=h8)
     else:
         ops.silu_and_mul_quant(h8, inter, a2_scale)
-    # row weights in sorted order: w_sorted[inv[t*k + j]] = topk_weights[t, j]
+        a2_s = a2_scale
     out2 = torch.empty(P, H, dtype=dt, device=dev)
-    rc = lib.b200_moe_grouped_gemm_fp8(_p(out2), _p(h8), _p(w2), _p(expert_ids), _p(npp),
-                                       _p(a2_scale), _p(w2_scale), None, P, E, H, I, bs,
-                                       1 if per_channel_quant else 0, _dt(out2), _stream())
-    _lib.check(rc, "moe_grouped_gemm_fp8")
+    grouped(out2, h8, w2, a2_s, w2_scale, H, I, a_rows=a2_rows)
     out = torch.empty(M, H, dtype=dt, device=dev)
-    tw = topk_weights.to(torch.float32).contiguous()
+    tw = None if apply_router_weight_on_input else topk_weights.to(torch.float32).contiguous()
     rc = lib.b200_moe_unpermute_reduce(_p(out), _p(out2), _p(inv), _p(tw), None, M, topk, H, out.stride(0),
                                        _dt(out), _stream())
     _lib.check(rc, "moe_unpermute")

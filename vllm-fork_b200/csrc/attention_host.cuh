@@ -110,7 +110,10 @@ static size_t ws_cum_bytes(int S) { return (size_t)(((S + 2) * 4 + 255) & ~255);
 template <int D, int NT, int MODE>
 static int launch(const CUtensorMap& tmK, const CUtensorMap& tmV, const Params& p, const Plan& pl,
                   cudaStream_t stream) {
-  static bool configured = false;
+  static bool configured_dev[64] = {};   // the attribute is per device
+  int cfg_dev_ = 0;
+  cudaGetDevice(&cfg_dev_);
+  bool& configured = configured_dev[cfg_dev_ & 63];
   static int configured_smem = 0;
   auto kern = paged_attn_decode_kernel<D, NT, MODE>;
   if (!configured || configured_smem < (int)pl.smem_bytes) {

@@ -475,7 +475,10 @@ static int make_kv8_tmap(CUtensorMap* tm, const void* base, int64_t nb, int64_t 
 template <bool QBF16, bool GENERAL>
 static int launch_tc8(const CUtensorMap& tmK, const CUtensorMap& tmV, const Params& p, cudaStream_t stream) {
   constexpr int smem = 4 * (int)TC_TILE + 4 * (int)TC8_RAW + 1024 + 256;
-  static bool configured = false;
+  static bool configured_dev[64] = {};   // the attribute is per device
+  int cfg_dev_ = 0;
+  cudaGetDevice(&cfg_dev_);
+  bool& configured = configured_dev[cfg_dev_ & 63];
   auto kern = varlen_attn_tc8_kernel<QBF16, GENERAL>;
   if (!configured) {
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -490,7 +493,10 @@ static int launch_tc8(const CUtensorMap& tmK, const CUtensorMap& tmV, const Para
 template <bool BF16, bool GENERAL>
 static int launch_tc(const CUtensorMap& tmK, const CUtensorMap& tmV, const Params& p, cudaStream_t stream) {
   constexpr int smem = 6 * (int)TC_TILE + 1024 + 256;
-  static bool configured = false;
+  static bool configured_dev[64] = {};   // the attribute is per device
+  int cfg_dev_ = 0;
+  cudaGetDevice(&cfg_dev_);
+  bool& configured = configured_dev[cfg_dev_ & 63];
   auto kern = varlen_attn_tc_kernel<BF16, GENERAL>;
   if (!configured) {
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -506,7 +512,10 @@ template <int D, int MODE>
 static int launch(const Params& p, cudaStream_t stream) {
   constexpr int ES = (MODE == BF16_FP8 || MODE == F16_FP8) ? 1 : 2;
   constexpr int smem = 2 * 2 * BN * D * ES + 128;
-  static bool configured = false;
+  static bool configured_dev[64] = {};   // the attribute is per device
+  int cfg_dev_ = 0;
+  cudaGetDevice(&cfg_dev_);
+  bool& configured = configured_dev[cfg_dev_ & 63];
   auto kern = varlen_attn_kernel<D, MODE>;
   if (!configured) {
     B200_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

@@ -44,6 +44,12 @@ struct Params {
   int stages;
   int tma_store;
   int split;   // K slices = CTAs per thread-block cluster (1, 1, split); 1 = no cluster
+  // grouped (fused-MoE) mode: grid = (token blocks of BN sorted rows, weight slabs); block b uses expert
+  // expert_ids[b] (weight slice e of the 3-D map, scale matrix b_s + e * bs_e) and is skipped when the id is
+  // negative or the block starts at / after *num_tokens_post_pad. Null expert_ids = plain GEMM.
+  const int32_t* expert_ids;
+  const int32_t* num_tokens_post_pad;
+  int64_t bs_e;
 };
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -75,6 +81,15 @@ __global__ void __launch_bounds__(NTHREADS, 1)
                              ((uint32_t)(BM >> 4) << 24);
   constexpr int NCH = BN / 16;
 
+  const bool grouped = p.expert_ids != nullptr;
+  const int wt = grouped ? blockIdx.y : blockIdx.x;   // weight slab
+  const int tt = grouped ? blockIdx.x : blockIdx.y;   // token tile
+  int expert = 0;
+  if (grouped) {
+    expert = p.expert_ids[tt];
+    if (expert < 0 || tt * BN >= *p.num_tokens_post_pad) return;   // uniform for the CTA
+  }
+
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_base = smem_u32(smem_raw);
   const uint32_t base = (raw_base + 1023u) & ~1023u;
@@ -91,8 +106,8 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   float* sc = reinterpret_cast<float*>(tail + 16);   // 16-byte aligned: base is 1024-aligned, offsets are x16
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int row0 = blockIdx.x * BM;   // weight rows (output columns)
-  const int col0 = blockIdx.y * BN;   // tokens (output rows)
+  const int row0 = wt * BM;   // weight rows (output columns)
+  const int col0 = tt * BN;   // tokens (output rows)
   // split-K: CTA `ks` of the cluster contracts k-blocks [kb0, kb0 + num_kb) of the tile
   const int total_kb = (p.K + BK - 1) / BK;
   const int ks = p.split > 1 ? (int)cluster_ctarank() : 0;
@@ -120,7 +135,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
     // ============================== TMA producer (warp-uniform loop, one elected lane issues: common.cuh elect_one)
     prefetch_tmap(&tmW);
     prefetch_tmap(&tmA);
-    const uint64_t pol_w = gridDim.y > 1 ? l2_policy_evict_last() : l2_policy_evict_first();
+    const uint64_t pol_w = (grouped || gridDim.y > 1) ? l2_policy_evict_last() : l2_policy_evict_first();
     const uint64_t pol_a = l2_policy_evict_last();
     int stage = 0;
     uint32_t phase = 0;
@@ -129,7 +144,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
       if (elect_one()) {
         const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES;
         mbar_arrive_expect_tx(bar_full + 8u * stage, STAGE_BYTES);
-        tma_load_2d(dst, &tmW, bar_full + 8u * stage, (kb0 + kb) * BK, row0, pol_w);
+        tma_load_3d(dst, &tmW, bar_full + 8u * stage, (kb0 + kb) * BK, row0, expert, pol_w);
         tma_load_2d(dst + W_BYTES, &tmA, bar_full + 8u * stage, (kb0 + kb) * BK, col0, pol_a);
       }
       __syncwarp();
@@ -164,7 +179,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
     const int et = wq * 32 + lane;        // 0..127: TMEM lane = weight row of the tile
     const int r = row0 + et;              // output column n
     const bool r_ok = r < p.N;
-    const float* bs_col = p.b_s + (int64_t)blockIdx.x * p.bs_n;
+    const float* bs_col = p.b_s + (int64_t)expert * p.bs_e + (int64_t)wt * p.bs_n;
     // this thread stages the combined scale of token (col0 + et) when et < BN
     const int my_m = col0 + et;
     const bool stage_it = et < BN;
@@ -306,7 +321,10 @@ static int launch(const CUtensorMap& tmW, const CUtensorMap& tmA, const CUtensor
   }
   p.stages = stages;
   const int smem = stages * (int)STAGE_BYTES + TAIL + 64 + 1024;
-  static bool configured = false;
+  static bool configured_dev[64] = {};   // the attribute is per device
+  int cfg_dev_ = 0;
+  cudaGetDevice(&cfg_dev_);
+  bool& configured = configured_dev[cfg_dev_ & 63];
   if (!configured) {
     B200_CUDA(cudaFuncSetAttribute(gemm_fp8_block_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    smem_max));
@@ -317,7 +335,7 @@ static int launch(const CUtensorMap& tmW, const CUtensorMap& tmA, const CUtensor
   // (split - 1) fp32 partial tiles must fit slice 0's pipeline smem.
   const int total_kb = (p.K + BK - 1) / BK;
   int split = 1;
-  if (grid.y == 1) {
+  if (grid.y == 1 && !p.expert_ids) {
     const int want = p.split;   // 0 = auto
     for (int sp = 8; sp >= 2; sp >>= 1) {
       const bool fits = (sp - 1) * BN * BM * 4 <= stages * (int)STAGE_BYTES && sp <= total_kb;
@@ -346,6 +364,15 @@ static int launch(const CUtensorMap& tmW, const CUtensorMap& tmA, const CUtensor
   cfg.numAttrs = 1;
   B200_CUDA(cudaLaunchKernelEx(&cfg, gemm_fp8_block_kernel<BN>, tmW, tmA, tmO, p));
   return B200_OK;
+}
+
+// weights: [K, N, E] (E = 1 for the plain GEMM)
+static int make_tmap_w(CUtensorMap* tm, const void* base, int rows, int K, int64_t ld_bytes, int experts) {
+  uint64_t dims[3] = {(uint64_t)K, (uint64_t)rows, (uint64_t)experts};
+  uint64_t strides[2] = {(uint64_t)ld_bytes, (uint64_t)ld_bytes * (uint64_t)rows};
+  uint32_t box[3] = {(uint32_t)BK, (uint32_t)BM, 1u};
+  return encode_tensor_map(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box,
+                           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
 }
 
 static int make_tmap_2d(CUtensorMap* tm, const void* base, int rows, int K, int64_t ld_bytes, int box_rows) {
@@ -393,7 +420,7 @@ extern "C" int b200_fp8_gemm_blockscaled(void* out, const void* a, const void* b
   const int bn = M <= 16 ? 16 : M <= 32 ? 32 : M <= 64 ? 64 : 128;
   CUtensorMap tmW, tmA, tmO;
   memset(&tmO, 0, sizeof(tmO));
-  int rc = make_tmap_2d(&tmW, b, N, K, ldb, BM);
+  int rc = make_tmap_w(&tmW, b, N, K, ldb, 1);
   if (rc) return rc;
   rc = make_tmap_2d(&tmA, a, M, K, lda, bn);
   if (rc) return rc;
@@ -409,6 +436,71 @@ extern "C" int b200_fp8_gemm_blockscaled(void* out, const void* a, const void* b
   dim3 grid((N + BM - 1) / BM, (M + bn - 1) / bn);
   B200_CHECK(grid.y <= 65535, B200_ERR_UNSUPPORTED, "cutlass_scaled_mm (blockwise): M too large (%d)", M);
   switch (bn) {
+    case 16: return launch<16>(tmW, tmA, tmO, p, grid, stream);
+    case 32: return launch<32>(tmW, tmA, tmO, p, grid, stream);
+    case 64: return launch<64>(tmW, tmA, tmO, p, grid, stream);
+    default: return launch<128>(tmW, tmA, tmO, p, grid, stream);
+  }
+}
+
+// Grouped (fused-MoE) form: fused_experts with block_shape = [128, 128]
+// (vllm/model_executor/layers/fused_moe/fused_moe.py:299-612 use_fp8_w8a8 + block_shape branch :478-560, w8a8 block
+// scales a_scale [rows, K/128], b_scale [E, N/128, K/128]).
+extern "C" int b200_moe_grouped_gemm_fp8_blockscaled(void* out, const void* a_sorted, const void* w,
+                                                     const int32_t* expert_ids,
+                                                     const int32_t* num_tokens_post_pad, const float* a_scales,
+                                                     const float* w_scales, int64_t max_rows, int num_experts,
+                                                     int N, int K, int block_size, int out_dtype,
+                                                     b200_stream_t stream_) {
+  using namespace b200;
+  using namespace b200::gemm8b;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  B200_CHECK(max_rows >= 0 && num_experts > 0 && N > 0 && K > 0, B200_ERR_INVALID,
+             "moe_grouped_gemm_fp8_blockscaled: bad sizes");
+  if (max_rows == 0) return B200_OK;
+  B200_CHECK(out && a_sorted && w && expert_ids && num_tokens_post_pad && a_scales && w_scales, B200_ERR_INVALID,
+             "moe_grouped_gemm_fp8_blockscaled: null pointer");
+  B200_CHECK(block_size == 16 || block_size == 32 || block_size == 64 || block_size == 128, B200_ERR_UNSUPPORTED,
+             "moe_grouped_gemm_fp8_blockscaled: block_size must be 16, 32, 64 or 128 (got %d)", block_size);
+  B200_CHECK(max_rows % block_size == 0 && max_rows < (1LL << 31), B200_ERR_INVALID,
+             "moe_grouped_gemm_fp8_blockscaled: the sorted buffer must hold a whole number of blocks");
+  B200_CHECK(K % 16 == 0 && N % 8 == 0, B200_ERR_INVALID,
+             "moe_grouped_gemm_fp8_blockscaled: K must be a multiple of 16 and N of 8");
+  B200_CHECK(out_dtype == B200_BF16 || out_dtype == B200_F16, B200_ERR_INVALID,
+             "moe_grouped_gemm_fp8_blockscaled: out dtype must be bf16 or f16");
+  B200_CHECK(((uintptr_t)a_sorted & 15) == 0 && ((uintptr_t)w & 15) == 0 && ((uintptr_t)out & 15) == 0,
+             B200_ERR_INVALID, "moe_grouped_gemm_fp8_blockscaled: tensors must be 16-byte aligned");
+  B200_CHECK(sm_count() > 0, B200_ERR_CUDA, "moe_grouped_gemm_fp8_blockscaled: no CUDA device (no CPU fallback)");
+  const int KB = (K + BK - 1) / BK, NB = (N + BM - 1) / BM;
+  Params p;
+  memset(&p, 0, sizeof(p));
+  p.out = out;
+  p.a_s = a_scales; p.b_s = w_scales;
+  p.as_m = KB; p.as_k = 1;          // a_scales [max_rows, KB] row-major
+  p.bs_k = 1; p.bs_n = KB;          // w_scales [E, NB, KB]
+  p.bs_e = (int64_t)NB * KB;
+  p.M = (int)max_rows; p.N = N; p.K = K;
+  p.ldo = N;
+  p.out_bf16 = out_dtype == B200_BF16;
+  p.split = 1;
+  p.tma_store = 1;
+  p.expert_ids = expert_ids;
+  p.num_tokens_post_pad = num_tokens_post_pad;
+  CUtensorMap tmW, tmA, tmO;
+  int rc = make_tmap_w(&tmW, w, N, K, K, num_experts);
+  if (rc) return rc;
+  rc = make_tmap_2d(&tmA, a_sorted, (int)max_rows, K, K, block_size);
+  if (rc) return rc;
+  {
+    uint64_t dims[2] = {(uint64_t)N, (uint64_t)max_rows};
+    uint64_t strides[1] = {(uint64_t)N * 2};
+    uint32_t box[2] = {(uint32_t)BM, (uint32_t)block_size};
+    rc = encode_tensor_map(&tmO, CU_TENSOR_MAP_DATA_TYPE_UINT16, 2, out, dims, strides, box,
+                           CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE);
+    if (rc) return rc;
+  }
+  dim3 grid((unsigned)(max_rows / block_size), NB);
+  switch (block_size) {
     case 16: return launch<16>(tmW, tmA, tmO, p, grid, stream);
     case 32: return launch<32>(tmW, tmA, tmO, p, grid, stream);
     case 64: return launch<64>(tmW, tmA, tmO, p, grid, stream);

@@ -287,7 +287,10 @@ static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, const CUtensor
   }
   p.stages = stages;
   const int smem = stages * (int)STAGE_BYTES + 16 * MAX_STAGES + 64 + 1024;
-  static bool configured = false;
+  static bool configured_dev[64] = {};   // the attribute is per device
+  int cfg_dev_ = 0;
+  cudaGetDevice(&cfg_dev_);
+  bool& configured = configured_dev[cfg_dev_ & 63];
   if (!configured) {
     B200_CUDA(cudaFuncSetAttribute(gemm_nvfp4_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    smem_max));

@@ -26,10 +26,10 @@ constexpr int BM = 128, BK = 128, UMMA_K = 32, NTHREADS = 192, MAX_STAGES = 8;
 struct Params {
   const int32_t* expert_ids;
   const int32_t* num_tokens_post_pad;
-  const float* a_scale;     // [1]
+  const float* a_scale;     // [1], or [P] one per sorted row (a_scale_per_row: per-token activation quant)
   const float* w_scale;     // [E] or [E, N]
   const float* row_weight;  // [P] nullable (topk weight of each sorted row)
-  int N, K, w_scale_per_channel, out_bf16, stages;
+  int N, K, w_scale_per_channel, a_scale_per_row, out_bf16, stages;
 };
 
 template <int BN>
@@ -121,7 +121,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
     const int n = row0 + wq * 32 + lane;
     const bool n_ok = n < p.N;
     const float ws = n_ok ? (p.w_scale_per_channel ? p.w_scale[(int64_t)e * p.N + n] : p.w_scale[e]) : 0.f;
-    const float as = p.a_scale[0];
+    const float as = p.a_scale_per_row ? 0.f : p.a_scale[0];
     const uint32_t tbase = tmem_d + ((uint32_t)(wq * 32) << 16);
     const uint32_t stile = base;
     uint32_t v0[16], v1[16];
@@ -132,8 +132,10 @@ __global__ void __launch_bounds__(NTHREADS, 1)
         const int c = col0 + (ch << 4) + j;
         const float rw_a = p.row_weight ? p.row_weight[c] : 1.f;
         const float rw_b = p.row_weight ? p.row_weight[c + 1] : 1.f;
-        const float oa = rw_a * (as * (ws * __uint_as_float(vv[j])));
-        const float ob = rw_b * (as * (ws * __uint_as_float(vv[j + 1])));
+        const float as_a = p.a_scale_per_row ? p.a_scale[c] : as;
+        const float as_b = p.a_scale_per_row ? p.a_scale[c + 1] : as;
+        const float oa = rw_a * (as_a * (ws * __uint_as_float(vv[j])));
+        const float ob = rw_b * (as_b * (ws * __uint_as_float(vv[j + 1])));
         const float send = (lane & 1) ? oa : ob;
         const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
         const float lo = (lane & 1) ? recv : oa;
@@ -190,7 +192,10 @@ static int launch(const CUtensorMap& tmW, const CUtensorMap& tmA, const CUtensor
   if (forced >= 2 && forced <= MAX_STAGES && forced * (int)STAGE_BYTES + 2048 <= smem_max) stages = forced;
   p.stages = stages;
   const int smem = stages * (int)STAGE_BYTES + 16 * MAX_STAGES + 64 + 1024;
-  static bool configured = false;
+  static bool configured_dev[64] = {};   // the attribute is per device
+  int cfg_dev_ = 0;
+  cudaGetDevice(&cfg_dev_);
+  bool& configured = configured_dev[cfg_dev_ & 63];
   if (!configured) {
     B200_CUDA(cudaFuncSetAttribute(moe_gemm_fp8_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
     configured = true;
@@ -208,8 +213,8 @@ extern "C" int b200_moe_grouped_gemm_fp8(void* out, const void* a_sorted, const 
                                          const int32_t* num_tokens_post_pad, const float* a_scale,
                                          const float* w_scale, const float* row_weight,
                                          int64_t max_rows, int num_experts, int N, int K,
-                                         int block_size, int w_scale_per_channel, int out_dtype,
-                                         b200_stream_t stream_) {
+                                         int block_size, int w_scale_per_channel, int a_scale_per_row,
+                                         int out_dtype, b200_stream_t stream_) {
   using namespace b200;
   using namespace b200::moegemm;
   cudaStream_t stream = (cudaStream_t)stream_;
@@ -262,6 +267,7 @@ extern "C" int b200_moe_grouped_gemm_fp8(void* out, const void* a_sorted, const 
   p.N = N;
   p.K = K;
   p.w_scale_per_channel = w_scale_per_channel;
+  p.a_scale_per_row = a_scale_per_row;
   p.out_bf16 = out_dtype == B200_BF16;
   p.stages = 0;
   dim3 grid((unsigned)(max_rows / block_size), (N + BM - 1) / BM);

@@ -253,6 +253,31 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// Gather of already-quantised rows (per-token / per-group activation quant happens in token order, before the
+// sort): dst[i, :] = src[sorted_token_ids[i] / topk, :] (bytes) and scale_dst[i, :] = scale_src[..., :] for
+// i < *num_tokens_post_pad; pad rows get zero bytes and zero scales (their GEMM output is 0 and never gathered).
+__global__ void __launch_bounds__(256)
+    moe_permute_rows_kernel(uint8_t* __restrict__ dst, const uint8_t* __restrict__ src,
+                            const int32_t* __restrict__ sorted_token_ids,
+                            const int32_t* __restrict__ num_tokens_post_pad, float* __restrict__ scale_dst,
+                            const float* __restrict__ scale_src, int scale_cols, int64_t scale_src_stride,
+                            int topk, int64_t numel, int row_vecs, int64_t src_stride_bytes) {
+  const int row = blockIdx.x;
+  if (row >= *num_tokens_post_pad) return;
+  const int32_t flat = sorted_token_ids[row];
+  uint4* d = reinterpret_cast<uint4*>(dst) + (int64_t)row * row_vecs;
+  if (flat >= numel || flat < 0) {
+    for (int v = threadIdx.x; v < row_vecs; v += blockDim.x) d[v] = make_uint4(0u, 0u, 0u, 0u);
+    for (int c = threadIdx.x; c < scale_cols; c += blockDim.x) scale_dst[(int64_t)row * scale_cols + c] = 0.f;
+    return;
+  }
+  const int64_t t = flat / topk;
+  const uint4* sp = reinterpret_cast<const uint4*>(src + t * src_stride_bytes);
+  for (int v = threadIdx.x; v < row_vecs; v += blockDim.x) d[v] = ld_nc_v4(sp + v);
+  for (int c = threadIdx.x; c < scale_cols; c += blockDim.x)
+    scale_dst[(int64_t)row * scale_cols + c] = scale_src[t * scale_src_stride + c];
+}
+
 // out[t, :] = sum_k w[t,k] * src[inv_perm[t*topk + k], :]  (fp32 accumulate; skipped if inv < 0)
 template <typename T>
 __global__ void __launch_bounds__(256)
@@ -603,6 +628,27 @@ extern "C" int b200_shuffle_rows(void* dst, const void* src, const int32_t* dst2
   const unsigned blocks = (unsigned)(dst_rows < cap ? dst_rows : cap);
   shuffle_rows_kernel<<<blocks, 256, 0, stream>>>((uint8_t*)dst, (const uint8_t*)src, dst2src_map, dst_rows,
                                                   src_rows, (int)(row_bytes / 16), src_stride_bytes);
+  B200_LAUNCH_CHECK();
+  return B200_OK;
+}
+
+extern "C" int b200_moe_permute_rows(void* dst, const void* src, const int32_t* sorted_token_ids,
+                                     const int32_t* num_tokens_post_pad, float* scale_dst, const float* scale_src,
+                                     int scale_cols, int64_t scale_src_stride, int64_t max_rows, int topk,
+                                     int64_t numel, int64_t row_bytes, int64_t src_stride_bytes,
+                                     b200_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  B200_CHECK(max_rows >= 0 && row_bytes > 0 && topk > 0 && scale_cols >= 0, B200_ERR_INVALID,
+             "moe_permute_rows: bad sizes");
+  if (max_rows == 0) return B200_OK;
+  B200_CHECK(dst && src && sorted_token_ids && num_tokens_post_pad && (scale_cols == 0 || (scale_dst && scale_src)),
+             B200_ERR_INVALID, "moe_permute_rows: null pointer");
+  B200_CHECK(row_bytes % 16 == 0 && src_stride_bytes % 16 == 0 && ((uintptr_t)src & 15) == 0 &&
+                 ((uintptr_t)dst & 15) == 0 && row_bytes / 16 < (1LL << 31),
+             B200_ERR_UNSUPPORTED, "moe_permute_rows: rows must be 16-byte aligned multiples of 16 bytes");
+  moe_permute_rows_kernel<<<(unsigned)max_rows, 256, 0, stream>>>(
+      (uint8_t*)dst, (const uint8_t*)src, sorted_token_ids, num_tokens_post_pad, scale_dst, scale_src, scale_cols,
+      scale_src_stride, topk, numel, (int)(row_bytes / 16), src_stride_bytes);
   B200_LAUNCH_CHECK();
   return B200_OK;
 }
