@@ -501,105 +501,111 @@ def tp_self_check(rank, world, dev, group):
     del busy_a
 
     # ---- (3) tiny model, TP=world vs TP=1
-    shape = decoder.TINY_TP
-    S, ctx, bs = 48, 64, BLOCK
-    cg = torch.Generator().manual_seed(5)
-    nblk = (ctx + bs - 1) // bs
-    nb = S * nblk + 8
-    bt = torch.randperm(nb, generator=cg)[: S * nblk].to(torch.int32).view(S, nblk)
-    tok0 = torch.randint(0, shape.vocab, (S,), generator=cg)
-    lens0 = torch.randint(1, ctx - 2, (S,), generator=cg)
-    # one global FP8 KV prefix per layer (random non-NaN e4m3 codes); a TP rank keeps its contiguous kv heads
-    kv_gen = torch.Generator().manual_seed(9)
-    kv_full = [(torch.randint(0, 0x70, (nb, bs, shape.kv_heads, 2 * shape.head_size), generator=kv_gen) |
-                (torch.randint(0, 2, (nb, bs, shape.kv_heads, 2 * shape.head_size), generator=kv_gen) << 7)
-                ).to(torch.uint8) for _ in range(shape.layers)]
+    # dense (TP) and sparse-MoE (TP attention + expert parallel; comm=fused is the second EP form:
+    # all-gather tokens -> local experts -> reduce-scatter) tiny models
+    tiny_notes = []
+    for shape in (decoder.TINY_TP, decoder.TINY_MOE_EP):
+        S, ctx, bs = 48, 64, BLOCK
+        cg = torch.Generator().manual_seed(5)
+        nblk = (ctx + bs - 1) // bs
+        nb = S * nblk + 8
+        bt = torch.randperm(nb, generator=cg)[: S * nblk].to(torch.int32).view(S, nblk)
+        tok0 = torch.randint(0, shape.vocab, (S,), generator=cg)
+        lens0 = torch.randint(1, ctx - 2, (S,), generator=cg)
+        # one global FP8 KV prefix per layer (random non-NaN e4m3 codes); a TP rank keeps its contiguous kv heads
+        kv_gen = torch.Generator().manual_seed(9)
+        kv_full = [(torch.randint(0, 0x70, (nb, bs, shape.kv_heads, 2 * shape.head_size), generator=kv_gen) |
+                    (torch.randint(0, 2, (nb, bs, shape.kv_heads, 2 * shape.head_size), generator=kv_gen) << 7)
+                    ).to(torch.uint8) for _ in range(shape.layers)]
 
-    def run(model, tokens_forced=None):
-        """two eager decode steps from the same synthetic state; returns (tokens[2, S], logits[2, S, V])"""
-        for li, L in enumerate(model.layers):
-            lo = model.tp_rank * model.hkv
-            L["kv"].copy_(kv_full[li][:, :, lo:lo + model.hkv])
-        toks, logs = [], []
-        tok = tok0.clone()
-        for step in range(2):
-            lens = lens0 + step
-            pos = lens - 1
-            model.token_ids.copy_(tok)
-            model.positions.copy_(pos)
-            model.seq_lens.copy_(lens.to(torch.int32))
-            model.block_table.copy_(bt)
-            model.slot_mapping.copy_(bt[torch.arange(S), pos // bs].long() * bs + pos % bs)
-            model.forward_device()
-            torch.cuda.synchronize(dev)
-            toks.append(model.next_tokens.cpu().clone())
-            logs.append(model.last_logits.float().cpu().clone())
-            tok = toks[-1] if tokens_forced is None else tokens_forced[step]
-        return torch.stack(toks), torch.stack(logs)
-
-    ref_t = ref_l = None
-    if rank == 0:
-        m1 = decoder.DecoderModel(shape, S, ctx, bs, dev, num_blocks=nb)
-        ref_t, ref_l = run(m1)
-        del m1
-    forced = [torch.empty(S, dtype=torch.int64, device=dev) for _ in range(2)]
-    if rank == 0:
-        for i in range(2):
-            forced[i].copy_(ref_t[i])
-    for i in range(2):
-        dist.broadcast(forced[i], 0, group=group)
-    forced = [f.cpu() for f in forced]
-    # (comm, multicast): the peer-pull data plane (multicast False) and, where the box has it, the NVLS one
-    cfgs = [("nccl", None), ("nvlink", False)] + ([("fused", False)] if world in (2, 4, 8) else [])
-    if have_mc:
-        cfgs += [("nvls", None)] + ([("fused", None)] if world in (2, 4, 8) else [])
-    comms = [c_ + ("+multimem" if (m_ is None and c_ != "nccl") else "") for c_, m_ in cfgs]
-    near_ties, identical, total, worst_rel = 0, 0, 0, 0.0
-    logits_by_comm = {}
-    for (comm, mcast), label in zip(cfgs, comms):
-        mN = decoder.DecoderModel(shape, S, ctx, bs, dev, tp_rank=rank, tp_size=world, tp_group=group,
-                                  comm=comm, num_blocks=nb, multicast=mcast)
-        t, lg = run(mN, forced)      # teacher-forced with the TP=1 tokens so step 2 sees the same context
-        logits_by_comm[label] = lg
-        comm = label
-        if mN.ar is not None:
-            torch.cuda.synchronize(dev)
-            mN.ar.close()
-        del mN
-        if rank == 0:
-            # TP changes where the bf16 / FP8 roundings fall (per-rank partial sums are rounded before the
-            # all-reduce, and the next layer re-quantises to FP8), so logits agree to FP8 noise, not bit for bit:
-            # require a small relative error, and that a differing greedy token is explained by it (the TP=1
-            # margin between the two candidates is below twice that row's largest logit deviation)
+        def run(model, tokens_forced=None):
+            """two eager decode steps from the same synthetic state; returns (tokens[2, S], logits[2, S, V])"""
+            for li, L in enumerate(model.layers):
+                lo = model.tp_rank * model.hkv
+                L["kv"].copy_(kv_full[li][:, :, lo:lo + model.hkv])
+            toks, logs = [], []
+            tok = tok0.clone()
             for step in range(2):
-                d = (lg[step] - ref_l[step]).abs()
-                rel = float(d.norm() / ref_l[step].norm())
-                worst_rel = max(worst_rel, rel)
-                if rel > 5e-2:
-                    raise AssertionError(f"tp_check: tiny model TP={world} comm={comm} step {step}: logits differ "
-                                         f"from TP=1 by {rel:.3e} (relative Frobenius)")
-                same = t[step] == ref_t[step]
-                identical += int(same.sum())
-                total += S
-                for sidx in (~same).nonzero().flatten().tolist():
-                    a, b = ref_l[step, sidx, ref_t[step, sidx]], ref_l[step, sidx, t[step, sidx]]
-                    if float(a - b) > 2.0 * float(d[sidx].max()):
-                        raise AssertionError(f"tp_check: tiny model TP={world} comm={comm} step {step} seq {sidx}: "
-                                             f"token {int(t[step, sidx])} vs TP=1 {int(ref_t[step, sidx])} (TP=1 logits "
-                                             f"{float(a):.5f} vs {float(b):.5f}, max logit deviation {float(d[sidx].max()):.5f})")
-                    near_ties += 1
-    # the fused reduce-scatter+norm+quant+all-gather kernel is arithmetically identical to all-reduce -> norm+quant
-    # with the rank-order NVLink all-reduce: the two decoders must produce the same logits bit for bit
-    if "fused" in logits_by_comm and not torch.equal(logits_by_comm["fused"], logits_by_comm["nvlink"]):  # peer-pull
-        raise AssertionError(f"tp_check: tiny model TP={world}: comm=fused and comm=nvlink logits are not bit-identical")
-    if world == 2 and not torch.equal(logits_by_comm["nccl"], logits_by_comm["nvlink"]):
-        raise AssertionError("tp_check: tiny model TP=2: NCCL and NVLink all-reduce decoders differ (a+b is order-free)")
-    if rank == 0 and identical < 0.9 * total:
-        raise AssertionError(f"tp_check: only {identical} of {total} greedy tokens equal TP=1")
+                lens = lens0 + step
+                pos = lens - 1
+                model.token_ids.copy_(tok)
+                model.positions.copy_(pos)
+                model.seq_lens.copy_(lens.to(torch.int32))
+                model.block_table.copy_(bt)
+                model.slot_mapping.copy_(bt[torch.arange(S), pos // bs].long() * bs + pos % bs)
+                model.forward_device()
+                torch.cuda.synchronize(dev)
+                toks.append(model.next_tokens.cpu().clone())
+                logs.append(model.last_logits.float().cpu().clone())
+                tok = toks[-1] if tokens_forced is None else tokens_forced[step]
+            return torch.stack(toks), torch.stack(logs)
+
+        ref_t = ref_l = None
+        if rank == 0:
+            m1 = decoder.DecoderModel(shape, S, ctx, bs, dev, num_blocks=nb)
+            ref_t, ref_l = run(m1)
+            del m1
+        forced = [torch.empty(S, dtype=torch.int64, device=dev) for _ in range(2)]
+        if rank == 0:
+            for i in range(2):
+                forced[i].copy_(ref_t[i])
+        for i in range(2):
+            dist.broadcast(forced[i], 0, group=group)
+        forced = [f.cpu() for f in forced]
+        # (comm, multicast): the peer-pull data plane (multicast False) and, where the box has it, the NVLS one
+        cfgs = [("nccl", None), ("nvlink", False)] + ([("fused", False)] if world in (2, 4, 8) else [])
+        if have_mc:
+            cfgs += [("nvls", None)] + ([("fused", None)] if world in (2, 4, 8) else [])
+        comms = [c_ + ("+multimem" if (m_ is None and c_ != "nccl") else "") for c_, m_ in cfgs]
+        near_ties, identical, total, worst_rel = 0, 0, 0, 0.0
+        logits_by_comm = {}
+        for (comm, mcast), label in zip(cfgs, comms):
+            mN = decoder.DecoderModel(shape, S, ctx, bs, dev, tp_rank=rank, tp_size=world, tp_group=group,
+                                      comm=comm, num_blocks=nb, multicast=mcast)
+            t, lg = run(mN, forced)      # teacher-forced with the TP=1 tokens so step 2 sees the same context
+            logits_by_comm[label] = lg
+            comm = label
+            if mN.ar is not None:
+                torch.cuda.synchronize(dev)
+                mN.ar.close()
+            del mN
+            if rank == 0:
+                # TP changes where the bf16 / FP8 roundings fall (per-rank partial sums are rounded before the
+                # all-reduce, and the next layer re-quantises to FP8), so logits agree to FP8 noise, not bit for bit:
+                # require a small relative error, and that a differing greedy token is explained by it (the TP=1
+                # margin between the two candidates is below twice that row's largest logit deviation)
+                for step in range(2):
+                    d = (lg[step] - ref_l[step]).abs()
+                    rel = float(d.norm() / ref_l[step].norm())
+                    worst_rel = max(worst_rel, rel)
+                    if rel > 5e-2:
+                        raise AssertionError(f"tp_check: tiny model TP={world} comm={comm} step {step}: logits differ "
+                                             f"from TP=1 by {rel:.3e} (relative Frobenius)")
+                    same = t[step] == ref_t[step]
+                    identical += int(same.sum())
+                    total += S
+                    for sidx in (~same).nonzero().flatten().tolist():
+                        a, b = ref_l[step, sidx, ref_t[step, sidx]], ref_l[step, sidx, t[step, sidx]]
+                        if float(a - b) > 2.0 * float(d[sidx].max()):
+                            raise AssertionError(f"tp_check: tiny model TP={world} comm={comm} step {step} seq {sidx}: "
+                                                 f"token {int(t[step, sidx])} vs TP=1 {int(ref_t[step, sidx])} (TP=1 logits "
+                                                 f"{float(a):.5f} vs {float(b):.5f}, max logit deviation {float(d[sidx].max()):.5f})")
+                        near_ties += 1
+        # the fused reduce-scatter+norm+quant+all-gather kernel is arithmetically identical to all-reduce -> norm+quant
+        # with the rank-order NVLink all-reduce: the two decoders must produce the same logits bit for bit
+        if "fused" in logits_by_comm and not torch.equal(logits_by_comm["fused"], logits_by_comm["nvlink"]):  # peer-pull
+            raise AssertionError(f"tp_check: tiny model TP={world}: comm=fused and comm=nvlink logits are not bit-identical")
+        if world == 2 and not torch.equal(logits_by_comm["nccl"], logits_by_comm["nvlink"]):
+            raise AssertionError("tp_check: tiny model TP=2: NCCL and NVLink all-reduce decoders differ (a+b is order-free)")
+        if rank == 0 and identical < 0.9 * total:
+            raise AssertionError(f"tp_check: only {identical} of {total} greedy tokens equal TP=1")
+        tiny_notes.append(f"{shape.name}, {S} seqs x 2 steps x comm {'/'.join(comms)}: {identical} of {total} greedy "
+                          f"tokens identical to TP=1, {near_ties} differ inside the measured logit deviation "
+                          f"(near-ties); logits vs TP=1 rel err <= {worst_rel:.2e}; peer-pull fused == nvlink logits "
+                          f"bit-identical")
     res["tiny_tokens"] = "match"
-    res["tiny_model"] = (f"{shape.name}, {S} seqs x 2 steps x comm {'/'.join(comms)}: {identical} of {total} greedy tokens "
-                         f"identical to TP=1, {near_ties} differ inside the measured logit deviation (near-ties); "
-                         f"logits vs TP=1 rel err <= {worst_rel:.2e}; peer-pull fused == nvlink logits bit-identical")
+    res["tiny_model"] = tiny_notes[0]
+    res["tiny_moe_model"] = tiny_notes[1]
     return res
 
 
@@ -635,8 +641,8 @@ def main():
             print(json.dumps({"tp_check": {"failed": repr(e)}, "rank": rank}), flush=True)
             sys.stderr.flush()
             os._exit(3)
-    if (shape.experts > 0 or a.quant == "nvfp4") and a.comm == "fused":
-        a.comm = "nvlink"   # MoE layers (expert parallel): the all-reduce follows fused_experts, no norm fusion
+    if a.quant == "nvfp4" and a.comm == "fused":
+        a.comm = "nvlink"   # NVFP4 linears take bf16 activations: no FP8-quantising norm fusion
     S, ctx = a.batch, a.ctx
     model = decoder.DecoderModel(shape, S, ctx, BLOCK, dev, tp_rank=rank, tp_size=world, tp_group=group,
                                  comm=a.comm, quant=a.quant, multicast=False if a.no_multicast else None)

@@ -53,6 +53,7 @@ TINY = ModelShape("tiny-llama-shaped", 512, 2, 8, 2, 128, 1024, 1024)
 # tiny shape whose heads / kv heads / inter divide by 8 ranks (bench.py's TP=N vs TP=1 self-check)
 TINY_TP = ModelShape("tiny-llama-shaped-tp8", 1024, 2, 16, 8, 128, 2048, 1024)
 TINY_MOE = ModelShape("tiny-mixtral-shaped", 512, 2, 8, 2, 128, 512, 1024, 1000000.0, 1e-5, 4, 2)
+TINY_MOE_EP = ModelShape("tiny-mixtral-shaped-ep8", 1024, 2, 16, 8, 128, 512, 1024, 1000000.0, 1e-5, 8, 2)
 
 # kernels launched per call of each op (our own kernels only), for the bench's gpu_launches claim
 LAUNCHES = {"quant_static": 1, "gemm": 1, "cache_write": 1, "attention": 2, "silu_quant": 1,
@@ -81,7 +82,6 @@ class DecoderModel:
         self.moe = s.experts > 0
         if self.moe:
             assert s.experts % tp_size == 0, "expert parallel: experts must divide over the ranks"
-            assert comm != "fused", "MoE layers: comm must be nccl or nvlink"
             assert quant == "fp8", "MoE layers: FP8 fused_experts only"
             self.e_lo, self.e_hi = tp.expert_shard(s.experts, tp_rank, tp_size)
         self.hq, self.hkv = s.heads // tp_size, s.kv_heads // tp_size
@@ -201,6 +201,10 @@ class DecoderModel:
             if self.comm == "fused":
                 self.x8_sym = self.ar.alloc((S, H), torch.float8_e4m3fn)
                 self.final_sym = self.ar.alloc((S, H), torch.bfloat16)
+                # MoE layers, second EP form (all-gather tokens -> local experts -> reduce-scatter,
+                # prepare_finalize/naive_dp_ep.py:112-210 with is_sequence_parallel): the gathered, normalised
+                # bf16 tokens every rank routes and feeds to its local experts
+                self.xn_sym = self.ar.alloc((S, H), torch.bfloat16) if self.moe else None
                 lo, hi = self.ar.rows_of_rank(S)
                 self.row_lo, self.row_hi = lo, hi
                 self.res_shard = torch.zeros((S + tp_size - 1) // tp_size, H, dtype=torch.bfloat16, device=self.dev)
@@ -361,9 +365,16 @@ class DecoderModel:
             if self.moe:
                 # MixtralMoE.forward (models/mixtral.py:145-160): router logits (bf16 replicated linear: library
                 # GEMM) -> topk_softmax (renormalised) -> fused_experts on the local experts -> all-reduce
-                red = self._all_reduce(pa)
-                n += 1 if self.ar is not None else 0
-                ops.fused_add_rms_norm(red, self.residual, L["post_norm"], s.eps); n += 1
+                if fused:
+                    # second EP form: ONE kernel reduce-scatters the o_proj partials, adds the row-sharded residual,
+                    # normalises and all-gathers the bf16 tokens (dispatch); the experts' partial sums are
+                    # reduce-scattered by the next layer's fused kernel (combine): no all-reduce of [S, H]
+                    self.ar.fused_add_rms_norm(self.xn_sym, pa, self.res_shard, L["post_norm"], s.eps, None); n += 1
+                    red = self.xn_sym
+                else:
+                    red = self._all_reduce(pa)
+                    n += 1 if self.ar is not None else 0
+                    ops.fused_add_rms_norm(red, self.residual, L["post_norm"], s.eps); n += 1
                 torch.matmul(red, L["gate_w_t"], out=self.router_logits)
                 fused_moe.topk_softmax(self.topk_w, self.topk_ids, self.tok_exp_idx, self.router_logits, True)
                 n += LAUNCHES["topk_softmax"]
@@ -373,8 +384,9 @@ class DecoderModel:
                                              a2_scale=L["a_d"])
                 n += LAUNCHES["fused_experts"]
                 pb.copy_(mo)
-                red = self._all_reduce(pb)
-                n += 1 if self.ar is not None else 0
+                if not fused:
+                    red = self._all_reduce(pb)
+                    n += 1 if self.ar is not None else 0
                 continue
             if fused:
                 self.ar.fused_add_rms_norm(x8, pa, self.res_shard, L["post_norm"], s.eps, L["a_gu"]); n += 1
