@@ -523,7 +523,7 @@ def tp_self_check(rank, world, dev, group):
             for li, L in enumerate(model.layers):
                 lo = model.tp_rank * model.hkv
                 L["kv"].copy_(kv_full[li][:, :, lo:lo + model.hkv])
-            toks, logs = [], []
+            toks, logs, routes = [], [], []
             tok = tok0.clone()
             for step in range(2):
                 lens = lens0 + step
@@ -533,17 +533,20 @@ def tp_self_check(rank, world, dev, group):
                 model.seq_lens.copy_(lens.to(torch.int32))
                 model.block_table.copy_(bt)
                 model.slot_mapping.copy_(bt[torch.arange(S), pos // bs].long() * bs + pos % bs)
+                model.routing_log = [] if shape.experts > 0 else None
                 model.forward_device()
                 torch.cuda.synchronize(dev)
                 toks.append(model.next_tokens.cpu().clone())
                 logs.append(model.last_logits.float().cpu().clone())
+                routes.append(torch.stack(model.routing_log) if shape.experts > 0 else torch.zeros(1, S, 1))
+                model.routing_log = None
                 tok = toks[-1] if tokens_forced is None else tokens_forced[step]
-            return torch.stack(toks), torch.stack(logs)
+            return torch.stack(toks), torch.stack(logs), torch.stack(routes)
 
         ref_t = ref_l = None
         if rank == 0:
             m1 = decoder.DecoderModel(shape, S, ctx, bs, dev, num_blocks=nb)
-            ref_t, ref_l = run(m1)
+            ref_t, ref_l, ref_r = run(m1)
             del m1
         forced = [torch.empty(S, dtype=torch.int64, device=dev) for _ in range(2)]
         if rank == 0:
@@ -557,12 +560,12 @@ def tp_self_check(rank, world, dev, group):
         if have_mc:
             cfgs += [("nvls", None)] + ([("fused", None)] if world in (2, 4, 8) else [])
         comms = [c_ + ("+multimem" if (m_ is None and c_ != "nccl") else "") for c_, m_ in cfgs]
-        near_ties, identical, total, worst_rel = 0, 0, 0, 0.0
+        near_ties, identical, total, worst_rel, flips = 0, 0, 0, 0.0, 0
         logits_by_comm = {}
         for (comm, mcast), label in zip(cfgs, comms):
             mN = decoder.DecoderModel(shape, S, ctx, bs, dev, tp_rank=rank, tp_size=world, tp_group=group,
                                       comm=comm, num_blocks=nb, multicast=mcast)
-            t, lg = run(mN, forced)      # teacher-forced with the TP=1 tokens so step 2 sees the same context
+            t, lg, rt = run(mN, forced)      # teacher-forced with the TP=1 tokens so step 2 sees the same context
             logits_by_comm[label] = lg
             comm = label
             if mN.ar is not None:
@@ -576,20 +579,27 @@ def tp_self_check(rank, world, dev, group):
                 # margin between the two candidates is below twice that row's largest logit deviation)
                 for step in range(2):
                     d = (lg[step] - ref_l[step]).abs()
-                    rel = float(d.norm() / ref_l[step].norm())
+                    # sparse MoE: a router near-tie resolved the other way sends a token to another expert and changes
+                    # its whole row; such rows (top-k id sets different from TP=1 in some layer) are counted, bounded
+                    # and left out of the numeric comparison
+                    kept = (rt[step] == ref_r[step]).all(dim=2).all(dim=0)
+                    flips += int((~kept).sum())
+                    d = d[kept]
+                    rel = float(d.norm() / ref_l[step][kept].norm())
                     worst_rel = max(worst_rel, rel)
                     if rel > 5e-2:
                         raise AssertionError(f"tp_check: tiny model TP={world} comm={comm} step {step}: logits differ "
                                              f"from TP=1 by {rel:.3e} (relative Frobenius)")
-                    same = t[step] == ref_t[step]
-                    identical += int(same.sum())
-                    total += S
+                    same = (t[step] == ref_t[step]) | ~kept
+                    identical += int((same & kept).sum())
+                    total += int(kept.sum())
+                    dfull = (lg[step] - ref_l[step]).abs()
                     for sidx in (~same).nonzero().flatten().tolist():
                         a, b = ref_l[step, sidx, ref_t[step, sidx]], ref_l[step, sidx, t[step, sidx]]
-                        if float(a - b) > 2.0 * float(d[sidx].max()):
+                        if float(a - b) > 2.0 * float(dfull[sidx].max()):
                             raise AssertionError(f"tp_check: tiny model TP={world} comm={comm} step {step} seq {sidx}: "
                                                  f"token {int(t[step, sidx])} vs TP=1 {int(ref_t[step, sidx])} (TP=1 logits "
-                                                 f"{float(a):.5f} vs {float(b):.5f}, max logit deviation {float(d[sidx].max()):.5f})")
+                                                 f"{float(a):.5f} vs {float(b):.5f}, max logit deviation {float(dfull[sidx].max()):.5f})")
                         near_ties += 1
         # the fused reduce-scatter+norm+quant+all-gather kernel is arithmetically identical to all-reduce -> norm+quant
         # with the rank-order NVLink all-reduce: the two decoders must produce the same logits bit for bit
@@ -599,10 +609,13 @@ def tp_self_check(rank, world, dev, group):
             raise AssertionError("tp_check: tiny model TP=2: NCCL and NVLink all-reduce decoders differ (a+b is order-free)")
         if rank == 0 and identical < 0.9 * total:
             raise AssertionError(f"tp_check: only {identical} of {total} greedy tokens equal TP=1")
+        if rank == 0 and flips > 0.15 * 2 * S * len(cfgs):
+            raise AssertionError(f"tp_check: {flips} rows routed differently from TP=1 (more than near-ties explain)")
         tiny_notes.append(f"{shape.name}, {S} seqs x 2 steps x comm {'/'.join(comms)}: {identical} of {total} greedy "
                           f"tokens identical to TP=1, {near_ties} differ inside the measured logit deviation "
                           f"(near-ties); logits vs TP=1 rel err <= {worst_rel:.2e}; peer-pull fused == nvlink logits "
-                          f"bit-identical")
+                          f"bit-identical" + (f"; {flips} rows left out (router near-ties routed to another expert)"
+                                              if shape.experts > 0 else ""))
     res["tiny_tokens"] = "match"
     res["tiny_model"] = tiny_notes[0]
     res["tiny_moe_model"] = tiny_notes[1]

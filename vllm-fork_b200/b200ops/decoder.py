@@ -229,6 +229,7 @@ class DecoderModel:
             self.h_sf = ops.create_fp4_scale_tensor(S, self.inter, self.dev, True)
         self.fuse_gate_up = max_seqs <= 64 and self.inter % 128 == 0 and not self.moe
         self.fuse_attn_quant = os.environ.get("B200_FUSE_ATTN_QUANT", "1") == "1"
+        self.routing_log = None   # list -> forward_device() appends every MoE layer's sorted top-k ids (eager only)
         self.attn_hook = None  # bench instrumentation: called around the attention launch
         self.graph = None
 
@@ -378,6 +379,8 @@ class DecoderModel:
                 torch.matmul(red, L["gate_w_t"], out=self.router_logits)
                 fused_moe.topk_softmax(self.topk_w, self.topk_ids, self.tok_exp_idx, self.router_logits, True)
                 n += LAUNCHES["topk_softmax"]
+                if self.routing_log is not None:   # bench.py tp_check: which rows were routed differently from TP=1
+                    self.routing_log.append(self.topk_ids.sort(dim=1).values.cpu())
                 mo = fused_moe.fused_experts(red, L["w1"], L["w2"], self.topk_w, self.topk_ids, use_fp8_w8a8=True,
                                              global_num_experts=s.experts, expert_map=self.expert_map,
                                              w1_scale=L["w1_s"], w2_scale=L["w2_s"], a1_scale=L["a_gu"],
