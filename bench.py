@@ -783,7 +783,7 @@ def main():
                                 f"({baseline_config_tag(shape, a.quant)})"),
                    "parallelism": (f"tp{world} attention + ep{world} experts" if shape.experts > 0 else f"tp{world}"), "tp_collective": (a.comm if world > 1 else None),
                    "nvswitch_multicast": (bool(model.ar.multicast) if model.ar is not None else None), "weights": "random init (dummy), per-tensor FP8 scales",
-                   "cuda_graph": not a.no_graph,
+                   "cuda_graph": not a.no_graph, "pdl_level": model.pdl,
                    "l2": "inputs larger than L2 (KV cache %.1f GB + weights per GPU)" %
                          (sum(L["kv"].numel() for L in model.layers) / 1e9),
                    "context": "seq_len fixed at ctx every step (the new token is written at position ctx-1)"},

@@ -55,6 +55,14 @@ B200_API const char* b200_last_error(void);
 B200_API int b200_version(void);
 /* Number of SMs of the current CUDA device (148 on B200), or a negative error code. */
 B200_API int b200_sm_count(void);
+/* Programmatic dependent launch between consecutive b200 kernels on a stream (results are unchanged):
+ *   0 = off; 1 (default) = the next kernel's prologue (barrier init, TMEM allocation, descriptor prefetch) runs
+ *   under the previous kernel's tail; 2 = the GEMMs additionally request their first ring pass of WEIGHT tiles
+ *   before waiting for the previous kernel -- the caller promises that the weight operand (`b` of
+ *   cutlass_scaled_mm / cutlass_scaled_fp4_mm) is not written by the kernel preceding the GEMM on the stream,
+ *   which holds for model weights. Initial value from env B200_PDL. Returns the previous level.
+ * Not part of the reference operator surface. */
+B200_API int b200_set_pdl(int level);
 
 /* ------------------------------------------------------------------------------------------------
  * KV-cache write.
@@ -146,7 +154,11 @@ B200_API int b200_fp8_quant_token_group(void* out, float* scales, const void* in
  * All byte strides and base pointers must be 16-byte aligned; head_size*sizeof(kv) >= 64.
  * block_table int32 [num_seqs, bt_stride]; seq_lens int32 [num_seqs]; block_size % 16 == 0.
  * workspace: b200_paged_attention_workspace_bytes(...) bytes of device memory owned by the caller
- * (the AttentionMetadataBuilder keeps one persistent buffer, like triton_attn.py:154-175).
+ * (the AttentionMetadataBuilder keeps one persistent buffer, like triton_attn.py:154-175). It must be
+ * ZERO-FILLED ONCE before its first use and not written by anyone else: its first 1024 bytes hold the arrival
+ * counters of the split-KV reduction (folded into the kernel: the last CTA to finish a piece of a sequence that
+ * was cut by CTA boundaries merges the pieces), which every launch leaves at zero again; the rest receives the
+ * fp32 partials. One launch at a time per workspace (launches on one stream are fine).
  * Everything is read on the device: no host sync, CUDA-graph safe.
  */
 typedef struct b200_paged_attn_args {

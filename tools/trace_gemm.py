@@ -9,7 +9,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "vllm-fork_b200"))
 NAMES = ["entry", "setup done", "first TMA issued", "first k-block landed", "last MMA committed",
-         "accumulator ready (epi)", "last TMA issued", "exit"]
+         "accumulator ready (epi)", "tile staged in smem (epi)", "exit"]
 
 
 def run(shapes):

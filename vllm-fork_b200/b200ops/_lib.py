@@ -107,6 +107,7 @@ SIGNATURES = {
     "b200_last_error": (C.c_char_p, []),
     "b200_version": (c_int, []),
     "b200_sm_count": (c_int, []),
+    "b200_set_pdl": (c_int, [c_int]),
     "b200_reshape_and_cache_flash": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int64,

@@ -56,7 +56,7 @@ TINY_MOE = ModelShape("tiny-mixtral-shaped", 512, 2, 8, 2, 128, 512, 1024, 10000
 TINY_MOE_EP = ModelShape("tiny-mixtral-shaped-ep8", 1024, 2, 16, 8, 128, 512, 1024, 1000000.0, 1e-5, 8, 2)
 
 # kernels launched per call of each op (our own kernels only), for the bench's gpu_launches claim
-LAUNCHES = {"quant_static": 1, "gemm": 1, "cache_write": 1, "attention": 2, "silu_quant": 1,
+LAUNCHES = {"quant_static": 1, "gemm": 1, "cache_write": 1, "attention": 1, "silu_quant": 1,
             # moe_align + permute/quant + grouped GEMM + silu/quant + grouped GEMM + unpermute/reduce
             "topk_softmax": 1, "fused_experts": 6}
 
@@ -72,8 +72,16 @@ class DecoderModel:
     def __init__(self, shape: ModelShape, max_seqs: int, max_ctx: int, block_size: int = 16,
                  device: str | torch.device = "cuda:0", tp_rank: int = 0, tp_size: int = 1,
                  tp_group=None, seed: int = 1234, kv_fp8: bool = True, num_blocks: int | None = None,
-                 comm: str = "nccl", quant: str = "fp8", multicast: bool | None = None):
+                 comm: str = "nccl", quant: str = "fp8", multicast: bool | None = None,
+                 pdl: int | None = 2):
         self.shape = s = shape
+        # programmatic dependent launch between the kernels of the step; level 2 = the GEMMs request their first
+        # weight tiles before waiting for the previous kernel (the weights are never written after init).
+        # B200_PDL in the environment wins (A/B runs); pdl=None leaves the library setting alone.
+        if pdl is not None and "B200_PDL" not in os.environ:
+            ops.set_pdl(pdl)
+        self.pdl = ops.set_pdl(0)
+        ops.set_pdl(self.pdl)
         assert quant in ("fp8", "nvfp4")
         self.quant = quant   # "nvfp4": W4A4 linears (scaled_fp4_quant -> cutlass_scaled_fp4_mm), FP8 KV cache
         self.dev = torch.device(device)

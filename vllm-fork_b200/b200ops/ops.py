@@ -319,6 +319,14 @@ def per_token_group_quant_fp8(x: torch.Tensor, group_size: int, eps: float = 1e-
 # ------------------------------------------------------------------------------------------------
 # FP8 W8A8 GEMM                                        reference: vllm/_custom_ops.py:756-804
 # ------------------------------------------------------------------------------------------------
+def set_pdl(level: int) -> int:
+    """Programmatic dependent launch between consecutive b200 kernels of a stream (include/b200ops.h
+    b200_set_pdl): 0 off, 1 prologue overlap (default), 2 + GEMM weight tiles requested before the wait (the
+    caller promises that GEMM weights are not written by the kernel preceding the GEMM). Returns the previous
+    level. Results are identical at every level."""
+    return int(_lib.load().b200_set_pdl(int(level)))
+
+
 def cutlass_scaled_mm_supports_fp8(cuda_device_capability: int) -> bool:
     """torch.ops._C.cutlass_scaled_mm_supports_fp8: this build targets sm_100a only."""
     return cuda_device_capability // 10 == 10
@@ -953,13 +961,15 @@ _workspaces: dict[tuple, torch.Tensor] = {}
 def paged_attention_workspace(num_seqs: int, num_heads: int, num_kv_heads: int, head_size: int,
                               device: torch.device) -> torch.Tensor:
     """Persistent split-KV workspace (the metadata builder owns it in the backend; cached here for
-    direct op calls). Sized once for the largest batch seen, like triton_attn.py:154-175."""
+    direct op calls). Sized once for the largest batch seen, like triton_attn.py:154-175. Zero-filled: its
+    first 1024 bytes are the arrival counters of the in-kernel split-KV reduction, which every launch leaves
+    at zero again."""
     lib = _lib.load()
     n = lib.b200_paged_attention_workspace_bytes(num_seqs, num_heads, num_kv_heads, head_size)
     key = (str(device), num_heads, head_size)
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < n:
-        ws = torch.empty(n, dtype=torch.uint8, device=device)
+        ws = torch.zeros(n, dtype=torch.uint8, device=device)
         _workspaces[key] = ws
     return ws
 

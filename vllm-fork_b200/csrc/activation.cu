@@ -25,6 +25,8 @@ __global__ void __launch_bounds__(256)
     silu_and_mul_kernel(void* __restrict__ out, const T* __restrict__ in, const float* __restrict__ scale,
                         int d, int64_t in_stride, int64_t out_stride) {
   constexpr int N = 16 / sizeof(T);
+  pdl_launch_dependents();
+  pdl_wait();   // `in` is the gate_up GEMM's output
   const int64_t tok = blockIdx.x;
   const T* xp = in + tok * in_stride;
   const T* yp = xp + d;
@@ -83,9 +85,11 @@ static int launch_silu(void* out, const void* in, const float* scale, int64_t nu
   if (chunks > want) chunks = want < 1 ? 1 : want;
   dim3 grid((unsigned)num_tokens, (unsigned)chunks);
   if (vec)
-    silu_and_mul_kernel<T, QUANT, true><<<grid, 256, 0, stream>>>(out, (const T*)in, scale, d, in_stride, out_stride);
+    B200_CUDA(launch_pdl(silu_and_mul_kernel<T, QUANT, true>, grid, dim3(256), 0, stream, out, (const T*)in, scale, d,
+                         in_stride, out_stride));
   else
-    silu_and_mul_kernel<T, QUANT, false><<<grid, 256, 0, stream>>>(out, (const T*)in, scale, d, in_stride, out_stride);
+    B200_CUDA(launch_pdl(silu_and_mul_kernel<T, QUANT, false>, grid, dim3(256), 0, stream, out, (const T*)in, scale, d,
+                         in_stride, out_stride));
   B200_LAUNCH_CHECK();
   return B200_OK;
 }

@@ -50,7 +50,7 @@ struct Params {
   const float* v_scale;
   const float* out_scale;   // nullable: fused static FP8 output
   const float* alibi;
-  int32_t* cum;      // workspace: [S + 2] tile prefix sums (+ tiles-per-CTA at [S+1])
+  int32_t* arrive;   // workspace: [n_cta] arrival counters of cut sequences (zero between launches)
   float* part_acc;   // workspace: [n_cta * 2][hq_chunk][D]
   float* part_ml;    // workspace: [n_cta * 2][hq_chunk][2]
   int64_t q_stride_s, q_stride_h, out_stride_s, out_stride_h, bt_stride;

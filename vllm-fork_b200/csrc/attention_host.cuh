@@ -105,7 +105,10 @@ static int make_plan(Plan& pl, int S, int Hq, int Hkv, int D, int es, int sms, i
   return B200_OK;
 }
 
-static size_t ws_cum_bytes(int S) { return (size_t)(((S + 2) * 4 + 255) & ~255); }
+// workspace head: arrival counters of the folded split-KV reduction, one per CTA, at a FIXED offset so that the
+// "zero between launches" invariant survives any change of batch size or head geometry
+constexpr size_t kWsCounterBytes = 1024;
+static_assert(kMaxCtas * sizeof(int32_t) <= kWsCounterBytes, "counter region too small");
 
 template <int D, int NT, int MODE>
 static int launch(const CUtensorMap& tmK, const CUtensorMap& tmV, const Params& p, const Plan& pl,
@@ -123,14 +126,7 @@ static int launch(const CUtensorMap& tmK, const CUtensorMap& tmV, const Params& 
     configured_smem = (int)pl.smem_bytes;
   }
   dim3 grid(pl.grid_x, pl.n_chunks);
-  kern<<<grid, NTHREADS, pl.smem_bytes, stream>>>(tmK, tmV, p);
-  B200_LAUNCH_CHECK();
-  dim3 rgrid(p.S, pl.n_chunks);
-  constexpr bool QBF16 = (MODE == BF16_BF16 || MODE == BF16_FP8);
-  int rthreads = p.hc * p.g * (D / 4);
-  rthreads = rthreads > 1024 ? 1024 : ((rthreads + 31) / 32) * 32;
-  paged_attn_reduce_kernel<QBF16><<<rgrid, rthreads, 0, stream>>>(p, D, pl.grid_x);
-  B200_LAUNCH_CHECK();
+  B200_CUDA(launch_pdl(kern, grid, dim3(NTHREADS), (size_t)pl.smem_bytes, stream, tmK, tmV, p));
   return B200_OK;
 }
 
@@ -142,7 +138,7 @@ extern "C" size_t b200_paged_attention_workspace_bytes(int num_seqs, int num_hea
   (void)num_kv_heads;
   using namespace b200::attn;
   if (num_seqs < 0 || num_heads <= 0 || head_size <= 0) return 0;
-  return ws_cum_bytes(num_seqs) + (size_t)kMaxCtas * 2 * num_heads * (head_size + 2) * sizeof(float);
+  return kWsCounterBytes + (size_t)kMaxCtas * 2 * num_heads * (head_size + 2) * sizeof(float);
 }
 
 extern "C" int b200_paged_attention_decode(const b200_paged_attn_args* a, b200_stream_t stream_) {
@@ -223,10 +219,10 @@ extern "C" int b200_paged_attention_decode(const b200_paged_attn_args* a, b200_s
   p.alibi = a->alibi_slopes;
   p.out_scale = a->output_scale;
   uint8_t* ws = reinterpret_cast<uint8_t*>(a->workspace);
-  p.cum = reinterpret_cast<int32_t*>(ws);
+  p.arrive = reinterpret_cast<int32_t*>(ws);
   const int n_cta = pl.grid_x * pl.n_chunks;
   const int hq_chunk = pl.hc * g;
-  p.part_ml = reinterpret_cast<float*>(ws + ws_cum_bytes(S));
+  p.part_ml = reinterpret_cast<float*>(ws + kWsCounterBytes);
   p.part_acc = p.part_ml + (size_t)n_cta * 2 * hq_chunk * 2;
   p.q_stride_s = a->q_stride_s;
   p.q_stride_h = a->q_stride_h;

@@ -1,6 +1,7 @@
 // b200ops -- error plumbing, device queries, TMA descriptor encoding.
 #include "common.cuh"
 
+#include <cstdlib>
 #include <mutex>
 
 namespace b200 {
@@ -54,6 +55,18 @@ int max_smem_optin() {
   }
   return g_smem_optin[d];
 }
+
+// programmatic dependent launch level: 0 off, 1 launch overlap (default), 2 + weight prefetch before the wait.
+// Initial value from B200_PDL; b200_set_pdl changes it.
+static int g_pdl = -1;
+int pdl_level() {
+  if (g_pdl < 0) {
+    const char* e = getenv("B200_PDL");
+    g_pdl = (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1;
+  }
+  return g_pdl;
+}
+bool pdl_enabled() { return pdl_level() > 0; }
 
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                     const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
@@ -110,6 +123,12 @@ extern "C" {
 const char* b200_last_error(void) { return b200::g_err; }
 
 int b200_version(void) { return 1000; }
+
+int b200_set_pdl(int level) {
+  const int prev = b200::pdl_level();
+  b200::g_pdl = level < 0 ? 0 : level > 2 ? 2 : level;
+  return prev;
+}
 
 int b200_sm_count(void) {
   int n = b200::sm_count();

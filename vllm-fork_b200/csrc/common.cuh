@@ -38,6 +38,33 @@ int cuda_fail(cudaError_t e, const char* what);
 
 int sm_count();                 // SMs of the current device (cached per device)
 int max_smem_optin();           // max dynamic smem per CTA (opt-in)
+// programmatic dependent launch between consecutive kernels of a stream (b200_set_pdl / env B200_PDL):
+// 0 = off, 1 = the next kernel's prologue overlaps the previous kernel's tail (default), 2 = the GEMMs also
+// request their first ring pass of WEIGHT tiles before griddepcontrol.wait (caller's promise: the weight
+// operand is not written by the kernel that precedes the GEMM on the stream -- true for model weights)
+int pdl_level();
+bool pdl_enabled();
+
+// Launch with the programmatic-stream-serialization attribute: the kernel may become resident while its
+// predecessor on the stream is still draining; everything that touches data produced by (or buffers read by) an
+// earlier kernel sits behind pdl_wait() inside the kernel. Captured into CUDA graphs as a programmatic edge.
+// Every kernel launched through this helper MUST execute pdl_wait() in at least one thread of every CTA that
+// reads or writes global memory, so that completion stays transitive along the stream.
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                     cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
 
 static inline int dtype_size(int dt) {
   switch (dt) {
@@ -141,6 +168,16 @@ __device__ __forceinline__ void st_na_v4(void* p, uint4 v) {
                "r"(v.z), "r"(v.w));
 }
 
+// ---- programmatic dependent launch (griddepcontrol; no-ops when the kernel was launched without the attribute)
+// launch_dependents: the next kernel on the stream may start its prologue as soon as SM resources free up;
+// wait: blocks until the preceding kernel has completed and its memory operations are visible.
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 // ---- mbarrier / TMA (sm_90+; used on sm_100a)
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
@@ -166,8 +203,14 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// Bounded: a barrier that never completes (a lost TMA, a dead peer CTA) traps after ~2^24 polls (seconds)
+// instead of hanging the GPU; the first poll is the fast path. Roles that would otherwise poll while the
+// PREVIOUS kernel is still running call pdl_wait() first, so the bound only ever covers this kernel's own work.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  uint32_t polls = 0;
   while (!mbar_try_wait(bar, parity)) {
+    if (++polls > (1u << 24)) __trap();
   }
 }
 // One lane of a CONVERGED warp. Single-thread roles (TMA producer, tcgen05.mma issuer) must be written as

@@ -42,6 +42,7 @@ struct Params {
   int swap;              // 1: rows operand = weight (out[c][r]); 0: rows operand = activation (out[r][c])
   int out_bf16;
   int stages;
+  int prefetch_w;        // PDL level 2: weight tiles of the first ring pass are requested before griddepcontrol.wait
   int tma_store;         // swap mode: stage the tile in smem and write it with one TMA store
   // GATED kernel only (gate_up GEMM + silu_and_mul + static FP8 quant): rows r and gate_rows + r of
   // the weight are the gate / up rows of output column r
@@ -85,7 +86,11 @@ __device__ __forceinline__ float gated_act(float g, float u) {
   }
 }
 
-template <int BN, bool GATED = false>
+// CB > 1 (decode, swap-AB): the CB batch tiles of one weight slab form a thread-block cluster (1, CB, 1). Each
+// CTA loads 128 / CB rows of every weight k-block and MULTICASTS them into all CB CTAs, so a weight byte crosses
+// the L2 -> SM fabric once per cluster instead of once per batch tile; a stage is recycled when the MMAs of all
+// CB CTAs have read it (multicast tcgen05.commit on every CTA's `empty` barrier).
+template <int BN, bool GATED = false, int CB = 1>
 __global__ void __launch_bounds__(NTHREADS, 1)
     gemm_fp8_kernel(const __grid_constant__ CUtensorMap tmR, const __grid_constant__ CUtensorMap tmC,
                     const __grid_constant__ CUtensorMap tmO, const Params p) {
@@ -112,6 +117,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) probe(p, 0);
+  pdl_launch_dependents();
   int rt = blockIdx.x, ct = blockIdx.y;
   if (p.raster_group > 0) {
     const int per_group = p.raster_group * p.col_tiles;
@@ -127,7 +133,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   if (threadIdx.x == 0) {
     for (int i = 0; i < stages; i++) {
       mbar_init(bar_full + 8u * i, 1);
-      mbar_init(bar_empty + 8u * i, 1);
+      mbar_init(bar_empty + 8u * i, CB);
     }
     mbar_init(bar_tmem, 1);
     mbar_fence_init();
@@ -141,6 +147,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   }
   tc_fence_before();
   __syncthreads();
+  if constexpr (CB > 1) cluster_sync_all();   // every CTA's barriers exist before any multicast traffic
   tc_fence_after();
   const uint32_t tmem_d = *tmem_holder;
   if (threadIdx.x == 0) probe(p, 1);
@@ -154,26 +161,63 @@ __global__ void __launch_bounds__(NTHREADS, 1)
     const uint64_t pol_a = l2_policy_evict_last();
     const uint64_t pol_r = p.swap ? pol_w : pol_a;
     const uint64_t pol_c = p.swap ? pol_a : pol_w;
-    int stage = 0;
-    uint32_t phase = 0;
-    for (int kb = 0; kb < num_kb; kb++) {
+    // Programmatic dependent launch: the weight operand does not depend on the previous kernel, so the first
+    // ring pass of weight tiles is requested before griddepcontrol.wait and streams from HBM while the
+    // predecessor drains; the activation tiles (the predecessor's output) follow after the wait.
+    auto load_w = [&](int stage, int kb) {
+      const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES;
+      if constexpr (CB > 1) {
+        // this CTA's slice of the weight k-block, delivered to every batch tile of the cluster
+        constexpr int SL = BM / CB;
+        const int rk = blockIdx.y;   // cluster (1, CB, 1), gridDim.y == CB: rank in the cluster
+        tma_load_2d_mc(dst + (uint32_t)(rk * SL * BK), &tmR, bar_full + 8u * stage, kb * BK, row0 + rk * SL,
+                       (uint16_t)((1u << CB) - 1u), pol_r);
+      } else if (p.swap) {
+        tma_load_2d(dst, &tmR, bar_full + 8u * stage, kb * BK, row0, pol_r);
+        if constexpr (GATED) tma_load_2d(dst + BM * BK, &tmR, bar_full + 8u * stage, kb * BK, p.gate_rows + row0, pol_r);
+      } else {
+        tma_load_2d(dst + R_BYTES, &tmC, bar_full + 8u * stage, kb * BK, col0, pol_c);
+      }
+    };
+    auto load_a = [&](int stage, int kb) {
+      const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES;
+      if (p.swap) tma_load_2d(dst + R_BYTES, &tmC, bar_full + 8u * stage, kb * BK, col0, pol_c);
+      else tma_load_2d(dst, &tmR, bar_full + 8u * stage, kb * BK, row0, pol_r);
+    };
+    const int pre = num_kb < stages ? num_kb : stages;
+    if (!p.prefetch_w) pdl_wait();
+    if (elect_one()) {
+      for (int kb = 0; kb < pre; kb++) {
+        mbar_arrive_expect_tx(bar_full + 8u * kb, STAGE_BYTES);
+        load_w(kb, kb);
+      }
+    }
+    __syncwarp();
+    if (p.prefetch_w) pdl_wait();
+    if (elect_one()) {
+      probe_kb(p, 0, 0);
+      for (int kb = 0; kb < pre; kb++) load_a(kb, kb);
+      probe(p, 2);
+      probe_kb(p, 1, 0);
+    }
+    __syncwarp();
+    int stage = pre == stages ? 0 : pre;
+    uint32_t phase = pre == stages ? 1u : 0u;
+    for (int kb = pre; kb < num_kb; kb++) {
       mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
       if (elect_one()) {
         probe_kb(p, 0, kb);
-        const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES;
         mbar_arrive_expect_tx(bar_full + 8u * stage, STAGE_BYTES);
-        tma_load_2d(dst, &tmR, bar_full + 8u * stage, kb * BK, row0, pol_r);
-        if constexpr (GATED) tma_load_2d(dst + BM * BK, &tmR, bar_full + 8u * stage, kb * BK, p.gate_rows + row0, pol_r);
-        tma_load_2d(dst + R_BYTES, &tmC, bar_full + 8u * stage, kb * BK, col0, pol_c);
-        if (kb == 0) probe(p, 2);
+        load_w(stage, kb);
+        load_a(stage, kb);
         probe_kb(p, 1, kb);
       }
       __syncwarp();
       if (++stage == stages) { stage = 0; phase ^= 1u; }
     }
-    if (lane == 0) probe(p, 6);
   } else if (warp == 1) {
     // ============================== MMA issuer (warp-uniform loop, one elected lane issues)
+    pdl_wait();   // nothing to issue before the previous kernel's output arrives: block instead of polling
     int stage = 0;
     uint32_t phase = 0;
     for (int kb = 0; kb < num_kb; kb++) {
@@ -198,7 +242,9 @@ __global__ void __launch_bounds__(NTHREADS, 1)
             tc_mma_f8(tmem_d + BN, du + (uint64_t)(k * UMMA_K >> 4), db + (uint64_t)(k * UMMA_K >> 4), IDESC,
                       (kb > 0 || k > 0) ? 1u : 0u);
         }
-        tc_commit(bar_empty + 8u * stage);  // frees the smem slot when the MMAs have read it
+        // frees the smem slot when the MMAs have read it (in every CTA that multicasts into it)
+        if constexpr (CB > 1) tc_commit_mc(bar_empty + 8u * stage, (uint16_t)((1u << CB) - 1u));
+        else tc_commit(bar_empty + 8u * stage);
         probe_kb(p, 3, kb);
         if (kb == num_kb - 1) {
           tc_commit(bar_tmem);  // accumulator complete
@@ -211,6 +257,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   } else {
     // ============================== epilogue (4 warps, one TMEM lane quarter each)
     const int wq = warp & 3;
+    pdl_wait();   // scales / bias may be the previous kernel's output; `out` may still be read by it
     mbar_wait(bar_tmem, 0);
     tc_fence_after();
     if (warp == 2 && lane == 0) probe(p, 5);
@@ -320,6 +367,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
       fence_proxy_async();  // generic-proxy smem writes -> visible to the TMA (async proxy)
       asm volatile("bar.sync 1, 128;" ::: "memory");
       if (warp == 2 && lane == 0) {
+        probe(p, 6);
         asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];" ::"l"(&tmO),
                      "r"(row0), "r"(col0), "r"(stile)
                      : "memory");
@@ -380,6 +428,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   }
   tc_fence_before();
   __syncthreads();
+  if constexpr (CB > 1) cluster_sync_all();   // peers may still commit onto this CTA's barriers
   if (threadIdx.x == 0) probe(p, 7);
   if (warp == 1) {
     tc_fence_after();
@@ -388,7 +437,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   }
 }
 
-template <int BN, bool GATED = false>
+template <int BN, bool GATED = false, int CB = 1>
 static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, const CUtensorMap& tmO, Params& p, dim3 grid,
                   cudaStream_t stream) {
   constexpr uint32_t STAGE_BYTES = (GATED ? 2 : 1) * BM * BK + BN * BK;
@@ -402,6 +451,7 @@ static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, const CUtensor
   static const int forced_stages = [] { const char* e = getenv("B200_GEMM_STAGES"); return e ? atoi(e) : 0; }();
   if (forced_stages >= 2 && forced_stages < stages) stages = forced_stages;
   p.stages = stages;
+  p.prefetch_w = pdl_level() >= 2;
   p.trace = g_trace;
   const int smem = stages * (int)STAGE_BYTES + 16 * MAX_STAGES + 64 + 1024;
   static bool configured_dev[64] = {};   // the attribute is per device
@@ -409,12 +459,29 @@ static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, const CUtensor
   cudaGetDevice(&cfg_dev_);
   bool& configured = configured_dev[cfg_dev_ & 63];
   if (!configured) {
-    B200_CUDA(cudaFuncSetAttribute(gemm_fp8_kernel<BN, GATED>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    B200_CUDA(cudaFuncSetAttribute(gemm_fp8_kernel<BN, GATED, CB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    smem_max));
     configured = true;
   }
-  gemm_fp8_kernel<BN, GATED><<<grid, NTHREADS, smem, stream>>>(tmR, tmC, tmO, p);
-  B200_LAUNCH_CHECK();
+  if constexpr (CB > 1) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(NTHREADS);
+    cfg.dynamicSmemBytes = (size_t)smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute at[2];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 1;
+    at[0].val.clusterDim.y = CB;
+    at[0].val.clusterDim.z = 1;
+    at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl_enabled() ? 2 : 1;
+    B200_CUDA(cudaLaunchKernelEx(&cfg, gemm_fp8_kernel<BN, GATED, CB>, tmR, tmC, tmO, p));
+    return B200_OK;
+  }
+  B200_CUDA(launch_pdl(gemm_fp8_kernel<BN, GATED>, grid, dim3(NTHREADS), (size_t)smem, stream, tmR, tmC, tmO, p));
   return B200_OK;
 }
 
@@ -471,6 +538,7 @@ extern "C" int b200_fp8_gemm(void* out, const void* a, const void* b, const floa
   memset(&tmO, 0, sizeof(tmO));
   int rc;
   int bn;
+  int cb = 1;   // batch tiles per cluster (weight multicast), swap mode only
   const int sms = sm_count();
   if (swap) {
     // rows = weight [N,K], cols = activation [M,K]. Pick the batch tile BN (and with it the number
@@ -497,10 +565,14 @@ extern "C" int b200_fp8_gemm(void* out, const void* a, const void* b, const floa
     p.R = N; p.C = M;
     p.r_scale = b_scale; p.r_scale_vec = b_scale_per_col;
     p.c_scale = a_scale; p.c_scale_vec = a_scale_per_row;
-    rc = make_tmap_2d(&tmR, b, N, K, ldb, BM);
+    // 2 or 4 batch tiles per weight slab: one thread-block cluster per slab, weight k-blocks multicast
+    // (B200_GEMM_CLUSTER=0 keeps every CTA on its own loads)
+    static const int use_cluster = [] { const char* e = getenv("B200_GEMM_CLUSTER"); return e ? atoi(e) : 1; }();
+    const int gy = (M + bn - 1) / bn;
+    if (use_cluster && (gy == 2 || gy == 4) && bn >= 32 && bn <= 128) cb = gy;
+    rc = make_tmap_2d(&tmR, b, N, K, ldb, BM / cb);
     if (rc) return rc;
     rc = make_tmap_2d(&tmC, a, M, K, lda, bn);
-    if (rc) return rc;
     if (((uintptr_t)out & 15) == 0 && (ldo * 2) % 16 == 0) {
       uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
       uint64_t strides[1] = {(uint64_t)ldo * 2};
@@ -526,6 +598,19 @@ extern "C" int b200_fp8_gemm(void* out, const void* a, const void* b, const floa
     p.col_tiles = grid.y;
     p.raster_group = 16;
     grid = dim3(grid.x * grid.y, 1);
+  }
+  if (cb == 2) {
+    switch (bn) {
+      case 32: return launch<32, false, 2>(tmR, tmC, tmO, p, grid, stream);
+      case 64: return launch<64, false, 2>(tmR, tmC, tmO, p, grid, stream);
+      default: return launch<128, false, 2>(tmR, tmC, tmO, p, grid, stream);
+    }
+  }
+  if (cb == 4) {
+    switch (bn) {
+      case 32: return launch<32, false, 4>(tmR, tmC, tmO, p, grid, stream);
+      default: return launch<64, false, 4>(tmR, tmC, tmO, p, grid, stream);
+    }
   }
   switch (bn) {
     case 16: return launch<16>(tmR, tmC, tmO, p, grid, stream);

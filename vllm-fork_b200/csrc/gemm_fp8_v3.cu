@@ -55,6 +55,7 @@ struct Params {
   int64_t ldo;
   int r_scale_vec, c_scale_vec;
   int swap, out_bf16, stages, tma_store;
+  int prefetch_w;         // PDL level 2 (decode, swap): weight tiles of the first ring pass precede griddepcontrol.wait
   int row_tiles, col_tiles, num_kb;   // tiles of 256 rows x BN cols, k-blocks per tile
   int pairs;
   // Work split. interleave = 0: stream-K, pair i takes the i-th equal contiguous range of the flattened
@@ -206,6 +207,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t cta = cluster_ctarank();
   const int pair = blockIdx.x >> 1;
+  pdl_launch_dependents();
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < stages; i++) {
@@ -247,19 +249,43 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
     int stage = 0;
     uint32_t phase = 0;
     Piece pc;
+    // Programmatic dependent launch, level 2 (decode): the weight tiles (rows operand) of the first ring pass do
+    // not depend on the previous kernel; they are requested before griddepcontrol.wait from a copy of the
+    // scheduler state, the activation tiles of the same k-blocks follow after the wait.
+    int pre = 0;
+    if (p.prefetch_w && p.swap) {
+      Sched s1 = sched;
+      while (pre < stages && next_piece(p, s1, &pc)) {
+        int rt, ct;
+        tile_coords(p, pc.tile, &rt, &ct);
+        const int row0 = rt * 2 * BM + (int)cta * BM;
+        for (int kb = pc.kb0; kb < pc.kb1 && pre < stages; kb++, pre++) {
+          if (elect_one()) {
+            if (cta == 0) mbar_arrive_expect_tx(bar_full + 8u * pre, 2 * STAGE_BYTES);
+            tma_load_2d_2sm(base + (uint32_t)pre * STAGE_BYTES, &tmR, bar_full + 8u * pre, kb * BK, row0, pol_r);
+          }
+          __syncwarp();
+        }
+      }
+    }
+    pdl_wait();
+    int n = 0;
     while (next_piece(p, sched, &pc)) {
       int rt, ct;
       tile_coords(p, pc.tile, &rt, &ct);
       const int row0 = rt * 2 * BM + (int)cta * BM;
       const int col0 = ct * BN + (int)cta * (BN / 2);
-      for (int kb = pc.kb0; kb < pc.kb1; kb++) {
-        mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
+      for (int kb = pc.kb0; kb < pc.kb1; kb++, n++) {
+        const bool w_in_flight = n < pre;   // first ring pass: slot free, weights already requested
+        if (!w_in_flight) mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
         if (elect_one()) {
           const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES;
           // the leader's barrier counts the bytes of BOTH CTAs (the peer's complete_tx may land first:
           // the tx-count simply goes negative until the leader's expect_tx)
-          if (cta == 0) mbar_arrive_expect_tx(bar_full + 8u * stage, 2 * STAGE_BYTES);
-          tma_load_2d_2sm(dst, &tmR, bar_full + 8u * stage, kb * BK, row0, pol_r);
+          if (!w_in_flight) {
+            if (cta == 0) mbar_arrive_expect_tx(bar_full + 8u * stage, 2 * STAGE_BYTES);
+            tma_load_2d_2sm(dst, &tmR, bar_full + 8u * stage, kb * BK, row0, pol_r);
+          }
           tma_load_2d_2sm(dst + R_BYTES, &tmC, bar_full + 8u * stage, kb * BK, col0, pol_c);
         }
         __syncwarp();
@@ -268,6 +294,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
     }
   } else if (warp == 1) {
     // ============================== MMA issuer: one elected lane of the LEADER CTA drives both tensor cores
+    pdl_wait();   // nothing to issue before the previous kernel's output arrives: block instead of polling
     if (cta == 0) {
       int stage = 0;
       uint32_t phase = 0;
@@ -310,6 +337,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
     uint32_t tphase[2] = {0, 0};
     Piece pc;
     int n = 0;
+    pdl_wait();   // scales / workspace flags / `out` are shared with the previous kernel on the stream
     uint16_t* out16 = reinterpret_cast<uint16_t*>(p.out);
     const uint16_t* bias16 = reinterpret_cast<const uint16_t*>(p.bias);
     auto to_f32 = [&](uint16_t h) -> float {
@@ -633,8 +661,9 @@ static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, const CUtensor
   // a split tile costs more than the idle half wave, timeline in profiles/r1c_gemm_v3.md)
   p.interleave = ((!p.swap && tiles >= 4 * (int64_t)p.pairs) || (p.swap && tiles >= (int64_t)p.pairs)) ? 1 : 0;
   p.raster_group = (p.interleave && !p.swap) ? 8 : 0;
-  gemm_fp8_v3_kernel<BN><<<p.pairs * 2, NTHREADS, smem, stream>>>(tmR, tmC, tmO, p);
-  B200_LAUNCH_CHECK();
+  p.prefetch_w = pdl_level() >= 2;
+  B200_CUDA(launch_pdl(gemm_fp8_v3_kernel<BN>, dim3(p.pairs * 2), dim3(NTHREADS), (size_t)smem, stream, tmR, tmC,
+                       tmO, p));
   return B200_OK;
 }
 

@@ -42,6 +42,7 @@ struct Params {
   int R, C, K;            // weight rows (N), batch (M), reduction
   int r_scale_vec, c_scale_vec;
   int out_bf16, stages, num_kb, split;
+  int prefetch_w;         // PDL level 2: weight tiles of the first ring pass precede griddepcontrol.wait
 };
 
 using namespace b200::tc;
@@ -123,6 +124,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   const int tile = blockIdx.x / (2 * split);
   const int kb0 = p.num_kb * s / split, kb1 = p.num_kb * (s + 1) / split;
   const int row0 = tile * 2 * BM + (int)h * BM;   // this CTA's first weight row
+  pdl_launch_dependents();
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < stages; i++) {
@@ -150,9 +152,28 @@ __global__ void __launch_bounds__(NTHREADS, 1)
     prefetch_tmap(&tmC);
     const uint64_t pol_w = l2_policy_evict_first();   // weights stream once
     const uint64_t pol_a = l2_policy_evict_last();    // the batch is re-read by every cluster
-    int stage = 0;
-    uint32_t phase = 0;
-    for (int kb = kb0; kb < kb1; kb++) {
+    // Programmatic dependent launch: weight tiles of the first ring pass before griddepcontrol.wait (level 2),
+    // the activation tiles (the previous kernel's output) after it
+    const int nkb = kb1 - kb0;
+    const int pre = nkb < stages ? nkb : stages;
+    if (!p.prefetch_w) pdl_wait();
+    if (elect_one()) {
+      for (int i = 0; i < pre; i++) {
+        if (h == 0) mbar_arrive_expect_tx(bar_full + 8u * i, 2 * STAGE_BYTES);
+        tma_load_2d_2sm(base + (uint32_t)i * STAGE_BYTES, &tmR, bar_full + 8u * i, (kb0 + i) * BK, row0, pol_w);
+      }
+    }
+    __syncwarp();
+    if (p.prefetch_w) pdl_wait();
+    if (elect_one()) {
+      for (int i = 0; i < pre; i++)
+        tma_load_2d_2sm(base + (uint32_t)i * STAGE_BYTES + R_BYTES, &tmC, bar_full + 8u * i, (kb0 + i) * BK,
+                        (int)h * (BN / 2), pol_a);
+    }
+    __syncwarp();
+    int stage = pre == stages ? 0 : pre;
+    uint32_t phase = pre == stages ? 1u : 0u;
+    for (int kb = kb0 + pre; kb < kb1; kb++) {
       mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
       if (elect_one()) {
         const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES;
@@ -165,6 +186,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
     }
   } else if (warp == 1) {
     // ============================== MMA issuer: one elected lane of the even CTA drives both tensor cores
+    pdl_wait();   // nothing to issue before the previous kernel's output arrives: block instead of polling
     if (h == 0) {
       const uint16_t pair_mask = (uint16_t)(3u << (2 * s));
       int stage = 0;
@@ -189,6 +211,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
     }
     __syncwarp();
   } else {
+    pdl_wait();                // scales / bias / `out` are shared with the previous kernel on the stream
     mbar_wait(bar_tfull, 0);   // this pair's partial accumulator is complete, its pipeline smem idle
     tc_fence_after();
   }
@@ -402,13 +425,16 @@ static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, const CUtensor
   cfg.blockDim = dim3(NTHREADS);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute at[1];
+  cudaLaunchAttribute at[2];
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = 2 * split;
   at[0].val.clusterDim.y = 1;
   at[0].val.clusterDim.z = 1;
+  at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
+  p.prefetch_w = pdl_level() >= 2;
   B200_CUDA(cudaLaunchKernelEx(&cfg, gemm_fp8_v4_kernel<BN>, tmR, tmC, tmO, p));
   return B200_OK;
 }

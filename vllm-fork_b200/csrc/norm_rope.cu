@@ -23,6 +23,8 @@ __global__ void __launch_bounds__(256)
                     int hidden, int64_t in_stride, int64_t out_stride) {
   constexpr int N = 16 / sizeof(T);
   __shared__ float red[32];
+  pdl_launch_dependents();
+  pdl_wait();   // input / residual come from the previous kernel on the stream
   const int64_t row = blockIdx.x;
   T* in_row = input + row * in_stride;
   T* res_row = ADD ? residual + row * (int64_t)hidden : nullptr;
@@ -121,9 +123,8 @@ static int launch_norm(void* out, void* input, void* residual, const void* weigh
   const int nv = hidden / N;
   dim3 grid((unsigned)num_tokens);
 #define B200_NORM(RR)                                                                            \
-  rms_norm_kernel<T, ADD, QUANT, RR><<<grid, 256, 0, stream>>>(out, (T*)input, (T*)residual,      \
-                                                               (const T*)weight, scale, eps, hidden, \
-                                                               in_stride, out_stride)
+  B200_CUDA(launch_pdl(rms_norm_kernel<T, ADD, QUANT, RR>, grid, dim3(256), 0, stream, out, (T*)input,   \
+                       (T*)residual, (const T*)weight, scale, eps, hidden, in_stride, out_stride))
   if (nv <= 256) B200_NORM(1);
   else if (nv <= 512) B200_NORM(2);
   else if (nv <= 1024) B200_NORM(4);

@@ -27,6 +27,8 @@ __global__ void __launch_bounds__(256)
                           int kv_scale_stride, int vec_ok) {
   using out_t = typename std::conditional<FP8, uint8_t, T>::type;
   constexpr int N = 16 / sizeof(T);
+  pdl_launch_dependents();
+  pdl_wait();   // q / k / v are the qkv GEMM's output
   const int64_t tok = blockIdx.x;
   const int64_t pos = positions[tok];
   const int embed = rot_dim / 2;
@@ -156,10 +158,10 @@ extern "C" int b200_rope_and_cache_flash(const int64_t* positions, void* query, 
                      (page_stride * osz) % (8 * osz) == 0 && (head_stride * osz) % (8 * osz) == 0;
   dim3 grid((unsigned)num_tokens);
 #define B200_RC(T, NX, F8)                                                                                   \
-  rope_and_cache_kernel<T, NX, F8><<<grid, 256, 0, stream>>>(                                                \
+  B200_CUDA(launch_pdl(rope_and_cache_kernel<T, NX, F8>, grid, dim3(256), 0, stream,                         \
       positions, (T*)query, (T*)key, (const T*)value, (const T*)cos_sin_cache, key_cache, value_cache,       \
       slot_mapping, rot_dim, head_size, num_heads, num_kv_heads, block_size, query_stride, key_stride,       \
-      value_stride, block_stride, page_stride, head_stride, k_scale, v_scale, kv_scale_stride, vec_ok)
+      value_stride, block_stride, page_stride, head_stride, k_scale, v_scale, kv_scale_stride, vec_ok))
 #define B200_RC2(T)                         \
   do {                                      \
     if (is_neox) {                          \
