@@ -310,6 +310,17 @@ B200_API int b200_fp8_gemm_splitk(void* out, const void* a, const void* b, const
                                   int64_t ldb, int64_t ldo, int a_scale_per_row, int b_scale_per_col,
                                   int out_dtype, int split, b200_stream_t stream);
 
+/* Same contract as b200_fp8_gemm for decode batches (M <= 256): two SMs issue ONE tcgen05.mma.cta_group::2 of
+ * UMMA M = 128 per k-step (swap-AB: 128 weight rows x batch_tile batch rows), each CTA staging its 64 weight rows
+ * and HALF of the batch tile, which halves the bytes an SM has to pull from L2 (the bound of these kernels, ~65 B per
+ * clock and SM) against the one-CTA kernel. This is the tile shape of the reference's CUTLASS config for
+ * M in (64, 256] (c3x/scaled_mm_sm100_fp8_dispatch.cuh:118-134). batch_tile: 0 = auto (the smallest of 32 / 64 /
+ * 128 / 256 whose grid still fits one wave). No workspace. out must be 16-byte aligned with ldo * 2 a multiple of 16. */
+B200_API int b200_fp8_gemm_pair(void* out, const void* a, const void* b, const float* a_scale,
+                                const float* b_scale, const void* bias, int M, int N, int K, int64_t lda,
+                                int64_t ldb, int64_t ldo, int a_scale_per_row, int b_scale_per_col,
+                                int out_dtype, int batch_tile, b200_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Gated activation between the MLP / MoE GEMMs.
  * Replaces torch.ops._C.silu_and_mul (csrc/libtorch_stable/activation_kernels.cu:102-160,291-296):

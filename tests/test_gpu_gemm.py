@@ -228,3 +228,65 @@ def test_splitk_rejects_large_batches():
     one = torch.ones(1, device=DEV)
     with pytest.raises(RuntimeError, match="decode batches only"):
         _ops().cutlass_scaled_mm(x, w, one, one, torch.bfloat16, impl="v4")
+
+
+# ------------------------------------------------------------------ v5: CTA pairs of UMMA M = 128 (decode batches)
+V5_MNK = [(1, 256, 128), (16, 4096, 4096), (33, 1024, 1024), (64, 4096, 14336), (100, 6144, 4096),
+          (128, 8192, 1024), (128, 7168, 8192), (200, 272, 512), (256, 4096, 4096), (256, 6144, 4096),
+          (256, 4096, 14336), (250, 1296, 496), (129, 64, 128)]
+
+
+@pytest.mark.parametrize("bt", [0, 32, 64, 128, 256])
+@pytest.mark.parametrize("mnk", V5_MNK)
+def test_pair_shapes(mnk, bt):
+    run_case(*mnk, False, False, torch.bfloat16, False, impl="v5" if bt == 0 else f"v5:{bt}")
+
+
+@pytest.mark.parametrize("mnk", [(33, 1024, 1024), (256, 4096, 4096), (200, 272, 512)])
+@pytest.mark.parametrize("per_token,per_channel", [(True, False), (False, True), (True, True)])
+@pytest.mark.parametrize("out_dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("use_bias", [False, True])
+def test_pair_scales_bias_dtypes(mnk, per_token, per_channel, out_dtype, use_bias):
+    run_case(*mnk, per_token, per_channel, out_dtype, use_bias, seed=1, impl="v5")
+
+
+def test_pair_exact_and_bit_identical_to_v2():
+    """(a) integer-valued operands: bit-exact for every batch tile; (b) random operands: same k order and the same
+    epilogue arithmetic as the one-CTA kernel, so the outputs are bit-identical to v2."""
+    g = torch.Generator().manual_seed(4)
+    one = torch.tensor([0.5], device=DEV)
+    for M, N, K in [(7, 256, 128), (130, 384, 512), (256, 256, 1024), (256, 4096, 4096), (64, 1024, 14336),
+                    (255, 208, 256)]:
+        a = torch.randint(-2, 3, (M, K), generator=g).float()
+        w = torch.randint(-2, 3, (N, K), generator=g).float()
+        ref = ((a.double() @ w.double().t()).float() * 0.25).to(torch.bfloat16).float()
+        ag = to_fp8_bits(a).to(DEV).view(torch.float8_e4m3fn)
+        wg = to_fp8_bits(w).to(DEV).view(torch.float8_e4m3fn).t()
+        for bt in (0, 32, 64, 128, 256):
+            out = _ops().cutlass_scaled_mm(ag, wg, one, one, torch.bfloat16, impl="v5" if bt == 0 else f"v5:{bt}")
+            assert torch.equal(out.float().cpu(), ref), (M, N, K, bt)
+    for M, N, K in [(256, 6144, 4096), (100, 4096, 1024), (17, 1280, 8192)]:
+        a8 = to_fp8_bits(torch.randn(M, K, generator=g)).to(DEV).view(torch.float8_e4m3fn)
+        w8 = to_fp8_bits(torch.randn(N, K, generator=g)).to(DEV).view(torch.float8_e4m3fn).t()
+        sa, sb = torch.tensor([0.03], device=DEV), torch.tensor([0.02], device=DEV)
+        o2 = _ops().cutlass_scaled_mm(a8, w8, sa, sb, torch.bfloat16, impl="v2")
+        for bt in (0, 64, 256):
+            o5 = _ops().cutlass_scaled_mm(a8, w8, sa, sb, torch.bfloat16, impl="v5" if bt == 0 else f"v5:{bt}")
+            assert torch.equal(o5, o2), (M, N, K, bt)
+
+
+def test_pair_strided_and_rejections():
+    g = torch.Generator().manual_seed(6)
+    one = torch.ones(1, device=DEV)
+    # a is a column slice of a wider buffer, out a column slice of a wider output (strides are part of the ABI)
+    big = to_fp8_bits(torch.randn(40, 1024, generator=g)).to(DEV).view(torch.float8_e4m3fn)
+    a = big[:, 256:768]
+    w = to_fp8_bits(torch.randn(384, 512, generator=g)).to(DEV).view(torch.float8_e4m3fn)
+    wide = torch.zeros(40, 1024, dtype=torch.bfloat16, device=DEV)
+    o5 = _ops().cutlass_scaled_mm(a, w.t(), one, one, torch.bfloat16, out=wide[:, 128:512], impl="v5")
+    o2 = _ops().cutlass_scaled_mm(a.contiguous(), w.t(), one, one, torch.bfloat16, impl="v2")
+    assert torch.equal(o5, o2) and not wide[:, :128].any() and not wide[:, 512:].any()
+    x = torch.zeros(300, 256, dtype=torch.uint8, device=DEV).view(torch.float8_e4m3fn)
+    w0 = torch.zeros(256, 256, dtype=torch.uint8, device=DEV).view(torch.float8_e4m3fn).t()
+    with pytest.raises(RuntimeError, match="decode batches only"):
+        _ops().cutlass_scaled_mm(x, w0, one, one, torch.bfloat16, impl="v5")

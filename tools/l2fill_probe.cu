@@ -70,6 +70,9 @@ struct P {
   int w_kblocks;     // K / 128 of the weight matrix
   int stream_rows;   // > 0: pure HBM read test: every (CTA, iteration) reads its own contiguous tile of this many 128-byte rows
   int stages;
+  int w_advance;     // 1: after K / 128 k-blocks the CTA moves on to fresh weight rows (no re-read: a true HBM stream of
+                     //    [w_rows x 128 B] boxes at row pitch K, the access pattern of a row-major weight matrix)
+  int w_halves;      // 2: the weight box is issued as two boxes of w_rows / 2 rows (same bytes, more TMA operations)
 };
 
 
@@ -105,7 +108,15 @@ __global__ void __launch_bounds__(128, 1) fill_kernel(const __grid_constant__ CU
       const uint32_t dst = base + st * stage_bytes;
       mbar_expect_tx(bars + 8u * st, stage_bytes);
       if (p.stream_rows) tma_2d(dst, &tmAs, bars + 8u * st, 0, (it * (int)gridDim.x + (int)blockIdx.x) * p.stream_rows);
-      if (p.w_rows) tma_2d(dst, &tmW, bars + 8u * st, (it % p.w_kblocks) * 128, row0);
+      if (p.w_rows) {
+        const int r0 = p.w_advance ? (blockIdx.x + (it / p.w_kblocks) * (int)gridDim.x) * p.w_rows : row0;
+        if (p.w_halves == 2) {
+          tma_2d(dst, &tmW, bars + 8u * st, (it % p.w_kblocks) * 128, r0);
+          tma_2d(dst + (p.w_rows / 2) * 128u, &tmW, bars + 8u * st, (it % p.w_kblocks) * 128, r0 + p.w_rows / 2);
+        } else {
+          tma_2d(dst, &tmW, bars + 8u * st, (it % p.w_kblocks) * 128, r0);
+        }
+      }
       if (p.a_rows) {
         const int kb = it % p.a_kblocks;
         if (p.csz > 1)
@@ -162,13 +173,24 @@ int main() {
   cudaEvent_t e0, e1;
   CK(cudaEventCreate(&e0));
   CK(cudaEventCreate(&e1));
-  struct Cfg { int ctas, w_rows, a_rows, csz; const char* what; int stream_rows = 0; int stages = 4; };
+  struct Cfg { int ctas, w_rows, a_rows, csz; const char* what; int stream_rows = 0; int stages = 4; int adv = 0; int halves = 1; int kbytes = 0; };
   std::vector<Cfg> cfgs = {
       {sms, 0, 0, 1, "pure HBM read, contiguous 32 KB tiles, 4 stages (128 KB in flight per SM)", 256, 4},
       {sms, 0, 0, 1, "pure HBM read, contiguous 32 KB tiles, 6 stages (192 KB in flight per SM)", 256, 6},
       {sms, 0, 0, 1, "pure HBM read, contiguous 16 KB tiles, 12 stages (192 KB in flight per SM)", 128, 12},
       {sms, 0, 0, 1, "pure HBM read, contiguous 8 KB tiles, 24 stages (192 KB in flight per SM)", 64, 24},
       {sms, 128, 0, 1, "weights only (8x re-read: mostly L2), all SMs"},
+      {sms, 128, 0, 1, "ROW-MAJOR WEIGHT STREAM: 128-row x 128 B boxes at pitch 4096, fresh rows (HBM), 148 CTAs, 8 stages", 0, 8, 1},
+      {128, 128, 0, 1, "row-major weight stream, pitch 4096, 128 CTAs, 8 stages", 0, 8, 1},
+      {64, 128, 0, 1, "row-major weight stream, pitch 4096, 64 CTAs, 8 stages", 0, 8, 1},
+      {32, 128, 0, 1, "row-major weight stream, pitch 4096, 32 CTAs, 8 stages", 0, 8, 1},
+      {32, 128, 0, 1, "row-major weight stream, pitch 4096, 32 CTAs, 12 stages", 0, 12, 1},
+      {sms, 64, 0, 1, "row-major weight stream, 64-row boxes, pitch 4096, 148 CTAs, 16 stages", 0, 16, 1},
+      {sms, 128, 0, 1, "row-major weight stream, pitch 4096, 148 CTAs, 8 stages, two 64-row boxes per stage", 0, 8, 1, 2},
+      {sms, 128, 0, 1, "row-major weight stream, pitch 14336, 148 CTAs, 8 stages", 0, 8, 1, 1, 14336},
+      {32, 128, 0, 1, "row-major weight stream, pitch 14336, 32 CTAs, 8 stages", 0, 8, 1, 1, 14336},
+      {sms, 128, 64, 1, "row-major weight stream (fresh rows) + 64 shared rows, pitch 4096, 148 CTAs, 8 stages (v2 BN=64 traffic)", 0, 8, 1},
+      {128, 64, 64, 1, "row-major weight stream 64-row boxes + 64 shared rows, 128 CTAs, 12 stages (pair kernel traffic)", 0, 12, 1},
       {sms, 0, 256, 1, "shared 256-row block only, unicast, all SMs"},
       {16, 0, 256, 1, "shared block only, unicast, 16 SMs (per-SM ingest)"},
       {64, 0, 256, 1, "shared block only, unicast, 64 SMs"},
@@ -189,12 +211,17 @@ int main() {
     p.w_rows = c.w_rows;
     p.a_rows = c.a_rows;
     p.csz = c.csz;
+    const int Kc = c.kbytes ? c.kbytes : K;
     p.a_kblocks = K / 128;
-    p.w_kblocks = K / 128;
+    p.w_kblocks = Kc / 128;
+    p.w_advance = c.adv;
+    p.w_halves = c.halves;
     p.stream_rows = c.stream_rows;
     p.stages = c.stages;
     if (c.stream_rows) p.iters = (int)((int64_t)w_rows_total * K / 128 / c.stream_rows / c.ctas);
-    CUtensorMap tmW = make_map(w, K, w_rows_total, c.w_rows ? c.w_rows : 128);
+    const uint64_t w_rows_c = (uint64_t)w_rows_total * K / Kc;
+    CUtensorMap tmW = make_map(w, Kc, w_rows_c, c.w_rows ? c.w_rows / c.halves : 128);
+    if (c.adv) p.iters = (4 * 148 / c.ctas) * p.w_kblocks;   // ~300 MB of fresh rows in total: beyond L2 on every repetition
     CUtensorMap tmA = make_map(a, K, 256, c.a_rows ? c.a_rows : 128);
     CUtensorMap tmAs = c.stream_rows ? make_map(w, 128, (uint64_t)w_rows_total * K / 128, c.stream_rows)
                                      : make_map(a, K, 256, c.a_rows ? c.a_rows / c.csz : 128);

@@ -148,6 +148,11 @@ SIGNATURES = {
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64,
          c_int64, c_int64, c_int, c_int, c_int, c_void_p],
     ),
+    "b200_fp8_gemm_pair": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64,
+         c_int64, c_int64, c_int, c_int, c_int, c_int, c_void_p],
+    ),
     "b200_fp8_gemm_splitk": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64,

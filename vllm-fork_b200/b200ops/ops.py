@@ -333,13 +333,10 @@ def cutlass_scaled_mm_supports_fp8(cuda_device_capability: int) -> bool:
 
 
 # which FP8 GEMM kernel cutlass_scaled_mm launches: "v2" = one CTA per tile (csrc/gemm_fp8.cu),
-# "v3" = persistent CTA pairs (cta_group::2), whole-tile raster or stream-K (csrc/gemm_fp8_v3.cu). Both are
-# tcgen05 kernels with the same arithmetic and both are parity-green; this is a tuning switch (env
-# B200_GEMM_IMPL), not a fallback. "auto" (default) follows the measurements on B200
-# (gpurun_out/bg_v2.log, bg_v3.log): M > 256 -> v3 (8192^3: 3.05 vs 2.24 PFLOP/s; 4096^3: 2.29 vs 1.48),
-# decode batches (M <= 256, swap-AB) -> v2 (14.6 / 13.1 / 33.6 us vs 30.6 / 37.5 / 44.5 us on the Llama-8B qkv / o /
-# down shapes: the fp32 partial round trip of stream-K costs more than it balances there) except when N gives
-# every CTA pair at least one whole 256-row weight tile (gate_up: v3 34.4 us vs v2 38.7 us).
+# "v3" = persistent CTA pairs (cta_group::2, UMMA M = 256), whole-tile raster or stream-K (csrc/gemm_fp8_v3.cu),
+# "v4" = split-K over the CTA pairs of a cluster (csrc/gemm_fp8_v4.cu), "v5" = CTA pairs of UMMA M = 128 sharing the
+# batch tile (csrc/gemm_fp8_v5.cu). All are tcgen05 kernels with the same arithmetic and all are parity-green; this
+# is a tuning switch (env B200_GEMM_IMPL), not a fallback. "auto" (default) follows measurements on B200.
 GEMM_IMPL = os.environ.get("B200_GEMM_IMPL", "auto")
 _gemm_ws: dict[str, torch.Tensor] = {}
 _sms: dict[str, int] = {}
@@ -450,20 +447,27 @@ def cutlass_scaled_mm(
               1 if scale_a.numel() > 1 else 0, 1 if scale_b.numel() > 1 else 0, _dt(out))
     which = impl or GEMM_IMPL
     if which == "auto":
-        # decode batches go to v3 only when there are at least as many 256-row weight tiles as CTA pairs
-        # (gate_up: 34.4 vs 38.7 us at batch 256)
+        # Measured on B200 (profiles/r2t_gemm_impls.md, CUDA-graph timed, weights rotated beyond L2):
+        #  * M > 256, or at least as many 256-row weight tiles as CTA pairs (gate_up) -> v3 (persistent pairs);
+        #  * batches <= 64 with few weight tiles -> v4 (split-K over a cluster: the fp32 partial exchange is small);
+        #  * every other decode batch -> v5 (CTA pairs of UMMA M = 128: half the bytes pulled per SM; 10-25 % faster
+        #    than the one-CTA kernel v2 on the qkv / o / down shapes at batch 128-256);
+        #  * v2 remains for outputs that a TMA store cannot address (unaligned base or row stride).
         pairs = _sm_count(a.device) // 2
         tiles = (N + 255) // 256
+        aligned = out.data_ptr() % 16 == 0 and (out.stride(0) * 2) % 16 == 0
         if M > 256 or tiles >= pairs:
             which = "v3"
-        elif (tiles * 2 <= pairs and (M <= 64 or K >= 8192) and out.data_ptr() % 16 == 0
-              and (out.stride(0) * 2) % 16 == 0):
-            # few weight tiles and either a long K (down_proj: 24.5 vs 33.6 us at batch 256) or a small batch
-            # (9.3 vs 11.7 us at batch 16): split K over the CTA pairs of a cluster (csrc/gemm_fp8_v4.cu)
+        elif M <= 64 and tiles * 2 <= pairs and aligned:
             which = "v4"
+        elif aligned:
+            which = "v5"
         else:
             which = "v2"
-    if which.startswith("v4"):   # "v4" (auto split) or "v4:<split>"
+    if which.startswith("v5"):   # "v5" (auto batch tile) or "v5:<batch tile>": CTA pairs of UMMA M = 128
+        bt = int(which[3:]) if len(which) > 3 else 0
+        rc = lib.b200_fp8_gemm_pair(*common, bt, _stream())
+    elif which.startswith("v4"):   # "v4" (auto split) or "v4:<split>"
         split = int(which[3:]) if len(which) > 3 else 0
         rc = lib.b200_fp8_gemm_splitk(*common, split, _stream())
     elif which == "v3":

@@ -302,6 +302,8 @@ template <typename T, int N>
 __global__ void __launch_bounds__(NTHREADS, 1)
     allreduce_one_shot_kernel(Peers pe, uint8_t* __restrict__ out, const uint8_t* stage_src, int rank,
                               int64_t packs, int skip_end) {
+  pdl_launch_dependents();
+  pdl_wait();   // the input (and this context's epoch words) come from earlier kernels on the stream
   uint32_t epoch = pe.sig[rank]->epoch[blockIdx.x];
   stage_input<N>(pe, rank, stage_src, packs, packs);
   if (stage_src) barrier<N, true>(pe, rank, epoch);
@@ -319,6 +321,8 @@ template <typename T, int N>
 __global__ void __launch_bounds__(NTHREADS, 1)
     allreduce_two_shot_kernel(Peers pe, uint8_t* __restrict__ out, const uint8_t* stage_src, int rank,
                               int64_t packs, int skip_end) {
+  pdl_launch_dependents();
+  pdl_wait();   // the input (and this context's epoch words) come from earlier kernels on the stream
   uint32_t epoch = pe.sig[rank]->epoch[blockIdx.x];
   const int64_t part = (packs + N - 1) / N;          // packs per rank slice
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -356,6 +360,8 @@ template <typename T, int N>
 __global__ void __launch_bounds__(NTHREADS, 1)
     allreduce_multimem_kernel(Peers pe, uint8_t* __restrict__ out, uint8_t* mc_out, const uint8_t* stage_src, int rank,
                               int64_t packs) {
+  pdl_launch_dependents();
+  pdl_wait();   // the input (and this context's epoch words) come from earlier kernels on the stream
   uint32_t epoch = pe.sig[rank]->epoch[blockIdx.x];
   const int64_t part = (packs + N - 1) / N;
   stage_input<N>(pe, rank, stage_src, packs, mc_out ? part : packs);

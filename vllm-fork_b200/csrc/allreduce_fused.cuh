@@ -37,6 +37,8 @@ __global__ void __launch_bounds__(256, 1)
     allreduce_fused_norm_kernel(Peers pe, FusedParams fp, const uint8_t* stage_src, int rank) {
   constexpr int NP = 16 / sizeof(T);
   __shared__ float red[32];
+  pdl_launch_dependents();
+  pdl_wait();   // the GEMM output being reduced comes from the previous kernel on the stream
   uint32_t epoch = pe.sig[rank]->epoch[blockIdx.x];
   const int nv = fp.hidden / NP;            // packs per row
   stage_rows<N>(pe, rank, stage_src, fp.M, nv, fp.rows_per_rank);

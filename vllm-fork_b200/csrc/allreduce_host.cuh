@@ -64,10 +64,11 @@ static int launch_ar(const Peers& pe, void* out, const uint8_t* stage_src, int r
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   if (two_shot)
-    allreduce_two_shot_kernel<T, N><<<(int)blocks, NTHREADS, 0, stream>>>(pe, (uint8_t*)out, stage_src, rank, packs, skip_end);
+    B200_CUDA(launch_pdl(allreduce_two_shot_kernel<T, N>, dim3((unsigned)blocks), dim3(NTHREADS), 0, stream, pe,
+                         (uint8_t*)out, stage_src, rank, packs, skip_end));
   else
-    allreduce_one_shot_kernel<T, N><<<(int)blocks, NTHREADS, 0, stream>>>(pe, (uint8_t*)out, stage_src, rank, packs, skip_end);
-  B200_LAUNCH_CHECK();
+    B200_CUDA(launch_pdl(allreduce_one_shot_kernel<T, N>, dim3((unsigned)blocks), dim3(NTHREADS), 0, stream, pe,
+                         (uint8_t*)out, stage_src, rank, packs, skip_end));
   return B200_OK;
 }
 
@@ -93,8 +94,8 @@ static int launch_mc(const Peers& pe, void* out, uint8_t* mc_out, const uint8_t*
   const int cap = sm_count() < MAX_BLOCKS ? sm_count() : MAX_BLOCKS;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-  allreduce_multimem_kernel<T, N><<<(int)blocks, NTHREADS, 0, stream>>>(pe, (uint8_t*)out, mc_out, stage_src, rank, packs);
-  B200_LAUNCH_CHECK();
+  B200_CUDA(launch_pdl(allreduce_multimem_kernel<T, N>, dim3((unsigned)blocks), dim3(NTHREADS), 0, stream, pe,
+                       (uint8_t*)out, mc_out, stage_src, rank, packs));
   return B200_OK;
 }
 
@@ -121,9 +122,11 @@ static int launch_fused(const Peers& pe, const FusedParams& fp, const uint8_t* s
 #define B200_FUSED(RR)                                                                                   \
   do {                                                                                                   \
     if (fp.mc_out && pe.mc_in)                                                                           \
-      allreduce_fused_norm_kernel<T, N, QUANT, RR, true><<<blocks, 256, 0, stream>>>(pe, fp, stage_src, rank); \
+      B200_CUDA(launch_pdl(allreduce_fused_norm_kernel<T, N, QUANT, RR, true>, dim3((unsigned)blocks), dim3(256), 0,  \
+                           stream, pe, fp, stage_src, rank));                                            \
     else                                                                                                 \
-      allreduce_fused_norm_kernel<T, N, QUANT, RR, false><<<blocks, 256, 0, stream>>>(pe, fp, stage_src, rank); \
+      B200_CUDA(launch_pdl(allreduce_fused_norm_kernel<T, N, QUANT, RR, false>, dim3((unsigned)blocks), dim3(256), 0, \
+                           stream, pe, fp, stage_src, rank));                                            \
   } while (0)
   if (nv <= 256) B200_FUSED(1);
   else if (nv <= 512) B200_FUSED(2);

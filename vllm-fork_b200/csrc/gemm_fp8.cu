@@ -42,6 +42,7 @@ struct Params {
   int swap;              // 1: rows operand = weight (out[c][r]); 0: rows operand = activation (out[r][c])
   int out_bf16;
   int stages;
+  int pol_mode;          // tuning knob (B200_GEMM_POL): 0 = weights evict-first / activations evict-last, 1 = both normal
   int prefetch_w;        // PDL level 2: weight tiles of the first ring pass are requested before griddepcontrol.wait
   int tma_store;         // swap mode: stage the tile in smem and write it with one TMA store
   // GATED kernel only (gate_up GEMM + silu_and_mul + static FP8 quant): rows r and gate_rows + r of
@@ -157,14 +158,13 @@ __global__ void __launch_bounds__(NTHREADS, 1)
     prefetch_tmap(&tmR);
     prefetch_tmap(&tmC);
     // weights are streamed once; activations are re-read by every CTA
-    const uint64_t pol_w = l2_policy_evict_first();
-    const uint64_t pol_a = l2_policy_evict_last();
+    const uint64_t pol_w = p.pol_mode ? l2_policy_evict_normal() : l2_policy_evict_first();
+    const uint64_t pol_a = p.pol_mode ? l2_policy_evict_normal() : l2_policy_evict_last();
     const uint64_t pol_r = p.swap ? pol_w : pol_a;
     const uint64_t pol_c = p.swap ? pol_a : pol_w;
-    // Programmatic dependent launch: the weight operand does not depend on the previous kernel, so the first
-    // ring pass of weight tiles is requested before griddepcontrol.wait and streams from HBM while the
-    // predecessor drains; the activation tiles (the predecessor's output) follow after the wait.
-    auto load_w = [&](int stage, int kb) {
+    // One k-block = the rows tile (+ the up slab when GATED) and the cols tile. No run-time branch sits between
+    // elect_one() and the TMA instructions (ptxas would wrap each UTMALDG in an emulation loop, common.cuh).
+    auto load_rows = [&](int stage, int kb) {
       const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES;
       if constexpr (CB > 1) {
         // this CTA's slice of the weight k-block, delivered to every batch tile of the cluster
@@ -172,44 +172,47 @@ __global__ void __launch_bounds__(NTHREADS, 1)
         const int rk = blockIdx.y;   // cluster (1, CB, 1), gridDim.y == CB: rank in the cluster
         tma_load_2d_mc(dst + (uint32_t)(rk * SL * BK), &tmR, bar_full + 8u * stage, kb * BK, row0 + rk * SL,
                        (uint16_t)((1u << CB) - 1u), pol_r);
-      } else if (p.swap) {
+      } else {
         tma_load_2d(dst, &tmR, bar_full + 8u * stage, kb * BK, row0, pol_r);
         if constexpr (GATED) tma_load_2d(dst + BM * BK, &tmR, bar_full + 8u * stage, kb * BK, p.gate_rows + row0, pol_r);
-      } else {
-        tma_load_2d(dst + R_BYTES, &tmC, bar_full + 8u * stage, kb * BK, col0, pol_c);
       }
     };
-    auto load_a = [&](int stage, int kb) {
-      const uint32_t dst = base + (uint32_t)stage * STAGE_BYTES;
-      if (p.swap) tma_load_2d(dst + R_BYTES, &tmC, bar_full + 8u * stage, kb * BK, col0, pol_c);
-      else tma_load_2d(dst, &tmR, bar_full + 8u * stage, kb * BK, row0, pol_r);
+    auto load_cols = [&](int stage, int kb) {
+      tma_load_2d(base + (uint32_t)stage * STAGE_BYTES + R_BYTES, &tmC, bar_full + 8u * stage, kb * BK, col0, pol_c);
     };
-    const int pre = num_kb < stages ? num_kb : stages;
-    if (!p.prefetch_w) pdl_wait();
-    if (elect_one()) {
-      for (int kb = 0; kb < pre; kb++) {
-        mbar_arrive_expect_tx(bar_full + 8u * kb, STAGE_BYTES);
-        load_w(kb, kb);
+    int stage = 0, kb_next = 0;
+    uint32_t phase = 0;
+    if (p.prefetch_w) {
+      // Programmatic dependent launch, level 2 (decode, swap-AB: rows = weights): the weight tiles of the first
+      // ring pass do not depend on the previous kernel; they are requested BEFORE griddepcontrol.wait and stream
+      // from HBM while the predecessor drains. The activation tiles (its output) follow after the wait.
+      const int pre = num_kb < stages ? num_kb : stages;
+      if (elect_one()) {
+        for (int kb = 0; kb < pre; kb++) {
+          mbar_arrive_expect_tx(bar_full + 8u * kb, STAGE_BYTES);
+          load_rows(kb, kb);
+        }
       }
+      __syncwarp();
+      pdl_wait();
+      if (elect_one()) {
+        for (int kb = 0; kb < pre; kb++) load_cols(kb, kb);
+        probe(p, 2);
+      }
+      __syncwarp();
+      kb_next = pre;
+      if (pre == stages) phase = 1u; else stage = pre;
+    } else {
+      pdl_wait();
     }
-    __syncwarp();
-    if (p.prefetch_w) pdl_wait();
-    if (elect_one()) {
-      probe_kb(p, 0, 0);
-      for (int kb = 0; kb < pre; kb++) load_a(kb, kb);
-      probe(p, 2);
-      probe_kb(p, 1, 0);
-    }
-    __syncwarp();
-    int stage = pre == stages ? 0 : pre;
-    uint32_t phase = pre == stages ? 1u : 0u;
-    for (int kb = pre; kb < num_kb; kb++) {
+    for (int kb = kb_next; kb < num_kb; kb++) {
       mbar_wait(bar_empty + 8u * stage, phase ^ 1u);
       if (elect_one()) {
         probe_kb(p, 0, kb);
         mbar_arrive_expect_tx(bar_full + 8u * stage, STAGE_BYTES);
-        load_w(stage, kb);
-        load_a(stage, kb);
+        load_rows(stage, kb);
+        load_cols(stage, kb);
+        if (kb == 0) probe(p, 2);
         probe_kb(p, 1, kb);
       }
       __syncwarp();
@@ -451,7 +454,9 @@ static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, const CUtensor
   static const int forced_stages = [] { const char* e = getenv("B200_GEMM_STAGES"); return e ? atoi(e) : 0; }();
   if (forced_stages >= 2 && forced_stages < stages) stages = forced_stages;
   p.stages = stages;
-  p.prefetch_w = pdl_level() >= 2;
+  static const int pol_mode = [] { const char* e = getenv("B200_GEMM_POL"); return e ? atoi(e) : 0; }();
+  p.pol_mode = pol_mode;
+  p.prefetch_w = (p.swap && pdl_level() >= 2) ? 1 : 0;   // swap-AB: the rows operand is the weight
   p.trace = g_trace;
   const int smem = stages * (int)STAGE_BYTES + 16 * MAX_STAGES + 64 + 1024;
   static bool configured_dev[64] = {};   // the attribute is per device
@@ -490,8 +495,14 @@ static int make_tmap_2d(CUtensorMap* tm, const void* base, int rows, int K, int6
   uint64_t dims[2] = {(uint64_t)K, (uint64_t)rows};
   uint64_t strides[1] = {(uint64_t)ld_bytes};
   uint32_t box[2] = {(uint32_t)BK, (uint32_t)box_rows};
+  // tuning knob B200_GEMM_L2PROMO: 0 none, 1 64 B, 2 128 B, 3 256 B (default)
+  static const int promo = [] { const char* e = getenv("B200_GEMM_L2PROMO"); return e ? atoi(e) : 3; }();
+  const CUtensorMapL2promotion l2 = promo == 0 ? CU_TENSOR_MAP_L2_PROMOTION_NONE
+                                    : promo == 1 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B
+                                    : promo == 2 ? CU_TENSOR_MAP_L2_PROMOTION_L2_128B
+                                                 : CU_TENSOR_MAP_L2_PROMOTION_L2_256B;
   return encode_tensor_map(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, base, dims, strides, box,
-                           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B);
+                           CU_TENSOR_MAP_SWIZZLE_128B, l2);
 }
 
 }  // namespace gemm8
@@ -565,9 +576,11 @@ extern "C" int b200_fp8_gemm(void* out, const void* a, const void* b, const floa
     p.R = N; p.C = M;
     p.r_scale = b_scale; p.r_scale_vec = b_scale_per_col;
     p.c_scale = a_scale; p.c_scale_vec = a_scale_per_row;
-    // 2 or 4 batch tiles per weight slab: one thread-block cluster per slab, weight k-blocks multicast
-    // (B200_GEMM_CLUSTER=0 keeps every CTA on its own loads)
-    static const int use_cluster = [] { const char* e = getenv("B200_GEMM_CLUSTER"); return e ? atoi(e) : 1; }();
+    // 2 or 4 batch tiles per weight slab: optionally one thread-block cluster per slab with the weight k-blocks
+    // multicast (B200_GEMM_CLUSTER=1)
+    // Off by default: measured on B200 (profiles/r2r_gemm_matrix.md) the multicast variant is never faster - the
+    // k-block time of these kernels is set by the load latency x ring depth, not by L2 -> SM traffic.
+    static const int use_cluster = [] { const char* e = getenv("B200_GEMM_CLUSTER"); return e ? atoi(e) : 0; }();
     const int gy = (M + bn - 1) / bn;
     if (use_cluster && (gy == 2 || gy == 4) && bn >= 32 && bn <= 128) cb = gy;
     rc = make_tmap_2d(&tmR, b, N, K, ldb, BM / cb);
