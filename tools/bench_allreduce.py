@@ -18,7 +18,9 @@ def main():
     torch.cuda.set_device(rank)
     dev = torch.device(f"cuda:{rank}")
     dist.init_process_group("nccl", device_id=dev)
-    ar = B200AllReduce(None, dev, max_size=16 << 20, heap_size=64 << 20)
+    ar = B200AllReduce(None, dev, max_size=16 << 20, heap_size=96 << 20)
+    if rank == 0:
+        print(json.dumps({"multicast": ar.multicast_note}), flush=True)
 
     def timeit(fn, iters=20, reps=5):
         s2 = torch.cuda.Stream()
@@ -50,9 +52,23 @@ def main():
         t2 = timeit(lambda: ar.all_reduce(x, out=o, algo=2))
         ts = timeit(lambda: ar.all_reduce(xn, out=o, algo=1))
         tn = timeit(lambda: dist.all_reduce(xn))
+        row = {"bytes": nbytes, "world": world, "one_shot_us": round(t1, 2), "two_shot_us": round(t2, 2),
+               "one_shot_staged_us": round(ts, 2), "nccl_us": round(tn, 2)}
+        if ar.multicast:   # NVSwitch in-network reduction: private output / output broadcast by the switch
+            oh = ar.alloc(n, torch.bfloat16)
+            row["multimem_us"] = round(timeit(lambda: ar.all_reduce(x, out=o, algo=3)), 2)
+            row["multimem_bcast_us"] = round(timeit(lambda: ar.all_reduce(x, out=oh, algo=3)), 2)
+        if nbytes >= 65536 and n % 4096 == 0:
+            # the fused reduce-scatter + residual add + RMSNorm + FP8 quant + all-gather kernel on [M, 4096]
+            M, H = n // 4096, 4096
+            w = torch.ones(H, dtype=torch.bfloat16, device=dev)
+            shard = torch.zeros((M + world - 1) // world, H, dtype=torch.bfloat16, device=dev)
+            sc = torch.tensor([0.05], device=dev)
+            o8 = ar.alloc((M, H), torch.float8_e4m3fn)
+            x2 = x.view(M, H)
+            row["fused_norm_quant_us"] = round(timeit(lambda: ar.fused_add_rms_norm(o8, x2, shard, w, 1e-5, sc)), 2)
         if rank == 0:
-            print(json.dumps({"bytes": nbytes, "world": world, "one_shot_us": round(t1, 2), "two_shot_us": round(t2, 2),
-                              "one_shot_staged_us": round(ts, 2), "nccl_us": round(tn, 2)}), flush=True)
+            print(json.dumps(row), flush=True)
         torch.cuda.synchronize(); dist.barrier()
         ar._heap_used = start
     ar.close()

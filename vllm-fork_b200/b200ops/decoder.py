@@ -73,11 +73,17 @@ class DecoderModel:
                  device: str | torch.device = "cuda:0", tp_rank: int = 0, tp_size: int = 1,
                  tp_group=None, seed: int = 1234, kv_fp8: bool = True, num_blocks: int | None = None,
                  comm: str = "nccl", quant: str = "fp8", multicast: bool | None = None,
-                 pdl: int | None = 2):
+                 pdl: int | str | None = "auto"):
         self.shape = s = shape
-        # programmatic dependent launch between the kernels of the step; level 2 = the GEMMs request their first
-        # weight tiles before waiting for the previous kernel (the weights are never written after init).
-        # B200_PDL in the environment wins (A/B runs); pdl=None leaves the library setting alone.
+        # Programmatic dependent launch between the kernels of the step. "auto": level 2 on one GPU (the GEMMs request
+        # their first weight tiles before waiting for the previous kernel - the weights are never written after init;
+        # +13 % on a launch-bound step, profiles/r2s_small_pdl*.json), OFF with tensor parallelism: measured at 2 / 4 /
+        # 8 ranks (profiles/r2u_*, r2w_*) it is neutral with the one-shot NVLink all-reduce and 2-4 % SLOWER with the
+        # fused / multimem collectives, and one of nine 2-rank runs at level 2 ended in the all-reduce's bounded-spin
+        # trap (a peer 2 flags behind) - not understood yet, so not enabled. B200_PDL in the environment wins (A/B
+        # runs); pdl=None leaves the library setting alone.
+        if pdl == "auto":
+            pdl = 2 if tp_size == 1 else 0
         if pdl is not None and "B200_PDL" not in os.environ:
             ops.set_pdl(pdl)
         self.pdl = ops.set_pdl(0)
