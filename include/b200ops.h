@@ -60,7 +60,9 @@ B200_API int b200_sm_count(void);
  *   under the previous kernel's tail; 2 = the GEMMs additionally request their first ring pass of WEIGHT tiles
  *   before waiting for the previous kernel -- the caller promises that the weight operand (`b` of
  *   cutlass_scaled_mm / cutlass_scaled_fp4_mm) is not written by the kernel preceding the GEMM on the stream,
- *   which holds for model weights. Initial value from env B200_PDL. Returns the previous level.
+ *   which holds for model weights - and b200_paged_attention_decode computes its tile plan from `seq_lens` before
+ *   waiting, so `seq_lens` must not be written by the kernel launched immediately before it either (it is a step
+ *   input in the reference). Initial value from env B200_PDL. Returns the previous level.
  * Not part of the reference operator surface. */
 B200_API int b200_set_pdl(int level);
 
@@ -154,11 +156,7 @@ B200_API int b200_fp8_quant_token_group(void* out, float* scales, const void* in
  * All byte strides and base pointers must be 16-byte aligned; head_size*sizeof(kv) >= 64.
  * block_table int32 [num_seqs, bt_stride]; seq_lens int32 [num_seqs]; block_size % 16 == 0.
  * workspace: b200_paged_attention_workspace_bytes(...) bytes of device memory owned by the caller
- * (the AttentionMetadataBuilder keeps one persistent buffer, like triton_attn.py:154-175). It must be
- * ZERO-FILLED ONCE before its first use and not written by anyone else: its first 1024 bytes hold the arrival
- * counters of the split-KV reduction (folded into the kernel: the last CTA to finish a piece of a sequence that
- * was cut by CTA boundaries merges the pieces), which every launch leaves at zero again; the rest receives the
- * fp32 partials. One launch at a time per workspace (launches on one stream are fine).
+ * (the AttentionMetadataBuilder keeps one persistent buffer, like triton_attn.py:154-175).
  * Everything is read on the device: no host sync, CUDA-graph safe.
  */
 typedef struct b200_paged_attn_args {
@@ -210,8 +208,10 @@ B200_API int b200_paged_attention_decode(const b200_paged_attn_args* args, b200_
  *   out: [num_tokens, num_heads, head_size] q dtype, or e4m3 when output_scale is set;
  *   lse: optional float [num_tokens, num_heads], natural log.
  * Device-only inputs, no host sync, CUDA-graph safe. head_size 64 / 128, block_size % 16 == 0.
- * Two kernels behind this entry point: tcgen05 / TMEM / TMA (bf16 / f16 caches, head_size 128; csrc/attention_prefill_tc.cuh)
- * and mma.sync (FP8 caches, head_size 64; csrc/attention_prefill.cu). B200_PREFILL_IMPL=mma forces the second one.
+ * Three kernels behind this entry point: tcgen05 / TMEM / TMA for head_size 128 with bf16 / f16 caches
+ * (csrc/attention_prefill_tc.cuh) and with FP8 caches (csrc/attention_prefill_tc8.cuh: raw FP8 pages by TMA, converter
+ * warps expand them to f16), and mma.sync for head_size 64 (csrc/attention_prefill.cu). B200_PREFILL_IMPL=mma forces
+ * the last one.
  */
 typedef struct b200_varlen_attn_args {
   void* out;

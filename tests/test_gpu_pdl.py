@@ -1,7 +1,8 @@
-"""Programmatic dependent launch (b200_set_pdl) and the in-kernel split-KV reduction.
+"""Programmatic dependent launch (b200_set_pdl).
 PDL changes WHEN a kernel's prologue runs, never its result: the same chain of hot-path kernels must produce
-identical bytes at levels 0 / 1 / 2, eagerly and from a replayed CUDA graph. The attention kernel's arrival
-counters must re-arm themselves: many launches on one workspace with different cut patterns."""
+identical bytes at levels 0 / 1 / 2, eagerly and from a replayed CUDA graph. The split-KV attention (decode kernel +
+reduce kernel, both launched programmatically) must stay correct over many back-to-back launches on one workspace
+with different cut patterns."""
 import numpy as np
 import pytest
 import torch
@@ -129,10 +130,10 @@ def test_pdl_levels_give_identical_bytes(M):
         ops.set_pdl(prev)
 
 
-def test_split_kv_counters_rearm_across_launches():
+def test_split_kv_back_to_back_launches_on_one_workspace():
     """Ragged batches whose sequences are cut by CTA boundaries in different places, launched back to back on ONE
-    workspace (eager and without host syncs in between): every launch must match the oracle, i.e. the last-arriver
-    reduction re-arms its counters."""
+    workspace (eager and without host syncs in between): every launch must match the oracle - with programmatic
+    launches the reduce kernel of launch i and the decode kernel of launch i+1 are resident together."""
     gen = torch.Generator().manual_seed(5)
     Hq, Hkv, D, bs = 32, 8, 128, 16
     cases = []
@@ -158,7 +159,6 @@ def test_split_kv_counters_rearm_across_launches():
             ops.paged_attention_decode(out, q, kc, vc, bt, lens_d, D ** -0.5, max_seq_len=max(lens), workspace=ws)
             outs.append((out, ref, lens))
     torch.cuda.synchronize()
-    assert int(ws[:1024].view(torch.int32).abs().sum()) == 0, "arrival counters not re-armed"
     for out, ref, lens in outs:
         o = out.float().cpu().numpy()
         assert np.isfinite(o).all()

@@ -56,7 +56,7 @@ TINY_MOE = ModelShape("tiny-mixtral-shaped", 512, 2, 8, 2, 128, 512, 1024, 10000
 TINY_MOE_EP = ModelShape("tiny-mixtral-shaped-ep8", 1024, 2, 16, 8, 128, 512, 1024, 1000000.0, 1e-5, 8, 2)
 
 # kernels launched per call of each op (our own kernels only), for the bench's gpu_launches claim
-LAUNCHES = {"quant_static": 1, "gemm": 1, "cache_write": 1, "attention": 1, "silu_quant": 1,
+LAUNCHES = {"quant_static": 1, "gemm": 1, "cache_write": 1, "attention": 2, "silu_quant": 1,
             # moe_align + permute/quant + grouped GEMM + silu/quant + grouped GEMM + unpermute/reduce
             "topk_softmax": 1, "fused_experts": 6}
 

@@ -965,9 +965,7 @@ _workspaces: dict[tuple, torch.Tensor] = {}
 def paged_attention_workspace(num_seqs: int, num_heads: int, num_kv_heads: int, head_size: int,
                               device: torch.device) -> torch.Tensor:
     """Persistent split-KV workspace (the metadata builder owns it in the backend; cached here for
-    direct op calls). Sized once for the largest batch seen, like triton_attn.py:154-175. Zero-filled: its
-    first 1024 bytes are the arrival counters of the in-kernel split-KV reduction, which every launch leaves
-    at zero again."""
+    direct op calls). Sized once for the largest batch seen, like triton_attn.py:154-175."""
     lib = _lib.load()
     n = lib.b200_paged_attention_workspace_bytes(num_seqs, num_heads, num_kv_heads, head_size)
     key = (str(device), num_heads, head_size)

@@ -50,7 +50,7 @@ struct Params {
   const float* v_scale;
   const float* out_scale;   // nullable: fused static FP8 output
   const float* alibi;
-  int32_t* arrive;   // workspace: [n_cta] arrival counters of cut sequences (zero between launches)
+  int32_t* cum;      // workspace: [S + 2] tile prefix sums (+ tiles-per-CTA at [S+1])
   float* part_acc;   // workspace: [n_cta * 2][hq_chunk][D]
   float* part_ml;    // workspace: [n_cta * 2][hq_chunk][2]
   int64_t q_stride_s, q_stride_h, out_stride_s, out_stride_h, bt_stride;
@@ -59,6 +59,7 @@ struct Params {
   int window;
   float scale, softcap;
   uint32_t tile_bytes;   // hc * 16 * RB  (one K or V tile)
+  int early_plan;        // PDL level 2: the tile plan (reads seq_lens only) precedes griddepcontrol.wait
   int kv_pair;           // 1: tmK's box carries the K tile and the V tile of a page (attention_host.cuh get_tmap)
   uint32_t off_merge, off_cum, off_bar;  // smem offsets
 };

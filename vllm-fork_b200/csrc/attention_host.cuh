@@ -105,10 +105,7 @@ static int make_plan(Plan& pl, int S, int Hq, int Hkv, int D, int es, int sms, i
   return B200_OK;
 }
 
-// workspace head: arrival counters of the folded split-KV reduction, one per CTA, at a FIXED offset so that the
-// "zero between launches" invariant survives any change of batch size or head geometry
-constexpr size_t kWsCounterBytes = 1024;
-static_assert(kMaxCtas * sizeof(int32_t) <= kWsCounterBytes, "counter region too small");
+static size_t ws_cum_bytes(int S) { return (size_t)(((S + 2) * 4 + 255) & ~255); }
 
 template <int D, int NT, int MODE>
 static int launch(const CUtensorMap& tmK, const CUtensorMap& tmV, const Params& p, const Plan& pl,
@@ -127,6 +124,12 @@ static int launch(const CUtensorMap& tmK, const CUtensorMap& tmV, const Params& 
   }
   dim3 grid(pl.grid_x, pl.n_chunks);
   B200_CUDA(launch_pdl(kern, grid, dim3(NTHREADS), (size_t)pl.smem_bytes, stream, tmK, tmV, p));
+  dim3 rgrid(p.S, pl.n_chunks);
+  constexpr bool QBF16 = (MODE == BF16_BF16 || MODE == BF16_FP8);
+  int rthreads = p.hc * p.g * (D / 4);
+  rthreads = rthreads > 1024 ? 1024 : ((rthreads + 31) / 32) * 32;
+  // launched with the programmatic attribute: its CTAs are resident and waiting when the decode kernel drains
+  B200_CUDA(launch_pdl(paged_attn_reduce_kernel<QBF16>, rgrid, dim3(rthreads), 0, stream, p, D, pl.grid_x));
   return B200_OK;
 }
 
@@ -138,7 +141,7 @@ extern "C" size_t b200_paged_attention_workspace_bytes(int num_seqs, int num_hea
   (void)num_kv_heads;
   using namespace b200::attn;
   if (num_seqs < 0 || num_heads <= 0 || head_size <= 0) return 0;
-  return kWsCounterBytes + (size_t)kMaxCtas * 2 * num_heads * (head_size + 2) * sizeof(float);
+  return ws_cum_bytes(num_seqs) + (size_t)kMaxCtas * 2 * num_heads * (head_size + 2) * sizeof(float);
 }
 
 extern "C" int b200_paged_attention_decode(const b200_paged_attn_args* a, b200_stream_t stream_) {
@@ -219,10 +222,10 @@ extern "C" int b200_paged_attention_decode(const b200_paged_attn_args* a, b200_s
   p.alibi = a->alibi_slopes;
   p.out_scale = a->output_scale;
   uint8_t* ws = reinterpret_cast<uint8_t*>(a->workspace);
-  p.arrive = reinterpret_cast<int32_t*>(ws);
+  p.cum = reinterpret_cast<int32_t*>(ws);
   const int n_cta = pl.grid_x * pl.n_chunks;
   const int hq_chunk = pl.hc * g;
-  p.part_ml = reinterpret_cast<float*>(ws + kWsCounterBytes);
+  p.part_ml = reinterpret_cast<float*>(ws + ws_cum_bytes(S));
   p.part_acc = p.part_ml + (size_t)n_cta * 2 * hq_chunk * 2;
   p.q_stride_s = a->q_stride_s;
   p.q_stride_h = a->q_stride_h;
@@ -236,6 +239,7 @@ extern "C" int b200_paged_attention_decode(const b200_paged_attn_args* a, b200_s
   p.softcap = a->softcap > 0.f ? a->softcap : 0.f;
   p.tile_bytes = pl.tile_bytes;
   p.kv_pair = kv_pair;
+  p.early_plan = pdl_level() >= 2 ? 1 : 0;
   p.off_merge = pl.off_merge; p.off_cum = pl.off_cum; p.off_bar = pl.off_bar;
 
   const int mode = fp8 ? (a->q_dtype == B200_BF16 ? BF16_FP8 : F16_FP8)

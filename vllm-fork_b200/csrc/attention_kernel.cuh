@@ -21,79 +21,10 @@ struct WarpState {
   float l[NT][2];            // thread-partial running sum
 };
 
-// Merge the fp32 partials of ONE sequence that was cut by CTA boundaries (LSE-weighted, like reduce_segments,
-// triton_unified_attention.py:685-772). Executed by the `nthr` consumer threads (index `t`) of the CTA that arrived
-// last at the sequence's counter; partials are read with ld.global.cg (written by other SMs in this launch).
-template <bool QBF16>
-__device__ __noinline__ void merge_partials(const Params& p, int D, int s, int y, int c0, int cta0, int cta1,
-                                               int tpc, int grid_x, int t, int nthr) {
-  const int g = p.g;
-  const int hq_chunk = p.hc * g;
-  const float v_scale = (p.v_scale) ? *p.v_scale : 1.f;
-  uint16_t* obase = reinterpret_cast<uint16_t*>(p.out) + (int64_t)s * p.out_stride_s;
-  uint8_t* obase8 = reinterpret_cast<uint8_t*>(p.out) + (int64_t)s * p.out_stride_s;
-  const bool fp8_out = p.out_scale != nullptr;
-  const float qinv = fp8_out ? __fdiv_rn(1.0f, *p.out_scale) : 1.f;
-  const int d4n = D >> 2;
-  const int items = hq_chunk * d4n;
-  for (int i = t; i < items; i += nthr) {
-    const int h = i / d4n, d = (i - h * d4n) << 2;
-    float mstar = -INFINITY;
-    for (int c = cta0; c <= cta1; c++) {
-      const int slot = (c * tpc >= c0) ? 0 : 1;
-      const int64_t ps = ((int64_t)(y * grid_x + c)) * 2 + slot;
-      mstar = fmaxf(mstar, __ldcg(p.part_ml + (ps * hq_chunk + h) * 2));
-    }
-    float4 num = make_float4(0.f, 0.f, 0.f, 0.f);
-    float den = 0.f;
-    for (int c = cta0; c <= cta1; c++) {
-      const int slot = (c * tpc >= c0) ? 0 : 1;
-      const int64_t ps = ((int64_t)(y * grid_x + c)) * 2 + slot;
-      const float2 ml = __ldcg(reinterpret_cast<const float2*>(p.part_ml + (ps * hq_chunk + h) * 2));
-      const float f = ex2(ml.x - mstar);
-      const float4 a = __ldcg(reinterpret_cast<const float4*>(p.part_acc + (ps * hq_chunk + h) * D + d));
-      den += f * ml.y;
-      num.x += f * a.x; num.y += f * a.y; num.z += f * a.z; num.w += f * a.w;
-    }
-    const float inv = v_scale / den;
-    if (fp8_out) {
-      const float a0 = fmaxf(-448.f, fminf(num.x * inv * qinv, 448.f)), a1 = fmaxf(-448.f, fminf(num.y * inv * qinv, 448.f));
-      const float a2 = fmaxf(-448.f, fminf(num.z * inv * qinv, 448.f)), a3 = fmaxf(-448.f, fminf(num.w * inv * qinv, 448.f));
-      *reinterpret_cast<uint32_t*>(obase8 + (int64_t)(y * hq_chunk + h) * p.out_stride_h + d) =
-          (uint32_t)f32x2_to_e4m3x2(a0, a1) | ((uint32_t)f32x2_to_e4m3x2(a2, a3) << 16);
-    } else {
-      uint2 o;
-      o.x = pack2<QBF16>(num.x * inv, num.y * inv);
-      o.y = pack2<QBF16>(num.z * inv, num.w * inv);
-      *reinterpret_cast<uint2*>(obase + (int64_t)(y * hq_chunk + h) * p.out_stride_h + d) = o;
-    }
-    if (p.lse && d == 0) p.lse[(int64_t)s * p.Hq + y * hq_chunk + h] = (mstar + lg2(den)) * LN2;
-  }
-}
-
-// Empty sequence: defined output (zeros), lse = -inf. Executed by all threads of one CTA.
-__device__ __noinline__ void zero_fill_sequence(const Params& p, int D, int s, int y, int t, int nthr) {
-  const int hq_chunk = p.hc * p.g;
-  uint16_t* obase = reinterpret_cast<uint16_t*>(p.out) + (int64_t)s * p.out_stride_s;
-  uint8_t* obase8 = reinterpret_cast<uint8_t*>(p.out) + (int64_t)s * p.out_stride_s;
-  const bool fp8_out = p.out_scale != nullptr;
-  const int d4n = D >> 2;
-  const int items = hq_chunk * d4n;
-  for (int i = t; i < items; i += nthr) {
-    const int h = i / d4n, d = (i - h * d4n) << 2;
-    if (fp8_out)
-      *reinterpret_cast<uint32_t*>(obase8 + (int64_t)(y * hq_chunk + h) * p.out_stride_h + d) = 0u;
-    else
-      *reinterpret_cast<uint2*>(obase + (int64_t)(y * hq_chunk + h) * p.out_stride_h + d) = make_uint2(0u, 0u);
-  }
-  if (p.lse)
-    for (int h = t; h < hq_chunk; h += nthr) p.lse[(int64_t)s * p.Hq + y * hq_chunk + h] = -INFINITY;
-}
-
 template <int D, int NT, int MODE>
 __global__ void __launch_bounds__(NTHREADS, 1)
     paged_attn_decode_kernel(const __grid_constant__ CUtensorMap tmK,
-                             const __grid_constant__ CUtensorMap tmV, const __grid_constant__ Params p) {
+                             const __grid_constant__ CUtensorMap tmV, const Params p) {
   constexpr bool FP8 = (MODE == BF16_FP8 || MODE == F16_FP8);
   constexpr bool QBF16 = (MODE == BF16_BF16 || MODE == BF16_FP8);
   constexpr bool MMA_BF16 = (MODE == BF16_BF16);  // fp8 KV is expanded to f16 (exact)
@@ -104,9 +35,12 @@ __global__ void __launch_bounds__(NTHREADS, 1)
 
   extern __shared__ uint8_t smem_raw[];
   __shared__ int s_wsum[NW + 1];
-  __shared__ int s_last;   // 1: this CTA arrived last at the cut sequence's counter and merges its partials
+  // programmatic dependent launch: the reduce kernel (and whatever follows) may become resident now. q and the
+  // layer's KV rows are the previous kernels' output: everything that touches them sits behind pdl_wait(). At level 2
+  // (p.early_plan) the tile plan below, which reads only seq_lens, runs BEFORE the wait (the caller promises that
+  // seq_lens is not written by the kernel launched immediately before this one: it is a step input).
   pdl_launch_dependents();
-  pdl_wait();   // seq_lens / q / the layer's KV rows come from earlier kernels on the stream
+  if (!p.early_plan) pdl_wait();
   const uint32_t raw_base = smem_u32(smem_raw);
   const uint32_t base = (raw_base + 1023u) & ~1023u;  // swizzle atoms need 1024-B alignment
   uint8_t* smem = smem_raw + (base - raw_base);
@@ -156,11 +90,13 @@ __global__ void __launch_bounds__(NTHREADS, 1)
     }
     __syncthreads();
   }
+  if (p.early_plan) pdl_wait();   // from here on: global writes (workspace) and reads of q / KV
   const int T = cum[S];
   const int tpc = max((T + (int)gridDim.x - 1) / (int)gridDim.x, p.min_tpc);
-  // empty sequences get a defined output; CTA x takes sequences x, x + gridDim.x, ...
-  for (int s = blockIdx.x; s < S; s += gridDim.x)
-    if (cum[s + 1] == cum[s]) zero_fill_sequence(p, D, s, blockIdx.y, tid, NTHREADS);
+  if (blockIdx.x == 0 && blockIdx.y == 0) {
+    for (int i = tid; i <= S; i += NTHREADS) p.cum[i] = cum[i];
+    if (tid == 0) p.cum[S + 1] = tpc;
+  }
   const int a = blockIdx.x * tpc;
   const int b = min(T, a + tpc);
   if (a >= b) return;
@@ -666,29 +602,80 @@ __global__ void __launch_bounds__(NTHREADS, 1)
           }
         }
     }
-    if (!whole) {
-      // ---- split-KV reduction folded into this kernel: every CTA that holds a piece of sequence s bumps the
-      // sequence's counter after publishing its partial; the last one merges all pieces and re-arms the counter
-      // (it lives at the slot of the sequence's FIRST CTA: a CTA is the first CTA of at most one cut sequence)
-      const int cta0 = c0 / tpc, cta1 = (c1 - 1) / tpc;
-      __threadfence();
-      bar_sync_named(2, NW * 32);
-      if (cw == 0 && lane == 0) {
-        int* ctr = p.arrive + blockIdx.y * gridDim.x + cta0;
-        const int old = atomicAdd(ctr, 1);
-        const int last = (old == cta1 - cta0) ? 1 : 0;
-        if (last) *ctr = 0;
-        s_last = last;
-      }
-      bar_sync_named(2, NW * 32);
-      if (s_last) {
-        __threadfence();
-        merge_partials<QBF16>(p, D, s, blockIdx.y, c0, cta0, cta1, tpc, gridDim.x, cw * 32 + lane, NW * 32);
-      }
-      bar_sync_named(2, NW * 32);   // s_last is rewritten for the CTA's next cut sequence
-    }
     pos = seg_end;
     s++;
+  }
+}
+
+// Merge the partials of sequences that were cut by CTA boundaries; zero-fill empty sequences.
+// grid (S, n_chunks); each thread owns 4 consecutive d of one q-head (float4 partial loads).
+template <bool QBF16>
+__global__ void __launch_bounds__(1024)
+    paged_attn_reduce_kernel(const Params p, int D, int grid_x) {
+  pdl_launch_dependents();
+  pdl_wait();   // the partials and the tile prefix sums are the decode kernel's output
+  const int s = blockIdx.x;
+  const int y = blockIdx.y;
+  const int g = p.g;
+  const int hq_chunk = p.hc * g;
+  const int c0 = p.cum[s], c1 = p.cum[s + 1];
+  const int tpc = p.cum[p.S + 1];
+  const float v_scale = (p.v_scale) ? *p.v_scale : 1.f;
+  uint16_t* obase = reinterpret_cast<uint16_t*>(p.out) + (int64_t)s * p.out_stride_s;
+  uint8_t* obase8 = reinterpret_cast<uint8_t*>(p.out) + (int64_t)s * p.out_stride_s;
+  const bool fp8_out = p.out_scale != nullptr;
+  const float qinv = fp8_out ? __fdiv_rn(1.0f, *p.out_scale) : 1.f;
+  const int d4n = D >> 2;
+  const int items = hq_chunk * d4n;
+  if (c1 == c0) {
+    // empty sequence: defined output (zeros), lse = -inf
+    for (int i = threadIdx.x; i < items; i += blockDim.x) {
+      const int h = i / d4n, d = (i - h * d4n) << 2;
+      if (fp8_out)
+        *reinterpret_cast<uint32_t*>(obase8 + (int64_t)(y * hq_chunk + h) * p.out_stride_h + d) = 0u;
+      else
+        *reinterpret_cast<uint2*>(obase + (int64_t)(y * hq_chunk + h) * p.out_stride_h + d) =
+            make_uint2(0u, 0u);
+    }
+    if (p.lse)
+      for (int h = threadIdx.x; h < hq_chunk; h += blockDim.x)
+        p.lse[(int64_t)s * p.Hq + y * hq_chunk + h] = -INFINITY;
+    return;
+  }
+  const int cta0 = c0 / tpc, cta1 = (c1 - 1) / tpc;
+  if (cta0 == cta1) return;  // written directly by the attention kernel
+  for (int i = threadIdx.x; i < items; i += blockDim.x) {
+    const int h = i / d4n, d = (i - h * d4n) << 2;
+    float mstar = -INFINITY;
+    for (int c = cta0; c <= cta1; c++) {
+      const int slot = (c * tpc >= c0) ? 0 : 1;
+      const int64_t ps = ((int64_t)(y * grid_x + c)) * 2 + slot;
+      mstar = fmaxf(mstar, __ldg(p.part_ml + (ps * hq_chunk + h) * 2));
+    }
+    float4 num = make_float4(0.f, 0.f, 0.f, 0.f);
+    float den = 0.f;
+    for (int c = cta0; c <= cta1; c++) {
+      const int slot = (c * tpc >= c0) ? 0 : 1;
+      const int64_t ps = ((int64_t)(y * grid_x + c)) * 2 + slot;
+      const float2 ml = __ldg(reinterpret_cast<const float2*>(p.part_ml + (ps * hq_chunk + h) * 2));
+      const float f = ex2(ml.x - mstar);
+      const float4 a = __ldg(reinterpret_cast<const float4*>(p.part_acc + (ps * hq_chunk + h) * D + d));
+      den += f * ml.y;
+      num.x += f * a.x; num.y += f * a.y; num.z += f * a.z; num.w += f * a.w;
+    }
+    const float inv = v_scale / den;
+    if (fp8_out) {
+      const float a0 = fmaxf(-448.f, fminf(num.x * inv * qinv, 448.f)), a1 = fmaxf(-448.f, fminf(num.y * inv * qinv, 448.f));
+      const float a2 = fmaxf(-448.f, fminf(num.z * inv * qinv, 448.f)), a3 = fmaxf(-448.f, fminf(num.w * inv * qinv, 448.f));
+      *reinterpret_cast<uint32_t*>(obase8 + (int64_t)(y * hq_chunk + h) * p.out_stride_h + d) =
+          (uint32_t)f32x2_to_e4m3x2(a0, a1) | ((uint32_t)f32x2_to_e4m3x2(a2, a3) << 16);
+    } else {
+      uint2 o;
+      o.x = pack2<QBF16>(num.x * inv, num.y * inv);
+      o.y = pack2<QBF16>(num.z * inv, num.w * inv);
+      *reinterpret_cast<uint2*>(obase + (int64_t)(y * hq_chunk + h) * p.out_stride_h + d) = o;
+    }
+    if (p.lse && d == 0) p.lse[(int64_t)s * p.Hq + y * hq_chunk + h] = (mstar + lg2(den)) * LN2;
   }
 }
 
