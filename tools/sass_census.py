@@ -1,7 +1,7 @@
 """Instruction census of the shipped library: `cuobjdump -sass libb200ops.so`, per kernel, counting the SASS
 mnemonics that prove which hardware path a kernel uses (B200_PROFILING.md): UTCHMMA/UTCQMMA/UTCOMMA (tcgen05.mma
 f16 / f8f6f4 / block-scaled), UTCCP (tcgen05.cp), LDTM/STTM (tcgen05.ld/st), UTMALDG/UTMASTG (TMA), UBLKCP (bulk
-copy), HMMA (mma.sync), SYNCS (mbarrier), MULTIMEM, LDG/STG/LDS/STS totals.
+copy), HMMA (mma.sync), SYNCS (mbarrier), LDGMC (multimem.ld_reduce: in-switch reduction), LDG/STG/LDS/STS totals.
 usage: python tools/sass_census.py [lib.so] > profiles/r2_sass_census.md   (no GPU needed)"""
 import collections
 import os
@@ -12,7 +12,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "vllm-fork_b200", "b200ops", "libb200ops.so")
 WANT = ["UTCHMMA", "UTCQMMA", "UTCOMMA", "UTCCP", "LDTM", "STTM", "UTMALDG", "UTMASTG", "UBLKCP", "UTMAPF", "HMMA",
-        "SYNCS", "MULTIMEM", "LDG", "STG", "LDS", "STS", "ATOM", "RED", "MUFU", "total"]
+        "SYNCS", "LDGMC", "LDG", "STG", "LDS", "STS", "ATOM", "RED", "MUFU", "total"]
 
 
 def main():
