@@ -107,7 +107,7 @@ def bench_gemm(W):
             t_w, why = try_time(lambda i: W._C.cutlass_scaled_mm(ref, x, ws[i].t(), sa, sb, None), ncopy)
             byts = M * K + N * K + 2 * M * N
             report("cutlass_scaled_mm", f"{name} M={M} N={N} K={K}", t_o, t_w,
-                   why or f"ours {byts / t_o / 1e3:.0f} GB/s, {2.0 * M * N * K / t_o / 1e6:.0f} TFLOP/s")
+                   why or f"ours ({ops.LAST_GEMM_IMPL}) {byts / t_o / 1e3:.0f} GB/s, {2.0 * M * N * K / t_o / 1e6:.0f} TFLOP/s")
             del ws
 
 

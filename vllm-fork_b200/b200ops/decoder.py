@@ -77,13 +77,13 @@ class DecoderModel:
         self.shape = s = shape
         # Programmatic dependent launch between the kernels of the step. "auto": level 2 on one GPU (the GEMMs request
         # their first weight tiles before waiting for the previous kernel - the weights are never written after init;
-        # +13 % on a launch-bound step, profiles/r2s_small_pdl*.json), OFF with tensor parallelism: measured at 2 / 4 /
-        # 8 ranks (profiles/r2u_*, r2w_*) it is neutral with the one-shot NVLink all-reduce and 2-4 % SLOWER with the
-        # fused / multimem collectives, and one of nine 2-rank runs at level 2 ended in the all-reduce's bounded-spin
-        # trap (a peer 2 flags behind) - not understood yet, so not enabled. B200_PDL in the environment wins (A/B
-        # runs); pdl=None leaves the library setting alone.
+        # +13 % on a launch-bound step, profiles/r2s_small_pdl*.json), level 1 with tensor parallelism, where the NVLink
+        # collectives themselves stay plain launches (B200_PDL_AR, csrc/common.cuh): measured at 2 ranks
+        # (profiles/r3e_*.json) that is 1.8 % faster than no programmatic launch, while collectives that take part in
+        # it make the step 1-2 % slower (and one such run ended in the all-reduce's bounded-spin trap). B200_PDL in
+        # the environment wins (A/B runs); pdl=None leaves the library setting alone.
         if pdl == "auto":
-            pdl = 2 if tp_size == 1 else 0
+            pdl = 2 if tp_size == 1 else 1
         if pdl is not None and "B200_PDL" not in os.environ:
             ops.set_pdl(pdl)
         self.pdl = ops.set_pdl(0)

@@ -338,6 +338,7 @@ def cutlass_scaled_mm_supports_fp8(cuda_device_capability: int) -> bool:
 # batch tile (csrc/gemm_fp8_v5.cu). All are tcgen05 kernels with the same arithmetic and all are parity-green; this
 # is a tuning switch (env B200_GEMM_IMPL), not a fallback. "auto" (default) follows measurements on B200.
 GEMM_IMPL = os.environ.get("B200_GEMM_IMPL", "auto")
+LAST_GEMM_IMPL = ""
 _gemm_ws: dict[str, torch.Tensor] = {}
 _sms: dict[str, int] = {}
 
@@ -464,6 +465,8 @@ def cutlass_scaled_mm(
             which = "v5"
         else:
             which = "v2"
+    global LAST_GEMM_IMPL
+    LAST_GEMM_IMPL = which      # for benchmark tables: which kernel the dispatch picked
     if which.startswith("v5"):   # "v5" (auto batch tile) or "v5:<batch tile>": CTA pairs of UMMA M = 128
         bt = int(which[3:]) if len(which) > 3 else 0
         rc = lib.b200_fp8_gemm_pair(*common, bt, _stream())

@@ -62,6 +62,7 @@ struct Peers {
   const uint8_t* in[MAX_RANKS];   // input of every rank (already offset)
   uint8_t* tmp[MAX_RANKS];        // scratch of every rank (two-shot result slices)
   const uint8_t* mc_in;           // multicast address of the input (all ranks' copies at once), or null
+  int pdl_mode;                   // pdl_collective_mode(): when this kernel lets its dependents launch
 };
 
 // ---- NVSwitch in-network reduction (NVLS): one load from a multicast address returns the SUM over every rank's
@@ -302,7 +303,7 @@ template <typename T, int N>
 __global__ void __launch_bounds__(NTHREADS, 1)
     allreduce_one_shot_kernel(Peers pe, uint8_t* __restrict__ out, const uint8_t* stage_src, int rank,
                               int64_t packs, int skip_end) {
-  pdl_launch_dependents();
+  if (pe.pdl_mode == 0) pdl_launch_dependents();
   pdl_wait();   // the input (and this context's epoch words) come from earlier kernels on the stream
   uint32_t epoch = pe.sig[rank]->epoch[blockIdx.x];
   stage_input<N>(pe, rank, stage_src, packs, packs);
@@ -315,13 +316,14 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   // next collective overwrites before its start barrier: the promise cannot cover it, so never skip then.
   if (!skip_end || stage_src) barrier<N, false>(pe, rank, epoch);
   if (threadIdx.x == 0) pe.sig[rank]->epoch[blockIdx.x] = epoch;
+  if (pe.pdl_mode == 1) pdl_launch_dependents();
 }
 
 template <typename T, int N>
 __global__ void __launch_bounds__(NTHREADS, 1)
     allreduce_two_shot_kernel(Peers pe, uint8_t* __restrict__ out, const uint8_t* stage_src, int rank,
                               int64_t packs, int skip_end) {
-  pdl_launch_dependents();
+  if (pe.pdl_mode == 0) pdl_launch_dependents();
   pdl_wait();   // the input (and this context's epoch words) come from earlier kernels on the stream
   uint32_t epoch = pe.sig[rank]->epoch[blockIdx.x];
   const int64_t part = (packs + N - 1) / N;          // packs per rank slice
@@ -348,6 +350,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
   (void)skip_end;
   barrier<N, false>(pe, rank, epoch);
   if (threadIdx.x == 0) pe.sig[rank]->epoch[blockIdx.x] = epoch;
+  if (pe.pdl_mode == 1) pdl_launch_dependents();
 }
 
 // NVLS all-reduce. mc_out != null (output inside the symmetric buffer): two-shot in the switch - rank r reduces
@@ -360,7 +363,7 @@ template <typename T, int N>
 __global__ void __launch_bounds__(NTHREADS, 1)
     allreduce_multimem_kernel(Peers pe, uint8_t* __restrict__ out, uint8_t* mc_out, const uint8_t* stage_src, int rank,
                               int64_t packs) {
-  pdl_launch_dependents();
+  if (pe.pdl_mode == 0) pdl_launch_dependents();
   pdl_wait();   // the input (and this context's epoch words) come from earlier kernels on the stream
   uint32_t epoch = pe.sig[rank]->epoch[blockIdx.x];
   const int64_t part = (packs + N - 1) / N;
@@ -378,6 +381,7 @@ __global__ void __launch_bounds__(NTHREADS, 1)
     barrier<N, false>(pe, rank, epoch);  // inputs may be overwritten only after everyone has reduced them
   }
   if (threadIdx.x == 0) pe.sig[rank]->epoch[blockIdx.x] = epoch;
+  if (pe.pdl_mode == 1) pdl_launch_dependents();
 }
 
 }  // namespace ar

@@ -37,7 +37,7 @@ __global__ void __launch_bounds__(256, 1)
     allreduce_fused_norm_kernel(Peers pe, FusedParams fp, const uint8_t* stage_src, int rank) {
   constexpr int NP = 16 / sizeof(T);
   __shared__ float red[32];
-  pdl_launch_dependents();
+  if (pe.pdl_mode == 0) pdl_launch_dependents();
   pdl_wait();   // the GEMM output being reduced comes from the previous kernel on the stream
   uint32_t epoch = pe.sig[rank]->epoch[blockIdx.x];
   const int nv = fp.hidden / NP;            // packs per row
@@ -156,6 +156,7 @@ __global__ void __launch_bounds__(256, 1)
   }
   barrier<N, true>(pe, rank, epoch);  // every rank's pushes have landed; inputs may be overwritten
   if (threadIdx.x == 0) pe.sig[rank]->epoch[blockIdx.x] = epoch;
+  if (pe.pdl_mode == 1) pdl_launch_dependents();
 }
 
 }  // namespace ar

@@ -29,6 +29,7 @@ static int resolve_input(const Context* c, const void* in, size_t bytes, Peers* 
   }
   size_t off;
   pe->mc_in = nullptr;
+  pe->pdl_mode = pdl_collective_mode();
   const int reg = find_region(c, in, bytes, &off);
   if (reg >= 0) {
     // region 0: the user heap starts after signals + staging + scratch; staging/scratch themselves are
@@ -53,6 +54,21 @@ static int resolve_input(const Context* c, const void* in, size_t bytes, Peers* 
   return B200_OK;
 }
 
+// collectives: programmatic launch unless B200_PDL_AR=2 (then a plain launch: the kernel starts after its predecessor
+// has completed and lets its successor start only when it has completed itself)
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_ar_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, cudaStream_t stream,
+                                           Args&&... args) {
+  if (pdl_collective_mode() == 2) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.stream = stream;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+  }
+  return launch_pdl(kern, grid, block, 0, stream, std::forward<Args>(args)...);
+}
+
 template <typename T, int N>
 static int launch_ar(const Peers& pe, void* out, const uint8_t* stage_src, int rank, int64_t packs, bool two_shot,
                      int skip_end, cudaStream_t stream) {
@@ -64,11 +80,11 @@ static int launch_ar(const Peers& pe, void* out, const uint8_t* stage_src, int r
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   if (two_shot)
-    B200_CUDA(launch_pdl(allreduce_two_shot_kernel<T, N>, dim3((unsigned)blocks), dim3(NTHREADS), 0, stream, pe,
-                         (uint8_t*)out, stage_src, rank, packs, skip_end));
+    B200_CUDA(launch_ar_kernel(allreduce_two_shot_kernel<T, N>, dim3((unsigned)blocks), dim3(NTHREADS), stream, pe,
+                               (uint8_t*)out, stage_src, rank, packs, skip_end));
   else
-    B200_CUDA(launch_pdl(allreduce_one_shot_kernel<T, N>, dim3((unsigned)blocks), dim3(NTHREADS), 0, stream, pe,
-                         (uint8_t*)out, stage_src, rank, packs, skip_end));
+    B200_CUDA(launch_ar_kernel(allreduce_one_shot_kernel<T, N>, dim3((unsigned)blocks), dim3(NTHREADS), stream, pe,
+                               (uint8_t*)out, stage_src, rank, packs, skip_end));
   return B200_OK;
 }
 
@@ -94,8 +110,8 @@ static int launch_mc(const Peers& pe, void* out, uint8_t* mc_out, const uint8_t*
   const int cap = sm_count() < MAX_BLOCKS ? sm_count() : MAX_BLOCKS;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-  B200_CUDA(launch_pdl(allreduce_multimem_kernel<T, N>, dim3((unsigned)blocks), dim3(NTHREADS), 0, stream, pe,
-                       (uint8_t*)out, mc_out, stage_src, rank, packs));
+  B200_CUDA(launch_ar_kernel(allreduce_multimem_kernel<T, N>, dim3((unsigned)blocks), dim3(NTHREADS), stream, pe,
+                             (uint8_t*)out, mc_out, stage_src, rank, packs));
   return B200_OK;
 }
 
@@ -122,11 +138,11 @@ static int launch_fused(const Peers& pe, const FusedParams& fp, const uint8_t* s
 #define B200_FUSED(RR)                                                                                   \
   do {                                                                                                   \
     if (fp.mc_out && pe.mc_in)                                                                           \
-      B200_CUDA(launch_pdl(allreduce_fused_norm_kernel<T, N, QUANT, RR, true>, dim3((unsigned)blocks), dim3(256), 0,  \
-                           stream, pe, fp, stage_src, rank));                                            \
+      B200_CUDA(launch_ar_kernel(allreduce_fused_norm_kernel<T, N, QUANT, RR, true>, dim3((unsigned)blocks),    \
+                                 dim3(256), stream, pe, fp, stage_src, rank));                            \
     else                                                                                                 \
-      B200_CUDA(launch_pdl(allreduce_fused_norm_kernel<T, N, QUANT, RR, false>, dim3((unsigned)blocks), dim3(256), 0, \
-                           stream, pe, fp, stage_src, rank));                                            \
+      B200_CUDA(launch_ar_kernel(allreduce_fused_norm_kernel<T, N, QUANT, RR, false>, dim3((unsigned)blocks),   \
+                                 dim3(256), stream, pe, fp, stage_src, rank));                            \
   } while (0)
   if (nv <= 256) B200_FUSED(1);
   else if (nv <= 512) B200_FUSED(2);
@@ -395,6 +411,7 @@ extern "C" int b200_dcp_lse_merge(void* ctx, void* out, float* lse_out, const vo
   const int reg_l = find_region(c, attn_lse, lse_bytes, &off_l);
   B200_CHECK(reg_o >= 0 && reg_l >= 0, B200_ERR_INVALID,
              "dcp_lse_merge: attn_out and attn_lse must live in the symmetric heap (peers read them in place)");
+  pe.pdl_mode = 2;   // the DCP kernel is launched plainly
   for (int r = 0; r < c->world; r++) {
     pe.sig[r] = reinterpret_cast<Signal*>(c->regions[0].base[r]);
     pe.tmp[r] = nullptr;

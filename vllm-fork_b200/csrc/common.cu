@@ -67,6 +67,10 @@ int pdl_level() {
   return g_pdl;
 }
 bool pdl_enabled() { return pdl_level() > 0; }
+int pdl_collective_mode() {
+  static const int m = [] { const char* e = getenv("B200_PDL_AR"); return (e && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 2; }();
+  return m;
+}
 
 typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
                                     const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,

@@ -50,6 +50,12 @@ bool pdl_enabled();
 // earlier kernel sits behind pdl_wait() inside the kernel. Captured into CUDA graphs as a programmatic edge.
 // Every kernel launched through this helper MUST execute pdl_wait() in at least one thread of every CTA that
 // reads or writes global memory, so that completion stays transitive along the stream.
+// NVLink collectives and programmatic launch (env B200_PDL_AR): 2 (default) = collectives are launched and behave like
+// plain kernels; 0 = they are launched programmatically and let their dependents launch at kernel entry; 1 = only after
+// their last barrier. Measured at 2 ranks (profiles/r3e_*.json): with 0 / 1 the step is 1-2 % SLOWER than without any
+// programmatic launch, with 2 it is 1.8 % faster (the other kernels still overlap their prologues).
+int pdl_collective_mode();
+
 template <typename... KArgs, typename... Args>
 static inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem,
                                      cudaStream_t stream, Args&&... args) {
