@@ -350,6 +350,26 @@ def _sm_count(device: torch.device) -> int:
     return _sms[key]
 
 
+def pick_gemm_impl(M: int, N: int, K: int, out_tma_addressable: bool, sms: int) -> str:
+    """Which FP8 GEMM kernel `cutlass_scaled_mm` launches for an [M, K] x [K, N] problem on a GPU with `sms` SMs.
+    Measured on B200 (profiles/r2t_gemm_impls.md, r3d_vs_wheel_gemm.md; CUDA-graph timed, weights rotated beyond L2):
+     * M > 256, or at least as many 256-row weight tiles as CTA pairs (gate_up) -> "v3" (persistent pairs);
+     * batches <= 64 with few weight tiles -> "v4" (split-K over a cluster: the fp32 partial exchange is small);
+     * every other decode batch -> "v5" (CTA pairs of UMMA M = 128: half the bytes pulled per SM; 10-25 % faster
+       than the one-CTA kernel on the qkv / o / down shapes at batch 128-256);
+     * "v2" remains for outputs that a TMA store cannot address (unaligned base or row stride).
+    K does not enter the rule today (it did in round 1: long-K shapes went to v4 at every batch)."""
+    pairs = sms // 2
+    tiles = (N + 255) // 256
+    if M > 256 or tiles >= pairs:
+        return "v3"
+    if M <= 64 and tiles * 2 <= pairs and out_tma_addressable:
+        return "v4"
+    if out_tma_addressable:
+        return "v5"
+    return "v2"
+
+
 def _gemm_workspace(device: torch.device) -> torch.Tensor:
     """zero-initialised stream-K workspace of the v3 kernel, one per device (the kernel leaves its
     flags at zero, so it is shared by all calls that run on one stream at a time)."""
@@ -448,23 +468,8 @@ def cutlass_scaled_mm(
               1 if scale_a.numel() > 1 else 0, 1 if scale_b.numel() > 1 else 0, _dt(out))
     which = impl or GEMM_IMPL
     if which == "auto":
-        # Measured on B200 (profiles/r2t_gemm_impls.md, CUDA-graph timed, weights rotated beyond L2):
-        #  * M > 256, or at least as many 256-row weight tiles as CTA pairs (gate_up) -> v3 (persistent pairs);
-        #  * batches <= 64 with few weight tiles -> v4 (split-K over a cluster: the fp32 partial exchange is small);
-        #  * every other decode batch -> v5 (CTA pairs of UMMA M = 128: half the bytes pulled per SM; 10-25 % faster
-        #    than the one-CTA kernel v2 on the qkv / o / down shapes at batch 128-256);
-        #  * v2 remains for outputs that a TMA store cannot address (unaligned base or row stride).
-        pairs = _sm_count(a.device) // 2
-        tiles = (N + 255) // 256
-        aligned = out.data_ptr() % 16 == 0 and (out.stride(0) * 2) % 16 == 0
-        if M > 256 or tiles >= pairs:
-            which = "v3"
-        elif M <= 64 and tiles * 2 <= pairs and aligned:
-            which = "v4"
-        elif aligned:
-            which = "v5"
-        else:
-            which = "v2"
+        which = pick_gemm_impl(M, N, K, out.data_ptr() % 16 == 0 and (out.stride(0) * 2) % 16 == 0,
+                               _sm_count(a.device))
     global LAST_GEMM_IMPL
     LAST_GEMM_IMPL = which      # for benchmark tables: which kernel the dispatch picked
     if which.startswith("v5"):   # "v5" (auto batch tile) or "v5:<batch tile>": CTA pairs of UMMA M = 128
