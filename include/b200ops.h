@@ -63,6 +63,8 @@ B200_API int b200_sm_count(void);
  *   which holds for model weights - and b200_paged_attention_decode computes its tile plan from `seq_lens` before
  *   waiting, so `seq_lens` must not be written by the kernel launched immediately before it either (it is a step
  *   input in the reference). Initial value from env B200_PDL. Returns the previous level.
+ * The NVLink collectives (b200_allreduce_run, b200_allreduce_fused_add_rms_norm) are launched as plain kernels at every
+ * level unless env B200_PDL_AR is 0 / 1 (measured slower: DESIGN.md section 5).
  * Not part of the reference operator surface. */
 B200_API int b200_set_pdl(int level);
 
