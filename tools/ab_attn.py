@@ -33,7 +33,6 @@ def main():
         ws = torch.zeros(ops.paged_attention_workspace(S, Hq, Hkv, D, dev).numel() + 8192, dtype=torch.uint8, device=dev)
         outs = {}
         res = {}
-        levels = [int(x) for x in os.environ.get("AB_PDL", "1").split(",")]
         for rnd in range(2):               # A B A B: drift between the two shows up as a difference between rounds
             for name, fn in (("old", old.b200_paged_attention_decode), ("new", new_fn)):
                 lib.b200_paged_attention_decode = fn
