@@ -232,7 +232,7 @@ class DecoderModel:
             # global expert id -> local id or -1 (fused_moe/layer.py determine_expert_map)
             em = tp.expert_map(E, tp_rank, tp_size)
             self.expert_map = None if em is None else em.to(self.dev)
-        # gate_up GEMM + silu_and_mul + FP8 quant in one kernel. Measured (gpurun_out/bench4.json): at
+        # gate_up GEMM + silu_and_mul + FP8 quant in one kernel. Measured in round 1: at
         # batch 256 the GEMM is tensor-bound and the fused epilogue (silu on 4 warps of 112 CTAs, not
         # overlapped) costs more than the separate full-GPU activation kernel: 16.55 vs 15.95 ms/step.
         # It pays only while the GEMM is a weight stream (small batches).

@@ -223,8 +223,9 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 // warp-uniform loops with `if (elect_one())` around the issue instructions: under a divergent `if (lane == 0)`
 // ptxas cannot prove the operands of the uniform-datapath instructions (UTMALDG / UTCQMMA / UTCBAR) uniform and
 // wraps EVERY one of them in an ELECT ... BRA.U.ANY loop plus R2UR moves - measured on B200 as ~100 cycles per
-// TMA issue and ~65 cycles per MMA issue (profiles/r2f_trace_fine.txt), which bounds a k-block at ~480 cycles
-// whatever the tile width.
+// TMA issue and ~65 cycles per MMA issue, which bounded a k-block at ~480 cycles whatever the tile width (that
+// trace was lost with its container; with elect.sync the per-k-block trace profiles/r2q_trace.txt shows 52-59 cycles
+// from "slot free" to both TMA issues done and 58 cycles for the four MMAs + commit).
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred;
   asm volatile(
