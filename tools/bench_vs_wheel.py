@@ -5,7 +5,7 @@ Same tensors for both sides, every call captured in a CUDA graph (no host launch
 operand rotated over enough copies to exceed the 126 MB L2, CUDA-event timed. The wheel is LIBRARY code used as the
 race opponent only; nothing under b200ops imports it.
 
-    python tools/bench_vs_wheel.py [--out profiles/r2_vs_wheel.md] [--only gemm,fp4,quant,attn,moe]
+    python tools/bench_vs_wheel.py [--out profiles/<round>_vs_wheel.md] [--only gemm,fp4,quant,attn,moe]
 
 Prints one JSON line per case and writes a markdown table (ratio = wheel_us / ours_us: > 1 means ours is faster)."""
 import argparse

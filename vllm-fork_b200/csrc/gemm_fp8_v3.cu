@@ -5,7 +5,7 @@
 // csrc/libtorch_stable/quantization/w8a8/cutlass/scaled_mm_entry.cu:197-270):
 //   out[M,N] = a_scale (.) ( b_scale (.) (A[M,K] . B[K,N]) ) (+ bias[N]),  fp32 accumulate.
 //
-// Why a third kernel (measured on B200, profiles/r1b): at decode M = 256 the one-CTA kernel is bound
+// Why a third kernel (measured on B200, profiles/r1b_ncu_full.md): at decode M = 256 the one-CTA kernel is bound
 // by what one SM can pull in per k-block (16 KB of weights + 32 KB of activations at ~100 GB/s per SM),
 // loses ~25 % to wave quantisation (224 weight slabs on 148 SMs) and pays prologue + epilogue once per
 // tile. Here:
@@ -447,7 +447,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
         }
         // One chunk = 16 accumulator columns. Two chunks per iteration in a ROLLED loop, one store flavour per
         // instantiation: the unrolled 4-chunk / 3-flavour version was ~8000 SASS instructions of straight-line
-        // code and ran at instruction-fetch speed (30k cycles per tile vs 16k of MMAs, profiles/r1c).
+        // code and ran at instruction-fetch speed (30k cycles per tile vs 16k of MMAs; round-1 timeline).
         auto pack2 = [&](float lo, float hi) -> uint32_t {
           if (p.out_bf16) {
             __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
@@ -658,7 +658,8 @@ static int launch(const CUtensorMap& tmR, const CUtensorMap& tmC, const CUtensor
   // many tiles per pair: whole tiles in a grouped raster (L2 locality; the tail wave costs < 1 / (tiles / pairs));
   // few: stream-K so every pair streams the same number of k-blocks
   // (decode with more weight tiles than pairs, e.g. gate_up: whole tiles too -- the fp32 partial round trip of
-  // a split tile costs more than the idle half wave, timeline in profiles/r1c_gemm_v3.md)
+  // a split tile costs more than the idle half wave: v3 stream-K 30.7-44.2 us vs 14-30 us for the others at the
+  // qkv / o / down decode shapes, profiles/r2q_gemm_impls.jsonl)
   p.interleave = ((!p.swap && tiles >= 4 * (int64_t)p.pairs) || (p.swap && tiles >= (int64_t)p.pairs)) ? 1 : 0;
   p.raster_group = (p.interleave && !p.swap) ? 8 : 0;
   p.prefetch_w = pdl_level() >= 2;
