@@ -195,6 +195,32 @@ B200_API size_t b200_paged_attention_workspace_bytes(int num_seqs, int num_heads
                                                      int head_size);
 B200_API int b200_paged_attention_decode(const b200_paged_attn_args* args, b200_stream_t stream);
 
+/* Paged-attention decode for callers that cannot allocate device memory.
+ * No counterpart in the reference: vLLM always has torch's caching allocator at hand, so none of its operators
+ * needs this. It exists for users of this C ABI who do not - a worker whose device memory was fully handed out
+ * at start-up (weights, then every remaining byte as KV-cache blocks), for which a later cudaMalloc fails and
+ * stalls the device, and bindings from runtimes without a device allocator (cgo, JNI, plain ctypes) that hold
+ * only the buffers they were given.
+ *
+ * Same arguments, validation, kernels and results as b200_paged_attention_decode, except that
+ * args->workspace / args->workspace_bytes are IGNORED (pass NULL / 0): the split-KV scratch is a fixed
+ * B200_PAGED_ATTN_STATIC_WS_BYTES array inside the library's device image. Consequences a user must know:
+ *   - Limit. A shape whose b200_paged_attention_workspace_bytes(...) exceeds the array is refused with
+ *     B200_ERR_WORKSPACE (message names both numbers) before anything is launched. 8 MiB covers
+ *     num_heads * (head_size + 2) <= 5418 at any batch up to 16384 sequences: e.g. 32 or 40 query heads of
+ *     size 128 (Llama-3.1-8B unsharded, 70B from TP=2), 16 heads of size 256. Larger: use the regular entry.
+ *   - Footprint. Every GPU on which the process loads this library holds the 8 MiB until exit, used or not.
+ *   - Sharing. All calls on a device use the same array and it keeps the previous call's bytes. That is
+ *     harmless for results (each call writes what it reads; nothing has to be zero), but two calls that can
+ *     overlap on the GPU - different streams without an event between them, or different host threads - race
+ *     on it and corrupt each other's split sequences. Calls on ONE stream are ordered and safe.
+ *   - Set-up. The first call on each device resolves the array's device address (cudaGetSymbolAddress, with
+ *     that device current), which can make the runtime load the library's device code there. Make that first
+ *     call during initialisation, before any stream capture is begun. Later calls only read a table.
+ * The entry point itself calls no cudaMalloc / cudaFree / allocating library routine. */
+#define B200_PAGED_ATTN_STATIC_WS_BYTES (8u << 20)
+B200_API int b200_paged_attention_decode_static(const b200_paged_attn_args* args, b200_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Variable-length paged attention: prefill, chunked prefill and mixed batches (query_len >= 1).
  * Replaces the query_len > 1 branch of AttentionImpl.forward (vllm/v1/attention/backend.py:895-934)

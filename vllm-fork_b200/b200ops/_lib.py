@@ -265,6 +265,7 @@ SIGNATURES = {
                                    c_int, c_int, c_void_p]),
     "b200_paged_attention_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200_paged_attention_decode": (c_int, [C.POINTER(PagedAttnArgs), c_void_p]),
+    "b200_paged_attention_decode_static": (c_int, [C.POINTER(PagedAttnArgs), c_void_p]),
     "b200_paged_attention_varlen": (c_int, [C.POINTER(VarlenAttnArgs), c_void_p]),
 }
 

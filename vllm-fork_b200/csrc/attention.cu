@@ -163,3 +163,79 @@ __device__ __forceinline__ uint32_t swz_off(int tok, int chunk) {
 
 #include "attention_kernel.cuh"
 #include "attention_host.cuh"
+
+// ------------------------------------------------------------------------------------------------
+// b200_paged_attention_decode_static: paged-attention decode for callers that cannot allocate.
+//
+// Who that is: code that runs where no CUDA allocator may be invoked. Two kinds of caller are meant.
+// A serving worker whose device memory was measured and handed out at start-up -- whatever the
+// weights left over became KV-cache blocks -- has no headroom afterwards: a later cudaMalloc fails,
+// and it also synchronises the whole device in the middle of a decode step. And a binding written
+// against this C ABI from a runtime that owns no device allocator (a bare cgo / JNI / ctypes caller
+// that only holds the buffers it was handed) cannot produce a workspace pointer at all. The regular
+// entry point asks both for a split-KV workspace they have no means to provide; here the workspace
+// is a fixed array that is part of the library image.
+//
+// What it costs: B200_PAGED_ATTN_STATIC_WS_BYTES (8 MiB) of device memory on every GPU that loads
+// libb200ops.so, held until the process exits, whether or not this entry point is ever called.
+//
+// g_static_ws is only a device address inside device code. On the host the same name is the
+// runtime's registration handle for the symbol, so the address the kernels need is looked up
+// with cudaGetSymbolAddress -- once per device, with that device current, in static_ws_address().
+namespace b200 {
+namespace attn {
+
+constexpr size_t kStaticWsBytes = B200_PAGED_ATTN_STATIC_WS_BYTES;
+static __device__ __align__(256) unsigned char g_static_ws[kStaticWsBytes];
+
+static void* g_static_ws_addr[64] = {};   // device address of g_static_ws, per device ordinal
+static std::mutex g_static_ws_mu;
+
+// Device address of the scratch array on the CURRENT device. The first call on a device resolves
+// it (this may also make the runtime load the library's device code there); later calls are a
+// table read. Never allocates.
+static int static_ws_address(void** out) {
+  int dev = -1;
+  B200_CUDA(cudaGetDevice(&dev));
+  B200_CHECK(dev >= 0 && dev < 64, B200_ERR_UNSUPPORTED,
+             "paged_attention_decode_static: device ordinal %d outside the supported range 0..63", dev);
+  std::lock_guard<std::mutex> lk(g_static_ws_mu);
+  if (g_static_ws_addr[dev] == nullptr) {
+    void* ptr = nullptr;
+    B200_CUDA(cudaGetSymbolAddress(&ptr, g_static_ws));
+    B200_CHECK(ptr != nullptr && (reinterpret_cast<uintptr_t>(ptr) & 255) == 0, B200_ERR_CUDA,
+               "paged_attention_decode_static: the runtime returned an unusable scratch address (%p)", ptr);
+    g_static_ws_addr[dev] = ptr;
+  }
+  *out = g_static_ws_addr[dev];
+  return B200_OK;
+}
+
+}  // namespace attn
+}  // namespace b200
+
+extern "C" int b200_paged_attention_decode_static(const b200_paged_attn_args* a, b200_stream_t stream) {
+  using namespace b200;
+  using namespace b200::attn;
+  B200_CHECK(a != nullptr, B200_ERR_INVALID, "paged_attention_decode_static: null args");
+  // Size gate first: it needs no device, and an oversized request must never reach the kernels.
+  // (Nonsensical sizes make the query return 0; the regular entry point below names what is wrong.)
+  const size_t need = b200_paged_attention_workspace_bytes(a->num_seqs, a->num_heads, a->num_kv_heads,
+                                                           a->head_size);
+  B200_CHECK(need <= kStaticWsBytes, B200_ERR_WORKSPACE,
+             "paged_attention_decode_static: %d sequences x %d heads x head_size %d need %zu bytes of split-KV "
+             "scratch, the built-in array holds %zu; use b200_paged_attention_decode with a caller-owned workspace",
+             a->num_seqs, a->num_heads, a->head_size, need, kStaticWsBytes);
+  if (a->num_seqs == 0) return b200_paged_attention_decode(a, stream);   // nothing to launch
+  void* ws = nullptr;
+  int rc = static_ws_address(&ws);
+  if (rc != B200_OK) return rc;
+  // Same validation, plan, kernels and launch order as the regular entry point; only the workspace
+  // differs. Nothing in it has to start at zero: the decode kernel writes the tile prefix sums and
+  // every partial it later asks the reduce kernel to read, so stale bytes from the previous call
+  // (the array is shared by all callers and never cleared) are never consumed.
+  b200_paged_attn_args args = *a;
+  args.workspace = ws;
+  args.workspace_bytes = kStaticWsBytes;
+  return b200_paged_attention_decode(&args, stream);
+}
