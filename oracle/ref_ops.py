@@ -275,7 +275,7 @@ def w8a8_block_scaled_mm(a_bits, b_bits_nk, a_s, b_s, block=(128, 128)) -> np.nd
 
 
 # --------------------------------------------------------------------------------------------
-# Slot mapping.  vllm/v1/worker/block_table.py:182-211, 379-441 (no DCP)
+# Slot mapping.  vllm/v1/worker/block_table.py:182-211, 379-441 (no-CP form and the DCP interleave branch)
 # --------------------------------------------------------------------------------------------
 PAD_SLOT_ID = -1
 
@@ -285,6 +285,43 @@ def compute_slot_mapping(block_table: np.ndarray, req_indices: np.ndarray, posit
     """slot = block_table[req, pos // bs] * bs + pos % bs  (int64)."""
     blk = block_table[req_indices, positions // block_size].astype(np.int64)
     return blk * block_size + positions % block_size
+
+
+def compute_slot_mapping_dcp(block_table: np.ndarray, req_indices: np.ndarray, positions: np.ndarray,
+                             block_size: int, cp_world_size: int, cp_rank: int,
+                             cp_kv_cache_interleave_size: int = 1, kv_cache_block_size: int | None = None,
+                             blocks_per_kv_block: int = 1) -> np.ndarray:
+    """Slot mapping of ONE decode-context-parallel rank (vllm/v1/worker/block_table.py:413-441, the body of
+    _compute_slot_mapping_kernel). The KV of a request is dealt to the ranks in runs of `interleave` tokens: a
+    "virtual block" of kv_cache_block_size * world consecutive positions fills one local block on every rank.
+    Positions that live on another rank get PAD_SLOT_ID (the cache write skips negative slots).
+    Parity: no golden vector for this branch exists in the reference tests (tests/v1/worker/test_gpu_block_table.py
+    only constructs BlockTable with interleave 1) - pinned by the hand-worked case and the partition properties in
+    tests/test_oracle_dcp.py, and by get_dcp_local_seq_lens below (a second, independent reference function)."""
+    kvbs = block_size if kv_cache_block_size is None else kv_cache_block_size
+    W, I = int(cp_world_size), int(cp_kv_cache_interleave_size)
+    pos = np.asarray(positions).astype(np.int64)
+    virtual_block_size = kvbs * W                                              # :413
+    vbi = pos // virtual_block_size                                            # :419
+    vbo = pos - vbi * virtual_block_size                                       # :420
+    is_local = (vbo // I) % W == cp_rank                                       # :421-423
+    local_off = (vbo // (W * I)) * I + vbo % I                                 # :424-428
+    block_idx = vbi * blocks_per_kv_block + local_off // block_size            # :430-433
+    safe_idx = np.where(is_local, block_idx, 0)                                # masked load, other=0 (:434-438)
+    blk = block_table[np.asarray(req_indices), safe_idx].astype(np.int64)
+    slots = blk * block_size + local_off % block_size                          # :439-440
+    return np.where(is_local, slots, PAD_SLOT_ID).astype(np.int64)             # :441
+
+
+def dcp_local_seq_lens(seq_lens: np.ndarray, dcp_size: int, dcp_rank: int,
+                       cp_kv_cache_interleave_size: int = 1) -> np.ndarray:
+    """KV tokens of each sequence held by one rank (get_dcp_local_seq_lens,
+    vllm/v1/attention/backends/utils.py:958-995, dcp_rank given)."""
+    L = np.asarray(seq_lens).astype(np.int32)
+    I = int(cp_kv_cache_interleave_size)
+    base = L // I // dcp_size * I
+    rem = np.clip(L - base * dcp_size - dcp_rank * I, 0, I)
+    return (base + rem).astype(np.int32)
 
 
 # --------------------------------------------------------------------------------------------

@@ -128,3 +128,80 @@ def test_dcp_merge_world2_gloo():
     for p in procs:
         p.join(timeout=30)
     assert all(s == "ok" for _, s, _ in res), res
+
+
+# ---- DCP KV interleave: which rank stores which token (block_table.py:413-441) -------------------------------
+def test_dcp_slot_mapping_hand_worked_case():
+    """world 2, interleave 1, block_size 4: a virtual block is 8 positions; rank 0 keeps the even ones, packed."""
+    bt = np.array([[7, 3]], dtype=np.int32)
+    pos = np.arange(12)
+    req = np.zeros(12, dtype=np.int64)
+    r0 = ref_ops.compute_slot_mapping_dcp(bt, req, pos, 4, 2, 0, 1)
+    r1 = ref_ops.compute_slot_mapping_dcp(bt, req, pos, 4, 2, 1, 1)
+    assert r0.tolist() == [28, -1, 29, -1, 30, -1, 31, -1, 12, -1, 13, -1]
+    assert r1.tolist() == [-1, 28, -1, 29, -1, 30, -1, 31, -1, 12, -1, 13]
+    # interleave 2: runs of two tokens alternate between the ranks
+    r0 = ref_ops.compute_slot_mapping_dcp(bt, req, pos, 4, 2, 0, 2)
+    assert r0.tolist() == [28, 29, -1, -1, 30, 31, -1, -1, 12, 13, -1, -1]
+    # a single rank is the plain mapping
+    np.testing.assert_array_equal(ref_ops.compute_slot_mapping_dcp(bt, req[:8], pos[:8], 4, 1, 0, 1),
+                                  ref_ops.compute_slot_mapping(bt, req[:8], pos[:8], 4))
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("interleave", [1, 4, 16])
+@pytest.mark.parametrize("bs", [16, 32])
+def test_dcp_slot_mapping_partitions_every_sequence(world, interleave, bs):
+    """Every position is stored by exactly one rank; a rank's slots are distinct, fill its blocks from the
+    front, and their count is what get_dcp_local_seq_lens says that rank must attend over."""
+    if bs % interleave:
+        pytest.skip("the reference requires block_size % interleave == 0")
+    rng = np.random.default_rng(world * 100 + interleave + bs)
+    lens = np.array([1, interleave * world - 1, 777, 2048, 5], dtype=np.int32)
+    nblk = int((lens.max() + bs * world - 1) // (bs * world))
+    bt = rng.permutation(len(lens) * nblk).astype(np.int32).reshape(len(lens), nblk)
+    for s, L in enumerate(lens):
+        pos = np.arange(L)
+        req = np.full(L, s)
+        per_rank = [ref_ops.compute_slot_mapping_dcp(bt, req, pos, bs, world, r, interleave) for r in range(world)]
+        owners = np.stack([m >= 0 for m in per_rank]).sum(0)
+        assert (owners == 1).all()
+        for r, m in enumerate(per_rank):
+            loc = m[m >= 0]
+            assert len(np.unique(loc)) == len(loc)
+            assert len(loc) == int(ref_ops.dcp_local_seq_lens(lens[s:s + 1], world, r, interleave)[0])
+            # local token j (in position order) sits at local offset j: block_table[s, j // bs] * bs + j % bs
+            j = np.arange(len(loc))
+            np.testing.assert_array_equal(loc, bt[s, j // bs].astype(np.int64) * bs + j % bs)
+
+
+def test_dcp_sharded_cache_attention_merges_to_the_unsharded_result():
+    """Oracle-level end to end (flash_attn.py:859-872,1177): KV written through each rank's DCP slot mapping,
+    decode attention over each rank's local cache with its local lengths, LSE merge == attention over one cache."""
+    g = torch.Generator().manual_seed(5)
+    world, interleave, bs, Hq, Hkv, D = 4, 2, 16, 8, 2, 64
+    lens = [3, 129, 700]
+    S, nblk = len(lens), 44   # the unsharded cache needs ceil(700 / 16) blocks per row
+    key = [(torch.rand(L, Hkv, D, generator=g) * 2 - 1).to(torch.bfloat16) for L in lens]
+    val = [(torch.rand(L, Hkv, D, generator=g) * 2 - 1).to(torch.bfloat16) for L in lens]
+    q = (torch.rand(S, Hq, D, generator=g) * 2 - 1).to(torch.bfloat16)
+    bt = torch.randperm(S * nblk, generator=g).to(torch.int32).view(S, nblk)
+    one = torch.ones(1)
+    req = np.concatenate([np.full(L, s) for s, L in enumerate(lens)])
+    pos = np.concatenate([np.arange(L) for L in lens])
+
+    def attend(slots, local_lens):
+        kc = torch.zeros(S * nblk, bs, Hkv, D, dtype=torch.bfloat16)
+        vc = torch.zeros_like(kc)
+        ref_ops.reshape_and_cache_flash(torch.cat(key), torch.cat(val), kc, vc, torch.from_numpy(slots), "auto", one, one)
+        return ref_ops.paged_attention_decode(q, kc, vc, bt, torch.tensor(local_lens, dtype=torch.int32), D ** -0.5,
+                                              return_lse=True)
+
+    full, _ = attend(ref_ops.compute_slot_mapping(bt.numpy(), req, pos, bs), lens)
+    outs, lses = [], []
+    for r in range(world):
+        slots = ref_ops.compute_slot_mapping_dcp(bt.numpy(), req, pos, bs, world, r, interleave)
+        o, l = attend(slots, ref_ops.dcp_local_seq_lens(np.array(lens), world, r, interleave).tolist())
+        outs.append(torch.from_numpy(o).float()), lses.append(torch.from_numpy(l.astype(np.float32)))
+    merged, _ = ref_ops.dcp_lse_merge(outs, lses, dtype=torch.float32)
+    np.testing.assert_allclose(merged.numpy(), full, atol=2e-5, rtol=1e-5)
