@@ -737,13 +737,13 @@ def main():
     # overhead (eager events around a ~70 us kernel at TP=8 would mostly measure Python).
     side = torch.cuda.Stream(device=dev)
     side.wait_stream(torch.cuda.current_stream(dev))
-    with torch.cuda.stream(side):
+    with torch.cuda.stream(side), model.pdl_scope():
         for L in model.layers[:2]:
             model.attention_layer(L)
     torch.cuda.current_stream(dev).wait_stream(side)
     torch.cuda.synchronize(dev)
     attn_graph = torch.cuda.CUDAGraph()
-    with torch.cuda.graph(attn_graph):
+    with torch.cuda.graph(attn_graph), model.pdl_scope():   # same launch level as inside the step
         for L in model.layers:
             model.attention_layer(L)
     attn_graph.replay()

@@ -58,11 +58,16 @@ B200_API int b200_sm_count(void);
 /* Programmatic dependent launch between consecutive b200 kernels on a stream (results are unchanged):
  *   0 = off; 1 (default) = the next kernel's prologue (barrier init, TMEM allocation, descriptor prefetch) runs
  *   under the previous kernel's tail; 2 = the GEMMs additionally request their first ring pass of WEIGHT tiles
- *   before waiting for the previous kernel -- the caller promises that the weight operand (`b` of
- *   cutlass_scaled_mm / cutlass_scaled_fp4_mm) is not written by the kernel preceding the GEMM on the stream,
- *   which holds for model weights - and b200_paged_attention_decode computes its tile plan from `seq_lens` before
- *   waiting, so `seq_lens` must not be written by the kernel launched immediately before it either (it is a step
- *   input in the reference). Initial value from env B200_PDL. Returns the previous level.
+ *   before waiting for the previous kernel, and b200_paged_attention_decode computes its tile plan from `seq_lens`
+ *   before waiting. Because every b200 kernel releases its dependents at entry, such a pre-wait read can run beside
+ *   ANY earlier kernel of the programmatic chain, not only the one launched immediately before. The caller's
+ *   promise at level 2 is therefore: the weight operand (`b` of cutlass_scaled_mm / cutlass_scaled_fp4_mm) and
+ *   `seq_lens` are not written by any kernel launched on the stream since the last non-programmatic operation
+ *   (memcpy / memset, event wait, a foreign kernel, an NVLink collective in its default mode). That holds for model
+ *   weights (written at load time) and for `seq_lens` (a step input copied in before the step); a caller that
+ *   produces `b` on the stream must use level <= 1. The level is process-global host state: set it around your own
+ *   launches and restore the returned value (b200ops.decoder.DecoderModel.forward_device does).
+ *   Initial value from env B200_PDL. Returns the previous level.
  * The NVLink collectives (b200_allreduce_run, b200_allreduce_fused_add_rms_norm) are launched as plain kernels at every
  * level unless env B200_PDL_AR is 0 / 1 (measured slower: DESIGN.md section 5).
  * Not part of the reference operator surface. */

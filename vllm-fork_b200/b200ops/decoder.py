@@ -22,6 +22,7 @@ row-sharded across the ranks).
 from __future__ import annotations
 
 import dataclasses
+import contextlib
 import os
 
 import torch
@@ -82,12 +83,14 @@ class DecoderModel:
         # (profiles/r3e_*.json) that is 1.8 % faster than no programmatic launch, while collectives that take part in
         # it make the step 1-2 % slower (and one such run ended in the all-reduce's bounded-spin trap). B200_PDL in
         # the environment wins (A/B runs); pdl=None leaves the library setting alone.
+        # The level is a property of THIS model, applied around its own launches in forward_device() and restored
+        # afterwards: level 2 is a promise about this model's weights and must not leak to other callers of the
+        # process-global b200_set_pdl (a later cutlass_scaled_mm whose `b` was produced on-stream would inherit it).
         if pdl == "auto":
             pdl = 2 if tp_size == 1 else 1
-        if pdl is not None and "B200_PDL" not in os.environ:
-            ops.set_pdl(pdl)
-        self.pdl = ops.set_pdl(0)
-        ops.set_pdl(self.pdl)
+        lib_level = ops.set_pdl(0)
+        ops.set_pdl(lib_level)
+        self.pdl = lib_level if (pdl is None or "B200_PDL" in os.environ) else max(0, min(2, int(pdl)))
         assert quant in ("fp8", "nvfp4")
         self.quant = quant   # "nvfp4": W4A4 linears (scaled_fp4_quant -> cutlass_scaled_fp4_mm), FP8 KV cache
         self.dev = torch.device(device)
@@ -332,6 +335,21 @@ class DecoderModel:
 
     # ---- one decode step over the persistent device buffers
     def forward_device(self) -> None:
+        """Launch one decode step (eagerly or under capture) at this model's programmatic-launch level."""
+        with self.pdl_scope():
+            self._forward_device()
+
+    @contextlib.contextmanager
+    def pdl_scope(self):
+        """Launches inside the block use this model's programmatic-launch level; the library's level is restored on
+        exit (also when a launch raises)."""
+        prev = ops.set_pdl(self.pdl)
+        try:
+            yield
+        finally:
+            ops.set_pdl(prev)
+
+    def _forward_device(self) -> None:
         if self.quant == "nvfp4":
             return self._forward_nvfp4()
         s, D, S = self.shape, self.D, self.max_seqs

@@ -40,8 +40,13 @@ int sm_count();                 // SMs of the current device (cached per device)
 int max_smem_optin();           // max dynamic smem per CTA (opt-in)
 // programmatic dependent launch between consecutive kernels of a stream (b200_set_pdl / env B200_PDL):
 // 0 = off, 1 = the next kernel's prologue overlaps the previous kernel's tail (default), 2 = the GEMMs also
-// request their first ring pass of WEIGHT tiles before griddepcontrol.wait (caller's promise: the weight
-// operand is not written by the kernel that precedes the GEMM on the stream -- true for model weights)
+// request their first ring pass of WEIGHT tiles before griddepcontrol.wait.
+// The promise level 2 asks of the caller is wider than "the kernel just before": every b200 kernel signals
+// launch_dependents at ENTRY, before its own wait, so a chain of programmatic launches can be resident several
+// kernels deep and a GEMM's pre-wait prefetch may run beside ANY earlier kernel of that chain. The weight operand
+// (and seq_lens for the attention tile plan) must therefore not be written by any kernel launched on the stream
+// since the last NON-programmatic launch (a plain <<<>>> kernel, a memcpy / memset node, an event wait, or a
+// collective at B200_PDL_AR=2 all end the chain) -- true for model weights, which are only written at load time.
 int pdl_level();
 bool pdl_enabled();
 
