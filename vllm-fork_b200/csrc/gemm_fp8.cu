@@ -582,10 +582,13 @@ extern "C" int b200_fp8_gemm(void* out, const void* a, const void* b, const floa
     // k-block time of these kernels is set by the load latency x ring depth, not by L2 -> SM traffic.
     static const int use_cluster = [] { const char* e = getenv("B200_GEMM_CLUSTER"); return e ? atoi(e) : 0; }();
     const int gy = (M + bn - 1) / bn;
-    if (use_cluster && (gy == 2 || gy == 4) && bn >= 32 && bn <= 128) cb = gy;
+    // (only the <32|64|128, 2> and <32|64, 4> cluster kernels are built: four batch tiles of 128 stay unclustered,
+    // the tensor maps below are encoded for the tile width of the kernel that is dispatched)
+    if (use_cluster && ((gy == 2 && bn >= 32 && bn <= 128) || (gy == 4 && bn >= 32 && bn <= 64))) cb = gy;
     rc = make_tmap_2d(&tmR, b, N, K, ldb, BM / cb);
     if (rc) return rc;
     rc = make_tmap_2d(&tmC, a, M, K, lda, bn);
+    if (rc) return rc;
     if (((uintptr_t)out & 15) == 0 && (ldo * 2) % 16 == 0) {
       uint64_t dims[2] = {(uint64_t)N, (uint64_t)M};
       uint64_t strides[1] = {(uint64_t)ldo * 2};

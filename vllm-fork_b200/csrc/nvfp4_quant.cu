@@ -233,7 +233,9 @@ static int nvfp4_quant_launch(void* out, void* out_scale, const void* input, con
   const int threads = sf_cols_pad < 256 ? (sf_cols_pad + 31) / 32 * 32 : 256;
   const int gy = (sf_cols_pad + threads - 1) / threads;
   int gx = rows_pad;
-  const int cap = (148 * 8 + gy - 1) / gy;
+  const int sms = sm_count();
+  B200_CHECK(sms > 0, B200_ERR_CUDA, "%s: no CUDA device (no CPU fallback)", op);
+  const int cap = (sms * 8 + gy - 1) / gy;
   if (gx > cap) gx = cap;
   dim3 grid(gx, gy);
 #define B200_NVFP4_LAUNCH(T, G)                                                                       \
@@ -288,7 +290,9 @@ static int nvfp4_experts_quant_launch(void* out, void* out_scale, const void* in
   const int threads = sf_cols_pad < 256 ? (sf_cols_pad + 31) / 32 * 32 : 256;
   const int gy = (sf_cols_pad + threads - 1) / threads;
   int gx = M;
-  const int cap = (148 * 8 + gy - 1) / gy;
+  const int sms = sm_count();
+  B200_CHECK(sms > 0, B200_ERR_CUDA, "%s: no CUDA device (no CPU fallback)", op);
+  const int cap = (sms * 8 + gy - 1) / gy;
   if (gx > cap) gx = cap;
   dim3 grid(gx, gy);
   const size_t smem = (size_t)(num_experts + 1) * sizeof(int32_t);
