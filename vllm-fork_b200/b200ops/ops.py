@@ -339,7 +339,7 @@ def cutlass_scaled_mm_supports_fp8(cuda_device_capability: int) -> bool:
 # is a tuning switch (env B200_GEMM_IMPL), not a fallback. "auto" (default) follows measurements on B200.
 GEMM_IMPL = os.environ.get("B200_GEMM_IMPL", "auto")
 LAST_GEMM_IMPL = ""
-_gemm_ws: dict[str, torch.Tensor] = {}
+_gemm_ws: dict[tuple, torch.Tensor] = {}
 _sms: dict[str, int] = {}
 
 
@@ -371,13 +371,22 @@ def pick_gemm_impl(M: int, N: int, K: int, out_tma_addressable: bool, sms: int) 
 
 
 def _gemm_workspace(device: torch.device) -> torch.Tensor:
-    """zero-initialised stream-K workspace of the v3 kernel, one per device (the kernel leaves its
-    flags at zero, so it is shared by all calls that run on one stream at a time)."""
-    key = str(device)
+    """Zero-initialised stream-K workspace of the v3 kernel. The kernel leaves its flags at zero, so one buffer
+    serves every call that runs on ONE stream; two v3 GEMMs running concurrently on different streams would
+    corrupt each other's flags, hence one buffer per (device, stream) for eager launches. Under stream capture
+    the per-device buffer is used (no allocation or memset is recorded into the graph): graphs captured from
+    this module must not be replayed concurrently with each other on one device."""
+    if torch.cuda.is_current_stream_capturing():
+        key = (str(device), None)
+    else:
+        key = (str(device), torch.cuda.current_stream(device).cuda_stream)
     ws = _gemm_ws.get(key)
     if ws is None:
+        # (a first call under capture allocates + zeroes inside the graph's pool, as before: legal, one memset node)
         ws = torch.zeros(_lib.load().b200_fp8_gemm_v3_workspace_bytes(), dtype=torch.uint8, device=device)
         _gemm_ws[key] = ws
+        if key[1] is not None:   # warm-up call outside capture: the capture-time buffer is made now as well
+            _gemm_ws.setdefault((str(device), None), torch.zeros_like(ws))
     return ws
 
 
