@@ -63,6 +63,7 @@ struct Peers {
   uint8_t* tmp[MAX_RANKS];        // scratch of every rank (two-shot result slices)
   const uint8_t* mc_in;           // multicast address of the input (all ranks' copies at once), or null
   int pdl_mode;                   // pdl_collective_mode(): when this kernel lets its dependents launch
+  unsigned long long spin_ns;     // barrier wait limit in ns (spin_timeout_ns()); 0 = wait for ever, like the reference
 };
 
 // ---- NVSwitch in-network reduction (NVLS): one load from a multicast address returns the SUM over every rank's
@@ -119,10 +120,25 @@ __device__ __forceinline__ uint4 ld_peer_v4(const void* p) {
   return r;
 }
 
-// A dead or wedged peer must not hang the GPU (SURVEY section 5 "never hang"): every flag wait is
-// bounded by wall time (%globaltimer, checked every 1024 polls) and traps with a message, which turns a
-// hang into a CUDA error on the stream (the reference's barriers spin forever, custom_all_reduce.cuh:236-305).
-constexpr unsigned long long SPIN_TIMEOUT_NS = 20ull * 1000ull * 1000ull * 1000ull;  // 20 s
+// A dead or wedged peer should not hang the GPU for ever (SURVEY section 5 "never hang"): a flag wait is bounded by
+// wall time (%globaltimer, checked every 1024 polls) and traps with a message, which turns a hang into a CUDA error
+// on the stream. The limit has to outlast every LEGAL skew between ranks - a peer still compiling, loading weights,
+// capturing its graph, stopped in a debugger or in a GC pause - because the trap is a sticky error that takes the
+// whole TP group down: default 30 min, env B200_AR_TIMEOUT_S = seconds, 0 = never trap (the reference's behaviour:
+// its barriers spin for ever, custom_all_reduce.cuh:236-305). Read once per process, carried in Peers::spin_ns.
+inline unsigned long long spin_timeout_ns() {
+  static const unsigned long long ns = [] {
+    const char* e = getenv("B200_AR_TIMEOUT_S");
+    double sec = 1800.0;
+    if (e && *e) {
+      char* end = nullptr;
+      const double v = strtod(e, &end);
+      if (end != e && v >= 0.0) sec = v;
+    }
+    return (unsigned long long)(sec * 1e9);
+  }();
+  return ns;
+}
 
 __device__ __forceinline__ unsigned long long global_timer_ns() {
   unsigned long long t;
@@ -130,9 +146,10 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
   return t;
 }
 
-__device__ __noinline__ void spin_timeout(int rank, int peer, uint32_t want, uint32_t got) {
-  printf("b200ops all-reduce: rank %d CTA %d waited > 20 s for rank %d (flag %u, want %u): peer dead or "
-         "collective call order differs between ranks\n", rank, (int)blockIdx.x, peer, got, want);
+__device__ __noinline__ void spin_timeout(int rank, int peer, uint32_t want, uint32_t got, unsigned long long ns) {
+  printf("b200ops all-reduce: rank %d CTA %d waited > %llu s (B200_AR_TIMEOUT_S) for rank %d (flag %u, want %u): peer "
+         "dead or collective call order differs between ranks\n", rank, (int)blockIdx.x, ns / 1000000000ull, peer, got,
+         want);
   __trap();
 }
 
@@ -167,7 +184,7 @@ __device__ __forceinline__ void barrier(const Peers& pe, int rank, uint32_t& epo
       if ((polls & 1023u) == 0) {
         const unsigned long long now = global_timer_ns();
         if (t0 == 0) t0 = now;
-        else if (now - t0 > SPIN_TIMEOUT_NS) spin_timeout(rank, (int)threadIdx.x, epoch, v);
+        else if (pe.spin_ns != 0 && now - t0 > pe.spin_ns) spin_timeout(rank, (int)threadIdx.x, epoch, v, pe.spin_ns);
       }
     }
   }

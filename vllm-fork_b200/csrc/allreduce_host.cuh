@@ -30,6 +30,7 @@ static int resolve_input(const Context* c, const void* in, size_t bytes, Peers* 
   size_t off;
   pe->mc_in = nullptr;
   pe->pdl_mode = pdl_collective_mode();
+  pe->spin_ns = spin_timeout_ns();
   const int reg = find_region(c, in, bytes, &off);
   if (reg >= 0) {
     // region 0: the user heap starts after signals + staging + scratch; staging/scratch themselves are
@@ -412,6 +413,7 @@ extern "C" int b200_dcp_lse_merge(void* ctx, void* out, float* lse_out, const vo
   B200_CHECK(reg_o >= 0 && reg_l >= 0, B200_ERR_INVALID,
              "dcp_lse_merge: attn_out and attn_lse must live in the symmetric heap (peers read them in place)");
   pe.pdl_mode = 2;   // the DCP kernel is launched plainly
+  pe.spin_ns = spin_timeout_ns();
   for (int r = 0; r < c->world; r++) {
     pe.sig[r] = reinterpret_cast<Signal*>(c->regions[0].base[r]);
     pe.tmp[r] = nullptr;
