@@ -80,6 +80,18 @@ class B200AllReduce:
             want_symm = multicast is not False and os.environ.get("B200_AR_SYMM", "1") == "1"
             if want_symm:
                 mc_ptr = self._alloc_symmetric(group, total, ptrs)
+                # The symmetric path is taken by ALL ranks or by none: a rank that fell back alone would enter
+                # the IPC handle exchange below while its peers go straight to b200_allreduce_init + barrier
+                # (mismatched collectives = hang). Same for the multicast mapping.
+                flags: list = [None] * self.world_size
+                dist.all_gather_object(flags, (self._symm is not None, bool(mc_ptr)), group=group)
+                if not all(f[0] for f in flags):
+                    if self._symm is not None:
+                        self.multicast_note = "torch symmetric memory failed on a peer rank: CUDA-IPC path on all"
+                    self._symm = None
+                    mc_ptr = 0
+                elif not all(f[1] for f in flags):
+                    mc_ptr = 0
             if multicast is True and not mc_ptr:
                 raise RuntimeError(f"B200AllReduce: no NVSwitch multicast mapping ({self.multicast_note})")
             if self._symm is None:
