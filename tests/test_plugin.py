@@ -120,3 +120,71 @@ def test_plugin_registers_backend_through_vllm_registry():
         print("OK")
     """)
     assert "OK" in out
+
+
+def test_fused_experts_dispatcher_routes_fp8_silu_to_b200_and_delegates_the_rest():
+    """The stand-in the plugin installs for the reference's fused_experts (fused_moe.py:1587-1628): bound with the
+    original's signature (positional or keyword), FP8 W8A8 + SiLU on CUDA tensors -> b200 implementation, anything
+    else -> the function that was bound before. Pure host logic: both sides are recorded stand-ins."""
+    import types
+
+    import torch
+    from b200ops.vllm_plugin import make_fused_experts_dispatcher
+    calls = []
+
+    def original(hidden_states, w1, w2, topk_weights, topk_ids, inplace=False, activation="silu",
+                 apply_router_weight_on_input=False, global_num_experts=-1, expert_map=None, quant_config=None):
+        calls.append(("original", inplace))
+        return hidden_states
+
+    def ours(hidden_states, w1, w2, topk_weights, topk_ids, **kw):
+        calls.append(("b200", kw))
+        return hidden_states + 1
+
+    class CudaLike(torch.Tensor):   # a CPU tensor that claims to live on the GPU (host logic only)
+        @property
+        def is_cuda(self):
+            return True
+
+    disp = make_fused_experts_dispatcher(original, ours)
+    x = torch.zeros(2, 4).as_subclass(CudaLike)
+    w = torch.zeros(1)
+    qc = types.SimpleNamespace(use_fp8_w8a8=True, use_int8_w8a8=False, use_int8_w8a16=False, use_int4_w4a16=False,
+                               ocp_mx_scheme=None, per_act_token_quant=True, w1_scale=w, w2_scale=w, w1_zp=None,
+                               w2_zp=None, a1_scale=None, a2_scale=None, block_shape=[128, 128], w1_bias=None,
+                               w2_bias=None)
+    silu = types.SimpleNamespace(value="silu")
+    r = disp(x, w, w, w, w, False, silu, True, 8, None, qc)          # positional, enum-like activation
+    assert calls[-1][0] == "b200" and float(r[0, 0]) == 1.0
+    kw = calls[-1][1]
+    assert kw["use_fp8_w8a8"] and kw["per_channel_quant"] and kw["apply_router_weight_on_input"]
+    assert kw["global_num_experts"] == 8 and kw["block_shape"] == [128, 128] and kw["w1_scale"] is w
+    r = disp(x, w, w, w, w, inplace=True, quant_config=qc)            # keyword style, inplace writes the input
+    assert calls[-1][0] == "b200" and r is x and float(x[0, 0]) == 1.0
+    # everything the library does not cover goes back to the host framework's own function
+    n = len(calls)
+    disp(x, w, w, w, w, quant_config=None)                                              # unquantised
+    disp(x, w, w, w, w, activation=types.SimpleNamespace(value="gelu"), quant_config=qc)  # other activation
+    qc.w1_bias = w
+    disp(x, w, w, w, w, quant_config=qc)                                                # biases
+    qc.w1_bias = None
+    disp(torch.zeros(2, 4), w, w, w, w, quant_config=qc)                                # CPU tensor
+    assert [c[0] for c in calls[n:]] == ["original"] * 4
+    assert disp._b200_dispatcher and disp._b200_original is original
+
+
+def test_plugin_replaces_fused_experts_in_the_installed_vllm():
+    pytest.importorskip("vllm")
+    out = _run("""
+        import vllm.model_executor.layers.fused_moe as pkg
+        import vllm.model_executor.layers.fused_moe.fused_moe as mod
+        before = mod.fused_experts
+        from b200ops import vllm_plugin
+        vllm_plugin.register()
+        vllm_plugin.register()   # idempotent: no dispatcher around a dispatcher
+        assert mod.fused_experts is not before and mod.fused_experts._b200_dispatcher
+        assert mod.fused_experts._b200_original is before
+        assert pkg.fused_experts is mod.fused_experts
+        print("OK")
+    """)
+    assert "OK" in out
